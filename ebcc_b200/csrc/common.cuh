@@ -1,0 +1,81 @@
+// common.cuh -- shared declarations of the device layer (sm_100a).
+//
+// Data layout in HBM for a batch of B frames of H x W float32 (one JPEG 2000 tile each):
+//   in     [B][H][W] f32   input frames (H2D copy of the caller's buffer)
+//   coef   [B][H][W] f32   9/7 coefficients, Mallat layout, transformed in place level by level
+//   stat   [B]             min / max / flags per frame
+//   sym    [B][sym_stride] u8  EBCOT symbol stream per code-block: (ctx << 1 | bit), scan order
+//   cbout  [B][ncblks]     per code-block pass table (symbol counts, nmsedec, rates, distortion)
+//   mq     [B][mq_stride]  u8  MQ-coded bytes per code-block
+//   out    [B][out_stride] u8  finished J2K codestreams
+#pragma once
+#ifdef EBCC_CUEMU
+#include "cuemu.h"
+#else
+#include <cuda_runtime.h>
+#include <stdint.h>
+#define EBCC_LAUNCH(kern, grid, block, smem, stream, ...) kern<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#define EBCC_DYN_SMEM(type, name) extern __shared__ __align__(16) unsigned char name##_raw_[]; type *name = (type *)name##_raw_
+#endif
+#include <stddef.h>
+
+#define J2K_NRES 6
+#define J2K_MAXBANDS 16
+#define J2K_MAXPASSES 100
+#define J2K_CBLK 64
+
+// frame statistics written by k_minmax / k_minmax_final (reference: findMinMaxf + check_nan_inf,
+// src/ebcc_codec.c:515-533, :598-605)
+struct FrameStat {
+    float minv, maxv;
+    int flags;              // bit0: constant field, bit1: NaN/Inf present
+    int pad;
+    unsigned long long minkey, maxkey;
+};
+#define STAT_CONST 1
+#define STAT_NANINF 2
+
+struct BandDesc {
+    int resno, orient, level;
+    int offx, offy, bw, bh;      // position / size inside the Mallat-layout tile buffer
+    int cw, ch, first_cblk;
+    int numbps, expn, mant;
+    float stepsize;              // encoder Delta_b (tcd.c:1069-1084)
+    float stepsize_dec;          // decoder Delta_b (log2_gain 0)
+    double wnorm;                // norm(level,orient) * stepsize / 2^log2_gain   (t1.c:1416-1449)
+    // tag-tree shape of the band's single precinct (tgt.c:48-150): level 0 = leaves
+    int tt_nlev, tt_base;        // number of levels, first node index inside the frame's node arrays
+    int tt_off[8], tt_w[8], tt_h[8];
+};
+
+struct CblkDesc {
+    int band;
+    int tx, ty, w, h;            // rectangle inside the tile buffer
+    int gx, gy;                  // position in the band's code-block grid
+    int orient;
+    unsigned sym_off, sym_cap;   // byte offset / capacity inside the frame's symbol pool
+    unsigned mq_off, mq_cap;     // byte offset / capacity inside the frame's MQ pool
+};
+
+// per code-block result of tier-1 (opj_tcd_cblk_enc_t + opj_tcd_pass_t, tcd.h)
+struct CblkOut {
+    int numbps;
+    int totalpasses;
+    int datalen;
+    int numpasses;               // passes selected by PCRD
+    unsigned nsym_end[J2K_MAXPASSES];   // cumulative symbol count at the end of each pass
+    int nmsedec[J2K_MAXPASSES];
+    int rate[J2K_MAXPASSES];            // cumulative bytes (after OPJ's fix-ups)
+    double dist[J2K_MAXPASSES];         // cumulative distortion decrease
+};
+
+struct Plan {
+    int H, W, nbands, ncblks;
+    int res_w[J2K_NRES], res_h[J2K_NRES];
+    BandDesc bands[J2K_MAXBANDS];
+    int nnodes;                       // tag-tree nodes over all bands
+    int res_first[J2K_NRES], res_count[J2K_NRES];   // code-block index range of each resolution's packet
+    size_t sym_stride, mq_stride, out_stride;
+    int main_header_len;
+    unsigned char main_header[160];
+};

@@ -1,0 +1,491 @@
+// ebcc_cuda.cu -- device layer of the EBCC hot path for NVIDIA B200 (sm_100a) behind the C ABI of
+// include/ebcc_cuda.h.  One context = one GPU, one stream, one set of work buffers sized for a
+// batch of frames; a batch flows  H2D -> min/max -> (scale + DC shift + DWT) -> tier-1 context
+// modelling -> MQ coding -> PCRD + tier-2 -> compaction -> D2H  without host round trips.
+#include "common.cuh"
+#include "k_dwt.cuh"
+#include "k_t1.cuh"
+#include "k_t2.cuh"
+#include "../../include/ebcc_cuda.h"
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define CK(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess) {                                                                     \
+            fprintf(stderr, "[ebcc-cuda] %s failed at %s:%d: %s\n", #call, __FILE__, __LINE__,       \
+                    cudaGetErrorString(e_));                                                         \
+            return -1;                                                                               \
+        }                                                                                            \
+    } while (0)
+
+// ---- compaction of the per-frame codestreams into one contiguous buffer --------------------------
+__global__ void k_offsets(const ProbeOut *__restrict__ pout, unsigned long long *offs, int nframes)
+{
+    // single thread: nframes is small (<= a few thousand) and this is 8 bytes per frame
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long o = 0;
+        for (int i = 0; i < nframes; ++i) { offs[i] = o; o += (unsigned long long)((pout[i].stream_bytes + 15) & ~15); }
+        offs[nframes] = o;
+    }
+}
+
+__global__ void k_compact(const unsigned char *__restrict__ out_pool, const ProbeOut *__restrict__ pout,
+                          const unsigned long long *__restrict__ offs, unsigned char *packed, size_t out_stride)
+{
+    const int frame = blockIdx.y;
+    const int n16 = (pout[frame].stream_bytes + 15) >> 4;
+    const uint4 *src = (const uint4 *)(out_pool + (size_t)frame * out_stride);
+    uint4 *dst = (uint4 *)(packed + offs[frame]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
+// ---- host-side geometry (tcd.c:961-1264 for one tile at the canvas origin) ------------------------
+static int h_ceildivpow2(int a, int b) { return (int)(((long long)a + (1ll << b) - 1) >> b); }
+static int h_floorlog2(int a) { int l = 0; while (a > 1) { a >>= 1; l++; } return l; }
+
+static const double h_norms97[4][10] = {
+    {1.000, 1.965, 4.177, 8.403, 16.90, 33.84, 67.69, 135.3, 270.6, 540.9},
+    {2.022, 3.989, 8.355, 17.04, 34.27, 68.63, 137.3, 274.6, 549.0, 0},
+    {2.022, 3.989, 8.355, 17.04, 34.27, 68.63, 137.3, 274.6, 549.0, 0},
+    {2.080, 3.865, 8.307, 17.18, 34.71, 69.59, 139.3, 278.6, 557.2, 0}};
+
+static void put16(unsigned char *&p, unsigned v) { *p++ = (unsigned char)(v >> 8); *p++ = (unsigned char)v; }
+static void put32(unsigned char *&p, unsigned v) { put16(p, v >> 16); put16(p, v & 0xffff); }
+
+static void build_plan(int H, int W, Plan *pl, CblkDesc **cblks_out)
+{
+    memset(pl, 0, sizeof(*pl));
+    pl->H = H; pl->W = W;
+    for (int r = 0; r < J2K_NRES; ++r) {
+        pl->res_w[r] = h_ceildivpow2(W, J2K_NRES - 1 - r);
+        pl->res_h[r] = h_ceildivpow2(H, J2K_NRES - 1 - r);
+    }
+    int nb = 0, ncb = 0, nnodes = 0;
+    for (int r = 0; r < J2K_NRES; ++r) {
+        const int lvl = J2K_NRES - 1 - r;
+        pl->res_first[r] = ncb;
+        for (int bi = 0; bi < (r == 0 ? 1 : 3); ++bi) {
+            BandDesc *b = &pl->bands[nb];
+            const int orient = r == 0 ? 0 : bi + 1;
+            b->resno = r; b->orient = orient; b->level = lvl;
+            if (r == 0) {
+                b->bw = h_ceildivpow2(W, lvl); b->bh = h_ceildivpow2(H, lvl);
+            } else {
+                const int x0b = orient & 1, y0b = orient >> 1;
+                b->bw = h_ceildivpow2(W - (x0b << lvl), lvl + 1);
+                b->bh = h_ceildivpow2(H - (y0b << lvl), lvl + 1);
+                b->offx = x0b ? pl->res_w[r - 1] : 0;
+                b->offy = y0b ? pl->res_h[r - 1] : 0;
+            }
+            // explicit quantisation step (dwt.c:2176-2198, 1302-1311), band parameters (tcd.c:1069-1089)
+            int lv = lvl;
+            if (orient == 0 && lv >= 10) lv = 9; else if (orient > 0 && lv >= 9) lv = 8;
+            const double norm = h_norms97[orient][lv];
+            const int si = (int)floor((1.0 / norm) * 8192.0);
+            const int p = h_floorlog2(si) - 13, n = 11 - h_floorlog2(si);
+            b->mant = (n < 0 ? si >> -n : si << n) & 0x7ff;
+            b->expn = 16 - p;
+            const int log2_gain = orient == 0 ? 0 : (orient == 3 ? 2 : 1);
+            b->stepsize = (float)((1.0 + b->mant / 2048.0) * pow(2.0, (16 + log2_gain) - b->expn));
+            b->stepsize_dec = (float)((1.0 + b->mant / 2048.0) * pow(2.0, 16 - b->expn));
+            b->numbps = b->expn + 2 - 1;
+            {
+                double st = (double)b->stepsize;
+                st /= (1 << log2_gain);
+                b->wnorm = 1.0 * norm * st;
+            }
+            const bool empty = b->bw <= 0 || b->bh <= 0;
+            b->cw = empty ? 0 : (b->bw + 63) / 64;
+            b->ch = empty ? 0 : (b->bh + 63) / 64;
+            b->first_cblk = ncb;
+            ncb += b->cw * b->ch;
+            // tag tree shape
+            b->tt_base = nnodes;
+            int lw = b->cw, lh = b->ch, nl = 0, off = 0;
+            if (!empty) {
+                int nn;
+                do {
+                    b->tt_w[nl] = lw; b->tt_h[nl] = lh; b->tt_off[nl] = off;
+                    nn = lw * lh; off += nn;
+                    lw = (lw + 1) / 2; lh = (lh + 1) / 2; ++nl;
+                } while (nn > 1);
+            }
+            b->tt_nlev = nl; nnodes += off;
+            nb++;
+        }
+        pl->res_count[r] = ncb - pl->res_first[r];
+    }
+    pl->nbands = nb; pl->ncblks = ncb; pl->nnodes = nnodes;
+    CblkDesc *cb = (CblkDesc *)calloc((size_t)ncb, sizeof(CblkDesc));
+    size_t sym_off = 0, mq_off = 0;
+    for (int bi = 0; bi < nb; ++bi) {
+        const BandDesc *b = &pl->bands[bi];
+        for (int gy = 0; gy < b->ch; ++gy)
+            for (int gx = 0; gx < b->cw; ++gx) {
+                CblkDesc *c = &cb[b->first_cblk + gy * b->cw + gx];
+                c->band = bi; c->gx = gx; c->gy = gy; c->orient = b->orient;
+                c->w = (gx * 64 + 64 <= b->bw ? 64 : b->bw - gx * 64);
+                c->h = (gy * 64 + 64 <= b->bh ? 64 : b->bh - gy * 64);
+                c->tx = b->offx + gx * 64; c->ty = b->offy + gy * 64;
+                // symbols: <= 1.5 per sample per bit-plane (zero coding / refinement / run mode) + one sign
+                size_t cap = (size_t)c->w * c->h * (3 * (size_t)b->numbps / 2 + 2) + 32;
+                cap = (cap + 15) & ~(size_t)15;
+                c->sym_off = (unsigned)sym_off; c->sym_cap = (unsigned)cap; sym_off += cap;
+                size_t mcap = ((size_t)80 + (size_t)c->w * c->h * 4 + 15) & ~(size_t)15;
+                c->mq_off = (unsigned)mq_off; c->mq_cap = (unsigned)mcap; mq_off += mcap;
+            }
+    }
+    pl->sym_stride = (sym_off + 255) & ~(size_t)255;
+    pl->mq_stride = (mq_off + 255) & ~(size_t)255;
+    // main header: SOC SIZ COD QCD COM (j2k.c:13080-13133); 135 bytes for one component
+    unsigned char *p = pl->main_header;
+    put16(p, 0xFF4F);
+    put16(p, 0xFF51); put16(p, 41); put16(p, 0);
+    put32(p, (unsigned)W); put32(p, (unsigned)H); put32(p, 0); put32(p, 0);
+    put32(p, (unsigned)W); put32(p, (unsigned)H); put32(p, 0); put32(p, 0);
+    put16(p, 1); *p++ = 15; *p++ = 1; *p++ = 1;
+    put16(p, 0xFF52); put16(p, 12); *p++ = 0; *p++ = 0; put16(p, 1); *p++ = 0;
+    *p++ = 5; *p++ = 4; *p++ = 4; *p++ = 0; *p++ = 0;
+    put16(p, 0xFF5C); put16(p, 3 + 2 * (unsigned)nb); *p++ = (2 << 5) | 2;
+    for (int i = 0; i < nb; ++i) put16(p, (unsigned)((pl->bands[i].expn << 11) | pl->bands[i].mant));
+    static const char com[] = "Created by OpenJPEG version 2.5.3";
+    put16(p, 0xFF64); put16(p, (unsigned)(4 + sizeof(com) - 1)); put16(p, 1);
+    memcpy(p, com, sizeof(com) - 1); p += sizeof(com) - 1;
+    pl->main_header_len = (int)(p - pl->main_header);
+    size_t os = (size_t)((double)((unsigned long long)W * H * 16) * 1.4 / 8) + 500 + 256 + (size_t)pl->main_header_len;
+    pl->out_stride = (os + 255) & ~(size_t)255;
+    *cblks_out = cb;
+}
+
+// per-tile byte budget in f32 exactly as opj_j2k_update_rates (j2k.c:5376-5408); < 0 => all passes
+static int tile_maxlen(int H, int W, float base_cr, int main_header_bytes)
+{
+    float rate = base_cr / 2;                            // src/ebcc_codec.c:116
+    if (rate <= 1.0) return -1;                          // j2k.c:8159-8162
+    float r = (float)(((double)16 * (unsigned)W * (unsigned)H) / (rate * (float)8)) - 0.0f;
+    r -= (float)main_header_bytes / (float)1;
+    if (r < 30.0f) r = 30.0f;
+    unsigned long long tile_size = (unsigned long long)((double)((unsigned long long)W * H * 16) * 1.4 / 8) + 500;
+    unsigned len = (unsigned)tile_size - 12 - 4;
+    unsigned ml = (unsigned)ceil(r);
+    return (int)(ml < len ? ml : len);
+}
+
+static void fill_luts(T1Luts *l, MqTable *t)
+{
+    for (int i = 0; i < 128; ++i) {
+        double tt = i / 64.0, u = tt, v = tt - 1.5;
+        int a = (int)(floor((u * u - v * v) * 64.0 + 0.5) / 64.0 * 8192.0);
+        int b = (int)(floor((u * u) * 64.0 + 0.5) / 64.0 * 8192.0);
+        l->sig[i] = (short)(a > 0 ? a : 0); l->sig0[i] = (short)(b > 0 ? b : 0);
+        u = tt - 1.0; v = (i & 64) ? tt - 1.5 : tt - 0.5;
+        a = (int)(floor((u * u - v * v) * 64.0 + 0.5) / 64.0 * 8192.0);
+        b = (int)(floor((u * u) * 64.0 + 0.5) / 64.0 * 8192.0);
+        l->ref[i] = (short)(a > 0 ? a : 0); l->ref0[i] = (short)(b > 0 ? b : 0);
+    }
+    // MQ probability state machine, ISO/IEC 15444-1 table C.2: Qe, NMPS, NLPS, SWITCH
+    static const unsigned short qe[47] = {
+        0x5601, 0x3401, 0x1801, 0x0AC1, 0x0521, 0x0221, 0x5601, 0x5401, 0x4801, 0x3801, 0x3001, 0x2401,
+        0x1C01, 0x1601, 0x5601, 0x5401, 0x5101, 0x4801, 0x3801, 0x3401, 0x3001, 0x2801, 0x2401, 0x2201,
+        0x1C01, 0x1801, 0x1601, 0x1401, 0x1201, 0x1101, 0x0AC1, 0x09C1, 0x08A1, 0x0521, 0x0441, 0x02A1,
+        0x0221, 0x0141, 0x0111, 0x0085, 0x0049, 0x0025, 0x0015, 0x0009, 0x0005, 0x0001, 0x5601};
+    static const unsigned char nmps[47] = {1, 2, 3, 4, 5, 38, 7, 8, 9, 10, 11, 12, 13, 29, 15, 16, 17, 18, 19, 20, 21, 22, 23, 24,
+                                           25, 26, 27, 28, 29, 30, 31, 32, 33, 34, 35, 36, 37, 38, 39, 40, 41, 42, 43, 44, 45, 45, 46};
+    static const unsigned char nlps[47] = {1, 6, 9, 12, 29, 33, 6, 14, 14, 14, 17, 18, 20, 21, 14, 14, 15, 16, 17, 18, 19, 19, 20, 21,
+                                           22, 23, 24, 25, 26, 27, 28, 29, 30, 31, 32, 33, 34, 35, 36, 37, 38, 39, 40, 41, 42, 43, 46};
+    for (int i = 0; i < 47; ++i) {
+        unsigned sw = (i == 0 || i == 6 || i == 14) ? 1u : 0u;
+        t->e[i] = qe[i] | ((unsigned)nmps[i] << 16) | ((unsigned)nlps[i] << 22) | (sw << 28);
+    }
+}
+
+// ---- context ---------------------------------------------------------------------------------------
+struct ebcc_cuda_ctx {
+    int device;
+    cudaStream_t stream;
+    Plan plan;                 // host copy
+    CblkDesc *h_cblks;
+    Plan *d_plan;
+    CblkDesc *d_cblks;
+    BandDesc *d_bands;
+    T1Luts *d_luts;
+    MqTable *d_mqtab;
+    size_t cap_frames;
+    float *d_in, *d_coef;
+    FrameStat *d_stat;
+    unsigned char *d_sym, *d_mq, *d_out, *d_packed;
+    CblkOut *d_cbout;
+    int *d_maxlen, *d_body_off;
+    ProbeOut *d_pout;
+    unsigned long long *d_offs;
+    // pinned host mirrors
+    ProbeOut *h_pout;
+    FrameStat *h_stat;
+    unsigned long long *h_offs;
+    int *h_maxlen;
+    unsigned char *h_packed;
+    size_t h_packed_cap;
+    float *h_stage;            // pinned staging for pageable inputs
+    size_t h_stage_cap;
+    int profiling;
+    cudaEvent_t ev[EBCC_ST_COUNT + 1];
+    float stage_ms[EBCC_ST_COUNT];
+    int ev_valid;
+    unsigned long long launches;
+};
+
+extern "C" int ebcc_cuda_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+extern "C" ebcc_cuda_ctx *ebcc_cuda_ctx_create(int device)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device >= n) {
+        fprintf(stderr, "[ebcc-cuda] no CUDA device available (requested %d of %d): the EBCC B200 codec has no CPU path\n", device, n);
+        return NULL;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) return NULL;
+    ebcc_cuda_ctx *c = (ebcc_cuda_ctx *)calloc(1, sizeof(*c));
+    c->device = device;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { free(c); return NULL; }
+    for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventCreate(&c->ev[i]);
+    T1Luts luts; MqTable tab;
+    fill_luts(&luts, &tab);
+    if (cudaMalloc((void **)&c->d_luts, sizeof(luts)) != cudaSuccess || cudaMalloc((void **)&c->d_mqtab, sizeof(tab)) != cudaSuccess) { free(c); return NULL; }
+    cudaMemcpy(c->d_luts, &luts, sizeof(luts), cudaMemcpyHostToDevice);
+    cudaMemcpy(c->d_mqtab, &tab, sizeof(tab), cudaMemcpyHostToDevice);
+    return c;
+}
+
+static void free_buffers(ebcc_cuda_ctx *c)
+{
+    cudaFree(c->d_plan); cudaFree(c->d_cblks); cudaFree(c->d_in); cudaFree(c->d_coef); cudaFree(c->d_stat);
+    cudaFree(c->d_sym); cudaFree(c->d_mq); cudaFree(c->d_out); cudaFree(c->d_packed); cudaFree(c->d_cbout);
+    cudaFree(c->d_maxlen); cudaFree(c->d_body_off); cudaFree(c->d_pout); cudaFree(c->d_offs);
+    cudaFreeHost(c->h_pout); cudaFreeHost(c->h_stat); cudaFreeHost(c->h_offs); cudaFreeHost(c->h_maxlen);
+    cudaFreeHost(c->h_packed); cudaFreeHost(c->h_stage);
+    free(c->h_cblks);
+    c->d_plan = NULL; c->d_cblks = NULL; c->d_in = c->d_coef = NULL; c->d_stat = NULL;
+    c->d_sym = c->d_mq = c->d_out = c->d_packed = NULL; c->d_cbout = NULL; c->d_maxlen = c->d_body_off = NULL;
+    c->d_pout = NULL; c->d_offs = NULL; c->h_pout = NULL; c->h_stat = NULL; c->h_offs = NULL; c->h_maxlen = NULL;
+    c->h_packed = NULL; c->h_packed_cap = 0; c->h_stage = NULL; c->h_stage_cap = 0; c->h_cblks = NULL;
+    c->cap_frames = 0;
+}
+
+extern "C" void ebcc_cuda_ctx_destroy(ebcc_cuda_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    free_buffers(c);
+    cudaFree(c->d_luts); cudaFree(c->d_mqtab);
+    for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventDestroy(c->ev[i]);
+    cudaStreamDestroy(c->stream);
+    free(c);
+}
+
+extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes)
+{
+    if (!c || H < 32 || W < 32 || H > 2047 || W > 2047 || nframes == 0) return -1;
+    CK(cudaSetDevice(c->device));
+    if (c->cap_frames >= nframes && c->plan.H == (int)H && c->plan.W == (int)W) return 0;
+    CK(cudaStreamSynchronize(c->stream));
+    free_buffers(c);
+    build_plan((int)H, (int)W, &c->plan, &c->h_cblks);
+    const Plan *pl = &c->plan;
+    const size_t B = nframes, N = H * W;
+    CK(cudaMalloc((void **)&c->d_plan, sizeof(Plan)));
+    CK(cudaMalloc((void **)&c->d_cblks, sizeof(CblkDesc) * pl->ncblks));
+    CK(cudaMemcpy(c->d_plan, pl, sizeof(Plan), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c->d_cblks, c->h_cblks, sizeof(CblkDesc) * pl->ncblks, cudaMemcpyHostToDevice));
+    c->d_bands = (BandDesc *)((char *)c->d_plan + offsetof(Plan, bands));
+    CK(cudaMalloc((void **)&c->d_in, B * N * sizeof(float)));
+    CK(cudaMalloc((void **)&c->d_coef, B * N * sizeof(float)));
+    CK(cudaMalloc((void **)&c->d_stat, B * sizeof(FrameStat)));
+    CK(cudaMalloc((void **)&c->d_sym, B * pl->sym_stride));
+    CK(cudaMalloc((void **)&c->d_mq, B * pl->mq_stride));
+    CK(cudaMalloc((void **)&c->d_out, B * pl->out_stride));
+    CK(cudaMalloc((void **)&c->d_packed, B * pl->out_stride));
+    CK(cudaMalloc((void **)&c->d_cbout, B * pl->ncblks * sizeof(CblkOut)));
+    CK(cudaMalloc((void **)&c->d_maxlen, B * sizeof(int)));
+    CK(cudaMalloc((void **)&c->d_body_off, B * pl->ncblks * sizeof(int)));
+    CK(cudaMalloc((void **)&c->d_pout, B * sizeof(ProbeOut)));
+    CK(cudaMalloc((void **)&c->d_offs, (B + 1) * sizeof(unsigned long long)));
+    CK(cudaMallocHost((void **)&c->h_pout, B * sizeof(ProbeOut)));
+    CK(cudaMallocHost((void **)&c->h_stat, B * sizeof(FrameStat)));
+    CK(cudaMallocHost((void **)&c->h_offs, (B + 1) * sizeof(unsigned long long)));
+    CK(cudaMallocHost((void **)&c->h_maxlen, B * sizeof(int)));
+    c->cap_frames = nframes;
+    // large dynamic shared memory opt-ins
+    CK(cudaFuncSetAttribute(k_dwt_v<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(k_dwt_v<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(k_dwt_h, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(k_pcrd_t2, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    return 0;
+}
+
+static void mark(ebcc_cuda_ctx *c, int i)
+{
+    if (c->profiling) cudaEventRecord(c->ev[i], c->stream);
+}
+
+extern "C" int ebcc_cuda_upload(ebcc_cuda_ctx *c, const float *frames, size_t nframes)
+{
+    if (!c || nframes > c->cap_frames) return -1;
+    CK(cudaSetDevice(c->device));
+    const size_t bytes = nframes * (size_t)c->plan.H * c->plan.W * sizeof(float);
+    mark(c, EBCC_ST_H2D);
+    CK(cudaMemcpyAsync(c->d_in, frames, bytes, cudaMemcpyHostToDevice, c->stream));
+    return 0;
+}
+
+static int launch_dwt(ebcc_cuda_ctx *c, int B)
+{
+    const Plan *pl = &c->plan;
+    const int W = pl->W, H = pl->H;
+    for (int r = J2K_NRES - 1; r >= 1; --r) {
+        const int rw = pl->res_w[r], rh = pl->res_h[r];
+        // vertical: strips of CW columns, full height in shared memory
+        int CW = 32;
+        while ((size_t)rh * CW * sizeof(float) > 96 * 1024 && CW > 4) CW >>= 1;
+        dim3 bv((unsigned)CW, (unsigned)(512 / CW));
+        dim3 gv((unsigned)((rw + CW - 1) / CW), (unsigned)B);
+        size_t sv = (size_t)rh * CW * sizeof(float);
+        if (r == J2K_NRES - 1)
+            EBCC_LAUNCH(k_dwt_v<true>, gv, bv, sv, c->stream, c->d_in, c->d_coef, c->d_stat, W, H, rw, rh, pl->res_h[r - 1]);
+        else
+            EBCC_LAUNCH(k_dwt_v<false>, gv, bv, sv, c->stream, c->d_in, c->d_coef, c->d_stat, W, H, rw, rh, pl->res_h[r - 1]);
+        // horizontal: RH full rows per CTA
+        int RH = 4;
+        while ((size_t)rw * RH * sizeof(float) > 64 * 1024 && RH > 1) RH >>= 1;
+        dim3 bh(128, (unsigned)RH);
+        dim3 gh((unsigned)((rh + RH - 1) / RH), (unsigned)B);
+        EBCC_LAUNCH(k_dwt_h, gh, bh, (size_t)rw * RH * sizeof(float), c->stream, c->d_coef, W, H, rw, rh, pl->res_w[r - 1]);
+        c->launches += 2;
+    }
+    return 0;
+}
+
+extern "C" int ebcc_cuda_j2k_encode_resident(ebcc_cuda_ctx *c, size_t nframes, float base_cr)
+{
+    if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
+    CK(cudaSetDevice(c->device));
+    const Plan *pl = &c->plan;
+    const int B = (int)nframes, N = pl->H * pl->W;
+    const int ml = tile_maxlen(pl->H, pl->W, base_cr, pl->main_header_len);
+    for (int i = 0; i < B; ++i) c->h_maxlen[i] = ml;
+    CK(cudaMemcpyAsync(c->d_maxlen, c->h_maxlen, sizeof(int) * B, cudaMemcpyHostToDevice, c->stream));
+
+    mark(c, EBCC_ST_MINMAX);
+    EBCC_LAUNCH(k_stat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_stat, B);
+    EBCC_LAUNCH(k_minmax, dim3(74, (unsigned)B), dim3(256), 0, c->stream, c->d_in, c->d_stat, N);
+    EBCC_LAUNCH(k_minmax_final, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_in, c->d_stat, N, B);
+    c->launches += 3;
+
+    mark(c, EBCC_ST_DWT);
+    if (launch_dwt(c, B)) return -1;
+
+    mark(c, EBCC_ST_T1_CM);
+    EBCC_LAUNCH(k_t1_cm, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
+                c->d_coef, c->d_cblks, c->d_bands, c->d_luts, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks, pl->sym_stride);
+    mark(c, EBCC_ST_T1_MQ);
+    {
+        long long jobs = (long long)pl->ncblks * B;
+        long long warps = (jobs + MQ_LANES - 1) / MQ_LANES;
+        long long ctas = (warps * 32 + MQ_THREADS - 1) / MQ_THREADS;
+        EBCC_LAUNCH(k_t1_mq, dim3((unsigned)ctas), dim3(MQ_THREADS), 0, c->stream,
+                    c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride);
+    }
+    mark(c, EBCC_ST_PCRD_T2);
+    EBCC_LAUNCH(k_pcrd_t2, dim3((unsigned)B), dim3(T2_THREADS), t2_smem_bytes(pl->ncblks, pl->nnodes), c->stream,
+                c->d_plan, c->d_cblks, c->d_cbout, c->d_maxlen, c->d_out, c->d_body_off, c->d_pout, c->d_stat);
+    mark(c, EBCC_ST_BODIES);
+    EBCC_LAUNCH(k_t2_bodies, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(128), 0, c->stream,
+                c->d_plan, c->d_cblks, c->d_cbout, c->d_mq, c->d_body_off, c->d_out, c->d_pout);
+    EBCC_LAUNCH(k_offsets, dim3(1), dim3(32), 0, c->stream, c->d_pout, c->d_offs, B);
+    EBCC_LAUNCH(k_compact, dim3(8, (unsigned)B), dim3(256), 0, c->stream, c->d_out, c->d_pout, c->d_offs, c->d_packed, pl->out_stride);
+    c->launches += 6;
+    mark(c, EBCC_ST_D2H);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int ebcc_cuda_download(ebcc_cuda_ctx *c, size_t nframes, const uint8_t **streams, size_t *sizes,
+                                  float *minv, float *maxv, int *flags)
+{
+    if (!c || nframes > c->cap_frames) return -1;
+    CK(cudaSetDevice(c->device));
+    const int B = (int)nframes;
+    CK(cudaMemcpyAsync(c->h_pout, c->d_pout, sizeof(ProbeOut) * B, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(c->h_stat, c->d_stat, sizeof(FrameStat) * B, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(c->h_offs, c->d_offs, sizeof(unsigned long long) * (B + 1), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    const size_t total = (size_t)c->h_offs[B];
+    if (total > c->h_packed_cap) {
+        cudaFreeHost(c->h_packed);
+        c->h_packed_cap = total + total / 4 + 4096;
+        CK(cudaMallocHost((void **)&c->h_packed, c->h_packed_cap));
+    }
+    if (total) CK(cudaMemcpyAsync(c->h_packed, c->d_packed, total, cudaMemcpyDeviceToHost, c->stream));
+    if (c->profiling) cudaEventRecord(c->ev[EBCC_ST_COUNT], c->stream);
+    CK(cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < B; ++i) {
+        if (streams) streams[i] = c->h_packed + c->h_offs[i];
+        if (sizes) sizes[i] = (size_t)c->h_pout[i].stream_bytes;
+        if (minv) minv[i] = c->h_stat[i].minv;
+        if (maxv) maxv[i] = c->h_stat[i].maxv;
+        if (flags) flags[i] = c->h_stat[i].flags;
+    }
+    if (c->profiling) {
+        for (int s = 0; s < EBCC_ST_COUNT; ++s) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, c->ev[s], c->ev[s + 1]);
+            c->stage_ms[s] = ms;
+        }
+    }
+    return 0;
+}
+
+extern "C" int ebcc_cuda_j2k_encode_batch(ebcc_cuda_ctx *c, const float *frames, size_t nframes, size_t H, size_t W,
+                                          float base_cr, const uint8_t **streams, size_t *sizes, float *minv,
+                                          float *maxv, int *flags)
+{
+    if (ebcc_cuda_reserve(c, H, W, nframes)) return -1;
+    if (ebcc_cuda_upload(c, frames, nframes)) return -1;
+    if (ebcc_cuda_j2k_encode_resident(c, nframes, base_cr)) return -1;
+    return ebcc_cuda_download(c, nframes, streams, sizes, minv, maxv, flags);
+}
+
+extern "C" void ebcc_cuda_set_profiling(ebcc_cuda_ctx *c, int enabled) { if (c) c->profiling = enabled; }
+extern "C" float ebcc_cuda_stage_ms(ebcc_cuda_ctx *c, int stage) { return (c && stage >= 0 && stage < EBCC_ST_COUNT) ? c->stage_ms[stage] : -1.0f; }
+extern "C" int ebcc_cuda_sync(ebcc_cuda_ctx *c) { if (!c) return -1; CK(cudaSetDevice(c->device)); CK(cudaStreamSynchronize(c->stream)); return 0; }
+extern "C" unsigned long long ebcc_cuda_launch_count(ebcc_cuda_ctx *c) { return c ? c->launches : 0; }
+
+extern "C" int ebcc_cuda_debug_coef(ebcc_cuda_ctx *c, size_t frame, float *dst)
+{
+    if (!c || frame >= c->cap_frames) return -1;
+    const size_t N = (size_t)c->plan.H * c->plan.W;
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaMemcpy(dst, c->d_coef + frame * N, N * sizeof(float), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+extern "C" int ebcc_cuda_debug_cblk(ebcc_cuda_ctx *c, size_t frame, size_t cblk, int *numbps, int *totalpasses,
+                                    int *rates, double *dists, int *numpasses)
+{
+    if (!c || frame >= c->cap_frames || cblk >= (size_t)c->plan.ncblks) return -1;
+    CblkOut o;
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaMemcpy(&o, c->d_cbout + frame * c->plan.ncblks + cblk, sizeof(o), cudaMemcpyDeviceToHost));
+    *numbps = o.numbps; *totalpasses = o.totalpasses; *numpasses = o.numpasses;
+    for (int i = 0; i < o.totalpasses && i < J2K_MAXPASSES; ++i) { rates[i] = o.rate[i]; dists[i] = o.dist[i]; }
+    return 0;
+}

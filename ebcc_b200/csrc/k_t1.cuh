@@ -1,0 +1,480 @@
+// k_t1.cuh -- EBCOT tier-1 encoder, split in two kernels:
+//
+//   k_t1_cm : one CTA per 64x64 code-block.  Quantises the block (t1.c:2397-2425), then runs the
+//             bit-plane passes (cleanup / significance propagation / magnitude refinement) in
+//             PARALLEL over stripe columns and emits the (context, decision) symbol stream in
+//             scan order through a CTA-wide prefix sum.  The scan-order dependence of the
+//             significance state is resolved analytically: a neighbour counts as significant
+//             if it was before the pass, or becomes so in this pass AND precedes the sample in
+//             scan order.  For the cleanup pass "becomes significant" is known a priori
+//             (insignificant, not visited, bit set); for the significance-propagation pass it is
+//             the least fixed point of a monotone map, reached by iterating to convergence.
+//   k_t1_mq : one THREAD per code-block, several code-blocks per warp.  Serial MQ arithmetic
+//             coder (mqc.c / mqc_inl.h) over the symbol stream, pass rates as opj_t1_encode_cblk
+//             computes them (t1.c:2655-2723).
+//
+// Integer/latency bound; bit-exact with opj_t1_encode_cblk by construction.
+#pragma once
+#include "common.cuh"
+
+#define T1_THREADS 256
+#define T1_CPT 4                    // stripe columns per thread
+#define T1_SW 66                    // state row stride: 64 + border
+#define T1_NSTATE (18 * T1_SW)      // 16 stripes + border
+#define T1_SYMBUF 10240             // max symbols per pass: 1024 stripe columns x 10
+
+#define CTX_ZC 0
+#define CTX_SC 9
+#define CTX_MAG 14
+#define CTX_AGG 17
+#define CTX_UNI 18
+
+// distortion LUTs (t1_generate_luts.c:259-290), filled by the host at start-up
+struct T1Luts { short sig[128], sig0[128], ref[128], ref0[128]; };
+
+// zero-coding context from neighbour counts (Annex D table D.1; t1_generate_luts.c:48-128)
+__device__ __forceinline__ int t1_zc_ctx(int orient, int h, int v, int d)
+{
+    if (orient == 1) { int t = h; h = v; v = t; }
+    if (orient != 3) {
+        if (h == 0) { if (v == 0) return d == 0 ? 0 : (d == 1 ? 1 : 2); return v == 1 ? 3 : 4; }
+        if (h == 1) { if (v == 0) return d == 0 ? 5 : 6; return 7; }
+        return 8;
+    }
+    int hv = h + v;
+    if (d == 0) return hv == 0 ? 0 : (hv == 1 ? 1 : 2);
+    if (d == 1) return hv == 0 ? 3 : (hv == 1 ? 4 : 5);
+    if (d == 2) return hv == 0 ? 6 : 7;
+    return 8;
+}
+
+// sign context + xor bit from horizontal / vertical contributions in {-1,0,1}
+// entry (hc+1)*3+(vc+1) packs n (3 bits) | spb << 3
+__device__ __forceinline__ int t1_sc_lut(int hc, int vc)
+{
+    const unsigned long long tab = 0x4ull | (0x3ull << 4) | (0x2ull << 8) | (0x1ull << 12) | (0x0ull << 16) |
+                                   (0x1ull << 20) | (0x2ull << 24) | (0x3ull << 28) | (0x4ull << 32) |
+                                   (0x8ull << 0) | (0x8ull << 4) | (0x8ull << 8) | (0x8ull << 12);
+    return (int)((tab >> (4 * ((hc + 1) * 3 + (vc + 1)))) & 0xf);
+}
+__device__ __forceinline__ int t1_contrib(int sa, int na, int sb, int nb)
+{
+    int pos = min(1, (sa & (na ^ 1)) + (sb & (nb ^ 1)));
+    int neg = min(1, (sa & na) + (sb & nb));
+    return pos - neg;
+}
+
+// window of one stripe column: significance of rows -1..4 (bit r+1) for W / own / E columns and
+// sign bits in the same layout
+struct T1Win { unsigned L, C, R, gL, gC, gR; };
+
+__device__ __forceinline__ unsigned t1_six(unsigned up, unsigned mid, unsigned dn)
+{
+    return ((up >> 3) & 1u) | ((mid & 0xfu) << 1) | ((dn & 1u) << 5);
+}
+
+struct T1Sym { unsigned long long bits; int cnt; };
+__device__ __forceinline__ void t1_put(T1Sym &s, int ctx, int d)
+{
+    s.bits |= (unsigned long long)((ctx << 1) | d) << (6 * s.cnt);
+    s.cnt++;
+}
+
+// zero-coding context of row j given window w (L/C/R hold time-correct significance)
+__device__ __forceinline__ int t1_zc_of(const T1Win &w, int j, int orient)
+{
+    int h = ((w.L >> (j + 1)) & 1) + ((w.R >> (j + 1)) & 1);
+    int v = ((w.C >> j) & 1) + ((w.C >> (j + 2)) & 1);
+    int d = ((w.L >> j) & 1) + ((w.L >> (j + 2)) & 1) + ((w.R >> j) & 1) + ((w.R >> (j + 2)) & 1);
+    return CTX_ZC + t1_zc_ctx(orient, h, v, d);
+}
+__device__ __forceinline__ int t1_has_nb(const T1Win &w, int j)
+{
+    unsigned m3 = 7u << j;
+    return ((w.L & m3) | (w.R & m3) | (w.C & (5u << j))) != 0;
+}
+// sign coding of row j: emits (ctx, sign ^ spb)
+__device__ __forceinline__ void t1_sign(T1Sym &s, const T1Win &w, int j, int neg)
+{
+    int hc = t1_contrib((w.R >> (j + 1)) & 1, (w.gR >> (j + 1)) & 1, (w.L >> (j + 1)) & 1, (w.gL >> (j + 1)) & 1);
+    int vc = t1_contrib((w.C >> j) & 1, (w.gC >> j) & 1, (w.C >> (j + 2)) & 1, (w.gC >> (j + 2)) & 1);
+    int e = t1_sc_lut(hc, vc);
+    t1_put(s, CTX_SC + (e & 7), neg ^ (e >> 3));
+}
+
+__device__ __forceinline__ int t1_nm_sig(const T1Luts *l, unsigned x, int bpno)
+{ return bpno > 0 ? l->sig[(x >> bpno) & 127] : l->sig0[x & 127]; }
+__device__ __forceinline__ int t1_nm_ref(const T1Luts *l, unsigned x, int bpno)
+{ return bpno > 0 ? l->ref[(x >> bpno) & 127] : l->ref0[x & 127]; }
+
+// state word per stripe column: bits 0-3 significant, 4-7 visited-in-sigpass (pi), 8-11 refined (mu)
+#define ST_SIG(w) ((w) & 0xfu)
+#define ST_PI(w) (((w) >> 4) & 0xfu)
+#define ST_MU(w) (((w) >> 8) & 0xfu)
+
+__global__ void __launch_bounds__(T1_THREADS)
+k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, const BandDesc *__restrict__ bands,
+        const T1Luts *__restrict__ g_luts, CblkOut *cbout, unsigned char *sym_pool,
+        int W, int H, int ncblks, size_t sym_stride)
+{
+    __shared__ unsigned st[T1_NSTATE];      // state words
+    __shared__ unsigned sg[T1_NSTATE];      // sign nibbles (static)
+    __shared__ unsigned nw[T1_NSTATE];      // newly significant in the running pass
+    __shared__ unsigned char symbuf[T1_SYMBUF + 64];
+    __shared__ T1Luts luts;
+    __shared__ int warp_sum[T1_THREADS / 32];
+    __shared__ int s_max, s_nmsedec, s_total;
+
+    const int tid = threadIdx.x;
+    const int cbi = blockIdx.x, frame = blockIdx.y;
+    const CblkDesc cb = cblks[cbi];
+    const BandDesc *bd = &bands[cb.band];
+    const int bw = cb.w, bh = cb.h, orient = cb.orient;
+    const int nstripes = (bh + 3) >> 2, nsc = nstripes * bw;
+    CblkOut *out = cbout + (size_t)frame * ncblks + cbi;
+    unsigned char *sym = sym_pool + (size_t)frame * sym_stride + cb.sym_off;
+
+    for (int i = tid; i < T1_NSTATE; i += T1_THREADS) { st[i] = 0; sg[i] = 0; nw[i] = 0; }
+    for (int i = tid; i < (int)(sizeof(T1Luts) / 2); i += T1_THREADS) ((short *)&luts)[i] = ((const short *)g_luts)[i];
+    if (tid == 0) { s_max = 0; s_nmsedec = 0; }
+    __syncthreads();
+
+    // ---- quantise: lrintf((coef / stepsize) * 64) ------------------------------------------------
+    unsigned mag[T1_CPT][4];
+    int sidx[T1_CPT], lim[T1_CPT];
+    unsigned sgn4[T1_CPT];
+    const float stepsize = bd->stepsize;
+    const float *src = coef + (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx;
+    int mymax = 0;
+#pragma unroll
+    for (int k = 0; k < T1_CPT; ++k) {
+        int q = tid * T1_CPT + k;
+        sidx[k] = -1; lim[k] = 0; sgn4[k] = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) mag[k][j] = 0;
+        if (q < nsc) {
+            int s = q / bw, x = q - s * bw;
+            sidx[k] = (s + 1) * T1_SW + x + 1;
+            lim[k] = min(4, bh - 4 * s);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (j < lim[k]) {
+                    float c = src[(size_t)(4 * s + j) * W + x];
+                    int v = __float2int_rn(__fmul_rn(__fdiv_rn(c, stepsize), 64.0f));
+                    int a = v < 0 ? -v : v;
+                    mag[k][j] = (unsigned)a;
+                    if (v < 0) sgn4[k] |= 1u << j;
+                    mymax = max(mymax, a);
+                }
+            sg[sidx[k]] = sgn4[k];
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) mymax = max(mymax, __shfl_xor_sync(0xffffffffu, mymax, o));
+    if ((tid & 31) == 0) atomicMax(&s_max, mymax);
+    __syncthreads();
+    const int maxv = s_max;
+    const int numbps = maxv ? (32 - __clz(maxv)) - 6 : 0;     // floorlog2(max)+1-T1_NMSEDEC_FRACBITS
+    if (tid == 0) { out->numbps = numbps; out->totalpasses = 0; out->datalen = 0; out->numpasses = 0; }
+    if (numbps <= 0) return;
+
+    unsigned total_syms = 0;
+    int passno = 0;
+    for (int bpno = numbps - 1, passtype = 2; bpno >= 0; ++passno) {
+        const unsigned one = 1u << (bpno + 6);
+        T1Sym sy[T1_CPT];
+        unsigned upd_sig[T1_CPT], upd_pi[T1_CPT], upd_mu[T1_CPT];
+        int nmsedec = 0;
+
+        // ---- pass-specific preparation of nw[] ---------------------------------------------------
+        if (passtype == 2) {
+#pragma unroll
+            for (int k = 0; k < T1_CPT; ++k)
+                if (sidx[k] >= 0) {
+                    unsigned w = st[sidx[k]], bits = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) bits |= ((mag[k][j] & one) ? 1u : 0u) << j;
+                    nw[sidx[k]] = ~ST_SIG(w) & ~ST_PI(w) & bits & 0xfu;
+                }
+            __syncthreads();
+        } else if (passtype == 0) {
+#pragma unroll
+            for (int k = 0; k < T1_CPT; ++k) if (sidx[k] >= 0) nw[sidx[k]] = 0;
+            __syncthreads();
+        }
+
+        // ---- evaluate (sigpass iterates to the fixed point; the last sweep emits) ------------------
+        for (;;) {
+            int changed = 0;
+#pragma unroll
+            for (int k = 0; k < T1_CPT; ++k) {
+                sy[k].bits = 0; sy[k].cnt = 0; upd_sig[k] = 0; upd_pi[k] = 0; upd_mu[k] = 0;
+                if (sidx[k] < 0) continue;
+                const int p = sidx[k];
+                const unsigned cw = st[p];
+                T1Win w;
+                {
+                    unsigned lo = t1_six(ST_SIG(st[p - T1_SW - 1]), ST_SIG(st[p - 1]), ST_SIG(st[p + T1_SW - 1]));
+                    unsigned co = t1_six(ST_SIG(st[p - T1_SW]), ST_SIG(cw), ST_SIG(st[p + T1_SW]));
+                    unsigned ro = t1_six(ST_SIG(st[p - T1_SW + 1]), ST_SIG(st[p + 1]), ST_SIG(st[p + T1_SW + 1]));
+                    if (passtype != 1) {
+                        unsigned ln = t1_six(nw[p - T1_SW - 1], nw[p - 1], nw[p + T1_SW - 1]);
+                        unsigned cn = t1_six(nw[p - T1_SW], 0, 0);
+                        unsigned rn = t1_six(nw[p - T1_SW + 1], 0, 0);
+                        lo |= ln & 0x1fu; co |= cn & 1u; ro |= rn & 1u;
+                    }
+                    w.L = lo; w.C = co; w.R = ro;
+                    w.gL = t1_six(sg[p - T1_SW - 1], sg[p - 1], sg[p + T1_SW - 1]);
+                    w.gC = t1_six(sg[p - T1_SW], sgn4[k], sg[p + T1_SW]);
+                    w.gR = t1_six(sg[p - T1_SW + 1], sg[p + 1], sg[p + T1_SW + 1]);
+                }
+                const unsigned sig = ST_SIG(cw), pi = ST_PI(cw), mu = ST_MU(cw);
+                if (passtype == 0) {
+                    // significance propagation (t1.c:363-410, 479-580)
+                    unsigned coded = 0, fresh = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        if (j >= lim[k]) break;
+                        if (!((sig >> j) & 1) && t1_has_nb(w, j)) {
+                            int v = (mag[k][j] & one) ? 1 : 0;
+                            t1_put(sy[k], t1_zc_of(w, j, orient), v);
+                            if (v) {
+                                t1_sign(sy[k], w, j, (sgn4[k] >> j) & 1);
+                                nmsedec += t1_nm_sig(&luts, mag[k][j], bpno);
+                                fresh |= 1u << j;
+                                w.C |= 1u << (j + 1);
+                            }
+                            coded |= 1u << j;
+                        }
+                    }
+                    if (fresh != nw[p]) { nw[p] = fresh; changed = 1; }
+                    upd_sig[k] = fresh; upd_pi[k] = coded;
+                } else if (passtype == 1) {
+                    // magnitude refinement (t1.c:743-765, 814-922)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        if (j >= lim[k]) break;
+                        if (((sig >> j) & 1) && !((pi >> j) & 1)) {
+                            int ctx = ((mu >> j) & 1) ? CTX_MAG + 2 : (t1_has_nb(w, j) ? CTX_MAG + 1 : CTX_MAG);
+                            nmsedec += t1_nm_ref(&luts, mag[k][j], bpno);
+                            t1_put(sy[k], ctx, (mag[k][j] & one) ? 1 : 0);
+                            upd_mu[k] |= 1u << j;
+                        }
+                    }
+                } else {
+                    // cleanup with run-length mode (t1.c:1051-1116, 1163-1256)
+                    int runlen = 0, agg = 0;
+                    if (lim[k] == 4 && (sig | pi) == 0 && (w.L | w.C | w.R) == 0) {
+                        agg = 1;
+                        const unsigned fresh = nw[p];
+                        runlen = fresh ? (__ffs((int)fresh) - 1) : 4;
+                        t1_put(sy[k], CTX_AGG, runlen != 4);
+                        if (runlen != 4) { t1_put(sy[k], CTX_UNI, runlen >> 1); t1_put(sy[k], CTX_UNI, runlen & 1); }
+                    }
+                    if (runlen < 4) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            if (j >= lim[k]) break;
+                            if (j < runlen) continue;
+                            int v;
+                            if (agg && j == runlen) v = 1;
+                            else if (!(((sig | pi) >> j) & 1)) {
+                                v = (mag[k][j] & one) ? 1 : 0;
+                                t1_put(sy[k], t1_zc_of(w, j, orient), v);
+                            } else v = 0;
+                            if (v) {
+                                t1_sign(sy[k], w, j, (sgn4[k] >> j) & 1);
+                                nmsedec += t1_nm_sig(&luts, mag[k][j], bpno);
+                                w.C |= 1u << (j + 1);
+                            }
+                        }
+                    }
+                    upd_sig[k] = nw[p];
+                }
+            }
+            if (passtype != 0) break;
+            if (!__syncthreads_or(changed)) break;
+            nmsedec = 0;
+        }
+
+        // ---- CTA-wide exclusive scan of symbol counts, staged write of the symbol bytes ------------
+        int mycnt = 0;
+#pragma unroll
+        for (int k = 0; k < T1_CPT; ++k) mycnt += sy[k].cnt;
+        int incl = mycnt;
+        for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, o); if ((tid & 31) >= o) incl += t; }
+        if ((tid & 31) == 31) warp_sum[tid >> 5] = incl;
+        for (int o = 16; o > 0; o >>= 1) nmsedec += __shfl_xor_sync(0xffffffffu, nmsedec, o);
+        if ((tid & 31) == 0 && nmsedec) atomicAdd(&s_nmsedec, nmsedec);
+        __syncthreads();
+        int off = incl - mycnt;
+        for (int wi = 0; wi < (tid >> 5); ++wi) off += warp_sum[wi];
+        if (tid == T1_THREADS - 1) s_total = off + mycnt;
+#pragma unroll
+        for (int k = 0; k < T1_CPT; ++k) {
+            unsigned long long b = sy[k].bits;
+            for (int i = 0; i < sy[k].cnt; ++i) { symbuf[off++] = (unsigned char)(b & 63); b >>= 6; }
+        }
+        // ---- state update ---------------------------------------------------------------------------
+#pragma unroll
+        for (int k = 0; k < T1_CPT; ++k)
+            if (sidx[k] >= 0) {
+                unsigned w = st[sidx[k]];
+                if (passtype == 2) w = (w | upd_sig[k]) & ~0xf0u;                 // new significance, clear pi
+                else if (passtype == 0) w |= upd_sig[k] | (upd_pi[k] << 4);
+                else w |= upd_mu[k] << 8;
+                st[sidx[k]] = w;
+            }
+        __syncthreads();
+        const int total = s_total;
+        for (int i = tid; i < total; i += T1_THREADS) sym[total_syms + i] = symbuf[i];
+        total_syms += (unsigned)total;
+        if (tid == 0) { out->nsym_end[passno] = total_syms; out->nmsedec[passno] = s_nmsedec; s_nmsedec = 0; }
+        __syncthreads();
+        if (++passtype == 3) { passtype = 0; bpno--; }
+    }
+
+    // ---- distortion per pass: opj_t1_getwmsedec, accumulated in pass order (t1.c:1416-1449, 2655) --
+    if (tid == 0) {
+        out->totalpasses = passno;
+        const double wn = bd->wnorm;
+        double cum = 0.0;
+        for (int p = 0; p < passno; ++p) {
+            int bp = p == 0 ? numbps - 1 : numbps - 2 - (p - 1) / 3;
+            double w = __dmul_rn(wn, (double)(1 << bp));
+            w = __dmul_rn(w, __ddiv_rn(__dmul_rn(w, (double)out->nmsedec[p]), 8192.0));
+            cum = __dadd_rn(cum, w);
+            out->dist[p] = cum;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// MQ coder.  State table (Annex C table C.2; mqc.c:61-157) packed as qe | nmps<<16 | nlps<<22 | sw<<28.
+struct MqTable { unsigned e[47]; };
+
+#define MQ_LANES 8            // code-blocks per warp (lanes 0..MQ_LANES-1 of each warp are active)
+#define MQ_THREADS 128
+
+struct MqEnc {
+    unsigned a, c;
+    int ct;
+    int pos;                  // index of the pending (not yet stored) byte, -1 = OPJ's fake byte
+    unsigned pend;
+    unsigned char *dst;
+};
+
+__device__ __forceinline__ void mq_advance(MqEnc &q, unsigned nb)
+{
+    if (q.pos >= 0) q.dst[q.pos] = (unsigned char)q.pend;
+    q.pos++; q.pend = nb;
+}
+
+__device__ __forceinline__ void mq_byteout(MqEnc &q)
+{
+    if (q.pend == 0xff) {
+        mq_advance(q, (q.c >> 20) & 0xff); q.c &= 0xfffff; q.ct = 7;
+    } else if ((q.c & 0x8000000) == 0) {
+        mq_advance(q, (q.c >> 19) & 0xff); q.c &= 0x7ffff; q.ct = 8;
+    } else {
+        q.pend++;
+        if (q.pend == 0xff) {
+            q.c &= 0x7ffffff;
+            mq_advance(q, (q.c >> 20) & 0xff); q.c &= 0xfffff; q.ct = 7;
+        } else {
+            mq_advance(q, (q.c >> 19) & 0xff); q.c &= 0x7ffff; q.ct = 8;
+        }
+    }
+}
+
+__device__ __forceinline__ void mq_renorm(MqEnc &q)
+{
+    int s = __clz((int)q.a) - 16;           // shifts needed to bring bit 15 of a up
+    while (s > 0) {
+        int k = min(s, q.ct);
+        q.a <<= k; q.c <<= k; q.ct -= k; s -= k;
+        if (q.ct == 0) mq_byteout(q);
+    }
+}
+
+__global__ void __launch_bounds__(MQ_THREADS)
+k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char *__restrict__ sym_pool,
+        unsigned char *mq_pool, const MqTable *__restrict__ g_tab, int ncblks, int nframes,
+        size_t sym_stride, size_t mq_stride)
+{
+    __shared__ unsigned tab[47];
+    __shared__ unsigned ctxs[19 * MQ_THREADS];
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (tid < 47) tab[tid] = g_tab->e[tid];
+    __syncthreads();
+    const int warp_global = (blockIdx.x * MQ_THREADS + tid) >> 5;
+    const long long job = (long long)warp_global * MQ_LANES + lane;
+    if (lane >= MQ_LANES || job >= (long long)ncblks * nframes) return;
+    const int frame = (int)(job / ncblks), cbi = (int)(job - (long long)frame * ncblks);
+    const CblkDesc cb = cblks[cbi];
+    CblkOut *out = cbout + (size_t)frame * ncblks + cbi;
+    const int npasses = out->totalpasses;
+    if (npasses <= 0) return;
+    const unsigned char *sym = sym_pool + (size_t)frame * sym_stride + cb.sym_off;
+
+    unsigned *cx = ctxs + tid;           // context ctx lives at cx[ctx * MQ_THREADS]
+    for (int i = 0; i < 19; ++i) cx[i * MQ_THREADS] = tab[0] & 0xffffu;          // state 0, mps 0
+    cx[CTX_UNI * MQ_THREADS] = (tab[46] & 0xffffu) | (46u << 17);
+    cx[CTX_AGG * MQ_THREADS] = (tab[3] & 0xffffu) | (3u << 17);
+    cx[CTX_ZC * MQ_THREADS] = (tab[4] & 0xffffu) | (4u << 17);
+
+    MqEnc q;
+    q.a = 0x8000; q.c = 0; q.ct = 12; q.pos = -1; q.pend = 0;
+    q.dst = mq_pool + (size_t)frame * mq_stride + cb.mq_off;
+
+    unsigned i = 0;
+    uint4 buf = make_uint4(0, 0, 0, 0);
+    for (int p = 0; p < npasses; ++p) {
+        const unsigned end = out->nsym_end[p];
+        for (; i < end; ++i) {
+            if ((i & 15u) == 0) buf = *(const uint4 *)(sym + i);
+            unsigned wsel = (i >> 2) & 3u;
+            unsigned word = wsel == 0 ? buf.x : (wsel == 1 ? buf.y : (wsel == 2 ? buf.z : buf.w));
+            unsigned s = (word >> ((i & 3u) * 8)) & 0xffu;
+            const unsigned d = s & 1u, ctx = s >> 1;
+            unsigned w = cx[ctx * MQ_THREADS];
+            const unsigned qe = w & 0xffffu, mps = (w >> 16) & 1u, idx = w >> 17;
+            q.a -= qe;
+            if (d == mps) {
+                if (q.a & 0x8000u) { q.c += qe; continue; }
+                if (q.a < qe) q.a = qe; else q.c += qe;
+                unsigned ni = (tab[idx] >> 16) & 63u;
+                cx[ctx * MQ_THREADS] = (tab[ni] & 0xffffu) | (mps << 16) | (ni << 17);
+            } else {
+                if (q.a < qe) q.c += qe; else q.a = qe;
+                unsigned t = tab[idx];
+                unsigned ni = (t >> 22) & 63u, nm = mps ^ ((t >> 28) & 1u);
+                cx[ctx * MQ_THREADS] = (tab[ni] & 0xffffu) | (nm << 16) | (ni << 17);
+            }
+            mq_renorm(q);
+        }
+        if (p == npasses - 1) {
+            // opj_mqc_flush (mqc.c:212-227)
+            unsigned tempc = q.c + q.a;
+            q.c |= 0xffffu;
+            if (q.c >= tempc) q.c -= 0x8000u;
+            q.c <<= q.ct; mq_byteout(q);
+            q.c <<= q.ct; mq_byteout(q);
+            if (q.pend != 0xff) mq_advance(q, 0);
+            out->rate[p] = q.pos;
+        } else {
+            out->rate[p] = q.pos + 3;
+        }
+    }
+    // final pending byte (beyond numbytes) is never part of the stream; store for completeness
+    int last = q.pos;
+    out->datalen = last;
+    // monotone fix-up, then strip a trailing 0xFF from each pass (t1.c:2700-2723)
+    for (int p = npasses - 1; p >= 0; --p) {
+        int r = out->rate[p];
+        if (r > last) out->rate[p] = last; else last = r;
+    }
+    for (int p = 0; p < npasses; ++p) {
+        int r = out->rate[p];
+        if (r > 0 && q.dst[r - 1] == 0xff) out->rate[p] = r - 1;
+    }
+}

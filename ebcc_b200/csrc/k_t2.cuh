@@ -1,0 +1,407 @@
+// k_t2.cuh -- PCRD rate allocation + tier-2 packet assembly on the device.
+//
+//   k_pcrd_t2   : one CTA per (frame, rate probe).  Slope min/max, the <=128-step threshold
+//                 bisection of opj_tcd_rateallocate (tcd.c:465-712) with opj_tcd_makelayer's
+//                 inclusion rule (tcd.c:248-353), feasibility = exact tier-2 byte count.  Packet
+//                 headers (t2.c:662-1006) are generated in parallel: every code-block derives its
+//                 own tag-tree / pass-count / length bits in closed form, a CTA prefix sum places
+//                 them, and one warp per packet applies the 0xFF bit-stuffing rule of bio.c.
+//   k_t2_bodies : copies the selected MQ segments to their prefix-summed offsets and writes the
+//                 SOC..EOC markers (j2k.c:13080-13133, 4355, 4835, 5194).
+#pragma once
+#include "common.cuh"
+
+#define T2_THREADS 256
+#define T2_INF 0x3fffffff
+
+struct T2Smem {
+    int *numpasses;       // [ncblks] current allocation
+    int *prevn;           // [ncblks] allocation of the previous makelayer call
+    int *nbits;           // [ncblks+1] header bits of each block, then exclusive scan
+    int *bodylen;         // [ncblks+1] selected MQ bytes of each block, then exclusive scan
+    unsigned long long *hb;   // [2*ncblks] header bits, MSB-first packed from bit 127 down
+    int *nd_incl;         // [nnodes] any included leaf below
+    int *nd_imsb;         // [nnodes] min zero-bit-planes below
+    int *nd_first;        // [nnodes] raster index of first included leaf below
+    unsigned *bitbuf;     // [bitwords] packet header bits, MSB first
+};
+
+__host__ __device__ inline size_t t2_smem_bytes(int ncblks, int nnodes)
+{
+    size_t words = (size_t)ncblks * 4 + (size_t)nnodes * 3 + (size_t)ncblks * 4 /*hb*/ + (size_t)ncblks * 3 + 6 * 2 + 64;
+    return words * 4 + 64;
+}
+
+__device__ __forceinline__ int t2_floorlog2(int a) { return a > 1 ? 31 - __clz(a) : 0; }
+
+// append n bits (value v, n <= 32) to a 128-bit MSB-first accumulator
+__device__ __forceinline__ void hb_put(unsigned long long &hi, unsigned long long &lo, int &used, unsigned v, int n)
+{
+    for (int i = n - 1; i >= 0; --i) {
+        unsigned b = (v >> i) & 1u;
+        if (used < 64) hi |= (unsigned long long)b << (63 - used);
+        else lo |= (unsigned long long)b << (127 - used);
+        used++;
+    }
+}
+
+// CTA exclusive scan of a[0..n) in place; returns total.  All threads must call.
+__device__ int cta_exscan(int *a, int n, int *scratch /* >= T2_THREADS/32 + 1 */)
+{
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int per = (n + nt - 1) / nt;
+    const int b = min(n, tid * per), e = min(n, b + per);
+    int sum = 0;
+    for (int i = b; i < e; ++i) sum += a[i];
+    int incl = sum;
+    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, o); if ((tid & 31) >= o) incl += t; }
+    if ((tid & 31) == 31) scratch[tid >> 5] = incl;
+    __syncthreads();
+    int off = incl - sum;
+    for (int w = 0; w < (tid >> 5); ++w) off += scratch[w];
+    int total = 0;
+    for (int w = 0; w < (nt >> 5); ++w) total += scratch[w];
+    for (int i = b; i < e; ++i) { int v = a[i]; a[i] = off; off += v; }
+    __syncthreads();
+    return total;
+}
+
+// One tier-2 run over the current allocation.  Returns the total packet bytes (headers + bodies).
+// If dst != nullptr the packet headers are stored at their final offsets and body_off[k] receives
+// the destination offset of each included block's MQ segment.
+__device__ int t2_run(const Plan *__restrict__ plan, const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ co,
+                      T2Smem &s, int *scratch, unsigned char *dst, int *body_off)
+{
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int ncblks = plan->ncblks, nnodes = plan->nnodes;
+
+    // ---- tag-tree node aggregates, leaves first ------------------------------------------------
+    for (int k = tid; k < ncblks; k += nt) {
+        const CblkDesc &cb = cblks[k];
+        const BandDesc &bd = plan->bands[cb.band];
+        int node = bd.tt_base + cb.gy * bd.cw + cb.gx;
+        int np = s.numpasses[k];
+        s.nd_incl[node] = np > 0;
+        s.nd_imsb[node] = bd.numbps - co[k].numbps;
+        s.nd_first[node] = np > 0 ? (cb.gy * bd.cw + cb.gx) : T2_INF;
+        s.bodylen[k] = np > 0 ? co[k].rate[np - 1] : 0;
+    }
+    __syncthreads();
+    for (int l = 1; l < 8; ++l) {
+        for (int bi = 0; bi < plan->nbands; ++bi) {
+            const BandDesc &bd = plan->bands[bi];
+            if (l >= bd.tt_nlev) continue;
+            const int w = bd.tt_w[l], h = bd.tt_h[l], cwp = bd.tt_w[l - 1], chp = bd.tt_h[l - 1];
+            for (int n = tid; n < w * h; n += nt) {
+                int nx = n % w, ny = n / w;
+                int incl = 0, imsb = T2_INF, first = T2_INF;
+                for (int dy = 0; dy < 2; ++dy)
+                    for (int dx = 0; dx < 2; ++dx) {
+                        int cx = 2 * nx + dx, cy = 2 * ny + dy;
+                        if (cx < cwp && cy < chp) {
+                            int c = bd.tt_base + bd.tt_off[l - 1] + cy * cwp + cx;
+                            incl |= s.nd_incl[c];
+                            imsb = min(imsb, s.nd_imsb[c]);
+                            first = min(first, s.nd_first[c]);
+                        }
+                    }
+                int me = bd.tt_base + bd.tt_off[l] + n;
+                s.nd_incl[me] = incl; s.nd_imsb[me] = imsb; s.nd_first[me] = first;
+            }
+        }
+        __syncthreads();
+    }
+    (void)nnodes;
+
+    // ---- per-block header bits --------------------------------------------------------------------
+    for (int k = tid; k < ncblks; k += nt) {
+        const CblkDesc &cb = cblks[k];
+        const BandDesc &bd = plan->bands[cb.band];
+        unsigned long long hi = 0, lo = 0; int used = 0;
+        const int x = cb.gx, y = cb.gy, leaf = y * bd.cw + x;
+        // first block of a packet carries the "packet not empty" bit
+        if (k == plan->res_first[bd.resno]) hb_put(hi, lo, used, 1, 1);
+        // inclusion tag tree, threshold 1 (single layer)
+        for (int l = bd.tt_nlev - 1; l >= 0; --l) {
+            int mask = (1 << l) - 1;
+            if ((x & mask) || (y & mask)) continue;             // not the first visitor of this node
+            int node = bd.tt_base + bd.tt_off[l] + (y >> l) * bd.tt_w[l] + (x >> l);
+            int parent_ok = 1;
+            if (l + 1 < bd.tt_nlev)
+                parent_ok = s.nd_incl[bd.tt_base + bd.tt_off[l + 1] + (y >> (l + 1)) * bd.tt_w[l + 1] + (x >> (l + 1))];
+            if (parent_ok) hb_put(hi, lo, used, (unsigned)s.nd_incl[node], 1);
+        }
+        const int np = s.numpasses[k];
+        if (np > 0) {
+            // zero-bit-plane tag tree, threshold "infinite"
+            int pv = 0;
+            for (int l = bd.tt_nlev - 1; l >= 0; --l) {
+                int node = bd.tt_base + bd.tt_off[l] + (y >> l) * bd.tt_w[l] + (x >> l);
+                int v = s.nd_imsb[node];
+                if (s.nd_first[node] == leaf) {
+                    int z = v - pv;
+                    while (z > 0) { int c = min(z, 32); hb_put(hi, lo, used, 0, c); z -= c; }
+                    hb_put(hi, lo, used, 1, 1);
+                }
+                pv = v;
+            }
+            // number of passes (t2.c:184-197)
+            if (np == 1) hb_put(hi, lo, used, 0, 1);
+            else if (np == 2) hb_put(hi, lo, used, 2, 2);
+            else if (np <= 5) hb_put(hi, lo, used, 0xc | (unsigned)(np - 3), 4);
+            else if (np <= 36) hb_put(hi, lo, used, 0x1e0 | (unsigned)(np - 6), 9);
+            else hb_put(hi, lo, used, 0xff80 | (unsigned)(np - 37), 16);
+            // Lblock increment (comma code) and segment length (one codeword segment)
+            const int len = s.bodylen[k];
+            const int lg = t2_floorlog2(np);
+            int inc = t2_floorlog2(len) + 1 - (3 + lg);
+            if (inc < 0) inc = 0;
+            for (int i = 0; i < inc; ++i) hb_put(hi, lo, used, 1, 1);
+            hb_put(hi, lo, used, 0, 1);
+            hb_put(hi, lo, used, (unsigned)len, 3 + inc + lg);
+        }
+        s.hb[2 * k] = hi; s.hb[2 * k + 1] = lo; s.nbits[k] = used;
+    }
+    if (tid == 0) { s.nbits[ncblks] = 0; s.bodylen[ncblks] = 0; }
+    __syncthreads();
+    cta_exscan(s.nbits, ncblks + 1, scratch);        // nbits[k] = bit offset, nbits[ncblks] = total
+    cta_exscan(s.bodylen, ncblks + 1, scratch);
+
+    // ---- scatter the bits of every packet into one MSB-first bit buffer (32-bit aligned packets) ---
+    __shared__ int pk_bitbase[J2K_NRES], pk_nbits[J2K_NRES], pk_hdr[J2K_NRES], pk_off[J2K_NRES + 1];
+    __shared__ int bitwords;
+    if (tid == 0) {
+        int base = 0;
+        for (int r = 0; r < J2K_NRES; ++r) {
+            int f = plan->res_first[r], c = plan->res_count[r];
+            int nb = s.nbits[f + c] - s.nbits[f];
+            pk_bitbase[r] = base; pk_nbits[r] = nb;
+            base += ((nb + 31) & ~31) + 32;
+        }
+        bitwords = base >> 5;
+    }
+    __syncthreads();
+    for (int i = tid; i < bitwords; i += nt) s.bitbuf[i] = 0;
+    __syncthreads();
+    for (int k = tid; k < ncblks; k += nt) {
+        const int r = plan->bands[cblks[k].band].resno;
+        int dbit = pk_bitbase[r] + s.nbits[k] - s.nbits[plan->res_first[r]];
+        int remaining = s.nbits[k + 1] - s.nbits[k], src = 0;
+        const unsigned long long hi = s.hb[2 * k], lo = s.hb[2 * k + 1];
+        while (remaining > 0) {
+            int bo = dbit & 31, take = min(32 - bo, remaining);
+            unsigned long long xx = src < 64 ? ((hi << src) | (src ? (lo >> (64 - src)) : 0ull)) : (lo << (src - 64));
+            unsigned v = (unsigned)(xx >> (64 - take));
+            atomicOr(&s.bitbuf[dbit >> 5], v << (32 - bo - take));
+            dbit += take; src += take; remaining -= take;
+        }
+    }
+    __syncthreads();
+
+    // ---- bit stuffing (bio.c:75-84): one warp per packet; pass 0 sizes, pass 1 stores ---------------
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int pass = 0; pass < (dst ? 2 : 1); ++pass) {
+        if (warp < J2K_NRES) {
+            const int r = warp, nb = pk_nbits[r], base = pk_bitbase[r];
+            unsigned char *o = (pass == 1) ? dst + pk_off[r] : nullptr;
+            int p = 0, outpos = 0;
+            while (p < nb) {
+                const int q = p + 8 * lane;
+                unsigned byte = 0;
+                if (q < nb) {
+                    int gb = base + q, wi = gb >> 5, bo = gb & 31;
+                    unsigned long long two = ((unsigned long long)s.bitbuf[wi] << 32) | s.bitbuf[wi + 1];
+                    byte = (unsigned)(two >> (56 - bo)) & 0xffu;
+                }
+                const int nvalid = min(32, (nb - p + 7) >> 3);
+                const unsigned m = __ballot_sync(0xffffffffu, q < nb && byte == 0xffu);
+                const int first = m ? (__ffs((int)m) - 1) : 32;
+                if (first < nvalid) {
+                    if (o && lane <= first) o[outpos + lane] = (unsigned char)byte;
+                    outpos += first + 1; p += 8 * (first + 1);
+                    unsigned b7 = 0;
+                    if (p < nb) {
+                        int gb = base + p, wi = gb >> 5, bo = gb & 31;
+                        unsigned long long two = ((unsigned long long)s.bitbuf[wi] << 32) | s.bitbuf[wi + 1];
+                        b7 = (unsigned)(two >> (57 - bo)) & 0x7fu;
+                    }
+                    if (o && lane == 0) o[outpos] = (unsigned char)b7;
+                    outpos += 1; p += 7;
+                } else {
+                    if (o && lane < nvalid) o[outpos + lane] = (unsigned char)byte;
+                    outpos += nvalid; p += 8 * nvalid;
+                }
+            }
+            if (pass == 0 && lane == 0) pk_hdr[r] = outpos;
+        }
+        __syncthreads();
+        if (pass == 0) {
+            if (tid == 0) {
+                int off = 0;
+                for (int r = 0; r < J2K_NRES; ++r) {
+                    int f = plan->res_first[r], c = plan->res_count[r];
+                    pk_off[r] = off;
+                    off += pk_hdr[r] + (s.bodylen[f + c] - s.bodylen[f]);
+                }
+                pk_off[J2K_NRES] = off;
+            }
+            __syncthreads();
+        }
+    }
+    if (body_off) {
+        for (int k = tid; k < ncblks; k += nt) {
+            const int r = plan->bands[cblks[k].band].resno, f = plan->res_first[r];
+            body_off[k] = pk_off[r] + pk_hdr[r] + (s.bodylen[k] - s.bodylen[f]);
+        }
+    }
+    const int total = pk_off[J2K_NRES];
+    __syncthreads();
+    return total;
+}
+
+// opj_tcd_makelayer for one block (tcd.c:283-318): passes kept while thresh - dd/dr < DBL_EPSILON
+__device__ __forceinline__ int t2_makelayer_block(const CblkOut &c, double thresh)
+{
+    if (thresh < 0) return c.totalpasses;
+    int n = 0;
+    for (int p = 0; p < c.totalpasses; ++p) {
+        unsigned dr; double dd;
+        if (n == 0) { dr = (unsigned)c.rate[p]; dd = c.dist[p]; }
+        else { dr = (unsigned)(c.rate[p] - c.rate[n - 1]); dd = __dsub_rn(c.dist[p], c.dist[n - 1]); }
+        if (!dr) { if (dd != 0) n = p + 1; continue; }
+        if (__dsub_rn(thresh, __ddiv_rn(dd, (double)dr)) < 2.2204460492503131e-16) n = p + 1;
+    }
+    return n;
+}
+
+struct ProbeOut {
+    int total_bytes;       // tile-part body bytes (packets)
+    int stream_bytes;      // whole codestream length
+    int iters;
+    int pad;
+    double thresh;
+};
+
+// grid = (nframes); one probe per frame.  maxlen[frame] < 0 means "use every pass" (rates <= 1).
+__global__ void __launch_bounds__(T2_THREADS)
+k_pcrd_t2(const Plan *__restrict__ plan, const CblkDesc *__restrict__ cblks, CblkOut *cbout,
+          const int *__restrict__ maxlen_arr, unsigned char *out_pool, int *body_off_pool, ProbeOut *pout,
+          const FrameStat *__restrict__ stat)
+{
+    EBCC_DYN_SMEM(unsigned char, smem);
+    __shared__ double red_min[T2_THREADS / 32], red_max[T2_THREADS / 32];
+    __shared__ int scratch[T2_THREADS / 32 + 1];
+    const int tid = threadIdx.x, nt = blockDim.x, frame = blockIdx.x;
+    const int ncblks = plan->ncblks, nnodes = plan->nnodes;
+    if (stat && (stat[frame].flags & (STAT_CONST | STAT_NANINF))) {
+        if (tid == 0) { pout[frame].total_bytes = 0; pout[frame].stream_bytes = 0; pout[frame].iters = 0; pout[frame].thresh = 0; }
+        return;
+    }
+    CblkOut *co = cbout + (size_t)frame * ncblks;
+
+    T2Smem s;
+    {
+        unsigned long long *p8 = (unsigned long long *)smem;
+        s.hb = p8; p8 += 2 * (size_t)ncblks;
+        int *p = (int *)p8;
+        s.numpasses = p; p += ncblks;
+        s.prevn = p; p += ncblks;
+        s.nbits = p; p += ncblks + 1;
+        s.bodylen = p; p += ncblks + 1;
+        s.nd_incl = p; p += nnodes;
+        s.nd_imsb = p; p += nnodes;
+        s.nd_first = p; p += nnodes;
+        s.bitbuf = (unsigned *)p;
+    }
+
+    // ---- slope range over all passes (tcd.c:487-541) -------------------------------------------------
+    double mn = 1.7976931348623157e308, mx = 0.0;
+    for (int k = tid; k < ncblks; k += nt) {
+        const CblkOut &c = co[k];
+        for (int p = 0; p < c.totalpasses; ++p) {
+            int dr; double dd;
+            if (p == 0) { dr = c.rate[0]; dd = c.dist[0]; }
+            else { dr = c.rate[p] - c.rate[p - 1]; dd = __dsub_rn(c.dist[p], c.dist[p - 1]); }
+            if (dr == 0) continue;
+            double sl = __ddiv_rn(dd, (double)dr);
+            if (sl < mn) mn = sl;
+            if (sl > mx) mx = sl;
+        }
+        s.prevn[k] = 0;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        double a = __shfl_xor_sync(0xffffffffu, mn, o), b = __shfl_xor_sync(0xffffffffu, mx, o);
+        if (a < mn) mn = a;
+        if (b > mx) mx = b;
+    }
+    if ((tid & 31) == 0) { red_min[tid >> 5] = mn; red_max[tid >> 5] = mx; }
+    __syncthreads();
+    for (int w = 0; w < (nt >> 5); ++w) { if (red_min[w] < mn) mn = red_min[w]; if (red_max[w] > mx) mx = red_max[w]; }
+
+    const int maxlen = maxlen_arr[frame];
+    double goodthresh = -1.0;
+    int iters = 0;
+    if (maxlen >= 0) {
+        double lo = mn, hi = mx, thresh = 0, stable = 0;
+        int last_ok = 0;
+        for (int i = 0; i < 128; ++i) {
+            double nt_ = __dmul_rn(__dadd_rn(lo, hi), 0.5);
+            if (fabs(__dsub_rn(nt_, thresh)) <= __dmul_rn(0.5 * 1e-5, thresh)) break;
+            thresh = nt_;
+            iters++;
+            int same = 1;
+            for (int k = tid; k < ncblks; k += nt) {
+                int n = t2_makelayer_block(co[k], thresh);
+                if (n != s.prevn[k]) { same = 0; s.prevn[k] = n; }
+                s.numpasses[k] = n;
+            }
+            same = __syncthreads_and(same) && i != 0;
+            int fail;
+            if (same) fail = !last_ok;
+            else fail = t2_run(plan, cblks, co, s, scratch, nullptr, nullptr) > maxlen;
+            if (fail) { last_ok = 0; lo = thresh; continue; }
+            last_ok = 1; hi = thresh; stable = thresh;
+        }
+        goodthresh = stable == 0 ? thresh : stable;
+    }
+    for (int k = tid; k < ncblks; k += nt) {
+        int n = t2_makelayer_block(co[k], goodthresh);
+        s.numpasses[k] = n;
+        co[k].numpasses = n;
+    }
+    __syncthreads();
+
+    // ---- final tier-2 into the codestream: main header | SOT | SOD | packets | EOC ---------------------
+    unsigned char *o = out_pool + (size_t)frame * plan->out_stride;
+    const int hl = plan->main_header_len;
+    int total = t2_run(plan, cblks, co, s, scratch, o + hl + 14, body_off_pool + (size_t)frame * ncblks);
+    for (int i = tid; i < hl; i += nt) o[i] = plan->main_header[i];
+    if (tid == 0) {
+        unsigned char *t = o + hl;
+        unsigned psot = (unsigned)total + 14u;
+        t[0] = 0xff; t[1] = 0x90; t[2] = 0; t[3] = 10; t[4] = 0; t[5] = 0;
+        t[6] = (unsigned char)(psot >> 24); t[7] = (unsigned char)(psot >> 16); t[8] = (unsigned char)(psot >> 8); t[9] = (unsigned char)psot;
+        t[10] = 0; t[11] = 1; t[12] = 0xff; t[13] = 0x93;
+        t[14 + total] = 0xff; t[15 + total] = 0xd9;
+        pout[frame].total_bytes = total;
+        pout[frame].stream_bytes = hl + 14 + total + 2;
+        pout[frame].iters = iters;
+        pout[frame].thresh = goodthresh;
+    }
+}
+
+// grid = (ncblks, nframes): copy each included block's MQ segment behind its packet header
+__global__ void k_t2_bodies(const Plan *__restrict__ plan, const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cbout,
+                            const unsigned char *__restrict__ mq_pool, const int *__restrict__ body_off_pool,
+                            unsigned char *out_pool, const ProbeOut *__restrict__ pout)
+{
+    const int k = blockIdx.x, frame = blockIdx.y, ncblks = plan->ncblks;
+    if (pout[frame].stream_bytes == 0) return;
+    const CblkOut &c = cbout[(size_t)frame * ncblks + k];
+    const int np = c.numpasses;
+    if (np <= 0) return;
+    const int len = c.rate[np - 1];
+    const unsigned char *src = mq_pool + (size_t)frame * plan->mq_stride + cblks[k].mq_off;
+    unsigned char *dst = out_pool + (size_t)frame * plan->out_stride + plan->main_header_len + 14 + body_off_pool[(size_t)frame * ncblks + k];
+    for (int i = threadIdx.x; i < len; i += blockDim.x) dst[i] = src[i];
+}

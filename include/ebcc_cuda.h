@@ -1,0 +1,73 @@
+/*
+ * ebcc_cuda.h -- thin C ABI between the host C codec (ebcc_b200/csrc/ebcc_codec.c) and the CUDA
+ * device layer (ebcc_b200/csrc/ebcc_cuda.cu, sm_100a).  Plain pointers and sizes only.
+ *
+ * Every entry point replaces a CPU stage of the reference:
+ *   ebcc_cuda_j2k_encode_batch  <- findMinMaxf + u16 scaling + j2k_encode_internal
+ *                                  (src/ebcc_codec.c:676-693, :105-180 -> OpenJPEG opj_encode)
+ * All functions return 0 on success and a negative value on failure (after logging to stderr);
+ * there is no CPU fallback: without a CUDA device every call fails.
+ */
+#ifndef EBCC_CUDA_H
+#define EBCC_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ebcc_cuda_ctx ebcc_cuda_ctx;
+
+#define EBCC_FRAME_CONST 1      /* min == max: no codestream produced          */
+#define EBCC_FRAME_NANINF 2     /* NaN or Inf in the frame (reference exit(1)) */
+
+/* stage names for ebcc_cuda_stage_ms */
+enum {
+    EBCC_ST_H2D = 0, EBCC_ST_MINMAX, EBCC_ST_DWT, EBCC_ST_T1_CM, EBCC_ST_T1_MQ, EBCC_ST_PCRD_T2,
+    EBCC_ST_BODIES, EBCC_ST_D2H, EBCC_ST_COUNT
+};
+
+int ebcc_cuda_device_count(void);
+
+/* one context = one device + one stream + reusable work buffers; not thread-safe (callers lock) */
+ebcc_cuda_ctx *ebcc_cuda_ctx_create(int device);
+void ebcc_cuda_ctx_destroy(ebcc_cuda_ctx *ctx);
+
+/* size the work buffers for batches of up to nframes frames of height x width samples */
+int ebcc_cuda_reserve(ebcc_cuda_ctx *ctx, size_t height, size_t width, size_t nframes);
+
+/* host -> device copy of nframes frames (float32, C-contiguous) into the context's input buffer */
+int ebcc_cuda_upload(ebcc_cuda_ctx *ctx, const float *frames, size_t nframes);
+
+/* device pass over the resident batch: min/max, scaling, DWT, tier-1, PCRD, tier-2.
+ * base_cr is EBCC's compression ratio (OpenJPEG rate = base_cr / 2).  Asynchronous. */
+int ebcc_cuda_j2k_encode_resident(ebcc_cuda_ctx *ctx, size_t nframes, float base_cr);
+
+/* device -> host: waits for the pass, then returns per-frame codestream sizes, min, max, flags;
+ * streams[i] receives a pointer into a context-owned pinned buffer valid until the next call */
+int ebcc_cuda_download(ebcc_cuda_ctx *ctx, size_t nframes, const uint8_t **streams, size_t *sizes,
+                       float *minv, float *maxv, int *flags);
+
+/* convenience: reserve + upload + encode + download */
+int ebcc_cuda_j2k_encode_batch(ebcc_cuda_ctx *ctx, const float *frames, size_t nframes, size_t height,
+                               size_t width, float base_cr, const uint8_t **streams, size_t *sizes,
+                               float *minv, float *maxv, int *flags);
+
+/* profiling: when enabled, CUDA events bracket every stage on the context's stream */
+void ebcc_cuda_set_profiling(ebcc_cuda_ctx *ctx, int enabled);
+/* milliseconds spent in a stage during the last pass (valid after ebcc_cuda_sync) */
+float ebcc_cuda_stage_ms(ebcc_cuda_ctx *ctx, int stage);
+int ebcc_cuda_sync(ebcc_cuda_ctx *ctx);
+/* number of kernel launches issued by this context so far */
+unsigned long long ebcc_cuda_launch_count(ebcc_cuda_ctx *ctx);
+
+/* debug/test taps on the resident batch (device -> host copies of intermediates) */
+int ebcc_cuda_debug_coef(ebcc_cuda_ctx *ctx, size_t frame, float *dst);
+int ebcc_cuda_debug_cblk(ebcc_cuda_ctx *ctx, size_t frame, size_t cblk, int *numbps, int *totalpasses,
+                         int *rates, double *dists, int *numpasses);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
