@@ -1,0 +1,474 @@
+/*
+ * ebcc_codec.c -- host side of the B200-native EBCC codec (plain C).  Mirrors the driver of the
+ * reference (src/ebcc_codec.c) at its API boundary -- validation, env vars, 48-byte "EBCC" frame
+ * header, 80-byte "EBCK" chunk container, buffer ownership -- and hands every numerical stage to
+ * the CUDA layer through include/ebcc_cuda.h.  There is no CPU implementation of any stage here:
+ * without a CUDA device every encode/decode call logs a fatal error and returns 0.
+ */
+#include "../../include/ebcc_codec.h"
+#include "../../include/ebcc_cuda.h"
+#include <assert.h>
+#include <math.h>
+#include <pthread.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <unistd.h>
+
+/* ---- logging: levels as rxi log.c (reference src/log/log.h), EBCC_LOG_LEVEL (src/ebcc_codec.c:430-448) */
+enum { LOG_TRACE, LOG_DEBUG, LOG_INFO, LOG_WARN, LOG_ERROR, LOG_FATAL };
+static int g_log_level = LOG_WARN;
+static const char *const k_level_names[] = {"TRACE", "DEBUG", "INFO", "WARN", "ERROR", "FATAL"};
+
+static void ebcc_log(int level, const char *fmt, ...)
+{
+    if (level < g_log_level) return;
+    va_list ap;
+    fprintf(stderr, "%-5s ebcc_b200: ", k_level_names[level]);
+    va_start(ap, fmt);
+    vfprintf(stderr, fmt, ap);
+    va_end(ap);
+    fputc('\n', stderr);
+}
+
+void log_set_level_from_env(void)
+{
+    const char *env = getenv("EBCC_LOG_LEVEL");
+    g_log_level = LOG_WARN;
+    if (env) {
+        char *end;
+        long v = strtol(env, &end, 10);
+        if (*end != '\0') ebcc_log(LOG_WARN, "Ignore log level: %s, should be in [0, 5]", env);
+        else g_log_level = (int)v;
+    }
+}
+
+static const char *const k_residual_names[] = {"NONE", "MAX_ERROR", "RELATIVE_ERROR"};
+
+void print_config(codec_config_t *config)
+{
+    ebcc_log(LOG_INFO, "dimensions:\t(%lu, %lu, %lu)", config->dims[0], config->dims[1], config->dims[2]);
+    ebcc_log(LOG_INFO, "chunk dimensions:\t(%lu, %lu, %lu)", config->chunk_dims[0], config->chunk_dims[1], config->chunk_dims[2]);
+    ebcc_log(LOG_INFO, "base_cr:\t%f", config->base_cr);
+    if ((unsigned)config->residual_compression_type <= RELATIVE_ERROR)
+        ebcc_log(LOG_INFO, "residual type:\t%s", k_residual_names[config->residual_compression_type]);
+    if (config->residual_compression_type == MAX_ERROR) ebcc_log(LOG_INFO, "max error:\t%f", config->error);
+    if (config->residual_compression_type == RELATIVE_ERROR) ebcc_log(LOG_INFO, "relative error:\t%f", config->error);
+}
+
+void free_buffer(void *buffer) { if (buffer) free(buffer); }
+
+/* ---- serialised headers (reference src/ebcc_codec.c:190-217) -------------------------------------- */
+typedef struct {
+    uint8_t magic[4];
+    uint8_t version;
+    uint8_t flags;
+    uint16_t reserved;
+    uint32_t minval_bits;
+    uint32_t maxval_bits;
+    uint64_t coeffs_size;
+    uint32_t residual_minval_bits;
+    uint32_t residual_maxval_bits;
+    uint64_t compressed_size;
+    uint64_t tail_size;
+} ebcc_header_t;
+
+typedef struct {
+    uint8_t magic[4];
+    uint32_t version;
+    uint32_t ndims;
+    uint32_t reserved;
+    uint64_t dims[NDIMS];
+    uint64_t chunk_dims[NDIMS];
+    uint64_t num_chunks;
+    uint64_t chunk_size;
+} ebcc_chunking_header_t;
+
+_Static_assert(sizeof(ebcc_header_t) == 48, "EBCC header must be 48 bytes");
+_Static_assert(sizeof(ebcc_chunking_header_t) == 80, "EBCK header must be 80 bytes");
+
+static uint32_t float_to_bits(float v) { uint32_t b; memcpy(&b, &v, 4); return b; }
+static float bits_to_float(uint32_t b) { float v; memcpy(&v, &b, 4); return v; }
+
+static int checked_mul(size_t a, size_t b, size_t *out)
+{
+    if (a != 0 && b > SIZE_MAX / a) return 0;
+    *out = a * b;
+    return 1;
+}
+
+/* reference dims_are_valid (src/ebcc_codec.c:286-297) */
+static int dims_are_valid(const size_t dims[NDIMS])
+{
+    size_t h = 1;
+    for (size_t i = 0; i < NDIMS - 1; ++i)
+        if (dims[i] == 0 || !checked_mul(h, dims[i], &h)) return 0;
+    return h >= EBCC_MIN_INTERNAL_IMAGE_DIM && h <= EBCC_MAX_INTERNAL_IMAGE_DIM &&
+           dims[NDIMS - 1] >= EBCC_MIN_INTERNAL_IMAGE_DIM && dims[NDIMS - 1] <= EBCC_MAX_INTERNAL_IMAGE_DIM;
+}
+
+/* ---- process-wide device context, created lazily and re-created after fork ------------------------- */
+static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
+static ebcc_cuda_ctx *g_ctx = NULL;
+static pid_t g_ctx_pid = 0;
+
+static ebcc_cuda_ctx *get_ctx_locked(void)
+{
+    pid_t me = getpid();
+    if (g_ctx && g_ctx_pid == me) return g_ctx;
+    int dev = 0;
+    const char *env = getenv("EBCC_CUDA_DEVICE");
+    if (env) dev = atoi(env);
+    g_ctx = ebcc_cuda_ctx_create(dev);   /* a context inherited through fork is abandoned, not reused */
+    g_ctx_pid = me;
+    if (!g_ctx) ebcc_log(LOG_FATAL, "no usable CUDA device: this build of EBCC has no CPU code path");
+    return g_ctx;
+}
+
+static size_t max_batch_frames(void)
+{
+    const char *env = getenv("EBCC_BATCH_FRAMES");
+    long v = env ? atol(env) : 32;
+    return v > 0 ? (size_t)v : 32;
+}
+
+/* ---- frame assembly (reference src/ebcc_codec.c:870-907) ------------------------------------------- */
+typedef struct {
+    int const_field;
+    float minval, maxval;
+    float residual_minval, residual_maxval;
+    size_t coeffs_size;
+    const uint8_t *zstd; size_t zstd_size;
+    const uint8_t *j2k; size_t j2k_size;
+    size_t tot_size;
+} frame_parts_t;
+
+static size_t assemble_frame(const frame_parts_t *p, uint8_t **out)
+{
+    const size_t codec_size = p->const_field ? sizeof(uint64_t) : p->j2k_size;
+    const size_t out_size = sizeof(ebcc_header_t) + p->zstd_size + codec_size;
+    uint8_t *buf = (uint8_t *)malloc(out_size);
+    if (!buf) return 0;
+    ebcc_header_t h;
+    memset(&h, 0, sizeof(h));
+    memcpy(h.magic, EBCC_HEADER_MAGIC, 4);
+    h.version = EBCC_HEADER_VERSION;
+    if (p->const_field) h.flags |= EBCC_HEADER_FLAG_CONST_FIELD;
+    h.minval_bits = float_to_bits(p->minval);
+    h.maxval_bits = float_to_bits(p->maxval);
+    h.coeffs_size = (uint64_t)p->coeffs_size;
+    h.residual_minval_bits = float_to_bits(p->residual_minval);
+    h.residual_maxval_bits = float_to_bits(p->residual_maxval);
+    h.compressed_size = (uint64_t)p->zstd_size;
+    h.tail_size = (uint64_t)codec_size;
+    uint8_t *it = buf;
+    memcpy(it, &h, sizeof(h)); it += sizeof(h);
+    if (p->zstd_size) { memcpy(it, p->zstd, p->zstd_size); it += p->zstd_size; }
+    if (p->const_field) { uint64_t n = (uint64_t)p->tot_size; memcpy(it, &n, sizeof(n)); }
+    else memcpy(it, p->j2k, p->j2k_size);
+    *out = buf;
+    return out_size;
+}
+
+/* ---- batched encode --------------------------------------------------------------------------------- */
+size_t ebcc_encode_batch(const float *frames, size_t nframes, const codec_config_t *config, uint8_t **outs, size_t *sizes)
+{
+    log_set_level_from_env();
+    for (size_t i = 0; i < nframes; ++i) { outs[i] = NULL; sizes[i] = 0; }
+    if (!dims_are_valid(config->dims)) {
+        ebcc_log(LOG_FATAL, "Invalid EBCC dimensions: product(dims[0..%d]) and dims[%d] must be between %d and %d",
+                 NDIMS - 2, NDIMS - 1, EBCC_MIN_INTERNAL_IMAGE_DIM, EBCC_MAX_INTERNAL_IMAGE_DIM);
+        return 0;
+    }
+    if (config->dims[0] != 1) {
+        ebcc_log(LOG_FATAL, "multi-tile internal images (dims[0]=%lu > 1) are not implemented on the CUDA path yet", config->dims[0]);
+        return 0;
+    }
+    if (config->residual_compression_type != NONE) {
+        ebcc_log(LOG_FATAL, "residual modes MAX_ERROR / RELATIVE_ERROR are not implemented on the CUDA path yet");
+        return 0;
+    }
+    const size_t H = config->dims[1], W = config->dims[2], N = H * W;
+    const size_t maxb = max_batch_frames();
+    size_t done = 0;
+
+    pthread_mutex_lock(&g_mu);
+    ebcc_cuda_ctx *ctx = get_ctx_locked();
+    if (!ctx) { pthread_mutex_unlock(&g_mu); return 0; }
+    const uint8_t **streams = (const uint8_t **)malloc(sizeof(*streams) * maxb);
+    size_t *ssz = (size_t *)malloc(sizeof(size_t) * maxb);
+    float *mn = (float *)malloc(sizeof(float) * maxb), *mx = (float *)malloc(sizeof(float) * maxb);
+    int *fl = (int *)malloc(sizeof(int) * maxb);
+    for (size_t base = 0; base < nframes; base += maxb) {
+        const size_t nb = nframes - base < maxb ? nframes - base : maxb;
+        if (ebcc_cuda_j2k_encode_batch(ctx, frames + base * N, nb, H, W, config->base_cr, streams, ssz, mn, mx, fl)) {
+            ebcc_log(LOG_FATAL, "CUDA encode of frames %lu..%lu failed", base, base + nb - 1);
+            break;
+        }
+        for (size_t i = 0; i < nb; ++i) {
+            if (fl[i] & EBCC_FRAME_NANINF) {
+                /* reference check_nan_inf: log_fatal + exit(1) (src/ebcc_codec.c:598-605) */
+                ebcc_log(LOG_FATAL, "NaN or Inf found in data (frame %lu)", base + i);
+                exit(1);
+            }
+            frame_parts_t p;
+            memset(&p, 0, sizeof(p));
+            p.const_field = (fl[i] & EBCC_FRAME_CONST) != 0;
+            p.minval = mn[i]; p.maxval = mx[i];
+            p.j2k = streams[i]; p.j2k_size = ssz[i];
+            p.tot_size = N;
+            if (!p.const_field && p.j2k_size == 0) { ebcc_log(LOG_FATAL, "empty codestream for frame %lu", base + i); continue; }
+            sizes[base + i] = assemble_frame(&p, &outs[base + i]);
+            if (sizes[base + i]) done++;
+        }
+    }
+    free(streams); free(ssz); free(mn); free(mx); free(fl);
+    pthread_mutex_unlock(&g_mu);
+    return done;
+}
+
+size_t ebcc_encode(float *data, codec_config_t *config, uint8_t **out_buffer)
+{
+    size_t size = 0;
+    *out_buffer = NULL;
+    log_set_level_from_env();
+    print_config(config);
+    if (ebcc_encode_batch(data, 1, config, out_buffer, &size) != 1) return 0;
+    return size;
+}
+
+size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, size_t nframes, float **outs, size_t *counts)
+{
+    (void)streams; (void)stream_sizes; (void)outs;
+    log_set_level_from_env();
+    for (size_t i = 0; i < nframes; ++i) counts[i] = 0;
+    ebcc_log(LOG_FATAL, "ebcc_decode is not implemented on the CUDA path yet");
+    return 0;
+}
+
+size_t ebcc_decode(uint8_t *data, size_t data_size, float **out_buffer)
+{
+    size_t count = 0;
+    uint8_t *s[1] = {data};
+    if (ebcc_decode_batch(s, &data_size, 1, out_buffer, &count) != 1) return 0;
+    return count;
+}
+
+/* ---- N-D chunk container "EBCK" (reference src/ebcc_codec.c:920-1090, :1322-1449) --------------------- */
+static size_t ceil_div(size_t a, size_t b) { return a / b + (a % b != 0); }
+
+static size_t flat_offset(const size_t idx[NDIMS], const size_t dims[NDIMS])
+{
+    size_t o = idx[0];
+    for (size_t i = 1; i < NDIMS; ++i) o = o * dims[i] + idx[i];
+    return o;
+}
+
+static void chunk_origin(size_t linear, const size_t counts[NDIMS], const size_t cdims[NDIMS], size_t origin[NDIMS])
+{
+    for (size_t d = NDIMS; d-- > 0;) { origin[d] = (linear % counts[d]) * cdims[d]; linear /= counts[d]; }
+}
+
+/* edge chunks are padded by replicating the last valid sample along each axis (reference :339-351) */
+static void gather_chunk_padded(const float *data, float *chunk, const size_t dims[NDIMS], const size_t origin[NDIMS],
+                                const size_t cdims[NDIMS])
+{
+    size_t idx[NDIMS];
+    for (size_t a = 0; a < cdims[0]; ++a) {
+        idx[0] = origin[0] + a; if (idx[0] > dims[0] - 1) idx[0] = dims[0] - 1;
+        for (size_t b = 0; b < cdims[1]; ++b) {
+            idx[1] = origin[1] + b; if (idx[1] > dims[1] - 1) idx[1] = dims[1] - 1;
+            float *dst = chunk + (a * cdims[1] + b) * cdims[2];
+            for (size_t c = 0; c < cdims[2]; ++c) {
+                idx[2] = origin[2] + c; if (idx[2] > dims[2] - 1) idx[2] = dims[2] - 1;
+                dst[c] = data[flat_offset(idx, dims)];
+            }
+        }
+    }
+}
+
+static void scatter_chunk_cropped(const float *chunk, float *data, const size_t dims[NDIMS], const size_t origin[NDIMS],
+                                  const size_t cdims[NDIMS])
+{
+    size_t idx[NDIMS];
+    for (size_t a = 0; a < cdims[0]; ++a) {
+        idx[0] = origin[0] + a; if (idx[0] >= dims[0]) break;
+        for (size_t b = 0; b < cdims[1]; ++b) {
+            idx[1] = origin[1] + b; if (idx[1] >= dims[1]) break;
+            const float *src = chunk + (a * cdims[1] + b) * cdims[2];
+            for (size_t c = 0; c < cdims[2]; ++c) {
+                idx[2] = origin[2] + c; if (idx[2] >= dims[2]) break;
+                data[flat_offset(idx, dims)] = src[c];
+            }
+        }
+    }
+}
+
+size_t ebcc_encode_chunking(float *data, codec_config_t *config, uint8_t **out_buffer)
+{
+    log_set_level_from_env();
+    *out_buffer = NULL;
+    size_t cdims[NDIMS];
+    int all_zero = 1;
+    for (size_t i = 0; i < NDIMS; ++i) { cdims[i] = config->chunk_dims[i]; if (cdims[i]) all_zero = 0; }
+    if (all_zero) for (size_t i = 0; i < NDIMS; ++i) cdims[i] = config->dims[i];
+    if (!dims_are_valid(cdims)) {
+        ebcc_log(LOG_FATAL, "Invalid chunking dimensions: product(chunk_dims[0..%d]) and chunk_dims[%d] must be between %d and %d",
+                 NDIMS - 2, NDIMS - 1, EBCC_MIN_INTERNAL_IMAGE_DIM, EBCC_MAX_INTERNAL_IMAGE_DIM);
+        return 0;
+    }
+    size_t counts[NDIMS], chunk_size = 1, num_chunks = 1;
+    for (size_t i = 0; i < NDIMS; ++i) {
+        if (config->dims[i] == 0 || cdims[i] == 0) {
+            ebcc_log(LOG_FATAL, "Invalid chunking dimensions: dims and chunk_dims must be non-zero");
+            return 0;
+        }
+        counts[i] = ceil_div(config->dims[i], cdims[i]);
+        if (!checked_mul(chunk_size, cdims[i], &chunk_size) || !checked_mul(num_chunks, counts[i], &num_chunks)) {
+            ebcc_log(LOG_FATAL, "Invalid chunking dimensions: size overflow");
+            return 0;
+        }
+    }
+    /* gather every chunk (padded where it overhangs) into one contiguous batch for the device */
+    size_t total = 0;
+    if (!checked_mul(chunk_size, num_chunks, &total) || total > SIZE_MAX / sizeof(float)) {
+        ebcc_log(LOG_FATAL, "Invalid chunking dimensions: padded size overflow");
+        return 0;
+    }
+    int slabs = cdims[1] == config->dims[1] && cdims[2] == config->dims[2] && config->dims[0] % cdims[0] == 0;
+    float *batch = data;
+    if (!slabs) {
+        batch = (float *)malloc(total * sizeof(float));
+        if (!batch) { ebcc_log(LOG_FATAL, "Failed to allocate chunk buffer"); return 0; }
+        for (size_t k = 0; k < num_chunks; ++k) {
+            size_t origin[NDIMS];
+            chunk_origin(k, counts, cdims, origin);
+            gather_chunk_padded(data, batch + k * chunk_size, config->dims, origin, cdims);
+        }
+    }
+    codec_config_t cc = *config;
+    for (size_t i = 0; i < NDIMS; ++i) { cc.dims[i] = cdims[i]; cc.chunk_dims[i] = 0; }
+    uint8_t **outs = (uint8_t **)calloc(num_chunks, sizeof(*outs));
+    size_t *sizes = (size_t *)calloc(num_chunks, sizeof(size_t));
+    size_t ok = ebcc_encode_batch(batch, num_chunks, &cc, outs, sizes);
+    if (!slabs) free(batch);
+    size_t out_size = sizeof(ebcc_chunking_header_t);
+    for (size_t k = 0; k < num_chunks; ++k) out_size += sizeof(uint64_t) + sizes[k];
+    uint8_t *out = NULL;
+    if (ok == num_chunks) out = (uint8_t *)malloc(out_size);
+    if (!out) {
+        if (ok != num_chunks) ebcc_log(LOG_FATAL, "Failed to encode %lu of %lu chunks", num_chunks - ok, num_chunks);
+        for (size_t k = 0; k < num_chunks; ++k) free(outs[k]);
+        free(outs); free(sizes);
+        return 0;
+    }
+    ebcc_chunking_header_t h;
+    memset(&h, 0, sizeof(h));
+    memcpy(h.magic, EBCC_CHUNKING_HEADER_MAGIC, 4);
+    h.version = EBCC_CHUNKING_HEADER_VERSION;
+    h.ndims = NDIMS;
+    for (size_t i = 0; i < NDIMS; ++i) { h.dims[i] = config->dims[i]; h.chunk_dims[i] = cdims[i]; }
+    h.num_chunks = num_chunks; h.chunk_size = chunk_size;
+    uint8_t *it = out;
+    memcpy(it, &h, sizeof(h)); it += sizeof(h);
+    for (size_t k = 0; k < num_chunks; ++k) {
+        uint64_t n = sizes[k];
+        memcpy(it, &n, sizeof(n)); it += sizeof(n);
+        memcpy(it, outs[k], sizes[k]); it += sizes[k];
+        free(outs[k]);
+    }
+    free(outs); free(sizes);
+    *out_buffer = out;
+    return out_size;
+}
+
+size_t ebcc_encode_chunking_compat(float *data, codec_config_t *config, uint8_t **out_buffer)
+{
+    log_set_level_from_env();
+    codec_config_t cc = *config;
+    int all_zero = 1;
+    for (size_t i = 0; i < NDIMS; ++i) if (cc.chunk_dims[i]) { all_zero = 0; break; }
+    if (all_zero) {
+        cc.chunk_dims[0] = 1;
+        cc.chunk_dims[1] = cc.dims[1] > EBCC_MAX_INTERNAL_IMAGE_DIM ? 1024 : cc.dims[1];
+        cc.chunk_dims[2] = cc.dims[2] > EBCC_MAX_INTERNAL_IMAGE_DIM ? 1024 : cc.dims[2];
+        ebcc_log(LOG_INFO, "ebcc_encode_chunking_compat chunk dimensions: (%lu, %lu, %lu)", cc.chunk_dims[0], cc.chunk_dims[1], cc.chunk_dims[2]);
+    }
+    if (cc.residual_compression_type == RELATIVE_ERROR) {
+        /* global-range relative error becomes an absolute bound (reference :1077-1087); this is
+         * configuration arithmetic over the caller's array, not a codec stage */
+        size_t total = 1;
+        for (size_t i = 0; i < NDIMS; ++i)
+            if (!checked_mul(total, cc.dims[i], &total)) total = 0;
+        if (total == 0) { ebcc_log(LOG_FATAL, "Invalid EBCC dimensions: size overflow or zero-sized data"); return 0; }
+        float lo = data[0], hi = data[0];
+        for (size_t i = 0; i < total; ++i) {
+            if (isnan(data[i]) || isinf(data[i])) { ebcc_log(LOG_FATAL, "NaN or Inf found in data at index %lu", i); exit(1); }
+            if (data[i] > hi) hi = data[i];
+            if (data[i] < lo) lo = data[i];
+        }
+        cc.error *= hi - lo;
+        cc.residual_compression_type = MAX_ERROR;
+    }
+    return ebcc_encode_chunking(data, &cc, out_buffer);
+}
+
+size_t ebcc_decode_chunking(uint8_t *data, size_t data_size, float **out_buffer)
+{
+    log_set_level_from_env();
+    if (data_size < 4 || memcmp(data, EBCC_CHUNKING_HEADER_MAGIC, 4) != 0)
+        return ebcc_decode(data, data_size, out_buffer);       /* plain EBCC stream (reference :1326-1329) */
+    ebcc_chunking_header_t h;
+    if (data_size < sizeof(h)) { ebcc_log(LOG_FATAL, "Invalid chunked EBCC header: truncated"); return 0; }
+    memcpy(&h, data, sizeof(h));
+    if (h.version != EBCC_CHUNKING_HEADER_VERSION || h.ndims != NDIMS) {
+        ebcc_log(LOG_FATAL, "Invalid chunked EBCC header: unsupported version %u or ndims %u", h.version, h.ndims);
+        return 0;
+    }
+    size_t dims[NDIMS], cdims[NDIMS], counts[NDIMS], total = 1, chunk_size = 1, num_chunks = 1;
+    for (size_t i = 0; i < NDIMS; ++i) {
+        dims[i] = (size_t)h.dims[i]; cdims[i] = (size_t)h.chunk_dims[i];
+        if (dims[i] == 0 || cdims[i] == 0) { ebcc_log(LOG_FATAL, "Invalid chunked EBCC header: zero dimension"); return 0; }
+        counts[i] = ceil_div(dims[i], cdims[i]);
+        if (!checked_mul(total, dims[i], &total) || !checked_mul(chunk_size, cdims[i], &chunk_size) ||
+            !checked_mul(num_chunks, counts[i], &num_chunks)) {
+            ebcc_log(LOG_FATAL, "Invalid chunked EBCC header: size overflow");
+            return 0;
+        }
+    }
+    if (num_chunks != h.num_chunks || chunk_size != h.chunk_size || !dims_are_valid(cdims)) {
+        ebcc_log(LOG_FATAL, "Invalid chunked EBCC header: inconsistent chunk geometry");
+        return 0;
+    }
+    /* sequential scan of the length prefixes, then one batched decode */
+    uint8_t **streams = (uint8_t **)malloc(sizeof(*streams) * num_chunks);
+    size_t *ssz = (size_t *)malloc(sizeof(size_t) * num_chunks);
+    size_t *counts_out = (size_t *)calloc(num_chunks, sizeof(size_t));
+    float **outs = (float **)calloc(num_chunks, sizeof(*outs));
+    size_t off = sizeof(h), ok = 1;
+    for (size_t k = 0; k < num_chunks && ok; ++k) {
+        uint64_t n;
+        if (data_size - off < sizeof(n)) { ok = 0; break; }
+        memcpy(&n, data + off, sizeof(n)); off += sizeof(n);
+        if (n > data_size - off) { ok = 0; break; }
+        streams[k] = data + off; ssz[k] = (size_t)n; off += (size_t)n;
+    }
+    float *out = NULL;
+    size_t ret = 0;
+    if (!ok) ebcc_log(LOG_FATAL, "Invalid chunked EBCC stream: truncated chunk table");
+    else if (ebcc_decode_batch(streams, ssz, num_chunks, outs, counts_out) == num_chunks) {
+        out = (float *)malloc(total * sizeof(float));
+        for (size_t k = 0; k < num_chunks && out; ++k) {
+            if (counts_out[k] != chunk_size) { ebcc_log(LOG_FATAL, "chunk %lu decoded to %lu values, expected %lu", k, counts_out[k], chunk_size); free(out); out = NULL; break; }
+            size_t origin[NDIMS];
+            chunk_origin(k, counts, cdims, origin);
+            scatter_chunk_cropped(outs[k], out, dims, origin, cdims);
+        }
+        if (out) ret = total;
+    }
+    for (size_t k = 0; k < num_chunks; ++k) free(outs[k]);
+    free(outs); free(counts_out); free(streams); free(ssz);
+    *out_buffer = out;
+    return ret;
+}
