@@ -1,0 +1,262 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the EBCC hot path on B200 (contract in the task statement).
+
+Workload at N=1 (BASELINE.json configs[1]): mode NONE (JPEG 2000 base layer only), batch of 24 hourly
+721x1440 float32 frames, base_cr 30, synthetic ERA5-shaped fields (seeded spectral noise).
+A "step" = one pass of the compress path over the 24-frame batch.
+
+  value      GB/s of f32 input, inputs resident in HBM, device time from CUDA events on the library's
+             stream (sum of per-step event intervals; L2 flushed between steps outside the events)
+  e2e        same metric through the public C ABI ebcc_encode_batch() with HOST buffers: H2D of the
+             frames and D2H of the finished streams are inside the timed region
+  roofline   dominant kernel (tier-1 MQ coder), algorithmic bytes = frames * (4N + out_bytes)
+  cpu_baseline  the UNMODIFIED reference (oracle/_ref) on the host cores, bounded sample
+--impl reference: the reference's CPU implementation alone, all host cores, same metric / config.
+Multi-GPU (torchrun): frames are independent -> each rank compresses its own 24-frame batch on its own
+GPU, no data-path collective; weak scaling.
+"""
+import argparse
+import ctypes as C
+import json
+import multiprocessing as mp
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import harness as H  # noqa: E402
+
+FRAMES, HH, WW, BASE_CR = 24, 721, 1440, 30.0
+NSAMP = HH * WW
+STAGES = ["h2d", "minmax", "dwt", "t1_cm", "t1_mq", "pcrd_t2", "bodies", "d2h"]
+METRIC = "compress throughput, GB/s of f32 input (mode NONE, 24x721x1440, base_cr 30)"
+
+
+def make_frames(rank):
+    base = H.synth_stack(8)
+    reps = np.concatenate([base, base[::-1] + np.float32(0.25 * (rank + 1)), base * np.float32(1.01)], axis=0)
+    return np.ascontiguousarray(reps[:FRAMES], dtype=np.float32)
+
+
+# ---- reference CPU arm ------------------------------------------------------------------------------------
+def _ref_worker(args):
+    frames, reps = args
+    lib = H.ref_lib()
+    t0 = time.perf_counter()
+    n = 0
+    for _ in range(reps):
+        for f in frames:
+            n += len(H.encode(lib, f, (1, HH, WW), BASE_CR, H.NONE))
+    return time.perf_counter() - t0, n
+
+
+def cpu_reference_throughput(frames, cores, frames_per_core=1):
+    """all-core throughput of the reference: `cores` processes, each encoding its own frames."""
+    jobs = [([frames[(i * frames_per_core + j) % len(frames)] for j in range(frames_per_core)], 1) for i in range(cores)]
+    t0 = time.perf_counter()
+    with mp.get_context("fork").Pool(cores) as pool:
+        pool.map(_ref_worker, jobs)
+    dt = time.perf_counter() - t0
+    nfr = cores * frames_per_core
+    return nfr * NSAMP * 4 / dt / 1e9, nfr, dt
+
+
+class ClockSampler(threading.Thread):
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        super().__init__(daemon=True)
+        self.gpu, self.rows, self.stop_flag = gpu, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": int(self.rows[0][1]) if self.rows[0][1].isdigit() else None,
+                "reasons": reasons}
+
+
+def dist_setup(ngpus):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist  # noqa: F811
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, world, local, dist
+
+
+def allreduce_max(dist, local, value):
+    if dist is None:
+        return value
+    import torch
+    t = torch.tensor([value], dtype=torch.float64, device=torch.device("cuda", local))
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def barrier(dist):
+    if dist is not None:
+        import torch
+        dist.barrier()
+        torch.cuda.synchronize()
+
+
+def run_reference(args):
+    rank, world, local, dist = dist_setup(args.gpus)
+    if rank != 0:
+        return
+    if not H.have_ref():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libh5z_ebcc_ref.so not built"}))
+        return
+    cores = os.cpu_count() or 1
+    frames = make_frames(0)
+    for _ in range(min(args.warmup, 1)):
+        cpu_reference_throughput(frames, cores)
+    vals, t_total, nfr = [], 0.0, 0
+    for _ in range(args.steps):
+        v, n, dt = cpu_reference_throughput(frames, cores)
+        vals.append(v); t_total += dt; nfr += n
+    value = nfr * NSAMP * 4 / t_total / 1e9
+    sample = "%d frames per step (one 721x1440 frame per core, %d processes), %d steps" % (cores, cores, args.steps)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t_total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "mode NONE, 721x1440 f32 frames, base_cr 30, reference CPU filter on all host cores"},
+        "cpu_baseline": {"value": value, "unit": "GB/s", "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def run_ours(args):
+    rank, world, local, dist = dist_setup(args.gpus)
+    lib = C.CDLL(H.PROD_SO)   # fails loudly if the CUDA library is missing
+    lib.ebcc_cuda_ctx_create.restype = C.c_void_p
+    lib.ebcc_cuda_launch_count.restype = C.c_ulonglong
+    lib.ebcc_encode_batch.restype = C.c_size_t
+    lib.ebcc_cuda_device_count.restype = C.c_int
+    if lib.ebcc_cuda_device_count() <= 0:
+        raise SystemExit("bench.py: no CUDA device visible; the EBCC B200 path has no CPU fallback")
+    os.environ["EBCC_CUDA_DEVICE"] = str(local)
+    frames = make_frames(rank)
+    in_bytes = frames.nbytes
+
+    # ---- device-resident pass (value) ----
+    ctx = C.c_void_p(lib.ebcc_cuda_ctx_create(local))
+    assert ctx.value
+    assert lib.ebcc_cuda_reserve(ctx, C.c_size_t(HH), C.c_size_t(WW), C.c_size_t(FRAMES)) == 0
+    assert lib.ebcc_cuda_upload(ctx, frames.ctypes.data_as(C.c_void_p), C.c_size_t(FRAMES)) == 0
+    lib.ebcc_cuda_sync(ctx)
+    total, st = C.c_float(), (C.c_float * 8)()
+    sampler = ClockSampler(local); sampler.start()
+    barrier(dist)
+    l0 = lib.ebcc_cuda_launch_count(ctx)
+    rc = lib.ebcc_cuda_bench_resident(ctx, C.c_size_t(FRAMES), C.c_float(BASE_CR), args.steps, args.warmup,
+                                      C.c_size_t(256 << 20), C.byref(total), st)
+    assert rc == 0
+    launches = (lib.ebcc_cuda_launch_count(ctx) - l0) * args.steps // (args.steps + args.warmup)
+    barrier(dist)
+    dev_ms = allreduce_max(dist, local, total.value)
+    sizes = (C.c_size_t * FRAMES)()
+    lib.ebcc_cuda_download(ctx, C.c_size_t(FRAMES), None, sizes, None, None, None)
+    out_bytes = sum(sizes)
+    lib.ebcc_cuda_ctx_destroy(ctx)
+
+    # ---- end to end through the public C ABI with host buffers (e2e) ----
+    cfg = H.CodecConfig(); cfg.dims[:] = [1, HH, WW]; cfg.base_cr = BASE_CR; cfg.mode = H.NONE
+    outs, osz = (C.POINTER(C.c_uint8) * FRAMES)(), (C.c_size_t * FRAMES)()
+
+    def one_e2e():
+        n = lib.ebcc_encode_batch(frames.ctypes.data_as(C.c_void_p), C.c_size_t(FRAMES), C.byref(cfg), outs, osz)
+        assert n == FRAMES
+        tot = sum(osz)
+        for i in range(FRAMES):
+            lib.free_buffer(outs[i])
+        return tot
+    for _ in range(args.warmup):
+        one_e2e()
+    barrier(dist)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        d2h = one_e2e()
+    e2e_s = time.perf_counter() - t0
+    barrier(dist)
+    e2e_s = allreduce_max(dist, local, e2e_s)
+    sampler.stop_flag = True; sampler.join(timeout=2)
+
+    if rank != 0:
+        return
+    value = world * FRAMES * NSAMP * 4 * args.steps / (dev_ms * 1e-3) / 1e9
+    e2e = world * FRAMES * NSAMP * 4 * args.steps / e2e_s / 1e9
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:  # noqa: BLE001
+        pass
+    peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    stage = {n: st[i] / args.steps for i, n in enumerate(STAGES)}
+    dom = max(("t1_cm", "t1_mq", "dwt", "pcrd_t2"), key=lambda k: stage[k])
+    alg = {"t1_mq": FRAMES * NSAMP * 4 + out_bytes, "t1_cm": FRAMES * NSAMP * 4 + out_bytes,
+           "dwt": FRAMES * NSAMP * 4 * (1 + 2 * (4 / 3)), "pcrd_t2": out_bytes}[dom]
+    achieved = alg / (stage[dom] * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "BASELINE configs[1]: mode NONE, batch of 24 frames 721x1440 f32 per GPU, base_cr 30",
+                   "frames_per_gpu": FRAMES, "l2": "256 MiB scratch written between steps (outside the events)",
+                   "compressed_bytes_per_step": int(out_bytes), "cr": in_bytes / max(out_bytes, 1)},
+        "e2e": {"value": e2e, "unit": "GB/s", "h2d_bytes_per_step": int(in_bytes), "d2h_bytes_per_step": int(d2h)},
+        "gpu_launches": int(launches),
+        "stage_ms": stage,
+        "roofline": {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None,
+                     "note": "tier-1 is integer-issue/latency bound; the HBM fraction is reported for completeness"},
+        "clocks": sampler.summary(),
+    }
+    if world == 1 and H.have_ref() and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        v, n, dt = cpu_reference_throughput(frames, cores)
+        line["cpu_baseline"] = {"value": v, "unit": "GB/s", "cores": cores, "kind": "reference",
+                                "sample": "%d frames of the same workload, one per core process, %.1f s" % (n, dt)}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

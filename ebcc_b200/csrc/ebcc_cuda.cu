@@ -399,10 +399,13 @@ extern "C" int ebcc_cuda_j2k_encode_resident(ebcc_cuda_ctx *c, size_t nframes, f
     mark(c, EBCC_ST_T1_MQ);
     {
         long long jobs = (long long)pl->ncblks * B;
-        long long warps = (jobs + MQ_LANES - 1) / MQ_LANES;
+        const char *el = getenv("EBCC_MQ_LANES");
+        int lanes = el ? atoi(el) : 1;
+        if (lanes < 1 || lanes > 32) lanes = 1;
+        long long warps = (jobs + lanes - 1) / lanes;
         long long ctas = (warps * 32 + MQ_THREADS - 1) / MQ_THREADS;
         EBCC_LAUNCH(k_t1_mq, dim3((unsigned)ctas), dim3(MQ_THREADS), 0, c->stream,
-                    c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride);
+                    c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride, lanes);
     }
     mark(c, EBCC_ST_PCRD_T2);
     EBCC_LAUNCH(k_pcrd_t2, dim3((unsigned)B), dim3(T2_THREADS), t2_smem_bytes(pl->ncblks, pl->nnodes), c->stream,
@@ -487,5 +490,39 @@ extern "C" int ebcc_cuda_debug_cblk(ebcc_cuda_ctx *c, size_t frame, size_t cblk,
     CK(cudaMemcpy(&o, c->d_cbout + frame * c->plan.ncblks + cblk, sizeof(o), cudaMemcpyDeviceToHost));
     *numbps = o.numbps; *totalpasses = o.totalpasses; *numpasses = o.numpasses;
     for (int i = 0; i < o.totalpasses && i < J2K_MAXPASSES; ++i) { rates[i] = o.rate[i]; dists[i] = o.dist[i]; }
+    return 0;
+}
+
+// ---- device-side timing helper for bench.py -------------------------------------------------------------
+// Runs `warmup` untimed and `steps` timed passes over the resident batch.  Between passes a scratch buffer
+// larger than L2 is overwritten (outside the timed events) so every pass starts with a cold L2.  Times come
+// from CUDA events recorded on the context's own stream.
+extern "C" int ebcc_cuda_bench_resident(ebcc_cuda_ctx *c, size_t nframes, float base_cr, int steps, int warmup,
+                                        size_t flush_bytes, float *total_ms, float *stage_ms_sum)
+{
+    if (!c || steps <= 0) return -1;
+    CK(cudaSetDevice(c->device));
+    void *flush = NULL;
+    if (flush_bytes) CK(cudaMalloc(&flush, flush_bytes));
+    const int prev = c->profiling;
+    c->profiling = 1;
+    *total_ms = 0;
+    for (int s = 0; s < EBCC_ST_COUNT; ++s) stage_ms_sum[s] = 0;
+    for (int it = 0; it < warmup + steps; ++it) {
+        if (flush) CK(cudaMemsetAsync(flush, it & 0xff, flush_bytes, c->stream));
+        if (ebcc_cuda_j2k_encode_resident(c, nframes, base_cr)) { cudaFree(flush); return -1; }
+        CK(cudaStreamSynchronize(c->stream));
+        if (it >= warmup) {
+            float ms = 0;
+            CK(cudaEventElapsedTime(&ms, c->ev[EBCC_ST_MINMAX], c->ev[EBCC_ST_D2H]));
+            *total_ms += ms;
+            for (int s = EBCC_ST_MINMAX; s < EBCC_ST_D2H; ++s) {
+                CK(cudaEventElapsedTime(&ms, c->ev[s], c->ev[s + 1]));
+                stage_ms_sum[s] += ms;
+            }
+        }
+    }
+    c->profiling = prev;
+    if (flush) cudaFree(flush);
     return 0;
 }

@@ -352,7 +352,6 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
 // MQ coder.  State table (Annex C table C.2; mqc.c:61-157) packed as qe | nmps<<16 | nlps<<22 | sw<<28.
 struct MqTable { unsigned e[47]; };
 
-#define MQ_LANES 8            // code-blocks per warp (lanes 0..MQ_LANES-1 of each warp are active)
 #define MQ_THREADS 128
 
 struct MqEnc {
@@ -399,7 +398,7 @@ __device__ __forceinline__ void mq_renorm(MqEnc &q)
 __global__ void __launch_bounds__(MQ_THREADS)
 k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char *__restrict__ sym_pool,
         unsigned char *mq_pool, const MqTable *__restrict__ g_tab, int ncblks, int nframes,
-        size_t sym_stride, size_t mq_stride)
+        size_t sym_stride, size_t mq_stride, int lanes /* code-blocks per warp */)
 {
     __shared__ unsigned tab[47];
     __shared__ unsigned ctxs[19 * MQ_THREADS];
@@ -407,8 +406,8 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
     if (tid < 47) tab[tid] = g_tab->e[tid];
     __syncthreads();
     const int warp_global = (blockIdx.x * MQ_THREADS + tid) >> 5;
-    const long long job = (long long)warp_global * MQ_LANES + lane;
-    if (lane >= MQ_LANES || job >= (long long)ncblks * nframes) return;
+    const long long job = (long long)warp_global * lanes + lane;
+    if (lane >= lanes || job >= (long long)ncblks * nframes) return;
     const int frame = (int)(job / ncblks), cbi = (int)(job - (long long)frame * ncblks);
     const CblkDesc cb = cblks[cbi];
     CblkOut *out = cbout + (size_t)frame * ncblks + cbi;

@@ -62,6 +62,12 @@ int ebcc_cuda_sync(ebcc_cuda_ctx *ctx);
 /* number of kernel launches issued by this context so far */
 unsigned long long ebcc_cuda_launch_count(ebcc_cuda_ctx *ctx);
 
+/* bench helper: `warmup` untimed + `steps` timed device passes over the resident batch, L2 flushed
+ * (flush_bytes written) between passes outside the timed region; CUDA-event times on the context's
+ * stream.  total_ms: sum over timed passes; stage_ms_sum[EBCC_ST_COUNT]: per-stage sums. */
+int ebcc_cuda_bench_resident(ebcc_cuda_ctx *ctx, size_t nframes, float base_cr, int steps, int warmup,
+                             size_t flush_bytes, float *total_ms, float *stage_ms_sum);
+
 /* debug/test taps on the resident batch (device -> host copies of intermediates) */
 int ebcc_cuda_debug_coef(ebcc_cuda_ctx *ctx, size_t frame, float *dst);
 int ebcc_cuda_debug_cblk(ebcc_cuda_ctx *ctx, size_t frame, size_t cblk, int *numbps, int *totalpasses,
