@@ -238,13 +238,119 @@ size_t ebcc_encode(float *data, codec_config_t *config, uint8_t **out_buffer)
     return size;
 }
 
+/* ---- batched decode (reference ebcc_decode, src/ebcc_codec.c:1215-1320) --------------------------------- */
+typedef struct {
+    int ok, const_field;
+    float minval, maxval, rmin, rmax;
+    size_t coeffs_size, zstd_size, tail_size, tot_size;
+    const uint8_t *zstd, *tail;
+    size_t H, W;
+} parsed_stream_t;
+
+static uint32_t be32(const uint8_t *p) { return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]; }
+
+static int parse_stream(const uint8_t *data, size_t n, parsed_stream_t *ps)
+{
+    memset(ps, 0, sizeof(*ps));
+    if (n < sizeof(ebcc_header_t) || memcmp(data, EBCC_HEADER_MAGIC, 4) != 0) {
+        ebcc_log(LOG_FATAL, "legacy (header-less) EBCC streams are not supported by the CUDA codec");
+        return 0;
+    }
+    ebcc_header_t h;
+    memcpy(&h, data, sizeof(h));
+    if (h.version != EBCC_HEADER_VERSION) { ebcc_log(LOG_FATAL, "Unsupported EBCC header version: %u", h.version); return 0; }
+    size_t used = sizeof(h);
+    if (h.compressed_size > n - used) { ebcc_log(LOG_FATAL, "Invalid encoded data: truncated payload"); return 0; }
+    used += (size_t)h.compressed_size;
+    if (h.tail_size > n - used) { ebcc_log(LOG_FATAL, "Invalid encoded data: truncated payload"); return 0; }
+    used += (size_t)h.tail_size;
+    if (used != n) { ebcc_log(LOG_FATAL, "Invalid encoded data: payload size mismatch"); return 0; }
+    ps->minval = bits_to_float(h.minval_bits); ps->maxval = bits_to_float(h.maxval_bits);
+    ps->rmin = bits_to_float(h.residual_minval_bits); ps->rmax = bits_to_float(h.residual_maxval_bits);
+    ps->coeffs_size = (size_t)h.coeffs_size; ps->zstd_size = (size_t)h.compressed_size; ps->tail_size = (size_t)h.tail_size;
+    ps->zstd = data + sizeof(h); ps->tail = ps->zstd + ps->zstd_size;
+    ps->const_field = (h.flags & EBCC_HEADER_FLAG_CONST_FIELD) != 0;
+    if (ps->const_field) {
+        if (ps->tail_size != sizeof(uint64_t)) { ebcc_log(LOG_FATAL, "Invalid encoded data: const-field payload must contain uint64_t length"); return 0; }
+        uint64_t t; memcpy(&t, ps->tail, sizeof(t));
+        ps->tot_size = (size_t)t;
+        if (ps->zstd_size > 0 && ps->coeffs_size > 0) { ebcc_log(LOG_FATAL, "Invalid encoded data: residual data cannot be applied to const field"); return 0; }
+    } else {
+        /* image size from the SIZ marker: SOC(2) SIZ(2) Lsiz(2) Rsiz(2) Xsiz Ysiz XOsiz YOsiz XTsiz YTsiz */
+        if (ps->tail_size < 40 || ps->tail[0] != 0xff || ps->tail[1] != 0x4f || ps->tail[2] != 0xff || ps->tail[3] != 0x51) {
+            ebcc_log(LOG_FATAL, "Invalid encoded data: no JPEG 2000 codestream"); return 0;
+        }
+        const size_t X = be32(ps->tail + 8), Y = be32(ps->tail + 12), XT = be32(ps->tail + 24), YT = be32(ps->tail + 28);
+        if (be32(ps->tail + 16) || be32(ps->tail + 20) || X != XT || Y != YT) {
+            ebcc_log(LOG_FATAL, "multi-tile codestreams (dims[0] > 1) are not implemented on the CUDA path yet"); return 0;
+        }
+        ps->W = X; ps->H = Y; ps->tot_size = X * Y;
+        if (X < EBCC_MIN_INTERNAL_IMAGE_DIM || X > EBCC_MAX_INTERNAL_IMAGE_DIM || Y < EBCC_MIN_INTERNAL_IMAGE_DIM || Y > EBCC_MAX_INTERNAL_IMAGE_DIM) {
+            ebcc_log(LOG_FATAL, "Invalid encoded data: image size %lu x %lu out of range", Y, X); return 0;
+        }
+    }
+    ps->ok = 1;
+    return 1;
+}
+
 size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, size_t nframes, float **outs, size_t *counts)
 {
-    (void)streams; (void)stream_sizes; (void)outs;
     log_set_level_from_env();
-    for (size_t i = 0; i < nframes; ++i) counts[i] = 0;
-    ebcc_log(LOG_FATAL, "ebcc_decode is not implemented on the CUDA path yet");
-    return 0;
+    size_t done = 0;
+    parsed_stream_t *ps = (parsed_stream_t *)calloc(nframes ? nframes : 1, sizeof(*ps));
+    int *owned = (int *)calloc(nframes ? nframes : 1, sizeof(int));
+    for (size_t i = 0; i < nframes; ++i) {
+        counts[i] = 0;
+        if (!parse_stream(streams[i], stream_sizes[i], &ps[i])) continue;
+        if (ps[i].const_field) {
+            /* constant field: the stream carries one value and a count (reference :1265-1281, always mallocs) */
+            float *o = (float *)malloc(ps[i].tot_size * sizeof(float));
+            if (!o) { ps[i].ok = 0; continue; }
+            for (size_t k = 0; k < ps[i].tot_size; ++k) o[k] = ps[i].minval;
+            outs[i] = o; counts[i] = ps[i].tot_size; done++;
+        }
+    }
+    const size_t maxb = max_batch_frames();
+    const uint8_t **js = (const uint8_t **)malloc(sizeof(*js) * maxb);
+    size_t *jn = (size_t *)malloc(sizeof(size_t) * maxb), *idx = (size_t *)malloc(sizeof(size_t) * maxb);
+    float *mn = (float *)malloc(sizeof(float) * maxb), *mx = (float *)malloc(sizeof(float) * maxb);
+    float **dst = (float **)malloc(sizeof(float *) * maxb);
+    ebcc_residual_in *rs = (ebcc_residual_in *)calloc(maxb, sizeof(*rs));
+    pthread_mutex_lock(&g_mu);
+    ebcc_cuda_ctx *ctx = NULL;
+    size_t i = 0;
+    while (i < nframes) {
+        if (!ps[i].ok || ps[i].const_field) { ++i; continue; }
+        /* gather a run of frames with the same geometry */
+        const size_t H = ps[i].H, W = ps[i].W;
+        size_t nb = 0, j = i;
+        for (; j < nframes && nb < maxb; ++j) {
+            if (!ps[j].ok || ps[j].const_field) continue;
+            if (ps[j].H != H || ps[j].W != W) break;
+            if (!outs[j]) { outs[j] = (float *)malloc(H * W * sizeof(float)); owned[j] = 1; }
+            if (!outs[j]) { ps[j].ok = 0; continue; }
+            js[nb] = ps[j].tail; jn[nb] = ps[j].tail_size; mn[nb] = ps[j].minval; mx[nb] = ps[j].maxval; dst[nb] = outs[j]; idx[nb] = j;
+            memset(&rs[nb], 0, sizeof(rs[nb]));
+            if (ps[j].zstd_size > 0 && ps[j].coeffs_size > 0) {
+                rs[nb].zstd = ps[j].zstd; rs[nb].zstd_size = ps[j].zstd_size; rs[nb].coeffs_size = ps[j].coeffs_size;
+                rs[nb].rmin = ps[j].rmin; rs[nb].rmax = ps[j].rmax;
+            }
+            nb++;
+        }
+        if (nb) {
+            if (!ctx) ctx = get_ctx_locked();
+            int rc = ctx ? ebcc_cuda_decode_batch(ctx, js, jn, nb, H, W, mn, mx, rs, dst) : -1;
+            for (size_t k = 0; k < nb; ++k) {
+                if (rc == 0) { counts[idx[k]] = H * W; done++; }
+                else if (owned[idx[k]]) { free(outs[idx[k]]); outs[idx[k]] = NULL; }
+            }
+            if (rc) ebcc_log(LOG_FATAL, "CUDA decode of %lu frame(s) failed", nb);
+        }
+        i = j;
+    }
+    pthread_mutex_unlock(&g_mu);
+    free(js); free(jn); free(idx); free(mn); free(mx); free(dst); free(rs); free(ps); free(owned);
+    return done;
 }
 
 size_t ebcc_decode(uint8_t *data, size_t data_size, float **out_buffer)

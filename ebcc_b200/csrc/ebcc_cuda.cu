@@ -6,6 +6,8 @@
 #include "k_dwt.cuh"
 #include "k_t1.cuh"
 #include "k_t2.cuh"
+#include "k_dec.cuh"
+#include "k_idwt.cuh"
 #include "../../include/ebcc_cuda.h"
 #include <math.h>
 #include <stdio.h>
@@ -203,6 +205,21 @@ static void fill_luts(T1Luts *l, MqTable *t)
     }
 }
 
+static void fill_dec_luts(DecLuts *d, const MqTable *t)
+{
+    for (int o = 0; o < 4; ++o)
+        for (int nb = 0; nb < 512; ++nb) {
+            const int h = ((nb >> 3) & 1) + ((nb >> 5) & 1), v = ((nb >> 1) & 1) + ((nb >> 7) & 1);
+            const int dg = (nb & 1) + ((nb >> 2) & 1) + ((nb >> 6) & 1) + ((nb >> 8) & 1);
+            d->zc[o * 512 + nb] = (unsigned char)t1_zc_ctx(o, h, v, dg);
+        }
+    for (int st = 0; st < 47; ++st)
+        for (int mps = 0; mps < 2; ++mps) {
+            const unsigned e = t->e[st], qe = e & 0xffffu, nm = (e >> 16) & 63u, nl = (e >> 22) & 63u, sw = (e >> 28) & 1u;
+            d->mq[st * 2 + mps] = qe | ((nm * 2 + (unsigned)mps) << 16) | ((nl * 2 + ((unsigned)mps ^ sw)) << 24);
+        }
+}
+
 // ---- context ---------------------------------------------------------------------------------------
 struct ebcc_cuda_ctx {
     int device;
@@ -222,6 +239,20 @@ struct ebcc_cuda_ctx {
     int *d_maxlen, *d_body_off;
     ProbeOut *d_pout;
     unsigned long long *d_offs;
+    // decoder side
+    DecLuts *d_declut;
+    unsigned char *d_streams;  // [B][out_stride] codestreams to decode
+    int *d_slens, *d_status;
+    DecJob *d_jobs;            // [B][ncblks]
+    int *d_iplane;             // [B][H][W] tier-1 decoder output (integer, Mallat layout)
+    float *d_dcoef;            // [B][H][W] dequantised coefficients / IDWT work plane
+    float *d_dec;              // [B][H][W] decoded frames
+    ErrStat *d_es;
+    float *d_targets;
+    ErrStat *h_es;
+    int *h_status, *h_slens;
+    float *h_targets;
+    unsigned char *h_streams;  // pinned staging for codestream upload
     // pinned host mirrors
     ProbeOut *h_pout;
     FrameStat *h_stat;
@@ -262,6 +293,11 @@ extern "C" ebcc_cuda_ctx *ebcc_cuda_ctx_create(int device)
     if (cudaMalloc((void **)&c->d_luts, sizeof(luts)) != cudaSuccess || cudaMalloc((void **)&c->d_mqtab, sizeof(tab)) != cudaSuccess) { free(c); return NULL; }
     cudaMemcpy(c->d_luts, &luts, sizeof(luts), cudaMemcpyHostToDevice);
     cudaMemcpy(c->d_mqtab, &tab, sizeof(tab), cudaMemcpyHostToDevice);
+    DecLuts *dl = (DecLuts *)malloc(sizeof(DecLuts));
+    fill_dec_luts(dl, &tab);
+    if (cudaMalloc((void **)&c->d_declut, sizeof(DecLuts)) != cudaSuccess) { free(dl); free(c); return NULL; }
+    cudaMemcpy(c->d_declut, dl, sizeof(DecLuts), cudaMemcpyHostToDevice);
+    free(dl);
     return c;
 }
 
@@ -272,6 +308,11 @@ static void free_buffers(ebcc_cuda_ctx *c)
     cudaFree(c->d_maxlen); cudaFree(c->d_body_off); cudaFree(c->d_pout); cudaFree(c->d_offs);
     cudaFreeHost(c->h_pout); cudaFreeHost(c->h_stat); cudaFreeHost(c->h_offs); cudaFreeHost(c->h_maxlen);
     cudaFreeHost(c->h_packed); cudaFreeHost(c->h_stage);
+    cudaFree(c->d_streams); cudaFree(c->d_slens); cudaFree(c->d_status); cudaFree(c->d_jobs); cudaFree(c->d_iplane);
+    cudaFree(c->d_dcoef); cudaFree(c->d_dec); cudaFree(c->d_es); cudaFree(c->d_targets);
+    cudaFreeHost(c->h_es); cudaFreeHost(c->h_status); cudaFreeHost(c->h_slens); cudaFreeHost(c->h_targets); cudaFreeHost(c->h_streams);
+    c->d_streams = NULL; c->d_slens = c->d_status = NULL; c->d_jobs = NULL; c->d_iplane = NULL; c->d_dcoef = c->d_dec = NULL;
+    c->d_es = NULL; c->d_targets = NULL; c->h_es = NULL; c->h_status = c->h_slens = NULL; c->h_targets = NULL; c->h_streams = NULL;
     free(c->h_cblks);
     c->d_plan = NULL; c->d_cblks = NULL; c->d_in = c->d_coef = NULL; c->d_stat = NULL;
     c->d_sym = c->d_mq = c->d_out = c->d_packed = NULL; c->d_cbout = NULL; c->d_maxlen = c->d_body_off = NULL;
@@ -286,7 +327,7 @@ extern "C" void ebcc_cuda_ctx_destroy(ebcc_cuda_ctx *c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     free_buffers(c);
-    cudaFree(c->d_luts); cudaFree(c->d_mqtab);
+    cudaFree(c->d_luts); cudaFree(c->d_mqtab); cudaFree(c->d_declut);
     for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventDestroy(c->ev[i]);
     cudaStreamDestroy(c->stream);
     free(c);
@@ -323,8 +364,25 @@ extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nf
     CK(cudaMallocHost((void **)&c->h_stat, B * sizeof(FrameStat)));
     CK(cudaMallocHost((void **)&c->h_offs, (B + 1) * sizeof(unsigned long long)));
     CK(cudaMallocHost((void **)&c->h_maxlen, B * sizeof(int)));
+    CK(cudaMalloc((void **)&c->d_streams, B * pl->out_stride));
+    CK(cudaMalloc((void **)&c->d_slens, B * sizeof(int)));
+    CK(cudaMalloc((void **)&c->d_status, B * sizeof(int)));
+    CK(cudaMalloc((void **)&c->d_jobs, B * pl->ncblks * sizeof(DecJob)));
+    CK(cudaMalloc((void **)&c->d_iplane, B * N * sizeof(int)));
+    CK(cudaMalloc((void **)&c->d_dcoef, B * N * sizeof(float)));
+    CK(cudaMalloc((void **)&c->d_dec, B * N * sizeof(float)));
+    CK(cudaMalloc((void **)&c->d_es, B * sizeof(ErrStat)));
+    CK(cudaMalloc((void **)&c->d_targets, B * sizeof(float)));
+    CK(cudaMallocHost((void **)&c->h_es, B * sizeof(ErrStat)));
+    CK(cudaMallocHost((void **)&c->h_status, B * sizeof(int)));
+    CK(cudaMallocHost((void **)&c->h_slens, B * sizeof(int)));
+    CK(cudaMallocHost((void **)&c->h_targets, B * sizeof(float)));
+    CK(cudaMallocHost((void **)&c->h_streams, B * pl->out_stride));
     c->cap_frames = nframes;
     // large dynamic shared memory opt-ins
+    CK(cudaFuncSetAttribute(k_idwt_v, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(k_idwt_h, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    CK(cudaFuncSetAttribute(k_t2_parse, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(k_dwt_v<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(k_dwt_v<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(k_dwt_h, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -419,6 +477,83 @@ extern "C" int ebcc_cuda_j2k_encode_resident(ebcc_cuda_ctx *c, size_t nframes, f
     mark(c, EBCC_ST_D2H);
     CK(cudaGetLastError());
     return 0;
+}
+
+
+// ---- decoder back half on the resident batch: tier-1 decode -> dequant -> IDWT -> float frames ---------
+// jobs/pool describe where every code-block's MQ segment lives; if orig != NULL the error statistics of the
+// reconstruction against orig (per-frame targets in d_targets) are accumulated into d_es.
+static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, size_t pool_stride, const float *orig)
+{
+    const Plan *pl = &c->plan;
+    const int W = pl->W, H = pl->H, N = W * H;
+    CK(cudaMemsetAsync(c->d_iplane, 0, (size_t)B * N * sizeof(int), c->stream));
+    const long long njobs = (long long)pl->ncblks * B;
+    EBCC_LAUNCH(k_t1_dec, dim3((unsigned)((njobs + DEC_WARPS - 1) / DEC_WARPS)), dim3(DEC_WARPS * 32), 0, c->stream,
+                c->d_cblks, c->d_jobs, pool, pool_stride, c->d_declut, c->d_iplane, W, H, pl->ncblks, B);
+    EBCC_LAUNCH(k_dequant, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_iplane, c->d_dcoef, c->d_plan, B);
+    c->launches += 2;
+    for (int r = 1; r < J2K_NRES; ++r) {
+        const int rw = pl->res_w[r], rh = pl->res_h[r];
+        int RH = 4;
+        while ((size_t)rw * RH * sizeof(float) > 64 * 1024 && RH > 1) RH >>= 1;
+        EBCC_LAUNCH(k_idwt_h, dim3((unsigned)((rh + RH - 1) / RH), (unsigned)B), dim3(128, (unsigned)RH),
+                    (size_t)rw * RH * sizeof(float), c->stream, c->d_dcoef, W, H, rw, rh, pl->res_w[r - 1]);
+        int CW = 32;
+        while ((size_t)rh * CW * sizeof(float) > 96 * 1024 && CW > 4) CW >>= 1;
+        EBCC_LAUNCH(k_idwt_v, dim3((unsigned)((rw + CW - 1) / CW), (unsigned)B), dim3((unsigned)CW, (unsigned)(512 / CW)),
+                    (size_t)rh * CW * sizeof(float), c->stream, c->d_dcoef, W, H, rw, rh, pl->res_h[r - 1]);
+        c->launches += 2;
+    }
+    if (orig) { EBCC_LAUNCH(k_errstat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_es, B); c->launches++; }
+    EBCC_LAUNCH(k_finalize, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_dcoef, c->d_dec, c->d_stat, orig,
+                orig ? c->d_targets : (const float *)NULL, c->d_es, N);
+    c->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+__global__ void k_set_stat(FrameStat *stat, const float *mm, int n)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { stat[i].minv = mm[2 * i]; stat[i].maxv = mm[2 * i + 1]; stat[i].flags = 0; }
+}
+
+extern "C" int ebcc_cuda_decode_batch(ebcc_cuda_ctx *c, const uint8_t *const *streams, const size_t *sizes, size_t nframes,
+                                      size_t H, size_t W, const float *minv, const float *maxv, const ebcc_residual_in *res,
+                                      float *const *outs)
+{
+    if (ebcc_cuda_reserve(c, H, W, nframes)) return -1;
+    for (size_t i = 0; res && i < nframes; ++i)
+        if (res[i].zstd_size) { fprintf(stderr, "[ebcc-cuda] residual layer decode not implemented yet\n"); return -1; }
+    const Plan *pl = &c->plan;
+    const int B = (int)nframes;
+    const size_t N = H * W;
+    for (int i = 0; i < B; ++i) {
+        if (sizes[i] > pl->out_stride) { fprintf(stderr, "[ebcc-cuda] codestream %d too large (%zu bytes)\n", i, sizes[i]); return -1; }
+        memcpy(c->h_streams + (size_t)i * pl->out_stride, streams[i], sizes[i]);
+        c->h_slens[i] = (int)sizes[i];
+    }
+    // min / max travel in the (pinned) target array: 2 floats per frame would overflow it, so use h_es as scratch
+    float *mm = (float *)c->h_es;
+    for (int i = 0; i < B; ++i) { mm[2 * i] = minv[i]; mm[2 * i + 1] = maxv[i]; }
+    for (int i = 0; i < B; ++i)
+        CK(cudaMemcpyAsync(c->d_streams + (size_t)i * pl->out_stride, c->h_streams + (size_t)i * pl->out_stride, sizes[i],
+                           cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->d_slens, c->h_slens, sizeof(int) * B, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->d_es, mm, sizeof(float) * 2 * B, cudaMemcpyHostToDevice, c->stream));
+    EBCC_LAUNCH(k_set_stat, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_stat, (const float *)c->d_es, B);
+    EBCC_LAUNCH(k_t2_parse, dim3((unsigned)B), dim3(32), (size_t)pl->nnodes * 4 * sizeof(int), c->stream,
+                c->d_plan, c->d_cblks, c->d_streams, pl->out_stride, c->d_slens, c->d_jobs, c->d_status);
+    c->launches += 2;
+    if (run_decode_stage(c, B, c->d_streams, pl->out_stride, NULL)) return -1;
+    CK(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
+    for (int i = 0; i < B; ++i)
+        CK(cudaMemcpyAsync(outs[i], c->d_dec + (size_t)i * N, N * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    int bad = 0;
+    for (int i = 0; i < B; ++i) if (c->h_status[i] != PARSE_OK) { fprintf(stderr, "[ebcc-cuda] malformed JPEG 2000 codestream in frame %d\n", i); bad = 1; }
+    return bad ? -2 : 0;
 }
 
 extern "C" int ebcc_cuda_download(ebcc_cuda_ctx *c, size_t nframes, const uint8_t **streams, size_t *sizes,

@@ -33,7 +33,7 @@
 struct T1Luts { short sig[128], sig0[128], ref[128], ref0[128]; };
 
 // zero-coding context from neighbour counts (Annex D table D.1; t1_generate_luts.c:48-128)
-__device__ __forceinline__ int t1_zc_ctx(int orient, int h, int v, int d)
+__host__ __device__ __forceinline__ int t1_zc_ctx(int orient, int h, int v, int d)
 {
     if (orient == 1) { int t = h; h = v; v = t; }
     if (orient != 3) {

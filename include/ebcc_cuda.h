@@ -54,6 +54,21 @@ int ebcc_cuda_j2k_encode_batch(ebcc_cuda_ctx *ctx, const float *frames, size_t n
                                size_t width, float base_cr, const uint8_t **streams, size_t *sizes,
                                float *minv, float *maxv, int *flags);
 
+/* residual layer of one frame as stored in its EBCC stream (src/ebcc_codec.c:1294-1312); zstd_size == 0: none */
+typedef struct {
+    const uint8_t *zstd;
+    size_t zstd_size;
+    size_t coeffs_size;      /* SPIHT bytes after zstd decompression */
+    float rmin, rmax;        /* residual range used to de-normalise */
+} ebcc_residual_in;
+
+/* replaces j2k_decode_internal + ZSTD_decompress + spiht_decode + the residual add of ebcc_decode
+ * (src/ebcc_codec.c:1092-1136, :1294-1312): nframes J2K codestreams of the same H x W geometry are
+ * decoded on the device and written to outs[i] (host, H*W floats each). */
+int ebcc_cuda_decode_batch(ebcc_cuda_ctx *ctx, const uint8_t *const *j2k, const size_t *j2k_sizes, size_t nframes,
+                           size_t height, size_t width, const float *minv, const float *maxv,
+                           const ebcc_residual_in *res, float *const *outs);
+
 /* profiling: when enabled, CUDA events bracket every stage on the context's stream */
 void ebcc_cuda_set_profiling(ebcc_cuda_ctx *ctx, int enabled);
 /* milliseconds spent in a stage during the last pass (valid after ebcc_cuda_sync) */
