@@ -171,7 +171,294 @@ static size_t assemble_frame(const frame_parts_t *p, uint8_t **out)
     return out_size;
 }
 
-/* ---- batched encode --------------------------------------------------------------------------------- */
+/* ---- compression-ratio search: error_bound_j2k_compression (reference src/ebcc_codec.c:545-596) as a
+ * resumable state machine, so that a whole batch of frames advances in lock step, one device probe
+ * (ebcc_cuda_rate_probe) per round.  Pure control flow over the quantiles the device returns. */
+enum { PH_LO, PH_LO_WAIT, PH_HI, PH_HI_WAIT, PH_BIS, PH_BIS_WAIT, PH_DONE };
+typedef struct {
+    int phase;
+    float cr_lo, cr_hi, cur, pending, result;
+    double q, q_prev, target;
+} crsearch_t;
+
+static void crs_init(crsearch_t *s, float start_cr, double q0, double target)
+{
+    s->phase = PH_LO; s->cr_lo = s->cr_hi = start_cr; s->cur = start_cr; s->q = s->q_prev = q0; s->target = target;
+    s->pending = s->result = start_cr;
+}
+
+/* returns 1 when a probe at s->pending is needed (the caller stores its quantile in s->q), 0 when done */
+static int crs_advance(crsearch_t *s)
+{
+    const double eps = 1e-8;
+    for (;;) {
+        switch (s->phase) {
+        case PH_LO:
+            if (s->q < s->target && s->cr_lo >= 1. / 2) { s->cr_lo /= 2; s->pending = s->cr_lo; s->phase = PH_LO_WAIT; return 1; }
+            s->q = s->q_prev; s->phase = PH_HI; break;
+        case PH_LO_WAIT: s->phase = PH_LO; break;
+        case PH_HI:
+            if (s->q >= s->target && s->cr_hi <= 1000) { s->cr_hi *= 2; s->pending = s->cr_hi; s->phase = PH_HI_WAIT; return 1; }
+            if (s->q >= s->target) { s->result = s->cr_hi; s->phase = PH_DONE; return 0; }
+            s->q = s->q_prev; s->phase = PH_BIS; break;
+        case PH_HI_WAIT: s->phase = PH_HI; break;
+        case PH_BIS:
+            if ((fabs(s->q - s->target) > eps || s->q == 1.0) && s->cr_hi - s->cr_lo > 1.) {
+                s->cur = (s->cr_lo + s->cr_hi) / 2; s->pending = s->cur; s->phase = PH_BIS_WAIT; return 1;
+            }
+            s->result = s->cr_lo; s->phase = PH_DONE; return 0;
+        case PH_BIS_WAIT:
+            if (s->q < s->target) s->cr_hi = s->cur; else s->cr_lo = s->cur;
+            s->phase = PH_BIS; break;
+        default: return 0;
+        }
+    }
+}
+
+#define MEMO_MAX 96
+typedef struct { int n; float cr[MEMO_MAX]; unsigned long long n_over[MEMO_MAX]; } memo_t;
+
+static int memo_find(const memo_t *m, float cr, unsigned long long *n_over)
+{
+    for (int i = 0; i < m->n; ++i) if (m->cr[i] == cr) { *n_over = m->n_over[i]; return 1; }
+    return 0;
+}
+static void memo_put(memo_t *m, float cr, unsigned long long n_over)
+{
+    if (m->n < MEMO_MAX) { m->cr[m->n] = cr; m->n_over[m->n] = n_over; m->n++; }
+}
+
+/* runs the search for every frame with run[i] != 0; result_cr[i] receives the ratio the reference would settle on */
+static int search_batch(ebcc_cuda_ctx *ctx, size_t nb, const int *run, const float *start_cr, const double *q0, double target,
+                        const float *err_target, size_t tot_size, memo_t *memo, float *result_cr, float *last_cr)
+{
+    crsearch_t *st = (crsearch_t *)calloc(nb, sizeof(*st));
+    int *need = (int *)calloc(nb, sizeof(int));
+    ebcc_probe_result *pr = (ebcc_probe_result *)calloc(nb, sizeof(*pr));
+    int rc = 0;
+    for (size_t i = 0; i < nb; ++i) { if (run[i]) crs_init(&st[i], start_cr[i], q0[i], target); else st[i].phase = PH_DONE; result_cr[i] = start_cr[i]; }
+    for (;;) {
+        int any_dev = 0, any = 0;
+        for (size_t i = 0; i < nb; ++i) {
+            need[i] = 0;
+            while (st[i].phase != PH_DONE) {
+                if (!crs_advance(&st[i])) { result_cr[i] = st[i].result; break; }
+                any = 1;
+                unsigned long long n;
+                if (memo_find(&memo[i], st[i].pending, &n)) { st[i].q = 1. - ((double)n / tot_size); continue; }
+                need[i] = 1; any_dev = 1; break;
+            }
+        }
+        if (!any_dev) { if (!any) break; else continue; }
+        for (size_t i = 0; i < nb; ++i) if (need[i]) last_cr[i] = st[i].pending;
+        if (ebcc_cuda_rate_probe(ctx, nb, last_cr, err_target, 0, pr)) { rc = -1; break; }
+        for (size_t i = 0; i < nb; ++i) {
+            if (!need[i]) continue;
+            memo_put(&memo[i], st[i].pending, pr[i].n_over);
+            st[i].q = 1. - ((double)pr[i].n_over / tot_size);
+            ebcc_log(LOG_TRACE, "frame %lu: cr %f, 1-error_target_quantile: %.1e, jp2_length: %lu", i, st[i].pending, 1 - st[i].q, pr[i].stream_bytes);
+        }
+    }
+    free(st); free(need); free(pr);
+    return rc;
+}
+
+/* ---- batched encode: one pass of the reference's ebcc_encode (src/ebcc_codec.c:607-918) over nb frames -------- */
+static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size_t base, const codec_config_t *config,
+                        uint8_t **outs, size_t *sizes, size_t *done)
+{
+    const size_t H = config->dims[1], W = config->dims[2], N = H * W;
+    const residual_t mode = config->residual_compression_type;
+    int rc = -1;
+    double base_error_quantile = 1e-6;
+    const char *env_q = getenv("EBCC_INIT_BASE_ERROR_QUANTILE");
+    const int pure_disabled = getenv("EBCC_DISABLE_PURE_BASE_COMPRESSION_FALLBACK") != NULL;
+    const int consistency_disabled = getenv("EBCC_DISABLE_PURE_BASE_COMPRESSION_FALLBACK_CONSISTENCY") != NULL;
+    const int mean_adjust_disabled = getenv("EBCC_DISABLE_MEAN_ADJUSTMENT") != NULL;
+    if (env_q) base_error_quantile = strtod(env_q, NULL);
+    const double base_quantile_target = 1 - base_error_quantile;
+
+    const uint8_t **streams = (const uint8_t **)calloc(nb, sizeof(*streams));
+    size_t *ssz = (size_t *)calloc(nb, sizeof(size_t));
+    float *mn = (float *)calloc(nb, sizeof(float)), *mx = (float *)calloc(nb, sizeof(float));
+    int *fl = (int *)calloc(nb, sizeof(int));
+    float *cr = (float *)calloc(nb, sizeof(float)), *cr1 = (float *)calloc(nb, sizeof(float)), *cr2 = (float *)calloc(nb, sizeof(float));
+    float *tgt = (float *)calloc(nb, sizeof(float)), *start = (float *)calloc(nb, sizeof(float));
+    double *q0 = (double *)calloc(nb, sizeof(double)), *mean = (double *)calloc(nb, sizeof(double));
+    int *run = (int *)calloc(nb, sizeof(int)), *resid = (int *)calloc(nb, sizeof(int)), *pure_required = (int *)calloc(nb, sizeof(int));
+    memo_t *memo = (memo_t *)calloc(nb, sizeof(memo_t));
+    ebcc_probe_result *p0 = (ebcc_probe_result *)calloc(nb, sizeof(*p0)), *p1 = (ebcc_probe_result *)calloc(nb, sizeof(*p1)),
+                      *p2 = (ebcc_probe_result *)calloc(nb, sizeof(*p2));
+    uint8_t **j2k1 = (uint8_t **)calloc(nb, sizeof(*j2k1));
+    size_t *len1 = (size_t *)calloc(nb, sizeof(size_t)), *coeffs_size = (size_t *)calloc(nb, sizeof(size_t)), *tb = (size_t *)calloc(nb, sizeof(size_t));
+    const uint8_t **zs = (const uint8_t **)calloc(nb, sizeof(*zs));
+    uint8_t **zcopy = (uint8_t **)calloc(nb, sizeof(*zcopy));
+    size_t *zn = (size_t *)calloc(nb, sizeof(size_t));
+    float *perr = (float *)calloc(nb, sizeof(float)), *best_err = (float *)calloc(nb, sizeof(float));
+    double *psum = (double *)calloc(nb, sizeof(double)), *thi = (double *)calloc(nb, sizeof(double)), *tlo = (double *)calloc(nb, sizeof(double)),
+           *best_trunc = (double *)calloc(nb, sizeof(double));
+    int *use_pure = (int *)calloc(nb, sizeof(int));
+
+    if (ebcc_cuda_reserve(ctx, H, W, nb) || ebcc_cuda_upload(ctx, frames, nb) || ebcc_cuda_analyze_resident(ctx, nb)) goto out;
+    for (size_t i = 0; i < nb; ++i) { cr[i] = config->base_cr; tgt[i] = 0; }
+
+    if (mode == NONE) {
+        if (ebcc_cuda_rate_probe_streams_only(ctx, nb, cr)) goto out;
+    } else {
+        /* first encode + decode at base_cr (reference :693-712); targets need min/max, so fetch the frame statistics first */
+        if (ebcc_cuda_frame_stats(ctx, nb, mn, mx, fl)) goto out;
+        for (size_t i = 0; i < nb; ++i) {
+            float t = config->error;
+            if (mode == RELATIVE_ERROR) t *= (mx[i] - mn[i]);       /* get_data_range, reference :724-726 */
+            tgt[i] = t;
+        }
+        if (ebcc_cuda_rate_probe(ctx, nb, cr, tgt, 0, p0)) goto out;
+        for (size_t i = 0; i < nb; ++i) {
+            run[i] = !(fl[i] & (EBCC_FRAME_CONST | EBCC_FRAME_NANINF));
+            memo_put(&memo[i], cr[i], p0[i].n_over);
+            q0[i] = 1. - ((double)p0[i].n_over / N);
+            start[i] = config->base_cr;
+            mean[i] = p0[i].sum_err / N;                            /* get_mean_error after the first decode, :709 */
+        }
+        if (search_batch(ctx, nb, run, start, q0, base_quantile_target, tgt, N, memo, cr1, cr)) goto out;
+        if (ebcc_cuda_rate_probe(ctx, nb, cr1, tgt, 1, p1)) goto out;
+    }
+    if (ebcc_cuda_download(ctx, nb, streams, ssz, mn, mx, fl)) goto out;
+    for (size_t i = 0; i < nb; ++i) {
+        if (fl[i] & EBCC_FRAME_NANINF) {
+            /* reference check_nan_inf: log_fatal + exit(1) (src/ebcc_codec.c:598-605) */
+            ebcc_log(LOG_FATAL, "NaN or Inf found in data (frame %lu)", base + i);
+            exit(1);
+        }
+    }
+
+    if (mode != NONE) {
+        const int pure_done = base_quantile_target == 1.0;
+        int any_resid = 0;
+        for (size_t i = 0; i < nb; ++i) {
+            if (!run[i]) continue;
+            len1[i] = ssz[i];
+            j2k1[i] = (uint8_t *)malloc(ssz[i] ? ssz[i] : 1);
+            memcpy(j2k1[i], streams[i], ssz[i]);
+            const float cur_max_error = fmaxf(fabsf(p1[i].rmin), fabsf(p1[i].rmax));
+            resid[i] = !(cur_max_error <= tgt[i]);
+            best_err[i] = -1;
+            tb[i] = len1[i] * 8;
+            if (resid[i]) any_resid = 1;
+            ebcc_log(LOG_TRACE, "frame %lu: base cr %f, jp2_length %lu, max error %f, target %f", base + i, cr1[i], len1[i], cur_max_error, tgt[i]);
+        }
+        if (any_resid) {
+            /* SPIHT encode of the normalised residual + full decode check (reference :744-763) */
+            if (ebcc_cuda_residual_encode(ctx, nb, resid, tb, coeffs_size)) goto out;
+            for (size_t i = 0; i < nb; ++i) tb[i] = coeffs_size[i] * 8;
+            if (ebcc_cuda_residual_probe(ctx, nb, resid, tb, perr, psum)) goto out;
+            for (size_t i = 0; i < nb; ++i) {
+                if (!resid[i]) continue;
+                if (perr[i] > tgt[i]) {
+                    ebcc_log(LOG_INFO, "Could not reach error target of %f (%f instead). Retry with pure base compression.", tgt[i], perr[i]);
+                    resid[i] = 0; pure_required[i] = 1; coeffs_size[i] = 0;   /* coeffs_size stays coeffs_size_orig in the reference only until it is zeroed by the pure choice */
+                } else {
+                    best_err[i] = perr[i]; mean[i] = psum[i] / N;
+                    thi[i] = (double)coeffs_size[i] * 8; tlo[i] = 112.0; best_trunc[i] = thi[i];
+                }
+            }
+            /* truncation bisection (reference :766-796), all frames in lock step */
+            for (;;) {
+                int any = 0;
+                for (size_t i = 0; i < nb; ++i) {
+                    tb[i] = 0;
+                    if (!resid[i]) continue;
+                    if (((tgt[i] - best_err[i]) / tgt[i] > 1e-8) && (thi[i] - tlo[i] > 8 * 4)) {
+                        tb[i] = ((size_t)ceill((thi[i] + tlo[i]) / 2 / 8)) * 8;
+                        any = 1;
+                    }
+                }
+                if (!any) break;
+                int *act = (int *)calloc(nb, sizeof(int));
+                for (size_t i = 0; i < nb; ++i) act[i] = tb[i] != 0;
+                int prc = ebcc_cuda_residual_probe(ctx, nb, act, tb, perr, psum);
+                free(act);
+                if (prc) goto out;
+                for (size_t i = 0; i < nb; ++i) {
+                    if (!tb[i]) continue;
+                    if (perr[i] > tgt[i]) tlo[i] = (double)tb[i];
+                    else {
+                        thi[i] = (double)tb[i];
+                        if (perr[i] >= best_err[i]) { best_err[i] = perr[i]; best_trunc[i] = (double)tb[i]; mean[i] = psum[i] / N; }
+                    }
+                    ebcc_log(LOG_TRACE, "frame %lu: trunc_lo %.1f trunc_hi %.1f bytes %lu max error %f", base + i, tlo[i], thi[i], tb[i] / 8, perr[i]);
+                }
+            }
+            for (size_t i = 0; i < nb; ++i) {
+                if (resid[i]) coeffs_size[i] = (size_t)(best_trunc[i] / 8.);
+                if (coeffs_size[i] <= 16) coeffs_size[i] = 0;
+                if (!resid[i]) coeffs_size[i] = 0;
+            }
+            /* zstd stage on the device (reference :813-817) */
+            if (ebcc_cuda_residual_pack(ctx, nb, coeffs_size, zs, zn)) goto out;
+            for (size_t i = 0; i < nb; ++i) {
+                if (!zn[i]) continue;
+                zcopy[i] = (uint8_t *)malloc(zn[i]);
+                memcpy(zcopy[i], zs[i], zn[i]);
+            }
+        }
+        /* pure base-layer fallback (reference :819-854) */
+        if (!pure_done && !pure_disabled) {
+            for (size_t i = 0; i < nb; ++i) {
+                start[i] = consistency_disabled ? cr1[i] : config->base_cr;
+                unsigned long long n = 0;
+                memo_find(&memo[i], start[i], &n);
+                q0[i] = 1. - ((double)n / N);
+            }
+            if (search_batch(ctx, nb, run, start, q0, 1.0, tgt, N, memo, cr2, cr)) goto out;
+            if (ebcc_cuda_rate_probe(ctx, nb, cr2, tgt, 1, p2)) goto out;
+            if (ebcc_cuda_download(ctx, nb, streams, ssz, NULL, NULL, NULL)) goto out;
+            for (size_t i = 0; i < nb; ++i) {
+                if (!run[i]) continue;
+                if (ssz[i] < zn[i] + len1[i] || pure_required[i]) {
+                    if (ssz[i] < zn[i] + len1[i])
+                        ebcc_log(LOG_INFO, "Pure base compression (%lu) is better than base (%lu) + residual (%lu) compression (sum: %lu)",
+                                 ssz[i], len1[i], zn[i], zn[i] + len1[i]);
+                    use_pure[i] = 1; mean[i] = p2[i].sum_err / N; zn[i] = 0; coeffs_size[i] = 0;
+                }
+            }
+        }
+    }
+
+    for (size_t i = 0; i < nb; ++i) {
+        frame_parts_t p;
+        memset(&p, 0, sizeof(p));
+        p.const_field = (fl[i] & EBCC_FRAME_CONST) != 0;
+        p.minval = mn[i]; p.maxval = mx[i];
+        p.tot_size = N;
+        if (mode != NONE && run[i]) {
+            p.residual_minval = p1[i].rmin; p.residual_maxval = p1[i].rmax;
+            p.coeffs_size = coeffs_size[i];
+            p.zstd = zcopy[i]; p.zstd_size = zn[i];
+            if (use_pure[i]) { p.j2k = streams[i]; p.j2k_size = ssz[i]; }
+            else { p.j2k = j2k1[i]; p.j2k_size = len1[i]; }
+            ebcc_log(LOG_INFO, "Mean of compression error: %e", mean[i]);
+            if (!mean_adjust_disabled && fabs(mean[i]) > 1e-18) { p.minval += mean[i]; p.maxval += mean[i]; }
+        } else {
+            p.j2k = streams[i]; p.j2k_size = ssz[i];
+        }
+        if (!p.const_field && p.j2k_size == 0) { ebcc_log(LOG_FATAL, "empty codestream for frame %lu", base + i); continue; }
+        sizes[base + i] = assemble_frame(&p, &outs[base + i]);
+        if (sizes[base + i]) {
+            (*done)++;
+            ebcc_log(LOG_INFO, "coeffs_size: %lu, compressed_size: %lu, jp2_length: %lu, compression ratio: %f", p.coeffs_size, p.zstd_size,
+                     p.const_field ? sizeof(uint64_t) : p.j2k_size, (double)(N * sizeof(float)) / sizes[base + i]);
+        }
+    }
+    rc = 0;
+out:
+    for (size_t i = 0; i < nb; ++i) { free(j2k1[i]); free(zcopy[i]); }
+    free(streams); free(ssz); free(mn); free(mx); free(fl); free(cr); free(cr1); free(cr2); free(tgt); free(start); free(q0); free(mean);
+    free(run); free(resid); free(pure_required); free(memo); free(p0); free(p1); free(p2); free(j2k1); free(len1); free(coeffs_size); free(tb);
+    free(zs); free(zcopy); free(zn); free(perr); free(best_err); free(psum); free(thi); free(tlo); free(best_trunc); free(use_pure);
+    return rc;
+}
+
 size_t ebcc_encode_batch(const float *frames, size_t nframes, const codec_config_t *config, uint8_t **outs, size_t *sizes)
 {
     log_set_level_from_env();
@@ -185,45 +472,23 @@ size_t ebcc_encode_batch(const float *frames, size_t nframes, const codec_config
         ebcc_log(LOG_FATAL, "multi-tile internal images (dims[0]=%lu > 1) are not implemented on the CUDA path yet", config->dims[0]);
         return 0;
     }
-    if (config->residual_compression_type != NONE) {
-        ebcc_log(LOG_FATAL, "residual modes MAX_ERROR / RELATIVE_ERROR are not implemented on the CUDA path yet");
+    if ((unsigned)config->residual_compression_type > RELATIVE_ERROR) {
+        ebcc_log(LOG_FATAL, "unknown residual compression type %d", (int)config->residual_compression_type);
         return 0;
     }
-    const size_t H = config->dims[1], W = config->dims[2], N = H * W;
+    const size_t N = config->dims[1] * config->dims[2];
     const size_t maxb = max_batch_frames();
     size_t done = 0;
-
     pthread_mutex_lock(&g_mu);
     ebcc_cuda_ctx *ctx = get_ctx_locked();
     if (!ctx) { pthread_mutex_unlock(&g_mu); return 0; }
-    const uint8_t **streams = (const uint8_t **)malloc(sizeof(*streams) * maxb);
-    size_t *ssz = (size_t *)malloc(sizeof(size_t) * maxb);
-    float *mn = (float *)malloc(sizeof(float) * maxb), *mx = (float *)malloc(sizeof(float) * maxb);
-    int *fl = (int *)malloc(sizeof(int) * maxb);
     for (size_t base = 0; base < nframes; base += maxb) {
         const size_t nb = nframes - base < maxb ? nframes - base : maxb;
-        if (ebcc_cuda_j2k_encode_batch(ctx, frames + base * N, nb, H, W, config->base_cr, streams, ssz, mn, mx, fl)) {
+        if (encode_chunk(ctx, frames + base * N, nb, base, config, outs, sizes, &done)) {
             ebcc_log(LOG_FATAL, "CUDA encode of frames %lu..%lu failed", base, base + nb - 1);
             break;
         }
-        for (size_t i = 0; i < nb; ++i) {
-            if (fl[i] & EBCC_FRAME_NANINF) {
-                /* reference check_nan_inf: log_fatal + exit(1) (src/ebcc_codec.c:598-605) */
-                ebcc_log(LOG_FATAL, "NaN or Inf found in data (frame %lu)", base + i);
-                exit(1);
-            }
-            frame_parts_t p;
-            memset(&p, 0, sizeof(p));
-            p.const_field = (fl[i] & EBCC_FRAME_CONST) != 0;
-            p.minval = mn[i]; p.maxval = mx[i];
-            p.j2k = streams[i]; p.j2k_size = ssz[i];
-            p.tot_size = N;
-            if (!p.const_field && p.j2k_size == 0) { ebcc_log(LOG_FATAL, "empty codestream for frame %lu", base + i); continue; }
-            sizes[base + i] = assemble_frame(&p, &outs[base + i]);
-            if (sizes[base + i]) done++;
-        }
     }
-    free(streams); free(ssz); free(mn); free(mx); free(fl);
     pthread_mutex_unlock(&g_mu);
     return done;
 }

@@ -8,6 +8,8 @@
 #include "k_t2.cuh"
 #include "k_dec.cuh"
 #include "k_idwt.cuh"
+#include "k_spiht.cuh"
+#include "k_zstd.cuh"
 #include "../../include/ebcc_cuda.h"
 #include <math.h>
 #include <stdio.h>
@@ -253,6 +255,22 @@ struct ebcc_cuda_ctx {
     int *h_status, *h_slens;
     float *h_targets;
     unsigned char *h_streams;  // pinned staging for codestream upload
+    // residual layer (SPIHT + zstd)
+    SpGeom sg;
+    SpBufs sp;
+    float *d_sp_img0, *d_sp_img1;   // [B][Np] data / temp planes of the SPIHT wavelet transform
+    SpInfo *d_sp_info, *h_sp_info;
+    unsigned *d_sp_P, *h_sp_P, *d_sp_budget, *h_sp_budget;
+    int *d_sp_active, *h_sp_active, *d_step_tab;
+    float *d_sp_rmm, *h_sp_rmm;
+    ErrStat *d_es2, *h_es2;
+    unsigned char *d_zout, *h_zout; // [B][zstride] zstd frames
+    size_t zstride;
+    unsigned *d_zlen, *h_zlen, *d_zsrc_len, *h_zsrc_len;
+    unsigned char *d_zin, *h_zin;   // [B][zstride] zstd frames to decode (decode path)
+    ZEncWork *d_zenc_work;
+    ZDecWork *d_zdec_work;
+    unsigned *d_zcap, *h_zcap;
     // pinned host mirrors
     ProbeOut *h_pout;
     FrameStat *h_stat;
@@ -298,6 +316,14 @@ extern "C" ebcc_cuda_ctx *ebcc_cuda_ctx_create(int device)
     if (cudaMalloc((void **)&c->d_declut, sizeof(DecLuts)) != cudaSuccess) { free(dl); free(c); return NULL; }
     cudaMemcpy(c->d_declut, dl, sizeof(DecLuts), cudaMemcpyHostToDevice);
     free(dl);
+    {
+        // SPIHT top bit-plane for max = 2^k exactly as the reference's libm evaluates floor(log(max) / log(2.0))
+        // (spiht_re.c:60); configuration arithmetic, done once on the host with the same libm call
+        int tab[32];
+        for (int k = 0; k < 32; ++k) tab[k] = (int)floor(log(ldexp(1.0, k)) / log(2.0));
+        if (cudaMalloc((void **)&c->d_step_tab, sizeof(tab)) != cudaSuccess) { free(c); return NULL; }
+        cudaMemcpy(c->d_step_tab, tab, sizeof(tab), cudaMemcpyHostToDevice);
+    }
     return c;
 }
 
@@ -313,6 +339,20 @@ static void free_buffers(ebcc_cuda_ctx *c)
     cudaFreeHost(c->h_es); cudaFreeHost(c->h_status); cudaFreeHost(c->h_slens); cudaFreeHost(c->h_targets); cudaFreeHost(c->h_streams);
     c->d_streams = NULL; c->d_slens = c->d_status = NULL; c->d_jobs = NULL; c->d_iplane = NULL; c->d_dcoef = c->d_dec = NULL;
     c->d_es = NULL; c->d_targets = NULL; c->h_es = NULL; c->h_status = c->h_slens = NULL; c->h_targets = NULL; c->h_streams = NULL;
+    cudaFree(c->sp.coef); cudaFree(c->sp.D); cudaFree(c->sp.L); cudaFree(c->sp.lip0); cudaFree(c->sp.lip1); cudaFree(c->sp.lsp);
+    cudaFree(c->sp.lis0); cudaFree(c->sp.lis1); cudaFree(c->sp.sign_pos); cudaFree(c->sp.lsp_idx); cudaFree(c->sp.bits);
+    cudaFree(c->d_sp_img0); cudaFree(c->d_sp_img1); cudaFree(c->d_sp_info); cudaFree(c->d_sp_P); cudaFree(c->d_sp_budget);
+    cudaFree(c->d_sp_active); cudaFree(c->d_sp_rmm); cudaFree(c->d_es2); cudaFree(c->d_zout); cudaFree(c->d_zlen); cudaFree(c->d_zsrc_len);
+    cudaFree(c->d_zin); cudaFree(c->d_zenc_work); cudaFree(c->d_zdec_work); cudaFree(c->d_zcap); cudaFreeHost(c->h_zcap);
+    c->d_zenc_work = NULL; c->d_zdec_work = NULL; c->d_zcap = NULL; c->h_zcap = NULL;
+    cudaFreeHost(c->h_sp_info); cudaFreeHost(c->h_sp_P); cudaFreeHost(c->h_sp_budget); cudaFreeHost(c->h_sp_active);
+    cudaFreeHost(c->h_sp_rmm); cudaFreeHost(c->h_es2); cudaFreeHost(c->h_zout); cudaFreeHost(c->h_zlen); cudaFreeHost(c->h_zsrc_len);
+    cudaFreeHost(c->h_zin);
+    memset(&c->sp, 0, sizeof(c->sp));
+    c->d_sp_img0 = c->d_sp_img1 = NULL; c->d_sp_info = NULL; c->d_sp_P = c->d_sp_budget = NULL; c->d_sp_active = NULL; c->d_sp_rmm = NULL;
+    c->d_es2 = NULL; c->d_zout = NULL; c->d_zlen = c->d_zsrc_len = NULL; c->d_zin = NULL;
+    c->h_sp_info = NULL; c->h_sp_P = c->h_sp_budget = NULL; c->h_sp_active = NULL; c->h_sp_rmm = NULL; c->h_es2 = NULL; c->h_zout = NULL;
+    c->h_zlen = c->h_zsrc_len = NULL; c->h_zin = NULL;
     free(c->h_cblks);
     c->d_plan = NULL; c->d_cblks = NULL; c->d_in = c->d_coef = NULL; c->d_stat = NULL;
     c->d_sym = c->d_mq = c->d_out = c->d_packed = NULL; c->d_cbout = NULL; c->d_maxlen = c->d_body_off = NULL;
@@ -327,7 +367,7 @@ extern "C" void ebcc_cuda_ctx_destroy(ebcc_cuda_ctx *c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     free_buffers(c);
-    cudaFree(c->d_luts); cudaFree(c->d_mqtab); cudaFree(c->d_declut);
+    cudaFree(c->d_luts); cudaFree(c->d_mqtab); cudaFree(c->d_declut); cudaFree(c->d_step_tab);
     for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventDestroy(c->ev[i]);
     cudaStreamDestroy(c->stream);
     free(c);
@@ -378,6 +418,33 @@ extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nf
     CK(cudaMallocHost((void **)&c->h_slens, B * sizeof(int)));
     CK(cudaMallocHost((void **)&c->h_targets, B * sizeof(float)));
     CK(cudaMallocHost((void **)&c->h_streams, B * pl->out_stride));
+    {   // residual layer
+        SpGeom &g = c->sg;
+        g.W = (int)W; g.H = (int)H; g.Wp = ((int)W + 15) & ~15; g.Hp = ((int)H + 15) & ~15; g.lx = g.Wp >> SP_STAGES; g.ly = g.Hp >> SP_STAGES;
+        const size_t Np = (size_t)g.Wp * g.Hp;
+        c->sp.bits_words = pl->out_stride / 4 + 64;
+        c->zstride = pl->out_stride + 1024;
+        CK(cudaMalloc((void **)&c->sp.coef, B * Np * 4)); CK(cudaMalloc((void **)&c->sp.D, B * Np * 4)); CK(cudaMalloc((void **)&c->sp.L, B * Np * 4));
+        CK(cudaMalloc((void **)&c->sp.lip0, B * Np * 4)); CK(cudaMalloc((void **)&c->sp.lip1, B * Np * 4)); CK(cudaMalloc((void **)&c->sp.lsp, B * Np * 4));
+        CK(cudaMalloc((void **)&c->sp.lis0, B * Np * 8)); CK(cudaMalloc((void **)&c->sp.lis1, B * Np * 8));
+        CK(cudaMalloc((void **)&c->sp.sign_pos, B * Np * 4)); CK(cudaMalloc((void **)&c->sp.lsp_idx, B * Np * 4));
+        CK(cudaMalloc((void **)&c->sp.bits, B * c->sp.bits_words * 4));
+        CK(cudaMalloc((void **)&c->d_sp_img0, B * Np * 4)); CK(cudaMalloc((void **)&c->d_sp_img1, B * Np * 4));
+        CK(cudaMalloc((void **)&c->d_sp_info, B * sizeof(SpInfo))); CK(cudaMalloc((void **)&c->d_sp_P, B * 4)); CK(cudaMalloc((void **)&c->d_sp_budget, B * 4));
+        CK(cudaMalloc((void **)&c->d_sp_active, B * 4)); CK(cudaMalloc((void **)&c->d_sp_rmm, B * 8)); CK(cudaMalloc((void **)&c->d_es2, B * sizeof(ErrStat)));
+        CK(cudaMalloc((void **)&c->d_zout, B * c->zstride)); CK(cudaMalloc((void **)&c->d_zlen, B * 4)); CK(cudaMalloc((void **)&c->d_zsrc_len, B * 4));
+        CK(cudaMalloc((void **)&c->d_zin, B * c->zstride));
+        CK(cudaMalloc((void **)&c->d_zenc_work, B * sizeof(ZEncWork))); CK(cudaMalloc((void **)&c->d_zdec_work, B * sizeof(ZDecWork)));
+        CK(cudaMalloc((void **)&c->d_zcap, B * 4)); CK(cudaMallocHost((void **)&c->h_zcap, B * 4));
+        CK(cudaMallocHost((void **)&c->h_sp_info, B * sizeof(SpInfo))); CK(cudaMallocHost((void **)&c->h_sp_P, B * 4)); CK(cudaMallocHost((void **)&c->h_sp_budget, B * 4));
+        CK(cudaMallocHost((void **)&c->h_sp_active, B * 4)); CK(cudaMallocHost((void **)&c->h_sp_rmm, B * 8)); CK(cudaMallocHost((void **)&c->h_es2, B * sizeof(ErrStat)));
+        CK(cudaMallocHost((void **)&c->h_zout, B * c->zstride)); CK(cudaMallocHost((void **)&c->h_zlen, B * 4)); CK(cudaMallocHost((void **)&c->h_zsrc_len, B * 4));
+        CK(cudaMallocHost((void **)&c->h_zin, B * c->zstride));
+        CK(cudaFuncSetAttribute(k_sp_dwt_row, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CK(cudaFuncSetAttribute(k_sp_dwt_col, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CK(cudaFuncSetAttribute(k_sp_idwt_row, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        CK(cudaFuncSetAttribute(k_sp_idwt_col, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    }
     c->cap_frames = nframes;
     // large dynamic shared memory opt-ins
     CK(cudaFuncSetAttribute(k_idwt_v, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -432,16 +499,13 @@ static int launch_dwt(ebcc_cuda_ctx *c, int B)
     return 0;
 }
 
-extern "C" int ebcc_cuda_j2k_encode_resident(ebcc_cuda_ctx *c, size_t nframes, float base_cr)
+// stage 1 of the encoder: everything that does not depend on the compression ratio
+extern "C" int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *c, size_t nframes)
 {
     if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
     CK(cudaSetDevice(c->device));
     const Plan *pl = &c->plan;
     const int B = (int)nframes, N = pl->H * pl->W;
-    const int ml = tile_maxlen(pl->H, pl->W, base_cr, pl->main_header_len);
-    for (int i = 0; i < B; ++i) c->h_maxlen[i] = ml;
-    CK(cudaMemcpyAsync(c->d_maxlen, c->h_maxlen, sizeof(int) * B, cudaMemcpyHostToDevice, c->stream));
-
     mark(c, EBCC_ST_MINMAX);
     EBCC_LAUNCH(k_stat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_stat, B);
     EBCC_LAUNCH(k_minmax, dim3(74, (unsigned)B), dim3(256), 0, c->stream, c->d_in, c->d_stat, N);
@@ -465,20 +529,43 @@ extern "C" int ebcc_cuda_j2k_encode_resident(ebcc_cuda_ctx *c, size_t nframes, f
         EBCC_LAUNCH(k_t1_mq, dim3((unsigned)ctas), dim3(MQ_THREADS), 0, c->stream,
                     c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride, lanes);
     }
+    c->launches += 2;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// stage 2: PCRD + tier-2 for one compression ratio per frame; with_bodies also assembles the codestreams
+static int launch_rate_stage(ebcc_cuda_ctx *c, int B, const float *cr, int with_bodies)
+{
+    const Plan *pl = &c->plan;
+    for (int i = 0; i < B; ++i) c->h_maxlen[i] = tile_maxlen(pl->H, pl->W, cr[i], pl->main_header_len);
+    CK(cudaMemcpyAsync(c->d_maxlen, c->h_maxlen, sizeof(int) * B, cudaMemcpyHostToDevice, c->stream));
     mark(c, EBCC_ST_PCRD_T2);
     EBCC_LAUNCH(k_pcrd_t2, dim3((unsigned)B), dim3(T2_THREADS), t2_smem_bytes(pl->ncblks, pl->nnodes), c->stream,
                 c->d_plan, c->d_cblks, c->d_cbout, c->d_maxlen, c->d_out, c->d_body_off, c->d_pout, c->d_stat);
+    c->launches += 1;
     mark(c, EBCC_ST_BODIES);
-    EBCC_LAUNCH(k_t2_bodies, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(128), 0, c->stream,
-                c->d_plan, c->d_cblks, c->d_cbout, c->d_mq, c->d_body_off, c->d_out, c->d_pout);
-    EBCC_LAUNCH(k_offsets, dim3(1), dim3(32), 0, c->stream, c->d_pout, c->d_offs, B);
-    EBCC_LAUNCH(k_compact, dim3(8, (unsigned)B), dim3(256), 0, c->stream, c->d_out, c->d_pout, c->d_offs, c->d_packed, pl->out_stride);
-    c->launches += 6;
+    if (with_bodies) {
+        EBCC_LAUNCH(k_t2_bodies, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(128), 0, c->stream,
+                    c->d_plan, c->d_cblks, c->d_cbout, c->d_mq, c->d_body_off, c->d_out, c->d_pout);
+        EBCC_LAUNCH(k_offsets, dim3(1), dim3(32), 0, c->stream, c->d_pout, c->d_offs, B);
+        EBCC_LAUNCH(k_compact, dim3(8, (unsigned)B), dim3(256), 0, c->stream, c->d_out, c->d_pout, c->d_offs, c->d_packed, pl->out_stride);
+        c->launches += 3;
+    }
     mark(c, EBCC_ST_D2H);
     CK(cudaGetLastError());
     return 0;
 }
 
+extern "C" int ebcc_cuda_j2k_encode_resident(ebcc_cuda_ctx *c, size_t nframes, float base_cr)
+{
+    if (ebcc_cuda_analyze_resident(c, nframes)) return -1;
+    float *cr = (float *)malloc(sizeof(float) * nframes);
+    for (size_t i = 0; i < nframes; ++i) cr[i] = base_cr;
+    int rc = launch_rate_stage(c, (int)nframes, cr, 1);
+    free(cr);
+    return rc;
+}
 
 // ---- decoder back half on the resident batch: tier-1 decode -> dequant -> IDWT -> float frames ---------
 // jobs/pool describe where every code-block's MQ segment lives; if orig != NULL the error statistics of the
@@ -513,6 +600,193 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
     return 0;
 }
 
+
+// One probe of the compression-ratio search (emulate_j2k_compression, src/ebcc_codec.c:535-543) for every frame of
+// the resident batch: rate allocation at cr[i], real tier-1 decode of the truncated segments, IDWT, and the error
+// statistics against the original frame.  Synchronous; res[i] is filled for every frame.
+extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const float *cr, const float *targets,
+                                    int with_streams, ebcc_probe_result *res)
+{
+    if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
+    CK(cudaSetDevice(c->device));
+    const Plan *pl = &c->plan;
+    const int B = (int)nframes;
+    if (launch_rate_stage(c, B, cr, with_streams)) return -1;
+    for (int i = 0; i < B; ++i) c->h_targets[i] = targets[i];
+    CK(cudaMemcpyAsync(c->d_targets, c->h_targets, sizeof(float) * B, cudaMemcpyHostToDevice, c->stream));
+    const long long njobs = (long long)pl->ncblks * B;
+    EBCC_LAUNCH(k_jobs_from_enc, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cblks, c->d_cbout, c->d_jobs,
+                pl->ncblks, B);
+    c->launches++;
+    if (run_decode_stage(c, B, c->d_mq, pl->mq_stride, c->d_in)) return -1;
+    CK(cudaMemcpyAsync(c->h_es, c->d_es, sizeof(ErrStat) * B, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(c->h_pout, c->d_pout, sizeof(ProbeOut) * B, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < B; ++i) {
+        const ErrStat &e = c->h_es[i];
+        res[i].n_over = e.n_over;
+        memcpy(&res[i].max_err, &e.max_err_bits, 4);
+        unsigned k = e.rmin_key; k = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k; memcpy(&res[i].rmin, &k, 4);
+        k = e.rmax_key; k = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k; memcpy(&res[i].rmax, &k, 4);
+        res[i].sum_err = e.sum_err;
+        res[i].stream_bytes = (size_t)c->h_pout[i].stream_bytes;
+    }
+    return 0;
+}
+
+
+// ---- residual layer ------------------------------------------------------------------------------------------
+static int sp_col_cw(int ny) { int cw = 32; while ((size_t)2 * ny * cw * sizeof(float) > 160 * 1024 && cw > 1) cw >>= 1; return cw; }
+
+// SPIHT-encodes the normalised residual (original - reconstruction of the LAST rate probe) of every active frame with
+// a bit budget of trunc_bits[i] (spiht_encode, src/spiht/spiht_re.c:432-475; call site src/ebcc_codec.c:744-748).
+// The residual range is the one the last ebcc_cuda_rate_probe reported.  coeffs_size[i] receives the stream length.
+extern "C" int ebcc_cuda_residual_encode(ebcc_cuda_ctx *c, size_t nframes, const int *active, const size_t *trunc_bits, size_t *coeffs_size)
+{
+    if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
+    CK(cudaSetDevice(c->device));
+    const int B = (int)nframes;
+    const SpGeom g = c->sg;
+    const size_t Np = (size_t)g.Wp * g.Hp;
+    for (int i = 0; i < B; ++i) {
+        const ErrStat &e = c->h_es[i];
+        unsigned k = e.rmin_key; k = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k; memcpy(&c->h_sp_rmm[2 * i], &k, 4);
+        k = e.rmax_key; k = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k; memcpy(&c->h_sp_rmm[2 * i + 1], &k, 4);
+        c->h_sp_active[i] = active[i] ? 1 : 0;
+        size_t tb = trunc_bits[i];
+        if (tb + 128 + 64 > c->sp.bits_words * 32) tb = c->sp.bits_words * 32 - 192;
+        c->h_sp_budget[i] = (unsigned)tb;
+    }
+    CK(cudaMemcpyAsync(c->d_sp_rmm, c->h_sp_rmm, 8 * B, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->d_sp_active, c->h_sp_active, 4 * B, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->d_sp_budget, c->h_sp_budget, 4 * B, cudaMemcpyHostToDevice, c->stream));
+    EBCC_LAUNCH(k_sp_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_sp_info, c->d_sp_rmm, c->d_sp_budget, c->d_sp_active, B);
+    CK(cudaMemsetAsync(c->sp.sign_pos, 0, (size_t)B * Np * 4, c->stream));
+    CK(cudaMemsetAsync(c->sp.bits, 0, (size_t)B * c->sp.bits_words * 4, c->stream));
+    CK(cudaMemsetAsync(c->sp.D, 0, (size_t)B * Np * 4, c->stream));
+    CK(cudaMemsetAsync(c->sp.L, 0, (size_t)B * Np * 4, c->stream));
+    const dim3 ge(148 * 2, (unsigned)B);
+    EBCC_LAUNCH(k_sp_load, ge, dim3(256), 0, c->stream, c->d_in, c->d_dec, c->d_sp_img0, c->d_sp_info, g);
+    EBCC_LAUNCH(k_sp_subdc, ge, dim3(256), 0, c->stream, c->d_sp_img0, c->d_sp_info, g);
+    c->launches += 3;
+    for (int l = 0; l < SP_STAGES; ++l) {
+        const int nx = g.Wp >> l, ny = g.Hp >> l;
+        EBCC_LAUNCH(k_sp_dwt_row, dim3((unsigned)ny, (unsigned)B), dim3(256), (size_t)2 * nx * sizeof(float), c->stream,
+                    c->d_sp_img0, c->d_sp_img1, c->d_sp_info, g, nx);
+        const int cw = sp_col_cw(ny);
+        EBCC_LAUNCH(k_sp_dwt_col, dim3((unsigned)((nx + cw - 1) / cw), (unsigned)B), dim3((unsigned)cw, (unsigned)(512 / cw)),
+                    (size_t)2 * ny * cw * sizeof(float), c->stream, c->d_sp_img1, c->d_sp_img0, c->d_sp_info, g, nx, ny);
+        c->launches += 2;
+    }
+    EBCC_LAUNCH(k_sp_normalize, ge, dim3(256), 0, c->stream, c->d_sp_img0, c->sp.coef, c->d_sp_info, g);
+    EBCC_LAUNCH(k_sp_desc, dim3(148, (unsigned)B), dim3(256), 0, c->stream, c->sp.coef, c->sp.D, c->sp.L, c->d_sp_info, g, g.Wp / 4, g.Hp / 4, g.Wp / 2, g.Hp / 2);
+    EBCC_LAUNCH(k_sp_desc, dim3(148, (unsigned)B), dim3(256), 0, c->stream, c->sp.coef, c->sp.D, c->sp.L, c->d_sp_info, g, g.Wp / 8, g.Hp / 8, g.Wp / 4, g.Hp / 4);
+    EBCC_LAUNCH(k_sp_desc, dim3(148, (unsigned)B), dim3(256), 0, c->stream, c->sp.coef, c->sp.D, c->sp.L, c->d_sp_info, g, 0, 0, g.Wp / 8, g.Hp / 8);
+    EBCC_LAUNCH(k_sp_encode, dim3((unsigned)B), dim3(SP_THREADS), 0, c->stream, c->sp, c->d_sp_info, g, c->d_step_tab);
+    c->launches += 5;
+    CK(cudaMemcpyAsync(c->h_sp_info, c->d_sp_info, sizeof(SpInfo) * B, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaGetLastError());
+    for (int i = 0; i < B; ++i) if (active[i]) coeffs_size[i] = c->h_sp_info[i].nbytes;
+    return 0;
+}
+
+// inverse SPIHT transform of the plane in d_sp_img0 for every frame with P != 0 (idwt2full, dwt.h:305-317)
+static int sp_launch_inverse(ebcc_cuda_ctx *c, int B)
+{
+    const SpGeom g = c->sg;
+    for (int l = SP_STAGES - 1; l >= 0; --l) {
+        const int nx = g.Wp >> l, ny = g.Hp >> l;
+        const int cw = sp_col_cw(ny);
+        EBCC_LAUNCH(k_sp_idwt_col, dim3((unsigned)((nx + cw - 1) / cw), (unsigned)B), dim3((unsigned)cw, (unsigned)(512 / cw)),
+                    (size_t)2 * ny * cw * sizeof(float), c->stream, c->d_sp_img0, c->d_sp_img1, c->d_sp_P, g, nx, ny);
+        EBCC_LAUNCH(k_sp_idwt_row, dim3((unsigned)ny, (unsigned)B), dim3(256), (size_t)2 * nx * sizeof(float), c->stream,
+                    c->d_sp_img1, c->d_sp_img0, c->d_sp_P, g, nx);
+        c->launches += 2;
+    }
+    return 0;
+}
+
+// One probe of the truncation search (src/ebcc_codec.c:749-757, :775-780): what spiht_decode(buf, num_bits/8, ..., num_bits)
+// would reconstruct from the first num_bits[i] bits of frame i's stream, added to the base layer and compared with the
+// original frame.  Frames with active[i] == 0 are skipped.
+extern "C" int ebcc_cuda_residual_probe(ebcc_cuda_ctx *c, size_t nframes, const int *active, const size_t *num_bits, float *max_err, double *sum_err)
+{
+    if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
+    CK(cudaSetDevice(c->device));
+    const int B = (int)nframes;
+    const SpGeom g = c->sg;
+    for (int i = 0; i < B; ++i) {
+        unsigned P = 0;
+        if (active[i]) {
+            size_t nb = num_bits[i];
+            const size_t bits0 = (size_t)c->h_sp_budget[i] + 128;
+            if (nb > bits0) nb = bits0;
+            P = nb > 128 ? (unsigned)(nb - 128 + 1) : 1u;
+        }
+        c->h_sp_P[i] = P;
+    }
+    CK(cudaMemcpyAsync(c->d_sp_P, c->h_sp_P, 4 * B, cudaMemcpyHostToDevice, c->stream));
+    const dim3 ge(148 * 2, (unsigned)B);
+    EBCC_LAUNCH(k_sp_recon, ge, dim3(256), 0, c->stream, c->sp, c->d_sp_info, c->d_sp_P, c->d_sp_img0, g);
+    c->launches++;
+    if (sp_launch_inverse(c, B)) return -1;
+    EBCC_LAUNCH(k_errstat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_es2, B);
+    EBCC_LAUNCH(k_sp_errstat, ge, dim3(256), 0, c->stream, c->d_sp_img0, c->d_in, c->d_dec, c->d_sp_info, c->d_sp_P, c->d_es2, g);
+    c->launches += 2;
+    CK(cudaMemcpyAsync(c->h_es2, c->d_es2, sizeof(ErrStat) * B, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaGetLastError());
+    for (int i = 0; i < B; ++i) {
+        if (!active[i]) continue;
+        memcpy(&max_err[i], &c->h_es2[i].max_err_bits, 4);
+        sum_err[i] = c->h_es2[i].sum_err;
+    }
+    return 0;
+}
+
+// zstd stage (ZSTD_compress call site src/ebcc_codec.c:813-817): compresses the first coeffs_size[i] bytes of frame i's
+// SPIHT stream into a zstd frame on the device.  frames[i] points into a context-owned pinned buffer.
+extern "C" int ebcc_cuda_residual_pack(ebcc_cuda_ctx *c, size_t nframes, const size_t *coeffs_size, const uint8_t **frames, size_t *sizes)
+{
+    if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
+    CK(cudaSetDevice(c->device));
+    const int B = (int)nframes;
+    int any = 0;
+    for (int i = 0; i < B; ++i) { c->h_zsrc_len[i] = (unsigned)coeffs_size[i]; if (coeffs_size[i]) any = 1; frames[i] = NULL; sizes[i] = 0; }
+    if (!any) return 0;
+    CK(cudaMemcpyAsync(c->d_zsrc_len, c->h_zsrc_len, 4 * B, cudaMemcpyHostToDevice, c->stream));
+    EBCC_LAUNCH(k_zstd_compress, dim3((unsigned)B), dim3(ZC_THREADS), 0, c->stream, (const unsigned char *)c->sp.bits, c->sp.bits_words * 4,
+                c->d_zsrc_len, c->d_zout, c->zstride, c->d_zlen, c->d_zenc_work);
+    c->launches++;
+    CK(cudaMemcpyAsync(c->h_zlen, c->d_zlen, 4 * B, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < B; ++i)
+        if (c->h_zlen[i]) CK(cudaMemcpyAsync(c->h_zout + (size_t)i * c->zstride, c->d_zout + (size_t)i * c->zstride, c->h_zlen[i], cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaGetLastError());
+    for (int i = 0; i < B; ++i) { frames[i] = c->h_zout + (size_t)i * c->zstride; sizes[i] = c->h_zlen[i]; }
+    return 0;
+}
+
+// NONE mode: rate allocation + codestream assembly only
+extern "C" int ebcc_cuda_rate_probe_streams_only(ebcc_cuda_ctx *c, size_t nframes, const float *cr)
+{
+    if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
+    CK(cudaSetDevice(c->device));
+    return launch_rate_stage(c, (int)nframes, cr, 1);
+}
+
+extern "C" int ebcc_cuda_frame_stats(ebcc_cuda_ctx *c, size_t nframes, float *minv, float *maxv, int *flags)
+{
+    if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemcpyAsync(c->h_stat, c->d_stat, sizeof(FrameStat) * nframes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    for (size_t i = 0; i < nframes; ++i) { minv[i] = c->h_stat[i].minv; maxv[i] = c->h_stat[i].maxv; flags[i] = c->h_stat[i].flags; }
+    return 0;
+}
+
 __global__ void k_set_stat(FrameStat *stat, const float *mm, int n)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -524,8 +798,14 @@ extern "C" int ebcc_cuda_decode_batch(ebcc_cuda_ctx *c, const uint8_t *const *st
                                       float *const *outs)
 {
     if (ebcc_cuda_reserve(c, H, W, nframes)) return -1;
+    int any_res = 0;
     for (size_t i = 0; res && i < nframes; ++i)
-        if (res[i].zstd_size) { fprintf(stderr, "[ebcc-cuda] residual layer decode not implemented yet\n"); return -1; }
+        if (res[i].zstd_size) {
+            any_res = 1;
+            if (res[i].zstd_size + 16 > c->zstride || res[i].coeffs_size + 16 > c->sp.bits_words * 4) {
+                fprintf(stderr, "[ebcc-cuda] residual payload of frame %zu too large\n", i); return -1;
+            }
+        }
     const Plan *pl = &c->plan;
     const int B = (int)nframes;
     const size_t N = H * W;
@@ -547,12 +827,48 @@ extern "C" int ebcc_cuda_decode_batch(ebcc_cuda_ctx *c, const uint8_t *const *st
                 c->d_plan, c->d_cblks, c->d_streams, pl->out_stride, c->d_slens, c->d_jobs, c->d_status);
     c->launches += 2;
     if (run_decode_stage(c, B, c->d_streams, pl->out_stride, NULL)) return -1;
+    if (any_res) {
+        // residual layer: zstd frame -> SPIHT stream -> coefficient plane -> inverse transform -> add (src/ebcc_codec.c:1294-1312)
+        const SpGeom g = c->sg;
+        for (int i = 0; i < B; ++i) {
+            const int on = res[i].zstd_size != 0;
+            c->h_sp_active[i] = on; c->h_sp_budget[i] = 0; c->h_sp_P[i] = on ? 1u : 0u;
+            c->h_sp_rmm[2 * i] = res[i].rmin; c->h_sp_rmm[2 * i + 1] = res[i].rmax;
+            c->h_zsrc_len[i] = (unsigned)res[i].zstd_size; c->h_zcap[i] = (unsigned)res[i].coeffs_size;
+            if (on) {
+                memcpy(c->h_zin + (size_t)i * c->zstride, res[i].zstd, res[i].zstd_size);
+                CK(cudaMemcpyAsync(c->d_zin + (size_t)i * c->zstride, c->h_zin + (size_t)i * c->zstride, res[i].zstd_size, cudaMemcpyHostToDevice, c->stream));
+            }
+        }
+        CK(cudaMemcpyAsync(c->d_sp_rmm, c->h_sp_rmm, 8 * B, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->d_sp_active, c->h_sp_active, 4 * B, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->d_sp_budget, c->h_sp_budget, 4 * B, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->d_sp_P, c->h_sp_P, 4 * B, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->d_zsrc_len, c->h_zsrc_len, 4 * B, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->d_zcap, c->h_zcap, 4 * B, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemsetAsync(c->sp.bits, 0, (size_t)B * c->sp.bits_words * 4, c->stream));
+        EBCC_LAUNCH(k_sp_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_sp_info, c->d_sp_rmm, c->d_sp_budget, c->d_sp_active, B);
+        EBCC_LAUNCH(k_zstd_decompress, dim3((unsigned)B), dim3(32), 0, c->stream, c->d_zin, c->zstride, c->d_zsrc_len, (unsigned char *)c->sp.bits,
+                    c->sp.bits_words * 4, c->d_zcap, c->d_zlen, c->d_zdec_work);
+        EBCC_LAUNCH(k_sp_decode, dim3((unsigned)B), dim3(32), 0, c->stream, (const unsigned char *)c->sp.bits, c->sp.bits_words * 4, (const int *)c->d_zcap, c->sp,
+                    c->d_sp_info, c->d_sp_img0, g, c->d_maxlen);
+        c->launches += 3;
+        if (sp_launch_inverse(c, B)) return -1;
+        EBCC_LAUNCH(k_sp_add_residual, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_sp_img0, c->d_dec, c->d_sp_info, g);
+        c->launches++;
+        CK(cudaMemcpyAsync(c->h_zlen, c->d_zlen, 4 * B, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaMemcpyAsync(c->h_maxlen, c->d_maxlen, 4 * B, cudaMemcpyDeviceToHost, c->stream));
+    }
     CK(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
     for (int i = 0; i < B; ++i)
         CK(cudaMemcpyAsync(outs[i], c->d_dec + (size_t)i * N, N * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     int bad = 0;
     for (int i = 0; i < B; ++i) if (c->h_status[i] != PARSE_OK) { fprintf(stderr, "[ebcc-cuda] malformed JPEG 2000 codestream in frame %d\n", i); bad = 1; }
+    for (int i = 0; any_res && i < B; ++i)
+        if (res[i].zstd_size && (c->h_zlen[i] == 0xffffffffu || c->h_maxlen[i] != 0)) {
+            fprintf(stderr, "[ebcc-cuda] malformed residual layer (%s) in frame %d\n", c->h_zlen[i] == 0xffffffffu ? "zstd frame" : "SPIHT header", i); bad = 1;
+        }
     return bad ? -2 : 0;
 }
 
@@ -625,6 +941,18 @@ extern "C" int ebcc_cuda_debug_cblk(ebcc_cuda_ctx *c, size_t frame, size_t cblk,
     CK(cudaMemcpy(&o, c->d_cbout + frame * c->plan.ncblks + cblk, sizeof(o), cudaMemcpyDeviceToHost));
     *numbps = o.numbps; *totalpasses = o.totalpasses; *numpasses = o.numpasses;
     for (int i = 0; i < o.totalpasses && i < J2K_MAXPASSES; ++i) { rates[i] = o.rate[i]; dists[i] = o.dist[i]; }
+    return 0;
+}
+
+// test tap: SPIHT bitstream of a frame after ebcc_cuda_residual_encode
+extern "C" int ebcc_cuda_debug_spiht_stream(ebcc_cuda_ctx *c, size_t frame, uint8_t *dst, size_t cap, size_t *len)
+{
+    if (!c || frame >= c->cap_frames) return -1;
+    CK(cudaStreamSynchronize(c->stream));
+    const size_t n = c->h_sp_info[frame].nbytes;
+    *len = n;
+    if (n > cap) return -1;
+    CK(cudaMemcpy(dst, (const unsigned char *)c->sp.bits + frame * c->sp.bits_words * 4, n, cudaMemcpyDeviceToHost));
     return 0;
 }
 

@@ -44,6 +44,33 @@ int ebcc_cuda_upload(ebcc_cuda_ctx *ctx, const float *frames, size_t nframes);
  * base_cr is EBCC's compression ratio (OpenJPEG rate = base_cr / 2).  Asynchronous. */
 int ebcc_cuda_j2k_encode_resident(ebcc_cuda_ctx *ctx, size_t nframes, float base_cr);
 
+/* The encoder in two stages, for the compression-ratio search of MAX_ERROR / RELATIVE_ERROR
+ * (error_bound_j2k_compression, src/ebcc_codec.c:545-596): analyze = everything independent of the ratio
+ * (min/max, scaling, DWT, tier-1), run once; rate_probe = PCRD + tier-2 at cr[i] for frame i followed by a
+ * real decode of the truncated code-block segments and the error statistics against the original frame
+ * (emulate_j2k_compression + get_error_target_quantile / get_max_error / get_mean_error / findMinMaxf on the
+ * residual, src/ebcc_codec.c:464-543).  with_streams != 0 also assembles the codestreams for ebcc_cuda_download. */
+typedef struct {
+    unsigned long long n_over;   /* samples with |d - decoded| > targets[i] */
+    float max_err;               /* max |d - decoded| */
+    float rmin, rmax;            /* min / max of d - decoded */
+    double sum_err;              /* sum of (d - decoded), double accumulation */
+    size_t stream_bytes;         /* codestream length at this ratio */
+} ebcc_probe_result;
+int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *ctx, size_t nframes);
+int ebcc_cuda_rate_probe(ebcc_cuda_ctx *ctx, size_t nframes, const float *cr, const float *targets, int with_streams,
+                         ebcc_probe_result *res);
+
+int ebcc_cuda_rate_probe_streams_only(ebcc_cuda_ctx *ctx, size_t nframes, const float *cr);
+int ebcc_cuda_frame_stats(ebcc_cuda_ctx *ctx, size_t nframes, float *minv, float *maxv, int *flags);
+
+/* Residual layer on the resident batch (src/ebcc_codec.c:744-817): SPIHT encode of the normalised residual of the
+ * last rate probe with a bit budget (spiht_encode), probes of the truncation search (spiht_decode of a prefix +
+ * get_max_error / get_mean_error), and the zstd stage.  active[i] == 0 skips frame i. */
+int ebcc_cuda_residual_encode(ebcc_cuda_ctx *ctx, size_t nframes, const int *active, const size_t *trunc_bits, size_t *coeffs_size);
+int ebcc_cuda_residual_probe(ebcc_cuda_ctx *ctx, size_t nframes, const int *active, const size_t *num_bits, float *max_err, double *sum_err);
+int ebcc_cuda_residual_pack(ebcc_cuda_ctx *ctx, size_t nframes, const size_t *coeffs_size, const uint8_t **frames, size_t *sizes);
+
 /* device -> host: waits for the pass, then returns per-frame codestream sizes, min, max, flags;
  * streams[i] receives a pointer into a context-owned pinned buffer valid until the next call */
 int ebcc_cuda_download(ebcc_cuda_ctx *ctx, size_t nframes, const uint8_t **streams, size_t *sizes,
@@ -85,6 +112,7 @@ int ebcc_cuda_bench_resident(ebcc_cuda_ctx *ctx, size_t nframes, float base_cr, 
 
 /* debug/test taps on the resident batch (device -> host copies of intermediates) */
 int ebcc_cuda_debug_coef(ebcc_cuda_ctx *ctx, size_t frame, float *dst);
+int ebcc_cuda_debug_spiht_stream(ebcc_cuda_ctx *ctx, size_t frame, uint8_t *dst, size_t cap, size_t *len);
 int ebcc_cuda_debug_cblk(ebcc_cuda_ctx *ctx, size_t frame, size_t cblk, int *numbps, int *totalpasses,
                          int *rates, double *dists, int *numpasses);
 
