@@ -204,6 +204,34 @@ def run_ours(args):
     e2e_s = time.perf_counter() - t0
     barrier(dist)
     e2e_s = allreduce_max(dist, local, e2e_s)
+    # ---- other rows of the path through the same C ABI (reported, not the headline): decode, error-bounded modes ----
+    modes = {}
+    if world == 1:
+        lib.ebcc_decode_batch.restype = C.c_size_t
+
+        def time_mode(mode, err, label):
+            c2 = H.CodecConfig(); c2.dims[:] = [1, HH, WW]; c2.base_cr = BASE_CR; c2.mode = mode; c2.error = err
+            best_e = best_d = 1e9
+            for _ in range(2):
+                t0 = time.perf_counter()
+                n = lib.ebcc_encode_batch(frames.ctypes.data_as(C.c_void_p), C.c_size_t(FRAMES), C.byref(c2), outs, osz)
+                best_e = min(best_e, time.perf_counter() - t0)
+                assert n == FRAMES
+                ptrs = (C.c_void_p * FRAMES)(*[C.cast(outs[i], C.c_void_p).value for i in range(FRAMES)])
+                douts, cnts = (C.POINTER(C.c_float) * FRAMES)(), (C.c_size_t * FRAMES)()
+                t0 = time.perf_counter()
+                n = lib.ebcc_decode_batch(ptrs, osz, C.c_size_t(FRAMES), douts, cnts)
+                best_d = min(best_d, time.perf_counter() - t0)
+                assert n == FRAMES
+                worst = max(float(np.abs(np.ctypeslib.as_array(douts[i], shape=(cnts[i],)) - frames[i].ravel()).max()) for i in range(FRAMES))
+                tot = sum(osz)
+                for i in range(FRAMES):
+                    lib.free_buffer(outs[i]); lib.free_buffer(douts[i])
+            modes[label] = {"compress_GBps_e2e": in_bytes / best_e / 1e9, "decompress_GBps_e2e": in_bytes / best_d / 1e9,
+                            "cr": in_bytes / tot, "max_abs_err": worst}
+        time_mode(H.NONE, 0.0, "none")
+        time_mode(H.MAX_ERROR, 0.5, "max_error_0.5")
+        time_mode(H.MAX_ERROR, 0.1, "max_error_0.1")
     sampler.stop_flag = True; sampler.join(timeout=2)
 
     if rank != 0:
@@ -231,6 +259,7 @@ def run_ours(args):
         "e2e": {"value": e2e, "unit": "GB/s", "h2d_bytes_per_step": int(in_bytes), "d2h_bytes_per_step": int(d2h)},
         "gpu_launches": int(launches),
         "stage_ms": stage,
+        "modes": modes,
         "roofline": {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None,
                      "note": "tier-1 is integer-issue/latency bound; the HBM fraction is reported for completeness"},

@@ -171,6 +171,14 @@ static size_t assemble_frame(const frame_parts_t *p, uint8_t **out)
     return out_size;
 }
 
+/* ---- optional wall-clock breakdown of the device calls (EBCC_PROFILE=1), printed to stderr ---------- */
+#include <time.h>
+enum { TM_ANALYZE, TM_PROBE, TM_RESID_ENC, TM_RESID_PROBE, TM_PACK, TM_DOWNLOAD, TM_COUNT };
+static const char *const k_tm_names[TM_COUNT] = {"upload+analyze", "rate probes", "spiht encode", "spiht probes", "zstd pack", "download"};
+static double g_tm[TM_COUNT]; static int g_tm_calls[TM_COUNT]; static int g_profile = 0;
+static double now_ms(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return t.tv_sec * 1e3 + t.tv_nsec * 1e-6; }
+#define TIMED(slot, expr) ({ double t0_ = g_profile ? now_ms() : 0; int r_ = (expr); if (g_profile) { g_tm[slot] += now_ms() - t0_; g_tm_calls[slot]++; } r_; })
+
 /* ---- compression-ratio search: error_bound_j2k_compression (reference src/ebcc_codec.c:545-596) as a
  * resumable state machine, so that a whole batch of frames advances in lock step, one device probe
  * (ebcc_cuda_rate_probe) per round.  Pure control flow over the quantiles the device returns. */
@@ -251,7 +259,7 @@ static int search_batch(ebcc_cuda_ctx *ctx, size_t nb, const int *run, const flo
         }
         if (!any_dev) { if (!any) break; else continue; }
         for (size_t i = 0; i < nb; ++i) if (need[i]) last_cr[i] = st[i].pending;
-        if (ebcc_cuda_rate_probe(ctx, nb, last_cr, err_target, 0, pr)) { rc = -1; break; }
+        if (TIMED(TM_PROBE, ebcc_cuda_rate_probe(ctx, nb, last_cr, err_target, 0, pr))) { rc = -1; break; }
         for (size_t i = 0; i < nb; ++i) {
             if (!need[i]) continue;
             memo_put(&memo[i], st[i].pending, pr[i].n_over);
@@ -299,7 +307,10 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
            *best_trunc = (double *)calloc(nb, sizeof(double));
     int *use_pure = (int *)calloc(nb, sizeof(int));
 
-    if (ebcc_cuda_reserve(ctx, H, W, nb) || ebcc_cuda_upload(ctx, frames, nb) || ebcc_cuda_analyze_resident(ctx, nb)) goto out;
+    g_profile = getenv("EBCC_PROFILE") != NULL;
+    if (g_profile) { memset(g_tm, 0, sizeof(g_tm)); memset(g_tm_calls, 0, sizeof(g_tm_calls)); }
+    if (ebcc_cuda_reserve(ctx, H, W, nb)) goto out;
+    if (TIMED(TM_ANALYZE, ebcc_cuda_upload(ctx, frames, nb) || ebcc_cuda_analyze_resident(ctx, nb) || ebcc_cuda_sync(ctx))) goto out;
     for (size_t i = 0; i < nb; ++i) { cr[i] = config->base_cr; tgt[i] = 0; }
 
     if (mode == NONE) {
@@ -312,7 +323,7 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
             if (mode == RELATIVE_ERROR) t *= (mx[i] - mn[i]);       /* get_data_range, reference :724-726 */
             tgt[i] = t;
         }
-        if (ebcc_cuda_rate_probe(ctx, nb, cr, tgt, 0, p0)) goto out;
+        if (TIMED(TM_PROBE, ebcc_cuda_rate_probe(ctx, nb, cr, tgt, 0, p0))) goto out;
         for (size_t i = 0; i < nb; ++i) {
             run[i] = !(fl[i] & (EBCC_FRAME_CONST | EBCC_FRAME_NANINF));
             memo_put(&memo[i], cr[i], p0[i].n_over);
@@ -321,9 +332,9 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
             mean[i] = p0[i].sum_err / N;                            /* get_mean_error after the first decode, :709 */
         }
         if (search_batch(ctx, nb, run, start, q0, base_quantile_target, tgt, N, memo, cr1, cr)) goto out;
-        if (ebcc_cuda_rate_probe(ctx, nb, cr1, tgt, 1, p1)) goto out;
+        if (TIMED(TM_PROBE, ebcc_cuda_rate_probe(ctx, nb, cr1, tgt, 1, p1))) goto out;
     }
-    if (ebcc_cuda_download(ctx, nb, streams, ssz, mn, mx, fl)) goto out;
+    if (TIMED(TM_DOWNLOAD, ebcc_cuda_download(ctx, nb, streams, ssz, mn, mx, fl))) goto out;
     for (size_t i = 0; i < nb; ++i) {
         if (fl[i] & EBCC_FRAME_NANINF) {
             /* reference check_nan_inf: log_fatal + exit(1) (src/ebcc_codec.c:598-605) */
@@ -349,9 +360,9 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
         }
         if (any_resid) {
             /* SPIHT encode of the normalised residual + full decode check (reference :744-763) */
-            if (ebcc_cuda_residual_encode(ctx, nb, resid, tb, coeffs_size)) goto out;
+            if (TIMED(TM_RESID_ENC, ebcc_cuda_residual_encode(ctx, nb, resid, tb, coeffs_size))) goto out;
             for (size_t i = 0; i < nb; ++i) tb[i] = coeffs_size[i] * 8;
-            if (ebcc_cuda_residual_probe(ctx, nb, resid, tb, perr, psum)) goto out;
+            if (TIMED(TM_RESID_PROBE, ebcc_cuda_residual_probe(ctx, nb, resid, tb, perr, psum))) goto out;
             for (size_t i = 0; i < nb; ++i) {
                 if (!resid[i]) continue;
                 if (perr[i] > tgt[i]) {
@@ -376,7 +387,7 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
                 if (!any) break;
                 int *act = (int *)calloc(nb, sizeof(int));
                 for (size_t i = 0; i < nb; ++i) act[i] = tb[i] != 0;
-                int prc = ebcc_cuda_residual_probe(ctx, nb, act, tb, perr, psum);
+                int prc = TIMED(TM_RESID_PROBE, ebcc_cuda_residual_probe(ctx, nb, act, tb, perr, psum));
                 free(act);
                 if (prc) goto out;
                 for (size_t i = 0; i < nb; ++i) {
@@ -395,7 +406,7 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
                 if (!resid[i]) coeffs_size[i] = 0;
             }
             /* zstd stage on the device (reference :813-817) */
-            if (ebcc_cuda_residual_pack(ctx, nb, coeffs_size, zs, zn)) goto out;
+            if (TIMED(TM_PACK, ebcc_cuda_residual_pack(ctx, nb, coeffs_size, zs, zn))) goto out;
             for (size_t i = 0; i < nb; ++i) {
                 if (!zn[i]) continue;
                 zcopy[i] = (uint8_t *)malloc(zn[i]);
@@ -411,8 +422,8 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
                 q0[i] = 1. - ((double)n / N);
             }
             if (search_batch(ctx, nb, run, start, q0, 1.0, tgt, N, memo, cr2, cr)) goto out;
-            if (ebcc_cuda_rate_probe(ctx, nb, cr2, tgt, 1, p2)) goto out;
-            if (ebcc_cuda_download(ctx, nb, streams, ssz, NULL, NULL, NULL)) goto out;
+            if (TIMED(TM_PROBE, ebcc_cuda_rate_probe(ctx, nb, cr2, tgt, 1, p2))) goto out;
+            if (TIMED(TM_DOWNLOAD, ebcc_cuda_download(ctx, nb, streams, ssz, NULL, NULL, NULL))) goto out;
             for (size_t i = 0; i < nb; ++i) {
                 if (!run[i]) continue;
                 if (ssz[i] < zn[i] + len1[i] || pure_required[i]) {
@@ -451,6 +462,11 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
         }
     }
     rc = 0;
+    if (g_profile) {
+        fprintf(stderr, "[ebcc profile] %lu frames:", nb);
+        for (int k = 0; k < TM_COUNT; ++k) fprintf(stderr, " %s %.1f ms/%d;", k_tm_names[k], g_tm[k], g_tm_calls[k]);
+        fputc('\n', stderr);
+    }
 out:
     for (size_t i = 0; i < nb; ++i) { free(j2k1[i]); free(zcopy[i]); }
     free(streams); free(ssz); free(mn); free(mx); free(fl); free(cr); free(cr1); free(cr2); free(tgt); free(start); free(q0); free(mean);

@@ -408,7 +408,9 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
     const int warp_global = (blockIdx.x * MQ_THREADS + tid) >> 5;
     const long long job = (long long)warp_global * lanes + lane;
     if (lane >= lanes || job >= (long long)ncblks * nframes) return;
-    const int frame = (int)(job / ncblks), cbi = (int)(job - (long long)frame * ncblks);
+    // frame varies fastest: the lanes of a warp code the same code-block position of different frames, whose
+    // symbol counts are similar, so a warp's lanes finish together
+    const int cbi = (int)(job / nframes), frame = (int)(job - (long long)cbi * nframes);
     const CblkDesc cb = cblks[cbi];
     CblkOut *out = cbout + (size_t)frame * ncblks + cbi;
     const int npasses = out->totalpasses;
