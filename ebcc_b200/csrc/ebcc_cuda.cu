@@ -246,7 +246,11 @@ struct ebcc_cuda_ctx {
     unsigned char *d_streams;  // [B][out_stride] codestreams to decode
     int *d_slens, *d_status;
     DecJob *d_jobs;            // [B][ncblks]
-    int *d_iplane;             // [B][H][W] tier-1 decoder output (integer, Mallat layout)
+    int *d_iplane;             // [B][H][W] tier-1 decoder output (integer, Mallat layout); the recording of the CR search
+    int *d_scratch;            // [B][H][W] per-probe real decodes of blocks the recording cannot serve
+    unsigned char *d_spass;    // [B][H][W] pass in which each sample became significant (recording)
+    DecState *d_dstate;        // [B][ncblks]
+    int use_recording;
     float *d_dcoef;            // [B][H][W] dequantised coefficients / IDWT work plane
     float *d_dec;              // [B][H][W] decoded frames
     ErrStat *d_es;
@@ -269,6 +273,9 @@ struct ebcc_cuda_ctx {
     unsigned *d_zlen, *h_zlen, *d_zsrc_len, *h_zsrc_len;
     unsigned char *d_zin, *h_zin;   // [B][zstride] zstd frames to decode (decode path)
     ZEncWork *d_zenc_work;
+    unsigned char *d_zblk;
+    unsigned *d_zblen;
+    int zmaxchunks;
     ZDecWork *d_zdec_work;
     unsigned *d_zcap, *h_zcap;
     // pinned host mirrors
@@ -334,7 +341,8 @@ static void free_buffers(ebcc_cuda_ctx *c)
     cudaFree(c->d_maxlen); cudaFree(c->d_body_off); cudaFree(c->d_pout); cudaFree(c->d_offs);
     cudaFreeHost(c->h_pout); cudaFreeHost(c->h_stat); cudaFreeHost(c->h_offs); cudaFreeHost(c->h_maxlen);
     cudaFreeHost(c->h_packed); cudaFreeHost(c->h_stage);
-    cudaFree(c->d_streams); cudaFree(c->d_slens); cudaFree(c->d_status); cudaFree(c->d_jobs); cudaFree(c->d_iplane);
+    cudaFree(c->d_streams); cudaFree(c->d_slens); cudaFree(c->d_status); cudaFree(c->d_jobs); cudaFree(c->d_iplane); cudaFree(c->d_scratch); cudaFree(c->d_spass); cudaFree(c->d_dstate);
+    c->d_scratch = NULL; c->d_spass = NULL; c->d_dstate = NULL;
     cudaFree(c->d_dcoef); cudaFree(c->d_dec); cudaFree(c->d_es); cudaFree(c->d_targets);
     cudaFreeHost(c->h_es); cudaFreeHost(c->h_status); cudaFreeHost(c->h_slens); cudaFreeHost(c->h_targets); cudaFreeHost(c->h_streams);
     c->d_streams = NULL; c->d_slens = c->d_status = NULL; c->d_jobs = NULL; c->d_iplane = NULL; c->d_dcoef = c->d_dec = NULL;
@@ -343,7 +351,7 @@ static void free_buffers(ebcc_cuda_ctx *c)
     cudaFree(c->sp.lis0); cudaFree(c->sp.lis1); cudaFree(c->sp.sign_pos); cudaFree(c->sp.lsp_idx); cudaFree(c->sp.bits);
     cudaFree(c->d_sp_img0); cudaFree(c->d_sp_img1); cudaFree(c->d_sp_info); cudaFree(c->d_sp_P); cudaFree(c->d_sp_budget);
     cudaFree(c->d_sp_active); cudaFree(c->d_sp_rmm); cudaFree(c->d_es2); cudaFree(c->d_zout); cudaFree(c->d_zlen); cudaFree(c->d_zsrc_len);
-    cudaFree(c->d_zin); cudaFree(c->d_zenc_work); cudaFree(c->d_zdec_work); cudaFree(c->d_zcap); cudaFreeHost(c->h_zcap);
+    cudaFree(c->d_zin); cudaFree(c->d_zenc_work); cudaFree(c->d_zblk); cudaFree(c->d_zblen); c->d_zblk = NULL; c->d_zblen = NULL; cudaFree(c->d_zdec_work); cudaFree(c->d_zcap); cudaFreeHost(c->h_zcap);
     c->d_zenc_work = NULL; c->d_zdec_work = NULL; c->d_zcap = NULL; c->h_zcap = NULL;
     cudaFreeHost(c->h_sp_info); cudaFreeHost(c->h_sp_P); cudaFreeHost(c->h_sp_budget); cudaFreeHost(c->h_sp_active);
     cudaFreeHost(c->h_sp_rmm); cudaFreeHost(c->h_es2); cudaFreeHost(c->h_zout); cudaFreeHost(c->h_zlen); cudaFreeHost(c->h_zsrc_len);
@@ -409,6 +417,9 @@ extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nf
     CK(cudaMalloc((void **)&c->d_status, B * sizeof(int)));
     CK(cudaMalloc((void **)&c->d_jobs, B * pl->ncblks * sizeof(DecJob)));
     CK(cudaMalloc((void **)&c->d_iplane, B * N * sizeof(int)));
+    CK(cudaMalloc((void **)&c->d_scratch, B * N * sizeof(int)));
+    CK(cudaMalloc((void **)&c->d_spass, B * N));
+    CK(cudaMalloc((void **)&c->d_dstate, B * pl->ncblks * sizeof(DecState)));
     CK(cudaMalloc((void **)&c->d_dcoef, B * N * sizeof(float)));
     CK(cudaMalloc((void **)&c->d_dec, B * N * sizeof(float)));
     CK(cudaMalloc((void **)&c->d_es, B * sizeof(ErrStat)));
@@ -434,7 +445,9 @@ extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nf
         CK(cudaMalloc((void **)&c->d_sp_active, B * 4)); CK(cudaMalloc((void **)&c->d_sp_rmm, B * 8)); CK(cudaMalloc((void **)&c->d_es2, B * sizeof(ErrStat)));
         CK(cudaMalloc((void **)&c->d_zout, B * c->zstride)); CK(cudaMalloc((void **)&c->d_zlen, B * 4)); CK(cudaMalloc((void **)&c->d_zsrc_len, B * 4));
         CK(cudaMalloc((void **)&c->d_zin, B * c->zstride));
-        CK(cudaMalloc((void **)&c->d_zenc_work, B * sizeof(ZEncWork))); CK(cudaMalloc((void **)&c->d_zdec_work, B * sizeof(ZDecWork)));
+        c->zmaxchunks = (int)((c->sp.bits_words * 4 + Z_CHUNK - 1) / Z_CHUNK);
+        CK(cudaMalloc((void **)&c->d_zenc_work, B * c->zmaxchunks * sizeof(ZEncWork)));
+        CK(cudaMalloc((void **)&c->d_zblk, B * c->zmaxchunks * (size_t)Z_BLK_STRIDE)); CK(cudaMalloc((void **)&c->d_zblen, B * c->zmaxchunks * 4)); CK(cudaMalloc((void **)&c->d_zdec_work, B * sizeof(ZDecWork)));
         CK(cudaMalloc((void **)&c->d_zcap, B * 4)); CK(cudaMallocHost((void **)&c->h_zcap, B * 4));
         CK(cudaMallocHost((void **)&c->h_sp_info, B * sizeof(SpInfo))); CK(cudaMallocHost((void **)&c->h_sp_P, B * 4)); CK(cudaMallocHost((void **)&c->h_sp_budget, B * 4));
         CK(cudaMallocHost((void **)&c->h_sp_active, B * 4)); CK(cudaMallocHost((void **)&c->h_sp_rmm, B * 8)); CK(cudaMallocHost((void **)&c->h_es2, B * sizeof(ErrStat)));
@@ -506,6 +519,13 @@ extern "C" int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *c, size_t nframes)
     CK(cudaSetDevice(c->device));
     const Plan *pl = &c->plan;
     const int B = (int)nframes, N = pl->H * pl->W;
+    {
+        const char *nr = getenv("EBCC_NO_RECORDING");   // debugging aid: every probe decodes every block for real
+        c->use_recording = !(nr && nr[0] == '1');
+        const long long nb = (long long)pl->ncblks * B;
+        EBCC_LAUNCH(k_dstate_reset, dim3((unsigned)((nb + 255) / 256)), dim3(256), 0, c->stream, c->d_dstate, nb);
+        c->launches++;
+    }
     mark(c, EBCC_ST_MINMAX);
     EBCC_LAUNCH(k_stat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_stat, B);
     EBCC_LAUNCH(k_minmax, dim3(74, (unsigned)B), dim3(256), 0, c->stream, c->d_in, c->d_stat, N);
@@ -574,11 +594,16 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
 {
     const Plan *pl = &c->plan;
     const int W = pl->W, H = pl->H, N = W * H;
-    CK(cudaMemsetAsync(c->d_iplane, 0, (size_t)B * N * sizeof(int), c->stream));
     const long long njobs = (long long)pl->ncblks * B;
+    const bool probe = orig != NULL;         // probe of the CR search: jobs come from the encoder, the recording is used
     EBCC_LAUNCH(k_t1_dec, dim3((unsigned)((njobs + DEC_WARPS - 1) / DEC_WARPS)), dim3(DEC_WARPS * 32), 0, c->stream,
-                c->d_cblks, c->d_jobs, pool, pool_stride, c->d_declut, c->d_iplane, W, H, pl->ncblks, B);
-    EBCC_LAUNCH(k_dequant, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_iplane, c->d_dcoef, c->d_plan, B);
+                c->d_cblks, c->d_jobs, pool, pool_stride, c->d_declut, c->d_iplane, probe ? c->d_spass : (unsigned char *)NULL, c->d_scratch,
+                probe ? (const CblkOut *)c->d_cbout : (const CblkOut *)NULL, probe ? c->d_dstate : (DecState *)NULL, W, H, pl->ncblks, B);
+    if (probe)
+        EBCC_LAUNCH(k_recon_dequant, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_plan, c->d_cbout, c->d_dstate, c->d_jobs,
+                    c->d_iplane, c->d_spass, c->d_scratch, c->d_dcoef);
+    else
+        EBCC_LAUNCH(k_dequant, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_iplane, c->d_dcoef, c->d_plan, B);
     c->launches += 2;
     for (int r = 1; r < J2K_NRES; ++r) {
         const int rw = pl->res_w[r], rh = pl->res_h[r];
@@ -615,8 +640,8 @@ extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const floa
     for (int i = 0; i < B; ++i) c->h_targets[i] = targets[i];
     CK(cudaMemcpyAsync(c->d_targets, c->h_targets, sizeof(float) * B, cudaMemcpyHostToDevice, c->stream));
     const long long njobs = (long long)pl->ncblks * B;
-    EBCC_LAUNCH(k_jobs_from_enc, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cblks, c->d_cbout, c->d_jobs,
-                pl->ncblks, B);
+    EBCC_LAUNCH(k_jobs_from_enc, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cblks, c->d_cbout, c->d_dstate, c->d_jobs,
+                pl->ncblks, B, c->use_recording);
     c->launches++;
     if (run_decode_stage(c, B, c->d_mq, pl->mq_stride, c->d_in)) return -1;
     CK(cudaMemcpyAsync(c->h_es, c->d_es, sizeof(ErrStat) * B, cudaMemcpyDeviceToHost, c->stream));
@@ -756,8 +781,14 @@ extern "C" int ebcc_cuda_residual_pack(ebcc_cuda_ctx *c, size_t nframes, const s
     for (int i = 0; i < B; ++i) { c->h_zsrc_len[i] = (unsigned)coeffs_size[i]; if (coeffs_size[i]) any = 1; frames[i] = NULL; sizes[i] = 0; }
     if (!any) return 0;
     CK(cudaMemcpyAsync(c->d_zsrc_len, c->h_zsrc_len, 4 * B, cudaMemcpyHostToDevice, c->stream));
-    EBCC_LAUNCH(k_zstd_compress, dim3((unsigned)B), dim3(ZC_THREADS), 0, c->stream, (const unsigned char *)c->sp.bits, c->sp.bits_words * 4,
-                c->d_zsrc_len, c->d_zout, c->zstride, c->d_zlen, c->d_zenc_work);
+    size_t maxn = 0;
+    for (int i = 0; i < B; ++i) if (coeffs_size[i] > maxn) maxn = coeffs_size[i];
+    const int nch = (int)((maxn + Z_CHUNK - 1) / Z_CHUNK);
+    EBCC_LAUNCH(k_zstd_compress_chunks, dim3((unsigned)nch, (unsigned)B), dim3(ZC_THREADS), 0, c->stream, (const unsigned char *)c->sp.bits,
+                c->sp.bits_words * 4, c->d_zsrc_len, c->d_zblk, c->d_zblen, c->zmaxchunks, c->d_zenc_work);
+    EBCC_LAUNCH(k_zstd_assemble, dim3((unsigned)B), dim3(256), 0, c->stream, c->d_zblk, c->d_zblen, c->zmaxchunks, c->d_zsrc_len, c->d_zout,
+                c->zstride, c->d_zlen);
+    c->launches++;
     c->launches++;
     CK(cudaMemcpyAsync(c->h_zlen, c->d_zlen, 4 * B, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));

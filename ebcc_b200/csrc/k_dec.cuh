@@ -17,7 +17,14 @@
 #include "k_t1.cuh"
 #include "k_t2.cuh"
 
-struct DecJob { int np; int numbps; unsigned off; int len; };
+// mode: 0 = nothing to do, 1 = decode into the recording plane (iplane + pass-of-significance plane),
+//       2 = decode into the scratch plane (a truncation the recording cannot reproduce, see DecState)
+struct DecJob { int np; int numbps; unsigned off; int len; int mode; int pad; };
+
+// What the recording of a block holds (compression-ratio search): np_dec passes were decoded; bit p of bad[] is set
+// when "decode only passes 0..p from the segment truncated at rate[p]" is NOT proven identical to the first p+1
+// passes of the recorded decode (OPJ truncates non-terminated MQ segments at numbytes+3, which is not always enough).
+struct DecState { int np_dec; int pad; unsigned bad[4]; };
 
 // decoder-side LUTs: zero-coding context by (orient, 9-bit neighbourhood), filled by the host with
 // the same Annex-D rule the encoder evaluates arithmetically (t1_zc_ctx)
@@ -29,6 +36,7 @@ struct DecLuts {
 #define DEC_FW 66
 #define DEC_FWORDS (18 * DEC_FW)
 #define DEC_WARPS 4
+#define DEC_NSHADOW 3
 
 // flag word of one stripe column: bits 0-17 significance of the 3x6 neighbourhood
 // (bit (r+1)*3 + (dx+1), r = -1..4, dx = -1..1), bits 18-23 sign of own column rows -1..4,
@@ -39,64 +47,113 @@ struct DecLuts {
 #define DF_PI(ci) (1u << (24 + (ci)))
 #define DF_MU(ci) (1u << (28 + (ci)))
 
-struct MqDec {
-    unsigned a, c, ct;
-    int bp, len;
-    unsigned cur;                  // byte at bp
-    const unsigned char *data;
-};
+// byte-consuming half of the MQ decoder (C register, bit counter, read position) over a segment of len bytes
+// followed by the synthetic 0xFF 0xFF terminator of opj_mqc_init_dec
+struct MqCore { unsigned c, ct; int bp, len; unsigned cur; };
 
-__device__ __forceinline__ unsigned mqd_byte(const MqDec &q, int i)
+__device__ __forceinline__ unsigned mqc_byte(const MqCore &k, const unsigned char *data, int i)
 {
-    return (i >= 0 && i < q.len) ? (unsigned)q.data[i] : 0xffu;
+    return (i >= 0 && i < k.len) ? (unsigned)data[i] : 0xffu;
+}
+__device__ __forceinline__ void mqc_bytein(MqCore &k, const unsigned char *data)
+{
+    const unsigned nx = mqc_byte(k, data, k.bp + 1);
+    if (k.cur == 0xffu) {
+        if (nx > 0x8fu) { k.c += 0xff00u; k.ct = 8; }
+        else { k.bp++; k.cur = nx; k.c += nx << 9; k.ct = 7; }
+    } else { k.bp++; k.cur = nx; k.c += nx << 8; k.ct = 8; }
+}
+// n renormalisation shifts
+__device__ __forceinline__ void mqc_shift(MqCore &k, const unsigned char *data, int n)
+{
+    while (n > 0) {
+        if (k.ct == 0) mqc_bytein(k, data);
+        const int s = n < (int)k.ct ? n : (int)k.ct;
+        k.c <<= s; k.ct -= (unsigned)s; n -= s;
+    }
 }
 
-__device__ __forceinline__ void mqd_bytein(MqDec &q)
+struct MqDec {
+    unsigned a;
+    MqCore m;                      // the decoder proper
+    const unsigned char *data;
+    // truncation shadows (compression-ratio search only): shadow j replays the decoder on the segment cut at
+    // trunc[j] = rate[tp + j]; it forks from the main decoder the first time a byte at or beyond the cut is read
+    MqCore sh[DEC_NSHADOW];
+    int trunc[DEC_NSHADOW];        // cut length of slot j, < 0: slot unused
+    unsigned sh_on, sh_bad;        // bit j: slot j forked / diverged (or could not be verified)
+    int maxread;                   // highest byte index the main decoder has looked at
+};
+
+// nrem: renormalisation shifts of the current symbol still to be applied (a shadow forked in the middle of a
+// renormalisation has to finish it on its own)
+__device__ __forceinline__ void mqd_main_bytein(MqDec &q, int nrem)
 {
-    const unsigned nx = mqd_byte(q, q.bp + 1);
-    if (q.cur == 0xffu) {
-        if (nx > 0x8fu) { q.c += 0xff00u; q.ct = 8; }
-        else { q.bp++; q.cur = nx; q.c += nx << 9; q.ct = 7; }
-    } else { q.bp++; q.cur = nx; q.c += nx << 8; q.ct = 8; }
+    const int idx = q.m.bp + 1;
+    if (idx > q.maxread) q.maxread = idx;
+#pragma unroll
+    for (int j = 0; j < DEC_NSHADOW; ++j)
+        if (q.trunc[j] >= 0 && !((q.sh_on >> j) & 1u) && idx >= q.trunc[j]) {
+            q.sh[j] = q.m; q.sh[j].len = q.trunc[j]; q.sh_on |= 1u << j;
+            // the shadow's current byte may already lie beyond its cut (a cut inside the decoder's look-ahead)
+            if (q.sh[j].bp >= q.trunc[j]) q.sh_bad |= 1u << j;
+            mqc_bytein(q.sh[j], q.data);
+            mqc_shift(q.sh[j], q.data, nrem);
+        }
+    mqc_bytein(q.m, q.data);
 }
 
 __device__ __forceinline__ void mqd_init(MqDec &q, const unsigned char *data, int len)
 {
-    q.data = data; q.len = len; q.bp = 0;
-    q.cur = mqd_byte(q, 0);
-    q.c = q.cur << 16;
-    mqd_bytein(q);
-    q.c <<= 7; q.ct -= 7; q.a = 0x8000u;
-}
-
-__device__ __forceinline__ void mqd_renorm(MqDec &q)
-{
-    do {
-        if (q.ct == 0) mqd_bytein(q);
-        int k = __clz((int)q.a) - 16;          // shifts still needed
-        if ((unsigned)k > q.ct) k = (int)q.ct;
-        q.a <<= k; q.c <<= k; q.ct -= (unsigned)k;
-    } while (q.a < 0x8000u);
+    q.data = data; q.m.len = len; q.m.bp = 0;
+    q.m.cur = mqc_byte(q.m, data, 0);
+    q.m.c = q.m.cur << 16;
+    q.m.ct = 0;
+    q.sh_on = 0; q.sh_bad = 0; q.maxread = 1;
+#pragma unroll
+    for (int j = 0; j < DEC_NSHADOW; ++j) q.trunc[j] = -1;
+    mqc_bytein(q.m, data);
+    q.m.c <<= 7; q.m.ct -= 7; q.a = 0x8000u;
 }
 
 __device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned char *ctx, const unsigned *tab)
 {
     const unsigned st = *ctx, e = tab[st], qe = e & 0xffffu, mps = st & 1u;
-    unsigned d;
-    q.a -= qe;
-    if ((q.c >> 16) < qe) {
-        if (q.a < qe) { d = mps; *ctx = (unsigned char)((e >> 16) & 0xffu); }
-        else { d = mps ^ 1u; *ctx = (unsigned char)(e >> 24); }
-        q.a = qe;
-        mqd_renorm(q);
+    const unsigned a0 = q.a - qe;
+    unsigned d, a1 = a0;
+    bool ren;
+    if ((q.m.c >> 16) < qe) {
+        d = (a0 < qe) ? mps : (mps ^ 1u);
+        a1 = qe; ren = true;
     } else {
-        q.c -= qe << 16;
-        if ((q.a & 0x8000u) == 0) {
-            if (q.a < qe) { d = mps ^ 1u; *ctx = (unsigned char)(e >> 24); }
-            else { d = mps; *ctx = (unsigned char)((e >> 16) & 0xffu); }
-            mqd_renorm(q);
-        } else d = mps;
+        q.m.c -= qe << 16;
+        if ((a0 & 0x8000u) == 0) { d = (a0 < qe) ? (mps ^ 1u) : mps; ren = true; }
+        else { d = mps; ren = false; }
     }
+    const int nshift = ren ? __clz((int)a1) - 16 : 0;
+    if (q.sh_on) {
+#pragma unroll
+        for (int j = 0; j < DEC_NSHADOW; ++j)
+            if ((q.sh_on >> j) & 1u) {
+                MqCore &k = q.sh[j];
+                unsigned ds;
+                if ((k.c >> 16) < qe) ds = (a0 < qe) ? mps : (mps ^ 1u);
+                else { k.c -= qe << 16; ds = ((a0 & 0x8000u) == 0) ? ((a0 < qe) ? (mps ^ 1u) : mps) : mps; }
+                if (ds != d) q.sh_bad |= 1u << j;
+                else if (!((q.sh_bad >> j) & 1u)) mqc_shift(k, q.data, nshift);
+            }
+    }
+    if (ren) {
+        *ctx = (unsigned char)((d == mps) ? ((e >> 16) & 0xffu) : (e >> 24));
+        // main decoder: shifts with fork checks at every byte read
+        int n = nshift;
+        while (n > 0) {
+            if (q.m.ct == 0) mqd_main_bytein(q, n);
+            const int s = n < (int)q.m.ct ? n : (int)q.m.ct;
+            q.m.c <<= s; q.m.ct -= (unsigned)s; n -= s;
+        }
+        q.a = a1 << nshift;
+    } else q.a = a0;
     return d;
 }
 
@@ -106,7 +163,8 @@ struct T1DecState {
     const unsigned char *zc;     // zero-coding LUT of this orientation
     const unsigned *tab;
     int *plane;                  // top-left of the block inside the integer coefficient plane
-    int W;
+    unsigned char *spass;        // top-left of the block inside the pass-of-significance plane, or nullptr
+    int W, pass;
 };
 
 // sample (stripe word index p, row ci) becomes significant with sign s: update the neighbourhood bits
@@ -141,6 +199,12 @@ __device__ __forceinline__ unsigned t1d_sign(T1DecState &S, MqDec &q, int p, int
     return v ^ (unsigned)(e >> 3);
 }
 
+__device__ __forceinline__ void t1d_new_sig(T1DecState &S, int y, int x, unsigned sg, int oneplushalf)
+{
+    atomicAdd(S.plane + (size_t)y * S.W + x, sg ? -oneplushalf : oneplushalf);
+    if (S.spass) S.spass[(size_t)y * S.W + x] = (unsigned char)S.pass;
+}
+
 __device__ void t1d_clnpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
 {
     const int oneplushalf = 3 << bpno;
@@ -164,7 +228,7 @@ __device__ void t1d_clnpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
                 }
                 partial = 0;
                 const unsigned sg = t1d_sign(S, q, p, ci, f);
-                atomicAdd(S.plane + (size_t)(y0 + ci) * S.W + x, sg ? -oneplushalf : oneplushalf);
+                t1d_new_sig(S, y0 + ci, x, sg, oneplushalf);
                 t1d_set_sig(S, p, ci, sg, f);
             }
             S.F[p] = f & ~(0xfu << 24);
@@ -186,7 +250,7 @@ __device__ void t1d_sigpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
                     const unsigned ctx = S.zc[(f >> (ci * 3)) & 0x1ffu];
                     if (mqd_decode(q, S.cx + CTX_ZC + ctx, S.tab)) {
                         const unsigned sg = t1d_sign(S, q, p, ci, f);
-                        atomicAdd(S.plane + (size_t)(y0 + ci) * S.W + x, sg ? -oneplushalf : oneplushalf);
+                        t1d_new_sig(S, y0 + ci, x, sg, oneplushalf);
                         t1d_set_sig(S, p, ci, sg, f);
                     }
                     f |= DF_PI(ci);
@@ -220,10 +284,13 @@ __device__ void t1d_refpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
     }
 }
 
-// grid = ceil(ncblks * nframes / DEC_WARPS) CTAs of DEC_WARPS warps; plane must be zero on entry
+// grid = ceil(ncblks * nframes / DEC_WARPS) CTAs of DEC_WARPS warps.  Every job with mode != 0 first clears its block
+// region of the target plane (mode 1: iplane + spass, mode 2: scratch), then lane 0 decodes.  cbout != nullptr enables
+// the truncation shadows (rates come from the encoder's pass table) and dstate receives the verdicts.
 __global__ void __launch_bounds__(DEC_WARPS * 32)
 k_t1_dec(const CblkDesc *__restrict__ cblks, const DecJob *__restrict__ jobs, const unsigned char *__restrict__ pool,
-         size_t pool_stride, const DecLuts *__restrict__ g_luts, int *iplane, int W, int H, int ncblks, int nframes)
+         size_t pool_stride, const DecLuts *__restrict__ g_luts, int *iplane, unsigned char *spass, int *scratch,
+         const CblkOut *__restrict__ cbout, DecState *dstate, int W, int H, int ncblks, int nframes)
 {
     __shared__ unsigned F[DEC_WARPS][DEC_FWORDS];
     __shared__ unsigned char cxs[DEC_WARPS][32];
@@ -235,47 +302,150 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const DecJob *__restrict__ jobs, co
     const long long job = (long long)blockIdx.x * DEC_WARPS + warp;
     const bool live = job < (long long)ncblks * nframes;
     int frame = 0, cbi = 0;
-    DecJob jb; jb.np = 0; jb.numbps = 0; jb.off = 0; jb.len = 0;
+    DecJob jb; jb.np = 0; jb.numbps = 0; jb.off = 0; jb.len = 0; jb.mode = 0; jb.pad = 0;
     if (live) {
-        frame = (int)(job / ncblks); cbi = (int)(job - (long long)frame * ncblks);
-        jb = jobs[job];
+        // frame varies fastest so that the warps of a CTA (and neighbouring CTAs) hold blocks of similar length
+        cbi = (int)(job / nframes); frame = (int)(job - (long long)cbi * nframes);
+        jb = jobs[(size_t)frame * ncblks + cbi];
     }
-    const bool work = live && jb.np > 0 && jb.numbps > 0;
-    if (work) for (int i = lane; i < DEC_FWORDS; i += 32) F[warp][i] = 0;
+    const bool work = live && jb.mode != 0;
+    CblkDesc cb;
+    if (work) {
+        cb = cblks[cbi];
+        for (int i = lane; i < DEC_FWORDS; i += 32) F[warp][i] = 0;
+        // clear the block's region of the target plane(s)
+        int *dst = (jb.mode == 1 ? iplane : scratch) + (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx;
+        unsigned char *sp = (jb.mode == 1 && spass) ? spass + (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx : nullptr;
+        for (int i = lane; i < cb.w * cb.h; i += 32) {
+            const int y = i / cb.w, x = i - y * cb.w;
+            dst[(size_t)y * W + x] = 0;
+            if (sp) sp[(size_t)y * W + x] = 255;
+        }
+    }
     __syncthreads();
     if (!work || lane != 0) return;
 
-    const CblkDesc cb = cblks[cbi];
-    unsigned char *cx = cxs[warp];
-    for (int i = 0; i < 19; ++i) cx[i] = 0;
-    cx[CTX_UNI] = 46 << 1; cx[CTX_AGG] = 3 << 1; cx[CTX_ZC] = 4 << 1;
-    T1DecState S;
-    S.F = F[warp]; S.cx = cx; S.zc = zc + cb.orient * 512; S.tab = tab; S.W = W;
-    S.plane = iplane + (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx;
-    MqDec q;
-    mqd_init(q, pool + (size_t)frame * pool_stride + jb.off, jb.len);
-    int bpno = jb.numbps - 1, passtype = 2;
-    for (int p = 0; p < jb.np && bpno >= 0; ++p) {
-        if (passtype == 0) t1d_sigpass(S, q, cb.w, cb.h, bpno);
-        else if (passtype == 1) t1d_refpass(S, q, cb.w, cb.h, bpno);
-        else t1d_clnpass(S, q, cb.w, cb.h, bpno);
-        if (++passtype == 3) { passtype = 0; bpno--; }
+    DecState ds; ds.np_dec = 0; ds.pad = 0; ds.bad[0] = ds.bad[1] = ds.bad[2] = ds.bad[3] = 0;
+    DecState *dsp = (dstate && jb.mode == 1) ? dstate + (size_t)frame * ncblks + cbi : nullptr;
+    if (jb.np > 0 && jb.numbps > 0) {
+        unsigned char *cx = cxs[warp];
+        for (int i = 0; i < 19; ++i) cx[i] = 0;
+        cx[CTX_UNI] = 46 << 1; cx[CTX_AGG] = 3 << 1; cx[CTX_ZC] = 4 << 1;
+        T1DecState S;
+        S.F = F[warp]; S.cx = cx; S.zc = zc + cb.orient * 512; S.tab = tab; S.W = W; S.pass = 0;
+        const size_t o = (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx;
+        S.plane = (jb.mode == 1 ? iplane : scratch) + o;
+        S.spass = (jb.mode == 1 && spass) ? spass + o : nullptr;
+        MqDec q;
+        mqd_init(q, pool + (size_t)frame * pool_stride + jb.off, jb.len);
+        const int *rates = (cbout && jb.mode == 1) ? cbout[(size_t)frame * ncblks + cbi].rate : nullptr;
+        if (rates) {
+#pragma unroll
+            for (int j = 0; j < DEC_NSHADOW; ++j) {
+                q.trunc[j] = j < jb.np - 1 ? rates[j] : -1;
+                // cuts inside the two bytes the decoder reads while initialising cannot fork any more
+                if (q.trunc[j] >= 0 && q.trunc[j] <= q.maxread) { q.sh_on |= 1u << j; q.sh_bad |= 1u << j; }
+            }
+        }
+        int bpno = jb.numbps - 1, passtype = 2;
+        for (int p = 0; p < jb.np && bpno >= 0; ++p) {
+            S.pass = p;
+            if (passtype == 0) t1d_sigpass(S, q, cb.w, cb.h, bpno);
+            else if (passtype == 1) t1d_refpass(S, q, cb.w, cb.h, bpno);
+            else t1d_clnpass(S, q, cb.w, cb.h, bpno);
+            if (++passtype == 3) { passtype = 0; bpno--; }
+            if (rates && p < jb.np - 1) {
+                // verdict for "stop after pass p": slot 0.  Not forked => the decoder never looked beyond the cut.
+                if ((q.sh_bad & 1u) && p < 128) ds.bad[p >> 5] |= 1u << (p & 31);
+                // retire slot 0, shift the others down, arm a new last slot
+#pragma unroll
+                for (int j = 0; j + 1 < DEC_NSHADOW; ++j) { q.sh[j] = q.sh[j + 1]; q.trunc[j] = q.trunc[j + 1]; }
+                q.sh_on >>= 1; q.sh_bad >>= 1;
+                const int pn = p + DEC_NSHADOW;
+                const int tn = pn < jb.np - 1 ? rates[pn] : -1;
+                q.trunc[DEC_NSHADOW - 1] = tn;
+                if (tn >= 0 && tn <= q.maxread) { q.sh_on |= 1u << (DEC_NSHADOW - 1); q.sh_bad |= 1u << (DEC_NSHADOW - 1); }
+            }
+        }
+        ds.np_dec = jb.np;
     }
+    if (dsp) *dsp = ds;
 }
 
-// decode jobs for the encoder's own allocation (compression-ratio search): block k of a frame is
-// decoded from its MQ pool segment truncated at rate[numpasses-1]
-__global__ void k_jobs_from_enc(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cbout, DecJob *jobs,
-                                int ncblks, int nframes)
+// decode jobs for the encoder's own allocation (compression-ratio search).  Block k is recorded (mode 1) when the
+// allocation needs more passes than its recording holds, served from the recording (mode 0) when the recording can
+// reproduce "first numpasses passes", and decoded for real into the scratch plane (mode 2) otherwise.
+__global__ void k_jobs_from_enc(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cbout, const DecState *__restrict__ dstate,
+                                DecJob *jobs, int ncblks, int nframes, int use_recording)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (long long)ncblks * nframes) return;
     const int k = (int)(i % ncblks);
     const CblkOut &c = cbout[i];
     DecJob j;
-    j.np = c.numpasses; j.numbps = c.numbps; j.off = cblks[k].mq_off;
+    j.np = c.numpasses; j.numbps = c.numbps; j.off = cblks[k].mq_off; j.pad = 0;
     j.len = c.numpasses > 0 ? c.rate[c.numpasses - 1] : 0;
+    if (!use_recording) j.mode = 2;
+    else {
+        const DecState &d = dstate[i];
+        const int np = c.numpasses;
+        if (np > d.np_dec) j.mode = 1;
+        else if (np == d.np_dec || np == 0) j.mode = 0;
+        else j.mode = ((np - 1) < 128 && ((d.bad[(np - 1) >> 5] >> ((np - 1) & 31)) & 1u)) || (np - 1) >= 128 ? 2 : 0;
+    }
     jobs[i] = j;
+}
+
+__global__ void k_dstate_reset(DecState *d, long long n)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { d[i].np_dec = 0; d[i].pad = 0; d[i].bad[0] = d[i].bad[1] = d[i].bad[2] = d[i].bad[3] = 0; }
+}
+
+// Probe reconstruction: integer tier-1 output of "the first numpasses passes" for every sample, taken from the
+// recording (value after np_dec passes + pass of significance) or from the scratch plane (mode 2 blocks), then
+// dequantised: (float)v * (0.5f * stepsize_dec)  (t1.c:1853-1865).
+//   decoder units: |v| = 2*M + 2^b, M = magnitude bits decoded down to plane b, 2^b the half-bit bias
+//   (t1.c:582-1140: oneplushalf on significance, +-poshalf per refinement)
+__global__ void k_recon_dequant(const Plan *__restrict__ plan, const CblkOut *__restrict__ cbout, const DecState *__restrict__ dstate,
+                                const DecJob *__restrict__ jobs, const int *__restrict__ iplane, const unsigned char *__restrict__ spass,
+                                const int *__restrict__ scratch, float *coef)
+{
+    const int W = plan->W, H = plan->H, ncblks = plan->ncblks;
+    const size_t n = (size_t)W * H;
+    const int frame = blockIdx.y;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const int y = (int)(i / W), x = (int)(i - (size_t)y * W);
+        int r = 0;
+        while (r < J2K_NRES - 1 && (x >= plan->res_w[r] || y >= plan->res_h[r])) ++r;
+        int band = 0;
+        if (r > 0) {
+            const int o = (x >= plan->res_w[r - 1] ? 1 : 0) | (y >= plan->res_h[r - 1] ? 2 : 0);
+            band = 1 + 3 * (r - 1) + (o - 1);
+        }
+        const BandDesc &bd = plan->bands[band];
+        const int k = bd.first_cblk + ((y - bd.offy) >> 6) * bd.cw + ((x - bd.offx) >> 6);
+        const size_t bi = (size_t)frame * ncblks + k, si = (size_t)frame * n + i;
+        int v;
+        if (jobs[bi].mode == 2) v = scratch[si];
+        else {
+            const int np = cbout[bi].numpasses, npd = dstate[bi].np_dec;
+            v = np > 0 ? iplane[si] : 0;            // a block that was never included has no recording
+            if (np != npd && v != 0) {
+                const int ps = spass[si];
+                if (ps >= np) v = 0;
+                else {
+                    const int numbps = cbout[bi].numbps;
+                    const int kk = ps == 0 ? 0 : (ps + 2) / 3, kr = np / 3;
+                    const int b = numbps - 1 - (kr > kk ? kr : kk);
+                    const int a = v < 0 ? -v : v;
+                    const int mag = ((((a >> 1) >> b) << b) << 1) + (1 << b);
+                    v = v < 0 ? -mag : mag;
+                }
+            }
+        }
+        coef[si] = __fmul_rn((float)v, __fmul_rn(0.5f, bd.stepsize_dec));
+    }
 }
 
 // ---- tier-2 parse ---------------------------------------------------------------------------------
@@ -330,7 +500,7 @@ __global__ void k_t2_parse(const Plan *__restrict__ plan, const CblkDesc *__rest
     EBCC_DYN_SMEM(int, sm);
     const int frame = blockIdx.x, ncblks = plan->ncblks, nnodes = plan->nnodes;
     DecJob *jb = jobs + (size_t)frame * ncblks;
-    for (int k = threadIdx.x; k < ncblks; k += blockDim.x) { DecJob z; z.np = 0; z.numbps = 0; z.off = 0; z.len = 0; jb[k] = z; }
+    for (int k = threadIdx.x; k < ncblks; k += blockDim.x) { DecJob z; z.np = 0; z.numbps = 0; z.off = 0; z.len = 0; z.mode = 1; z.pad = 0; jb[k] = z; }
     TgtState incl, imsb;
     incl.val = sm; incl.low = sm + nnodes; imsb.val = sm + 2 * nnodes; imsb.low = sm + 3 * nnodes;
     for (int i = threadIdx.x; i < nnodes; i += blockDim.x) { incl.val[i] = 999; incl.low[i] = 0; imsb.val[i] = 999; imsb.low[i] = 0; }
@@ -383,7 +553,7 @@ __global__ void k_t2_parse(const Plan *__restrict__ plan, const CblkDesc *__rest
             while (bi_bit(b)) { if (b.err || ++inc > 32) return; }
             const int nbits = 3 + inc + t2_floorlog2(np);
             if (nbits > 32) return;
-            j.np = np; j.len = (int)bi_read(b, nbits); j.off = 0;
+            j.np = np; j.len = (int)bi_read(b, nbits); j.off = 0; j.mode = 1; j.pad = 0;
             if (b.err || j.len < 0) return;
             jb[k] = j;
         }

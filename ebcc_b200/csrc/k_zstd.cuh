@@ -18,6 +18,7 @@
 #define ZC_THREADS 32
 #define Z_MAGIC 0xFD2FB528u
 #define Z_BLOCK_MAX (128 * 1024)
+#define Z_CHUNK (16 * 1024)          // block size of the compressor: one block per CTA, blocks of a frame in parallel
 #define Z_HUF_MAXLOG 11
 
 // ---- shared tables ----------------------------------------------------------------------------------------
@@ -407,13 +408,13 @@ __device__ __forceinline__ int zw_close(ZBitW &b)
 struct ZSeq { unsigned ll, ml; };          // literal run length, match length (offset is always the repeat offset 1)
 
 struct ZEncWork {
-    unsigned char lit[Z_BLOCK_MAX];
-    ZSeq seq[Z_BLOCK_MAX / 4 + 8];
+    unsigned char lit[Z_CHUNK];
+    ZSeq seq[Z_CHUNK / 4 + 8];
     ZFseEntry ll[64], ml[64], wt[64];
     unsigned hist[256];
     unsigned char nbits[256];
     unsigned short code[256];
-    unsigned char tmp[Z_BLOCK_MAX + 1024];
+    unsigned char tmp[2 * Z_CHUNK + 1024];
 };
 
 // tANS encode step through the decoding table: find the entry of symbol s whose state interval contains x
@@ -593,14 +594,14 @@ __device__ int z_write_literals(ZEncWork *w, unsigned char *dst, int cap, int nl
                 int pos = tl, ok = 1;
                 const int streams = nlit < 1024 ? 1 : 4;
                 if (streams == 1) {
-                    const int sl = z_huf_enc_stream(t + pos, Z_BLOCK_MAX + 1024 - pos, lit, nlit, w->code, w->nbits);
+                    const int sl = z_huf_enc_stream(t + pos, 2 * Z_CHUNK + 1024 - pos, lit, nlit, w->code, w->nbits);
                     if (sl < 0) ok = 0; else pos += sl;
                 } else {
                     const int seg = (nlit + 3) / 4;
                     int jt = pos; pos += 6;
                     for (int k = 0; k < 4 && ok; ++k) {
                         const int a = k * seg, len = k < 3 ? seg : nlit - 3 * seg;
-                        const int sl = z_huf_enc_stream(t + pos, Z_BLOCK_MAX + 1024 - pos, lit + a, len, w->code, w->nbits);
+                        const int sl = z_huf_enc_stream(t + pos, 2 * Z_CHUNK + 1024 - pos, lit + a, len, w->code, w->nbits);
                         if (sl < 0 || sl > 65535) { ok = 0; break; }
                         if (k < 3) { t[jt + 2 * k] = (unsigned char)sl; t[jt + 2 * k + 1] = (unsigned char)(sl >> 8); }
                         pos += sl;
@@ -688,31 +689,62 @@ __device__ int z_compress_block(ZEncWork *w, const unsigned char *src, int n, un
     return pos + sl_bytes;
 }
 
-// grid = nframes, block = ZC_THREADS (thread 0 works).  in: [frame][in_stride], in_len[frame] bytes (0 = skip);
-// out: [frame][out_stride]; out_len[frame] = frame bytes.
-__global__ void k_zstd_compress(const unsigned char *__restrict__ in, size_t in_stride, const unsigned *__restrict__ in_len,
-                                unsigned char *out, size_t out_stride, unsigned *out_len, ZEncWork *work)
+// Compressor, stage 1: grid = (maxchunks, nframes), block = ZC_THREADS (thread 0 works).  Chunk j of frame i
+// (Z_CHUNK bytes of in[i]) becomes one zstd block (3-byte header + body) in blk[i][j]; blen[i][j] = its size.
+// Blocks of a frame are independent: every block carries its own Huffman table, sequences use predefined tables
+// and only the repeat offset 1, which no block ever changes.
+#define Z_BLK_STRIDE (Z_CHUNK + 16)
+__global__ void k_zstd_compress_chunks(const unsigned char *__restrict__ in, size_t in_stride, const unsigned *__restrict__ in_len,
+                                       unsigned char *blk, unsigned *blen, int maxchunks, ZEncWork *work)
 {
-    const int frame = blockIdx.x;
+    const int frame = blockIdx.y, j = blockIdx.x;
     if (threadIdx.x != 0) return;
+    const int n = (int)in_len[frame], a = j * Z_CHUNK;
+    unsigned *bl = blen + (size_t)frame * maxchunks + j;
+    if (a >= n) { *bl = 0; return; }
+    const unsigned char *src = in + (size_t)frame * in_stride + a;
+    unsigned char *dst = blk + ((size_t)frame * maxchunks + j) * Z_BLK_STRIDE;
+    ZEncWork *w = work + (size_t)frame * maxchunks + j;
+    const int len = n - a < Z_CHUNK ? n - a : Z_CHUNK, last = a + len >= n;
+    int cs = z_compress_block(w, src, len, dst + 3, len - 1);
+    unsigned bh;
+    if (cs > 0 && cs < len) bh = (unsigned)last | (2u << 1) | ((unsigned)cs << 3);
+    else { cs = len; bh = (unsigned)last | (0u << 1) | ((unsigned)len << 3); for (int k = 0; k < len; ++k) dst[3 + k] = src[k]; }
+    dst[0] = (unsigned char)bh; dst[1] = (unsigned char)(bh >> 8); dst[2] = (unsigned char)(bh >> 16);
+    *bl = (unsigned)(3 + cs);
+}
+
+// stage 2: grid = nframes, block = 256: frame header + the blocks at their prefix-summed offsets
+__global__ void k_zstd_assemble(const unsigned char *__restrict__ blk, const unsigned *__restrict__ blen, int maxchunks,
+                                const unsigned *__restrict__ in_len, unsigned char *out, size_t out_stride, unsigned *out_len)
+{
+    __shared__ unsigned off[512];
+    const int frame = blockIdx.x;
     const int n = (int)in_len[frame];
-    if (n == 0) { out_len[frame] = 0; return; }
-    const unsigned char *src = in + (size_t)frame * in_stride;
+    if (n == 0) { if (threadIdx.x == 0) out_len[frame] = 0; return; }
+    const int nch = (n + Z_CHUNK - 1) / Z_CHUNK;
     unsigned char *dst = out + (size_t)frame * out_stride;
-    ZEncWork *w = work + frame;
-    int pos = 0;
-    dst[pos++] = 0x28; dst[pos++] = 0xB5; dst[pos++] = 0x2F; dst[pos++] = 0xFD;
-    dst[pos++] = (unsigned char)((2 << 6) | (1 << 5));       // 4-byte content size, single segment, no checksum
-    dst[pos++] = (unsigned char)n; dst[pos++] = (unsigned char)(n >> 8); dst[pos++] = (unsigned char)(n >> 16); dst[pos++] = (unsigned char)(n >> 24);
-    for (int a = 0; a < n; a += Z_BLOCK_MAX) {
-        const int len = n - a < Z_BLOCK_MAX ? n - a : Z_BLOCK_MAX, last = a + len >= n;
-        const int cap = (int)out_stride - pos - 3;
-        int cs = z_compress_block(w, src + a, len, dst + pos + 3, cap < len ? cap : len - 1);
-        unsigned bh;
-        if (cs > 0 && cs < len) bh = (unsigned)last | (2u << 1) | ((unsigned)cs << 3);
-        else { cs = len; bh = (unsigned)last | (0u << 1) | ((unsigned)len << 3); for (int k = 0; k < len; ++k) dst[pos + 3 + k] = src[a + k]; }
-        dst[pos] = (unsigned char)bh; dst[pos + 1] = (unsigned char)(bh >> 8); dst[pos + 2] = (unsigned char)(bh >> 16);
-        pos += 3 + cs;
+    const unsigned *bl = blen + (size_t)frame * maxchunks;
+    for (int base = 0; base < nch; base += 511) {
+        const int cnt = nch - base < 511 ? nch - base : 511;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned o = base == 0 ? 9u : off[511];
+            if (base == 0) {
+                dst[0] = 0x28; dst[1] = 0xB5; dst[2] = 0x2F; dst[3] = 0xFD;
+                dst[4] = (unsigned char)((2 << 6) | (1 << 5));       // 4-byte content size, single segment, no checksum
+                dst[5] = (unsigned char)n; dst[6] = (unsigned char)(n >> 8); dst[7] = (unsigned char)(n >> 16); dst[8] = (unsigned char)(n >> 24);
+            }
+            for (int k = 0; k < cnt; ++k) { off[k] = o; o += bl[base + k]; }
+            off[511] = o;
+        }
+        __syncthreads();
+        for (int k = 0; k < cnt; ++k) {
+            const unsigned char *src = blk + ((size_t)frame * maxchunks + base + k) * Z_BLK_STRIDE;
+            const unsigned len = bl[base + k], o = off[k];
+            for (unsigned t = threadIdx.x; t < len; t += blockDim.x) dst[o + t] = src[t];
+        }
+        __syncthreads();
+        if (threadIdx.x == 0 && base + cnt >= nch) out_len[frame] = off[511];
     }
-    out_len[frame] = (unsigned)pos;
 }

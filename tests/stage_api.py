@@ -113,3 +113,33 @@ def check_residual_stage(frame, cr, verbose=False, probes=(1.0, 0.5, 0.23, 0.07)
     finally:
         lib.ebcc_cuda_ctx_destroy(ctx)
     return bool(ok)
+
+
+def probe_sequence(frames, crs, target, recording):
+    """error statistics of a sequence of rate probes over a resident batch; recording=False forces a real tier-1
+    decode of every block in every probe (EBCC_NO_RECORDING=1)"""
+    import os
+    f = np.ascontiguousarray(frames, dtype=np.float32)
+    b, h, w = f.shape
+    if recording:
+        os.environ.pop("EBCC_NO_RECORDING", None)
+    else:
+        os.environ["EBCC_NO_RECORDING"] = "1"
+    lib = cuda_api()
+    ctx = C.c_void_p(lib.ebcc_cuda_ctx_create(0))
+    assert ctx.value
+    out = []
+    try:
+        assert lib.ebcc_cuda_reserve(ctx, h, w, b) == 0
+        assert lib.ebcc_cuda_upload(ctx, f.ctypes.data, b) == 0
+        assert lib.ebcc_cuda_analyze_resident(ctx, b) == 0
+        for cr in crs:
+            crs_a = (C.c_float * b)(*([cr] * b))
+            tg = (C.c_float * b)(*([target] * b))
+            pr = (ProbeResult * b)()
+            assert lib.ebcc_cuda_rate_probe(ctx, b, crs_a, tg, 0, pr) == 0
+            out.append([(p.n_over, p.max_err, p.rmin, p.rmax, p.stream_bytes) for p in pr])
+    finally:
+        lib.ebcc_cuda_ctx_destroy(ctx)
+        os.environ.pop("EBCC_NO_RECORDING", None)
+    return out

@@ -113,3 +113,13 @@ def test_batch_equals_single_max_error(built):
         lib.free_buffer(outs[t])
         assert got == H.encode(lib, frames[t], (1, 160, 224), 20.0, H.MAX_ERROR, 0.1)
         assert np.abs(H.decode(lib, got) - frames[t].ravel()).max() <= 0.1
+
+
+def test_recording_equals_real_decodes(built):
+    """CR-search probes served from the pass recording (one tier-1 decode + truncation shadows) must give exactly the
+    statistics of probes that decode every block for real, for ratios below and above the recorded one."""
+    frames = H.synth_stack(3)
+    crs = [30.0, 60.0, 120.0, 90.0, 75.0, 82.5, 15.0, 7.5, 20.0, 45.0, 250.0, 2.0]
+    a = S.probe_sequence(frames, crs, 0.3, True)
+    b = S.probe_sequence(frames, crs, 0.3, False)
+    assert a == b
