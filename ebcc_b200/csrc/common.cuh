@@ -4,7 +4,7 @@
 //   in     [B][H][W] f32   input frames (H2D copy of the caller's buffer)
 //   coef   [B][H][W] f32   9/7 coefficients, Mallat layout, transformed in place level by level
 //   stat   [B]             min / max / flags per frame
-//   sym    [B][sym_stride] u8  EBCOT symbol stream per code-block: (ctx << 1 | bit), scan order
+//   sym    [B][sym_stride] u8  EBCOT symbol stream per code-block: (ctx << 2 | bit), scan order
 //   cbout  [B][ncblks]     per code-block pass table (symbol counts, nmsedec, rates, distortion)
 //   mq     [B][mq_stride]  u8  MQ-coded bytes per code-block
 //   out    [B][out_stride] u8  finished J2K codestreams

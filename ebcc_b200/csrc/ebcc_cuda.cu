@@ -540,14 +540,10 @@ extern "C" int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *c, size_t nframes)
                 c->d_coef, c->d_cblks, c->d_bands, c->d_luts, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks, pl->sym_stride);
     mark(c, EBCC_ST_T1_MQ);
     {
-        long long jobs = (long long)pl->ncblks * B;
-        const char *el = getenv("EBCC_MQ_LANES");
-        int lanes = el ? atoi(el) : 1;
-        if (lanes < 1 || lanes > 32) lanes = 1;
-        long long warps = (jobs + lanes - 1) / lanes;
-        long long ctas = (warps * 32 + MQ_THREADS - 1) / MQ_THREADS;
+        const long long jobs = (long long)pl->ncblks * B;        // one warp per code-block
+        const long long ctas = (jobs + MQ_WARPS - 1) / MQ_WARPS;
         EBCC_LAUNCH(k_t1_mq, dim3((unsigned)ctas), dim3(MQ_THREADS), 0, c->stream,
-                    c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride, lanes);
+                    c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride);
     }
     c->launches += 2;
     CK(cudaGetLastError());

@@ -9,9 +9,9 @@
 //             scan order.  For the cleanup pass "becomes significant" is known a priori
 //             (insignificant, not visited, bit set); for the significance-propagation pass it is
 //             the least fixed point of a monotone map, reached by iterating to convergence.
-//   k_t1_mq : one THREAD per code-block, several code-blocks per warp.  Serial MQ arithmetic
-//             coder (mqc.c / mqc_inl.h) over the symbol stream, pass rates as opj_t1_encode_cblk
-//             computes them (t1.c:2655-2723).
+//   k_t1_mq : one code-block per warp.  The warp stages the symbol stream through shared memory, lane 0
+//             runs the serial MQ arithmetic coder (mqc.c / mqc_inl.h) over it, pass rates as
+//             opj_t1_encode_cblk computes them (t1.c:2655-2723).
 //
 // Integer/latency bound; bit-exact with opj_t1_encode_cblk by construction.
 #pragma once
@@ -312,7 +312,7 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
 #pragma unroll
         for (int k = 0; k < T1_CPT; ++k) {
             unsigned long long b = sy[k].bits;
-            for (int i = 0; i < sy[k].cnt; ++i) { symbuf[off++] = (unsigned char)(b & 63); b >>= 6; }
+            for (int i = 0; i < sy[k].cnt; ++i) { symbuf[off++] = (unsigned char)(((b & 62) << 1) | (b & 1)); b >>= 6; }
         }
         // ---- state update ---------------------------------------------------------------------------
 #pragma unroll
@@ -349,10 +349,36 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
 }
 
 // ------------------------------------------------------------------------------------------------
-// MQ coder.  State table (Annex C table C.2; mqc.c:61-157) packed as qe | nmps<<16 | nlps<<22 | sw<<28.
+// MQ coder.  State table (Annex C table C.2; mqc.c:61-157) arrives packed as qe | nmps<<16 | nlps<<22 | sw<<28
+// and is repacked in shared memory so that every field of the per-symbol step is one mask away:
+//   [31:16] qe   [15:10] nlps   [7:2] nmps   [1] switch   [0] mps (0 in the table, live in the context word)
+// A context word is the table word of its state with the current MPS in bit 0; the symbol byte is
+// ctx << 2 | decision, i.e. already the byte offset of the context word.
 struct MqTable { unsigned e[47]; };
 
-#define MQ_THREADS 128
+#define MQ_WARPS 4
+#define MQ_THREADS (MQ_WARPS * 32)
+#define MQ_CHUNK 512                 // symbol bytes staged in shared memory per refill (16 per lane)
+
+// shared-memory accesses of the serial chain by 32-bit shared address: one LDS / STS each, no generic
+// address arithmetic (the host-side emulation build uses plain pointers)
+#ifdef EBCC_CUEMU
+typedef unsigned long long mq_saddr;
+#define MQ_SADDR(p) ((mq_saddr)(size_t)(p))
+#define MQ_OPAQUE(a) (a)
+__device__ __forceinline__ unsigned mq_ld8(mq_saddr a) { return *(const unsigned char *)(size_t)a; }
+__device__ __forceinline__ unsigned mq_ld32(mq_saddr a) { return *(const unsigned *)(size_t)a; }
+__device__ __forceinline__ void mq_st32(mq_saddr a, unsigned v) { *(unsigned *)(size_t)a = v; }
+#else
+typedef unsigned mq_saddr;
+#define MQ_SADDR(p) ((mq_saddr)__cvta_generic_to_shared(p))
+// keeps an address in a register instead of re-deriving the shared window base at every use
+__device__ __forceinline__ unsigned mq_opaque(unsigned a) { unsigned r; asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(a)); return r; }
+#define MQ_OPAQUE(a) mq_opaque(a)
+__device__ __forceinline__ unsigned mq_ld8(mq_saddr a) { unsigned v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ unsigned mq_ld32(mq_saddr a) { unsigned v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void mq_st32(mq_saddr a, unsigned v) { asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v)); }
+#endif
 
 struct MqEnc {
     unsigned a, c;
@@ -385,97 +411,115 @@ __device__ __forceinline__ void mq_byteout(MqEnc &q)
     }
 }
 
-__device__ __forceinline__ void mq_renorm(MqEnc &q)
+// end of coding pass p: segment length as opj_t1_encode_cblk records it (t1.c:2655-2699)
+__device__ __forceinline__ void mq_pass_end(MqEnc &q, CblkOut *out, int p, int npasses)
 {
-    int s = __clz((int)q.a) - 16;           // shifts needed to bring bit 15 of a up
-    while (s > 0) {
-        int k = min(s, q.ct);
-        q.a <<= k; q.c <<= k; q.ct -= k; s -= k;
-        if (q.ct == 0) mq_byteout(q);
+    if (p == npasses - 1) {
+        // opj_mqc_flush (mqc.c:212-227)
+        unsigned tempc = q.c + q.a;
+        q.c |= 0xffffu;
+        if (q.c >= tempc) q.c -= 0x8000u;
+        q.c <<= q.ct; mq_byteout(q);
+        q.c <<= q.ct; mq_byteout(q);
+        if (q.pend != 0xff) mq_advance(q, 0);
+        out->rate[p] = q.pos;
+    } else {
+        out->rate[p] = q.pos + 3;
     }
 }
 
+// One code-block per warp.  All 32 lanes move the symbol stream HBM -> registers -> shared memory in
+// 512-byte refills (the next refill is in flight while the current one is coded); lane 0 runs the serial
+// MQ chain out of shared memory: 1 LDS for the symbol, 1 LDS for the context word, and a fast path
+// (MPS, no renormalisation) of about a dozen instructions.
 __global__ void __launch_bounds__(MQ_THREADS)
 k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char *__restrict__ sym_pool,
         unsigned char *mq_pool, const MqTable *__restrict__ g_tab, int ncblks, int nframes,
-        size_t sym_stride, size_t mq_stride, int lanes /* code-blocks per warp */)
+        size_t sym_stride, size_t mq_stride)
 {
-    __shared__ unsigned tab[47];
-    __shared__ unsigned ctxs[19 * MQ_THREADS];
-    const int tid = threadIdx.x, lane = tid & 31;
-    if (tid < 47) tab[tid] = g_tab->e[tid];
+    __shared__ unsigned tab[48];
+    __shared__ unsigned ctxs[MQ_WARPS][20];
+    __shared__ __align__(16) unsigned char stage[MQ_WARPS][MQ_CHUNK + 16];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid < 47) {
+        const unsigned e = g_tab->e[tid];
+        tab[tid] = ((e & 0xffffu) << 16) | (((e >> 22) & 63u) << 10) | (((e >> 16) & 63u) << 2) | (((e >> 28) & 1u) << 1);
+    }
     __syncthreads();
-    const int warp_global = (blockIdx.x * MQ_THREADS + tid) >> 5;
-    const long long job = (long long)warp_global * lanes + lane;
-    if (lane >= lanes || job >= (long long)ncblks * nframes) return;
-    // frame varies fastest: the lanes of a warp code the same code-block position of different frames, whose
-    // symbol counts are similar, so a warp's lanes finish together
+    const long long job = (long long)blockIdx.x * MQ_WARPS + wid;
+    if (job >= (long long)ncblks * nframes) return;
     const int cbi = (int)(job / nframes), frame = (int)(job - (long long)cbi * nframes);
     const CblkDesc cb = cblks[cbi];
     CblkOut *out = cbout + (size_t)frame * ncblks + cbi;
     const int npasses = out->totalpasses;
     if (npasses <= 0) return;
+    const unsigned total = out->nsym_end[npasses - 1];
     const unsigned char *sym = sym_pool + (size_t)frame * sym_stride + cb.sym_off;
 
-    unsigned *cx = ctxs + tid;           // context ctx lives at cx[ctx * MQ_THREADS]
-    for (int i = 0; i < 19; ++i) cx[i * MQ_THREADS] = tab[0] & 0xffffu;          // state 0, mps 0
-    cx[CTX_UNI * MQ_THREADS] = (tab[46] & 0xffffu) | (46u << 17);
-    cx[CTX_AGG * MQ_THREADS] = (tab[3] & 0xffffu) | (3u << 17);
-    cx[CTX_ZC * MQ_THREADS] = (tab[4] & 0xffffu) | (4u << 17);
+    unsigned *cx = ctxs[wid];
+    if (lane < 19) cx[lane] = lane == CTX_UNI ? tab[46] : (lane == CTX_AGG ? tab[3] : (lane == CTX_ZC ? tab[4] : tab[0]));
 
     MqEnc q;
     q.a = 0x8000; q.c = 0; q.ct = 12; q.pos = -1; q.pend = 0;
     q.dst = mq_pool + (size_t)frame * mq_stride + cb.mq_off;
 
-    unsigned i = 0;
-    uint4 buf = make_uint4(0, 0, 0, 0);
-    for (int p = 0; p < npasses; ++p) {
-        const unsigned end = out->nsym_end[p];
-        for (; i < end; ++i) {
-            if ((i & 15u) == 0) buf = *(const uint4 *)(sym + i);
-            unsigned wsel = (i >> 2) & 3u;
-            unsigned word = wsel == 0 ? buf.x : (wsel == 1 ? buf.y : (wsel == 2 ? buf.z : buf.w));
-            unsigned s = (word >> ((i & 3u) * 8)) & 0xffu;
-            const unsigned d = s & 1u, ctx = s >> 1;
-            unsigned w = cx[ctx * MQ_THREADS];
-            const unsigned qe = w & 0xffffu, mps = (w >> 16) & 1u, idx = w >> 17;
-            q.a -= qe;
-            if (d == mps) {
-                if (q.a & 0x8000u) { q.c += qe; continue; }
-                if (q.a < qe) q.a = qe; else q.c += qe;
-                unsigned ni = (tab[idx] >> 16) & 63u;
-                cx[ctx * MQ_THREADS] = (tab[ni] & 0xffffu) | (mps << 16) | (ni << 17);
-            } else {
-                if (q.a < qe) q.c += qe; else q.a = qe;
-                unsigned t = tab[idx];
-                unsigned ni = (t >> 22) & 63u, nm = mps ^ ((t >> 28) & 1u);
-                cx[ctx * MQ_THREADS] = (tab[ni] & 0xffffu) | (nm << 16) | (ni << 17);
+    const mq_saddr sba = MQ_SADDR(stage[wid]), cxa = MQ_SADDR(cx), taba = MQ_OPAQUE(MQ_SADDR(tab));
+    unsigned i = 0, end = out->nsym_end[0];
+    int p = 0;
+    uint4 pre = make_uint4(0, 0, 0, 0);
+    if (lane * 16u < total) pre = *(const uint4 *)(sym + lane * 16u);
+    for (unsigned cbeg = 0; cbeg < total; cbeg += MQ_CHUNK) {
+        __syncwarp();
+        *(uint4 *)(stage[wid] + lane * 16) = pre;
+        const unsigned nxt = cbeg + MQ_CHUNK + lane * 16u;
+        if (nxt < total) pre = *(const uint4 *)(sym + nxt);
+        __syncwarp();
+        if (lane == 0) {
+            const unsigned cend = min(cbeg + MQ_CHUNK, total);
+            for (;;) {
+                const unsigned lim = min(end, cend);
+                mq_saddr sp = sba + (i - cbeg);
+                const mq_saddr sp_lim = sba + (lim - cbeg);
+                unsigned sn = mq_ld8(sp);
+                while (sp < sp_lim) {
+                    const unsigned s = sn;
+                    ++sp;
+                    sn = mq_ld8(sp);                      // next symbol in flight (one byte of slack behind the chunk)
+                    const mq_saddr ca = cxa + (s & 0xfcu);
+                    const unsigned w = mq_ld32(ca);
+                    const unsigned qe = w >> 16, lps = (s ^ w) & 1u;
+                    q.a -= qe;
+                    if (!(lps | (~q.a & 0x8000u))) { q.c += qe; continue; }       // MPS, interval still normalised
+                    // MPS: a < qe ? a = qe : c += qe;  LPS: a < qe ? c += qe : a = qe   (conditional exchange)
+                    if ((unsigned)(q.a < qe) != lps) q.a = qe; else q.c += qe;
+                    const unsigned nx = mq_ld32(taba + ((lps ? (w >> 8) : w) & 0xfcu));
+                    mq_st32(ca, nx | ((w ^ (lps & (w >> 1))) & 1u));
+                    // renormalise: n shifts bring bit 15 of a back up; a byte leaves every time ct reaches 0
+                    int n = __clz((int)q.a) - 16;
+                    q.a <<= n;
+                    while (n >= q.ct) { q.c <<= q.ct; n -= q.ct; mq_byteout(q); }
+                    q.c <<= n; q.ct -= n;
+                }
+                i = cbeg + (unsigned)(sp - sba);
+                if (i != end) break;                     // refill exhausted inside the pass
+                mq_pass_end(q, out, p, npasses);
+                if (++p == npasses) break;
+                end = out->nsym_end[p];
             }
-            mq_renorm(q);
-        }
-        if (p == npasses - 1) {
-            // opj_mqc_flush (mqc.c:212-227)
-            unsigned tempc = q.c + q.a;
-            q.c |= 0xffffu;
-            if (q.c >= tempc) q.c -= 0x8000u;
-            q.c <<= q.ct; mq_byteout(q);
-            q.c <<= q.ct; mq_byteout(q);
-            if (q.pend != 0xff) mq_advance(q, 0);
-            out->rate[p] = q.pos;
-        } else {
-            out->rate[p] = q.pos + 3;
         }
     }
-    // final pending byte (beyond numbytes) is never part of the stream; store for completeness
+    if (lane != 0) return;
+    for (; p < npasses; ++p) mq_pass_end(q, out, p, npasses);
+    // final pending byte (beyond numbytes) is never part of the stream
     int last = q.pos;
     out->datalen = last;
     // monotone fix-up, then strip a trailing 0xFF from each pass (t1.c:2700-2723)
-    for (int p = npasses - 1; p >= 0; --p) {
-        int r = out->rate[p];
-        if (r > last) out->rate[p] = last; else last = r;
+    for (int pp = npasses - 1; pp >= 0; --pp) {
+        int r = out->rate[pp];
+        if (r > last) out->rate[pp] = last; else last = r;
     }
-    for (int p = 0; p < npasses; ++p) {
-        int r = out->rate[p];
-        if (r > 0 && q.dst[r - 1] == 0xff) out->rate[p] = r - 1;
+    for (int pp = 0; pp < npasses; ++pp) {
+        int r = out->rate[pp];
+        if (r > 0 && q.dst[r - 1] == 0xff) out->rate[pp] = r - 1;
     }
 }
