@@ -540,10 +540,15 @@ extern "C" int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *c, size_t nframes)
                 c->d_coef, c->d_cblks, c->d_bands, c->d_luts, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks, pl->sym_stride);
     mark(c, EBCC_ST_T1_MQ);
     {
-        const long long jobs = (long long)pl->ncblks * B;        // one warp per code-block
-        const long long ctas = (jobs + MQ_WARPS - 1) / MQ_WARPS;
-        EBCC_LAUNCH(k_t1_mq, dim3((unsigned)ctas), dim3(MQ_THREADS), 0, c->stream,
-                    c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride);
+        const long long jobs = (long long)pl->ncblks * B;
+        const char *el = getenv("EBCC_MQ_LANES");                // code-blocks per warp: 1, 2, 4 or 8
+        const int lanes = el ? atoi(el) : MQ_DEFAULT_LANES;
+        const long long per_cta = (long long)MQ_WARPS * (lanes == 8 ? 8 : lanes == 4 ? 4 : lanes == 2 ? 2 : 1);
+        const dim3 grid((unsigned)((jobs + per_cta - 1) / per_cta)), block(MQ_THREADS);
+#define MQ_GO(LL) EBCC_LAUNCH(k_t1_mq<LL>, grid, block, 0, c->stream, c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, \
+                              c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride)
+        if (lanes == 8) MQ_GO(8); else if (lanes == 4) MQ_GO(4); else if (lanes == 2) MQ_GO(2); else MQ_GO(1);
+#undef MQ_GO
     }
     c->launches += 2;
     CK(cudaGetLastError());

@@ -350,14 +350,16 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
 
 // ------------------------------------------------------------------------------------------------
 // MQ coder.  State table (Annex C table C.2; mqc.c:61-157) arrives packed as qe | nmps<<16 | nlps<<22 | sw<<28
-// and is repacked in shared memory so that every field of the per-symbol step is one mask away:
-//   [31:16] qe   [15:10] nlps   [7:2] nmps   [1] switch   [0] mps (0 in the table, live in the context word)
-// A context word is the table word of its state with the current MPS in bit 0; the symbol byte is
-// ctx << 2 | decision, i.e. already the byte offset of the context word.
+// and is expanded to one word per (state, mps) pair, index p = 2 * state + mps:
+//   word(p) = qe << 16 | p << 3 | mps
+// Shared memory holds, per pair, the words of its two successors {after an MPS, after an LPS}.  A context is
+// a 16-byte record {word, word after MPS, word after LPS}: a state transition is a register select, and the
+// successors of the new state are fetched off the critical path.  The symbol byte is ctx << 2 | decision.
 struct MqTable { unsigned e[47]; };
 
 #define MQ_WARPS 4
 #define MQ_THREADS (MQ_WARPS * 32)
+#define MQ_DEFAULT_LANES 4
 #define MQ_CHUNK 512                 // symbol bytes staged in shared memory per refill (16 per lane)
 
 // shared-memory accesses of the serial chain by 32-bit shared address: one LDS / STS each, no generic
@@ -368,7 +370,9 @@ typedef unsigned long long mq_saddr;
 #define MQ_OPAQUE(a) (a)
 __device__ __forceinline__ unsigned mq_ld8(mq_saddr a) { return *(const unsigned char *)(size_t)a; }
 __device__ __forceinline__ unsigned mq_ld32(mq_saddr a) { return *(const unsigned *)(size_t)a; }
-__device__ __forceinline__ void mq_st32(mq_saddr a, unsigned v) { *(unsigned *)(size_t)a = v; }
+__device__ __forceinline__ uint2 mq_ld64(mq_saddr a) { return *(const uint2 *)(size_t)a; }
+__device__ __forceinline__ uint4 mq_ld128(mq_saddr a) { return *(const uint4 *)(size_t)a; }
+__device__ __forceinline__ void mq_st128(mq_saddr a, unsigned x, unsigned y, unsigned z) { *(uint4 *)(size_t)a = make_uint4(x, y, z, 0); }
 #else
 typedef unsigned mq_saddr;
 #define MQ_SADDR(p) ((mq_saddr)__cvta_generic_to_shared(p))
@@ -377,7 +381,9 @@ __device__ __forceinline__ unsigned mq_opaque(unsigned a) { unsigned r; asm vola
 #define MQ_OPAQUE(a) mq_opaque(a)
 __device__ __forceinline__ unsigned mq_ld8(mq_saddr a) { unsigned v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
 __device__ __forceinline__ unsigned mq_ld32(mq_saddr a) { unsigned v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-__device__ __forceinline__ void mq_st32(mq_saddr a, unsigned v) { asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v)); }
+__device__ __forceinline__ uint2 mq_ld64(mq_saddr a) { uint2 v; asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a)); return v; }
+__device__ __forceinline__ uint4 mq_ld128(mq_saddr a) { uint4 v; asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a)); return v; }
+__device__ __forceinline__ void mq_st128(mq_saddr a, unsigned x, unsigned y, unsigned z) { asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(a), "r"(x), "r"(y), "r"(z), "r"(0u)); }
 #endif
 
 struct MqEnc {
@@ -428,87 +434,126 @@ __device__ __forceinline__ void mq_pass_end(MqEnc &q, CblkOut *out, int p, int n
     }
 }
 
-// One code-block per warp.  All 32 lanes move the symbol stream HBM -> registers -> shared memory in
-// 512-byte refills (the next refill is in flight while the current one is coded); lane 0 runs the serial
-// MQ chain out of shared memory: 1 LDS for the symbol, 1 LDS for the context word, and a fast path
-// (MPS, no renormalisation) of about a dozen instructions.
+// L code-blocks per warp (L = 1, 2, 4, 8).  The 32 / L lanes of a group move their block's symbol stream
+// HBM -> registers -> shared memory in 512-byte refills (the next refill is in flight while the current one
+// is coded); the first lane of each group runs the serial MQ chain out of shared memory.  The coding lanes
+// advance in lock step: every stretch of symbols up to the nearest pass end of any of them has a uniform
+// trip count, the common step (MPS, interval still normalised) is shared by all lanes, and the state
+// update + renormalisation is one predicated region so that only byte output really diverges.
+template <int L>
 __global__ void __launch_bounds__(MQ_THREADS)
 k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char *__restrict__ sym_pool,
         unsigned char *mq_pool, const MqTable *__restrict__ g_tab, int ncblks, int nframes,
         size_t sym_stride, size_t mq_stride)
 {
-    __shared__ unsigned tab[48];
-    __shared__ unsigned ctxs[MQ_WARPS][20];
-    __shared__ __align__(16) unsigned char stage[MQ_WARPS][MQ_CHUNK + 16];
+    constexpr int G = 32 / L;                     // lanes per code-block
+    constexpr int R = MQ_CHUNK / (16 * G);        // 16-byte loads per lane and refill
+    constexpr unsigned CM = L == 1 ? 0x1u : (L == 2 ? 0x00010001u : (L == 4 ? 0x01010101u : 0x11111111u));
+    __shared__ __align__(16) uint2 tabn[96];      // pair -> {word after MPS, word after LPS}
+    __shared__ __align__(16) uint4 ctxs[MQ_WARPS * L][20];
+    __shared__ __align__(16) unsigned char stage[MQ_WARPS * L][MQ_CHUNK + 16];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (tid < 47) {
-        const unsigned e = g_tab->e[tid];
-        tab[tid] = ((e & 0xffffu) << 16) | (((e >> 22) & 63u) << 10) | (((e >> 16) & 63u) << 2) | (((e >> 28) & 1u) << 1);
-    }
+    auto word = [&](unsigned pr) { return ((g_tab->e[pr >> 1] & 0xffffu) << 16) | (pr << 3) | (pr & 1u); };
+    auto succ = [&](unsigned pr) {
+        const unsigned e = g_tab->e[pr >> 1], m = pr & 1u;
+        return make_uint2(word(((e >> 16) & 63u) * 2u + m), word(((e >> 22) & 63u) * 2u + (m ^ ((e >> 28) & 1u))));
+    };
+    if (tid < 94) tabn[tid] = succ(tid);
     __syncthreads();
-    const long long job = (long long)blockIdx.x * MQ_WARPS + wid;
-    if (job >= (long long)ncblks * nframes) return;
-    const int cbi = (int)(job / nframes), frame = (int)(job - (long long)cbi * nframes);
+    const int g = lane / G, gl = lane - g * G, blk = wid * L + g;
+    const bool coder = gl == 0;
+    const long long job = ((long long)blockIdx.x * MQ_WARPS + wid) * L + g;
+    const bool valid = job < (long long)ncblks * nframes;
+    // frame varies fastest: the lanes of a warp code the same code-block position of different frames, whose
+    // symbol counts are similar
+    const int cbi = valid ? (int)(job / nframes) : 0, frame = valid ? (int)(job - (long long)cbi * nframes) : 0;
     const CblkDesc cb = cblks[cbi];
     CblkOut *out = cbout + (size_t)frame * ncblks + cbi;
-    const int npasses = out->totalpasses;
-    if (npasses <= 0) return;
-    const unsigned total = out->nsym_end[npasses - 1];
+    const int npasses = valid ? max(out->totalpasses, 0) : 0;
+    const unsigned total = npasses > 0 ? out->nsym_end[npasses - 1] : 0u;
+    unsigned maxtotal = total;
+    for (int o = 16; o > 0; o >>= 1) maxtotal = max(maxtotal, __shfl_xor_sync(0xffffffffu, maxtotal, o));
     const unsigned char *sym = sym_pool + (size_t)frame * sym_stride + cb.sym_off;
 
-    unsigned *cx = ctxs[wid];
-    if (lane < 19) cx[lane] = lane == CTX_UNI ? tab[46] : (lane == CTX_AGG ? tab[3] : (lane == CTX_ZC ? tab[4] : tab[0]));
+    uint4 *cx = ctxs[blk];
+    for (int k = gl; k < 19; k += G) {
+        const unsigned pr = k == CTX_UNI ? 92u : (k == CTX_AGG ? 6u : (k == CTX_ZC ? 8u : 0u));
+        const uint2 nx = tabn[pr];
+        cx[k] = make_uint4(word(pr), nx.x, nx.y, 0);
+    }
+    for (int k = gl; k < 16; k += G) stage[blk][MQ_CHUNK + k] = 0;       // look-ahead slack behind the refill
 
     MqEnc q;
     q.a = 0x8000; q.c = 0; q.ct = 12; q.pos = -1; q.pend = 0;
     q.dst = mq_pool + (size_t)frame * mq_stride + cb.mq_off;
 
-    const mq_saddr sba = MQ_SADDR(stage[wid]), cxa = MQ_SADDR(cx), taba = MQ_OPAQUE(MQ_SADDR(tab));
-    unsigned i = 0, end = out->nsym_end[0];
+    unsigned char *stg = stage[blk];
+    const mq_saddr sba = MQ_SADDR(stg), cxa = MQ_SADDR(cx), taba = MQ_OPAQUE(MQ_SADDR(tabn));
+    unsigned i = 0, end = npasses > 0 ? out->nsym_end[0] : 0xffffffffu;
     int p = 0;
-    uint4 pre = make_uint4(0, 0, 0, 0);
-    if (lane * 16u < total) pre = *(const uint4 *)(sym + lane * 16u);
-    for (unsigned cbeg = 0; cbeg < total; cbeg += MQ_CHUNK) {
+    uint4 pre[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const unsigned o = (gl + r * G) * 16u;
+        pre[r] = o < total ? *(const uint4 *)(sym + o) : make_uint4(0, 0, 0, 0);
+    }
+    for (unsigned cbeg = 0; cbeg < maxtotal; cbeg += MQ_CHUNK) {
         __syncwarp();
-        *(uint4 *)(stage[wid] + lane * 16) = pre;
-        const unsigned nxt = cbeg + MQ_CHUNK + lane * 16u;
-        if (nxt < total) pre = *(const uint4 *)(sym + nxt);
+#pragma unroll
+        for (int r = 0; r < R; ++r) *(uint4 *)(stg + (gl + r * G) * 16) = pre[r];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const unsigned o = cbeg + MQ_CHUNK + (gl + r * G) * 16u;
+            if (o < total) pre[r] = *(const uint4 *)(sym + o);
+        }
         __syncwarp();
-        if (lane == 0) {
-            const unsigned cend = min(cbeg + MQ_CHUNK, total);
-            for (;;) {
-                const unsigned lim = min(end, cend);
-                mq_saddr sp = sba + (i - cbeg);
-                const mq_saddr sp_lim = sba + (lim - cbeg);
-                unsigned sn = mq_ld8(sp);
-                while (sp < sp_lim) {
-                    const unsigned s = sn;
-                    ++sp;
-                    sn = mq_ld8(sp);                      // next symbol in flight (one byte of slack behind the chunk)
-                    const mq_saddr ca = cxa + (s & 0xfcu);
-                    const unsigned w = mq_ld32(ca);
-                    const unsigned qe = w >> 16, lps = (s ^ w) & 1u;
-                    q.a -= qe;
-                    if (!(lps | (~q.a & 0x8000u))) { q.c += qe; continue; }       // MPS, interval still normalised
+        if (!coder) continue;
+        const unsigned cend = min(cbeg + MQ_CHUNK, total);
+        for (;;) {
+            const bool act = i < cend;
+            const unsigned m = __ballot_sync(CM, act);
+            if (m == 0) break;
+            // symbols every active lane can code before one of them reaches a pass end (or the refill ends)
+            unsigned n = act ? min(end, cend) - i : 0xffffffffu;
+            for (int o = G; o < 32; o <<= 1) n = min(n, __shfl_xor_sync(CM, n, o));
+            if (!act) continue;
+            // software pipeline: symbol k + 2 and the context record of symbol k + 1 are in flight while
+            // symbol k is coded; a record changed by symbol k is forwarded when symbol k + 1 uses it too
+            mq_saddr sp = sba + (i - cbeg);
+            unsigned s0 = mq_ld8(sp), s1 = mq_ld8(sp + 1);
+            mq_saddr ca = cxa + ((s0 & 0xfcu) << 2);
+            uint4 r = mq_ld128(ca);
+#pragma unroll 2
+            for (unsigned k = 0; k < n; ++k) {
+                const mq_saddr can = cxa + ((s1 & 0xfcu) << 2);
+                uint4 rn = mq_ld128(can);
+                ++sp;
+                const unsigned s2 = mq_ld8(sp + 1);
+                const unsigned qe = r.x >> 16, lps = (s0 ^ r.x) & 1u;
+                q.a -= qe; q.c += qe;                     // the MPS / no-renormalisation outcome
+                if (lps | (~q.a & 0x8000u)) {
                     // MPS: a < qe ? a = qe : c += qe;  LPS: a < qe ? c += qe : a = qe   (conditional exchange)
-                    if ((unsigned)(q.a < qe) != lps) q.a = qe; else q.c += qe;
-                    const unsigned nx = mq_ld32(taba + ((lps ? (w >> 8) : w) & 0xfcu));
-                    mq_st32(ca, nx | ((w ^ (lps & (w >> 1))) & 1u));
-                    // renormalise: n shifts bring bit 15 of a back up; a byte leaves every time ct reaches 0
-                    int n = __clz((int)q.a) - 16;
-                    q.a <<= n;
-                    while (n >= q.ct) { q.c <<= q.ct; n -= q.ct; mq_byteout(q); }
-                    q.c <<= n; q.ct -= n;
+                    if ((unsigned)(q.a < qe) != lps) { q.a = qe; q.c -= qe; }
+                    const unsigned w = lps ? r.z : r.y;
+                    const uint2 nx = mq_ld64(taba + (w & 0x3f8u));
+                    // renormalise: nsh shifts bring bit 15 of a back up; a byte leaves every time ct reaches 0
+                    int nsh = __clz((int)q.a) - 16;
+                    q.a <<= nsh;
+                    while (nsh >= q.ct) { q.c <<= q.ct; nsh -= q.ct; mq_byteout(q); }
+                    q.c <<= nsh; q.ct -= nsh;
+                    mq_st128(ca, w, nx.x, nx.y);
+                    if (can == ca) { rn.x = w; rn.y = nx.x; rn.z = nx.y; }
                 }
-                i = cbeg + (unsigned)(sp - sba);
-                if (i != end) break;                     // refill exhausted inside the pass
+                s0 = s1; s1 = s2; r = rn; ca = can;
+            }
+            i += n;
+            if (i == end) {
                 mq_pass_end(q, out, p, npasses);
-                if (++p == npasses) break;
-                end = out->nsym_end[p];
+                end = ++p < npasses ? out->nsym_end[p] : 0xffffffffu;
             }
         }
     }
-    if (lane != 0) return;
+    if (!coder || npasses <= 0) return;
     for (; p < npasses; ++p) mq_pass_end(q, out, p, npasses);
     // final pending byte (beyond numbytes) is never part of the stream
     int last = q.pos;

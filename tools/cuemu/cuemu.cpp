@@ -3,6 +3,7 @@
 #include <stdio.h>
 #include <time.h>
 #include <ucontext.h>
+#include <map>
 #include <vector>
 
 cuemu_dim3 threadIdx, blockIdx, blockDim, gridDim;
@@ -21,7 +22,9 @@ const std::function<void()> *g_body = nullptr;
 int bar_arrived = 0; unsigned bar_gen = 0; int bar_acc[2] = {0, 0};
 // per-warp rendezvous
 struct WarpSync { int arrived; unsigned gen; uint64_t slot[2][32]; unsigned ballot[2]; };
-std::vector<WarpSync> warps;
+// one rendezvous state per (warp, participant mask): groups of lanes with different masks may be
+// waiting at different rendezvous at the same time
+std::vector<std::map<unsigned, WarpSync>> warps;
 
 int linear_tid(const dim3 &t) { return (int)(t.x + blockDim.x * (t.y + blockDim.y * t.z)); }
 
@@ -57,7 +60,7 @@ void cuemu_launch(dim3 grid, dim3 block, size_t dyn_smem, const std::function<vo
             for (unsigned bx = 0; bx < grid.x; ++bx) {
                 blockIdx = dim3(bx, by, bz);
                 fibers.assign((size_t)nthreads, Fiber());
-                warps.assign((size_t)(nthreads + 31) / 32, WarpSync());
+                warps.assign((size_t)(nthreads + 31) / 32, std::map<unsigned, WarpSync>());
                 bar_arrived = 0; nalive = nthreads;
                 for (int t = 0; t < nthreads; ++t) {
                     Fiber &f = fibers[t];
@@ -99,12 +102,12 @@ int __syncthreads_or(int pred) { return cta_barrier(pred, 0) != 0; }
 int __syncthreads_count(int pred) { return cta_barrier(pred, 1); }
 int __syncthreads_and(int pred) { return cta_barrier(pred, 2); }
 
-// warp rendezvous among the lanes named in mask; returns generation used
-static unsigned warp_rendezvous(unsigned mask, uint64_t v, int pred)
+// warp rendezvous among the lanes named in mask; returns the state and the generation used
+static WarpSync &warp_rendezvous(unsigned mask, uint64_t v, int pred, unsigned &g)
 {
     int t = linear_tid(threadIdx), w = t / 32, lane = t % 32;
-    WarpSync &ws = warps[w];
-    unsigned g = ws.gen;
+    WarpSync &ws = warps[w][mask];
+    g = ws.gen;
     if (ws.arrived == 0) ws.ballot[g & 1] = 0;
     ws.slot[g & 1][lane] = v;
     if (pred) ws.ballot[g & 1] |= 1u << lane;
@@ -116,21 +119,23 @@ static unsigned warp_rendezvous(unsigned mask, uint64_t v, int pred)
         if (ws.arrived >= need) { ws.gen++; ws.arrived = 0; break; }
         yield_fiber();
     }
-    return g;
+    return ws;
 }
 
-void __syncwarp(unsigned mask) { warp_rendezvous(mask, 0, 0); }
+void __syncwarp(unsigned mask) { unsigned g; warp_rendezvous(mask, 0, 0, g); }
 unsigned __ballot_sync(unsigned mask, int pred)
 {
-    unsigned g = warp_rendezvous(mask, 0, pred);
-    return warps[linear_tid(threadIdx) / 32].ballot[g & 1] & mask;
+    unsigned g;
+    WarpSync &ws = warp_rendezvous(mask, 0, pred, g);
+    return ws.ballot[g & 1] & mask;
 }
 int __any_sync(unsigned mask, int pred) { return __ballot_sync(mask, pred) != 0; }
 int __all_sync(unsigned mask, int pred) { return __ballot_sync(mask, !pred) == 0; }
 uint64_t cuemu_shfl_partial(unsigned mask, uint64_t v, int src)
 {
-    unsigned g = warp_rendezvous(mask, v, 0);
-    return warps[linear_tid(threadIdx) / 32].slot[g & 1][src & 31];
+    unsigned g;
+    WarpSync &ws = warp_rendezvous(mask, v, 0, g);
+    return ws.slot[g & 1][src & 31];
 }
 uint64_t cuemu_shfl(uint64_t v, int src) { return cuemu_shfl_partial(0xffffffffu, v, src); }
 
