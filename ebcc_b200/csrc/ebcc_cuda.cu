@@ -250,6 +250,7 @@ struct ebcc_cuda_ctx {
     int *d_scratch;            // [B][H][W] per-probe real decodes of blocks the recording cannot serve
     unsigned char *d_spass;    // [B][H][W] pass in which each sample became significant (recording)
     DecState *d_dstate;        // [B][ncblks]
+    unsigned *d_decsave;       // [B][ncblks][DEC_SAVE_WORDS] decoder state of each block's recording (resumed by later probes)
     int use_recording;
     float *d_dcoef;            // [B][H][W] dequantised coefficients / IDWT work plane
     float *d_dec;              // [B][H][W] decoded frames
@@ -341,8 +342,8 @@ static void free_buffers(ebcc_cuda_ctx *c)
     cudaFree(c->d_maxlen); cudaFree(c->d_body_off); cudaFree(c->d_pout); cudaFree(c->d_offs);
     cudaFreeHost(c->h_pout); cudaFreeHost(c->h_stat); cudaFreeHost(c->h_offs); cudaFreeHost(c->h_maxlen);
     cudaFreeHost(c->h_packed); cudaFreeHost(c->h_stage);
-    cudaFree(c->d_streams); cudaFree(c->d_slens); cudaFree(c->d_status); cudaFree(c->d_jobs); cudaFree(c->d_iplane); cudaFree(c->d_scratch); cudaFree(c->d_spass); cudaFree(c->d_dstate);
-    c->d_scratch = NULL; c->d_spass = NULL; c->d_dstate = NULL;
+    cudaFree(c->d_streams); cudaFree(c->d_slens); cudaFree(c->d_status); cudaFree(c->d_jobs); cudaFree(c->d_iplane); cudaFree(c->d_scratch); cudaFree(c->d_spass); cudaFree(c->d_dstate); cudaFree(c->d_decsave);
+    c->d_scratch = NULL; c->d_spass = NULL; c->d_dstate = NULL; c->d_decsave = NULL;
     cudaFree(c->d_dcoef); cudaFree(c->d_dec); cudaFree(c->d_es); cudaFree(c->d_targets);
     cudaFreeHost(c->h_es); cudaFreeHost(c->h_status); cudaFreeHost(c->h_slens); cudaFreeHost(c->h_targets); cudaFreeHost(c->h_streams);
     c->d_streams = NULL; c->d_slens = c->d_status = NULL; c->d_jobs = NULL; c->d_iplane = NULL; c->d_dcoef = c->d_dec = NULL;
@@ -420,6 +421,7 @@ extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nf
     CK(cudaMalloc((void **)&c->d_scratch, B * N * sizeof(int)));
     CK(cudaMalloc((void **)&c->d_spass, B * N));
     CK(cudaMalloc((void **)&c->d_dstate, B * pl->ncblks * sizeof(DecState)));
+    CK(cudaMalloc((void **)&c->d_decsave, B * pl->ncblks * (size_t)DEC_SAVE_WORDS * sizeof(unsigned)));
     CK(cudaMalloc((void **)&c->d_dcoef, B * N * sizeof(float)));
     CK(cudaMalloc((void **)&c->d_dec, B * N * sizeof(float)));
     CK(cudaMalloc((void **)&c->d_es, B * sizeof(ErrStat)));
@@ -599,7 +601,8 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
     const bool probe = orig != NULL;         // probe of the CR search: jobs come from the encoder, the recording is used
     EBCC_LAUNCH(k_t1_dec, dim3((unsigned)((njobs + DEC_WARPS - 1) / DEC_WARPS)), dim3(DEC_WARPS * 32), 0, c->stream,
                 c->d_cblks, c->d_jobs, pool, pool_stride, c->d_declut, c->d_iplane, probe ? c->d_spass : (unsigned char *)NULL, c->d_scratch,
-                probe ? (const CblkOut *)c->d_cbout : (const CblkOut *)NULL, probe ? c->d_dstate : (DecState *)NULL, W, H, pl->ncblks, B);
+                probe ? (const CblkOut *)c->d_cbout : (const CblkOut *)NULL, probe ? c->d_dstate : (DecState *)NULL,
+                probe ? c->d_decsave : (unsigned *)NULL, W, H, pl->ncblks, B);
     if (probe)
         EBCC_LAUNCH(k_recon_dequant, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_plan, c->d_cbout, c->d_dstate, c->d_jobs,
                     c->d_iplane, c->d_spass, c->d_scratch, c->d_dcoef);

@@ -17,14 +17,23 @@
 #include "k_t1.cuh"
 #include "k_t2.cuh"
 
-// mode: 0 = nothing to do, 1 = decode into the recording plane (iplane + pass-of-significance plane),
-//       2 = decode into the scratch plane (a truncation the recording cannot reproduce, see DecState)
+// mode: 0 = nothing to do, 1 = decode into the recording plane (iplane + pass-of-significance plane), continuing
+//       the block's saved decoder state if it has one,
+//       2 = decode into the scratch plane (a truncation the recording cannot reproduce, see DecState),
+//       3 = the scratch plane already holds exactly this decode (same block, same pass count)
 struct DecJob { int np; int numbps; unsigned off; int len; int mode; int pad; };
 
-// What the recording of a block holds (compression-ratio search): np_dec passes were decoded; bit p of bad[] is set
-// when "decode only passes 0..p from the segment truncated at rate[p]" is NOT proven identical to the first p+1
-// passes of the recorded decode (OPJ truncates non-terminated MQ segments at numbytes+3, which is not always enough).
-struct DecState { int np_dec; int pad; unsigned bad[4]; };
+// What the recording of a block holds (compression-ratio search): np_dec passes were decoded FROM THE COMPLETE
+// SEGMENT (all passes the encoder produced), so a later probe that needs more passes continues where the recording
+// stopped (decoder state in the save area).  Bit p of bad[] is set when "decode only passes 0..p from the segment
+// truncated at rate[p]" is NOT proven identical to the first p+1 passes of the recorded decode (OPJ truncates
+// non-terminated MQ segments at numbytes+3, which is not always enough).  scratch_np: pass count of the real
+// truncated decode the scratch plane currently holds for this block (0 = none).
+struct DecState { int np_dec; int scratch_np; unsigned bad[4]; };
+
+// per-block save area of a recording (32-bit words): flag words, then the serial decoder's registers
+#define DEC_SAVE_MQ DEC_FWORDS_C
+#define DEC_SAVE_WORDS 1280
 
 // decoder-side LUTs: zero-coding context by (orient, 9-bit neighbourhood), filled by the host with
 // the same Annex-D rule the encoder evaluates arithmetically (t1_zc_ctx)
@@ -35,6 +44,7 @@ struct DecLuts {
 
 #define DEC_FW 66
 #define DEC_FWORDS (18 * DEC_FW)
+#define DEC_FWORDS_C (18 * 66)
 #define DEC_WARPS 4
 #define DEC_NSHADOW 3
 
@@ -284,13 +294,70 @@ __device__ void t1d_refpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
     }
 }
 
-// grid = ceil(ncblks * nframes / DEC_WARPS) CTAs of DEC_WARPS warps.  Every job with mode != 0 first clears its block
-// region of the target plane (mode 1: iplane + spass, mode 2: scratch), then lane 0 decodes.  cbout != nullptr enables
-// the truncation shadows (rates come from the encoder's pass table) and dstate receives the verdicts.
+// coding passes p0 .. p1-1 of one block (pass 0 = cleanup of the top bit-plane, then sig / ref / cleanup per plane).
+// rates != nullptr: truncation shadows for the cuts rates[0 .. nrates-1]; the verdict of cut p lands in ds.bad when
+// pass p ends.
+__device__ void t1d_passes(T1DecState &S, MqDec &q, int w, int h, int numbps, int p0, int p1,
+                           const int *rates, int nrates, DecState &ds)
+{
+    for (int p = p0; p < p1; ++p) {
+        const int passtype = p == 0 ? 2 : (p - 1) % 3, bpno = p == 0 ? numbps - 1 : numbps - 2 - (p - 1) / 3;
+        if (bpno < 0) break;
+        S.pass = p;
+        if (passtype == 0) t1d_sigpass(S, q, w, h, bpno);
+        else if (passtype == 1) t1d_refpass(S, q, w, h, bpno);
+        else t1d_clnpass(S, q, w, h, bpno);
+        if (rates) {
+            // verdict for "stop after pass p": slot 0.  Not forked => the decoder never looked beyond the cut.
+            if ((q.sh_bad & 1u) && p < 128) ds.bad[p >> 5] |= 1u << (p & 31);
+            // retire slot 0, shift the others down, arm a new last slot
+#pragma unroll
+            for (int j = 0; j + 1 < DEC_NSHADOW; ++j) { q.sh[j] = q.sh[j + 1]; q.trunc[j] = q.trunc[j + 1]; }
+            q.sh_on >>= 1; q.sh_bad >>= 1;
+            const int pn = p + DEC_NSHADOW;
+            const int tn = pn < nrates ? rates[pn] : -1;
+            q.trunc[DEC_NSHADOW - 1] = tn;
+            if (tn >= 0 && tn <= q.maxread) { q.sh_on |= 1u << (DEC_NSHADOW - 1); q.sh_bad |= 1u << (DEC_NSHADOW - 1); }
+        }
+    }
+}
+
+// serial decoder registers <-> save area
+__device__ __forceinline__ void mqd_save(const MqDec &q, const unsigned char *cx, unsigned *o)
+{
+    int k = 0;
+    o[k++] = q.a; o[k++] = q.m.c; o[k++] = q.m.ct; o[k++] = (unsigned)q.m.bp; o[k++] = (unsigned)q.m.len; o[k++] = q.m.cur;
+#pragma unroll
+    for (int j = 0; j < DEC_NSHADOW; ++j) {
+        o[k++] = q.sh[j].c; o[k++] = q.sh[j].ct; o[k++] = (unsigned)q.sh[j].bp; o[k++] = (unsigned)q.sh[j].len; o[k++] = q.sh[j].cur;
+        o[k++] = (unsigned)q.trunc[j];
+    }
+    o[k++] = q.sh_on; o[k++] = q.sh_bad; o[k++] = (unsigned)q.maxread;
+    for (int i = 0; i < 20; i += 4) o[k++] = cx[i] | (cx[i + 1] << 8) | (cx[i + 2] << 16) | ((unsigned)cx[i + 3] << 24);
+}
+__device__ __forceinline__ void mqd_load(MqDec &q, unsigned char *cx, const unsigned *o)
+{
+    int k = 0;
+    q.a = o[k++]; q.m.c = o[k++]; q.m.ct = o[k++]; q.m.bp = (int)o[k++]; q.m.len = (int)o[k++]; q.m.cur = o[k++];
+#pragma unroll
+    for (int j = 0; j < DEC_NSHADOW; ++j) {
+        q.sh[j].c = o[k++]; q.sh[j].ct = o[k++]; q.sh[j].bp = (int)o[k++]; q.sh[j].len = (int)o[k++]; q.sh[j].cur = o[k++];
+        q.trunc[j] = (int)o[k++];
+    }
+    q.sh_on = o[k++]; q.sh_bad = o[k++]; q.maxread = (int)o[k++];
+    for (int i = 0; i < 20; i += 4) { const unsigned v = o[k++]; cx[i] = v & 0xff; cx[i + 1] = (v >> 8) & 0xff; cx[i + 2] = (v >> 16) & 0xff; cx[i + 3] = v >> 24; }
+}
+
+// grid = ceil(ncblks * nframes / DEC_WARPS) CTAs of DEC_WARPS warps; lane 0 of a warp decodes, the warp moves state.
+//   plain decode (ebcc_decode; cbout == nullptr): mode-1 jobs from k_t2_parse, decoded into iplane.
+//   CR search (cbout, dstate, save given): mode 1 continues the block's recording from the complete segment up to
+//   jb.np passes with truncation shadows; if the cut this probe needs turns out not to be reproducible the warp
+//   decodes the truncated segment for real into the scratch plane right away (job becomes mode 2).  Mode 2 does only
+//   that.  The block region of a plane is cleared before a decode that starts at pass 0.
 __global__ void __launch_bounds__(DEC_WARPS * 32)
-k_t1_dec(const CblkDesc *__restrict__ cblks, const DecJob *__restrict__ jobs, const unsigned char *__restrict__ pool,
+k_t1_dec(const CblkDesc *__restrict__ cblks, DecJob *jobs, const unsigned char *__restrict__ pool,
          size_t pool_stride, const DecLuts *__restrict__ g_luts, int *iplane, unsigned char *spass, int *scratch,
-         const CblkOut *__restrict__ cbout, DecState *dstate, int W, int H, int ncblks, int nframes)
+         const CblkOut *__restrict__ cbout, DecState *dstate, unsigned *save, int W, int H, int ncblks, int nframes)
 {
     __shared__ unsigned F[DEC_WARPS][DEC_FWORDS];
     __shared__ unsigned char cxs[DEC_WARPS][32];
@@ -299,77 +366,97 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const DecJob *__restrict__ jobs, co
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int i = tid; i < 94; i += blockDim.x) tab[i] = g_luts->mq[i];
     for (int i = tid; i < 4 * 512; i += blockDim.x) zc[i] = g_luts->zc[i];
-    const long long job = (long long)blockIdx.x * DEC_WARPS + warp;
-    const bool live = job < (long long)ncblks * nframes;
-    int frame = 0, cbi = 0;
-    DecJob jb; jb.np = 0; jb.numbps = 0; jb.off = 0; jb.len = 0; jb.mode = 0; jb.pad = 0;
-    if (live) {
-        // frame varies fastest so that the warps of a CTA (and neighbouring CTAs) hold blocks of similar length
-        cbi = (int)(job / nframes); frame = (int)(job - (long long)cbi * nframes);
-        jb = jobs[(size_t)frame * ncblks + cbi];
-    }
-    const bool work = live && jb.mode != 0;
-    CblkDesc cb;
-    if (work) {
-        cb = cblks[cbi];
-        for (int i = lane; i < DEC_FWORDS; i += 32) F[warp][i] = 0;
-        // clear the block's region of the target plane(s)
-        int *dst = (jb.mode == 1 ? iplane : scratch) + (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx;
-        unsigned char *sp = (jb.mode == 1 && spass) ? spass + (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx : nullptr;
-        for (int i = lane; i < cb.w * cb.h; i += 32) {
-            const int y = i / cb.w, x = i - y * cb.w;
-            dst[(size_t)y * W + x] = 0;
-            if (sp) sp[(size_t)y * W + x] = 255;
-        }
-    }
     __syncthreads();
-    if (!work || lane != 0) return;
+    const long long job = (long long)blockIdx.x * DEC_WARPS + warp;
+    if (job >= (long long)ncblks * nframes) return;
+    // frame varies fastest so that the warps of a CTA (and neighbouring CTAs) hold blocks of similar length
+    const int cbi = (int)(job / nframes), frame = (int)(job - (long long)cbi * nframes);
+    const size_t bi = (size_t)frame * ncblks + cbi;
+    const DecJob jb = jobs[bi];
+    if (jb.mode != 1 && jb.mode != 2) return;
+    const CblkDesc cb = cblks[cbi];
+    const bool search = cbout != nullptr && dstate != nullptr && save != nullptr;
+    DecState ds; ds.np_dec = 0; ds.scratch_np = 0; ds.bad[0] = ds.bad[1] = ds.bad[2] = ds.bad[3] = 0;
+    if (search) ds = dstate[bi];
+    unsigned *sv = search ? save + bi * DEC_SAVE_WORDS : nullptr;
+    const size_t o = (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx;
+    const unsigned char *seg = pool + (size_t)frame * pool_stride + jb.off;
+    unsigned char *cx = cxs[warp];
+    T1DecState S;
+    S.F = F[warp]; S.cx = cx; S.zc = zc + cb.orient * 512; S.tab = tab; S.W = W; S.pass = 0;
+    int mode = jb.mode;
 
-    DecState ds; ds.np_dec = 0; ds.pad = 0; ds.bad[0] = ds.bad[1] = ds.bad[2] = ds.bad[3] = 0;
-    DecState *dsp = (dstate && jb.mode == 1) ? dstate + (size_t)frame * ncblks + cbi : nullptr;
-    if (jb.np > 0 && jb.numbps > 0) {
-        unsigned char *cx = cxs[warp];
-        for (int i = 0; i < 19; ++i) cx[i] = 0;
-        cx[CTX_UNI] = 46 << 1; cx[CTX_AGG] = 3 << 1; cx[CTX_ZC] = 4 << 1;
-        T1DecState S;
-        S.F = F[warp]; S.cx = cx; S.zc = zc + cb.orient * 512; S.tab = tab; S.W = W; S.pass = 0;
-        const size_t o = (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx;
-        S.plane = (jb.mode == 1 ? iplane : scratch) + o;
-        S.spass = (jb.mode == 1 && spass) ? spass + o : nullptr;
-        MqDec q;
-        mqd_init(q, pool + (size_t)frame * pool_stride + jb.off, jb.len);
-        const int *rates = (cbout && jb.mode == 1) ? cbout[(size_t)frame * ncblks + cbi].rate : nullptr;
-        if (rates) {
-#pragma unroll
-            for (int j = 0; j < DEC_NSHADOW; ++j) {
-                q.trunc[j] = j < jb.np - 1 ? rates[j] : -1;
-                // cuts inside the two bytes the decoder reads while initialising cannot fork any more
-                if (q.trunc[j] >= 0 && q.trunc[j] <= q.maxread) { q.sh_on |= 1u << j; q.sh_bad |= 1u << j; }
+    if (mode == 1) {
+        const bool resume = search && ds.np_dec > 0;
+        if (resume) {
+            for (int i = lane; i < DEC_FWORDS; i += 32) F[warp][i] = sv[i];
+        } else {
+            for (int i = lane; i < DEC_FWORDS; i += 32) F[warp][i] = 0;
+            for (int i = lane; i < cb.w * cb.h; i += 32) {
+                const int y = i / cb.w, x = i - y * cb.w;
+                iplane[o + (size_t)y * W + x] = 0;
+                if (spass) spass[o + (size_t)y * W + x] = 255;
             }
         }
-        int bpno = jb.numbps - 1, passtype = 2;
-        for (int p = 0; p < jb.np && bpno >= 0; ++p) {
-            S.pass = p;
-            if (passtype == 0) t1d_sigpass(S, q, cb.w, cb.h, bpno);
-            else if (passtype == 1) t1d_refpass(S, q, cb.w, cb.h, bpno);
-            else t1d_clnpass(S, q, cb.w, cb.h, bpno);
-            if (++passtype == 3) { passtype = 0; bpno--; }
-            if (rates && p < jb.np - 1) {
-                // verdict for "stop after pass p": slot 0.  Not forked => the decoder never looked beyond the cut.
-                if ((q.sh_bad & 1u) && p < 128) ds.bad[p >> 5] |= 1u << (p & 31);
-                // retire slot 0, shift the others down, arm a new last slot
+        __syncwarp();
+        if (lane == 0 && jb.np > 0 && jb.numbps > 0) {
+            S.plane = iplane + o; S.spass = spass ? spass + o : nullptr;
+            MqDec q;
+            const int *rates = search ? cbout[bi].rate : nullptr;
+            const int nrates = search ? cbout[bi].totalpasses : 0;
+            if (resume) { mqd_load(q, cx, sv + DEC_SAVE_MQ); q.data = seg; }
+            else {
+                for (int i = 0; i < 20; ++i) cx[i] = 0;
+                cx[CTX_UNI] = 46 << 1; cx[CTX_AGG] = 3 << 1; cx[CTX_ZC] = 4 << 1;
+                mqd_init(q, seg, jb.len);
+                if (rates) {
 #pragma unroll
-                for (int j = 0; j + 1 < DEC_NSHADOW; ++j) { q.sh[j] = q.sh[j + 1]; q.trunc[j] = q.trunc[j + 1]; }
-                q.sh_on >>= 1; q.sh_bad >>= 1;
-                const int pn = p + DEC_NSHADOW;
-                const int tn = pn < jb.np - 1 ? rates[pn] : -1;
-                q.trunc[DEC_NSHADOW - 1] = tn;
-                if (tn >= 0 && tn <= q.maxread) { q.sh_on |= 1u << (DEC_NSHADOW - 1); q.sh_bad |= 1u << (DEC_NSHADOW - 1); }
+                    for (int j = 0; j < DEC_NSHADOW; ++j) {
+                        q.trunc[j] = j < nrates ? rates[j] : -1;
+                        // cuts inside the two bytes the decoder reads while initialising cannot fork any more
+                        if (q.trunc[j] >= 0 && q.trunc[j] <= q.maxread) { q.sh_on |= 1u << j; q.sh_bad |= 1u << j; }
+                    }
+                }
             }
+            t1d_passes(S, q, cb.w, cb.h, jb.numbps, ds.np_dec, jb.np, rates, nrates, ds);
+            ds.np_dec = jb.np;
+            if (search) mqd_save(q, cx, sv + DEC_SAVE_MQ);
         }
-        ds.np_dec = jb.np;
+        __syncwarp();
+        if (!search) return;
+        for (int i = lane; i < DEC_FWORDS; i += 32) sv[i] = F[warp][i];
+        // the cut this probe needs: rate[np - 1]
+        int need = 0;
+        if (lane == 0) {
+            const int pc = jb.np - 1;
+            need = jb.np > 0 && (pc >= 128 || ((ds.bad[pc >> 5] >> (pc & 31)) & 1u));
+            if (need && ds.scratch_np == jb.np) { need = 0; jobs[bi].mode = 3; }
+        }
+        need = __shfl_sync(0xffffffffu, need, 0);
+        if (!need) { if (lane == 0) dstate[bi] = ds; return; }
+        mode = 2;
+        __syncwarp();
     }
-    if (dsp) *dsp = ds;
+
+    // mode 2: real decode of the segment cut at rate[np - 1] into the scratch plane
+    for (int i = lane; i < DEC_FWORDS; i += 32) F[warp][i] = 0;
+    for (int i = lane; i < cb.w * cb.h; i += 32) {
+        const int y = i / cb.w, x = i - y * cb.w;
+        scratch[o + (size_t)y * W + x] = 0;
+    }
+    __syncwarp();
+    if (lane != 0) return;
+    if (jb.np > 0 && jb.numbps > 0) {
+        for (int i = 0; i < 20; ++i) cx[i] = 0;
+        cx[CTX_UNI] = 46 << 1; cx[CTX_AGG] = 3 << 1; cx[CTX_ZC] = 4 << 1;
+        S.plane = scratch + o; S.spass = nullptr;
+        MqDec q;
+        mqd_init(q, seg, search ? cbout[bi].rate[jb.np - 1] : jb.len);
+        DecState dummy = ds;
+        t1d_passes(S, q, cb.w, cb.h, jb.numbps, 0, jb.np, nullptr, 0, dummy);
+    }
+    if (search) { ds.scratch_np = jb.np; dstate[bi] = ds; }
+    if (jb.mode == 1) jobs[bi].mode = 2;
 }
 
 // decode jobs for the encoder's own allocation (compression-ratio search).  Block k is recorded (mode 1) when the
@@ -383,15 +470,16 @@ __global__ void k_jobs_from_enc(const CblkDesc *__restrict__ cblks, const CblkOu
     const int k = (int)(i % ncblks);
     const CblkOut &c = cbout[i];
     DecJob j;
-    j.np = c.numpasses; j.numbps = c.numbps; j.off = cblks[k].mq_off; j.pad = 0;
-    j.len = c.numpasses > 0 ? c.rate[c.numpasses - 1] : 0;
+    const int np = c.numpasses;
+    j.np = np; j.numbps = c.numbps; j.off = cblks[k].mq_off; j.pad = 0;
+    j.len = np > 0 ? c.rate[np - 1] : 0;
     if (!use_recording) j.mode = 2;
+    else if (np == 0) j.mode = 0;
     else {
         const DecState &d = dstate[i];
-        const int np = c.numpasses;
-        if (np > d.np_dec) j.mode = 1;
-        else if (np == d.np_dec || np == 0) j.mode = 0;
-        else j.mode = ((np - 1) < 128 && ((d.bad[(np - 1) >> 5] >> ((np - 1) & 31)) & 1u)) || (np - 1) >= 128 ? 2 : 0;
+        if (np > d.np_dec) { j.mode = 1; j.len = c.datalen; }          // record (on) from the complete segment
+        else if ((np - 1) < 128 && !((d.bad[(np - 1) >> 5] >> ((np - 1) & 31)) & 1u)) j.mode = 0;
+        else j.mode = d.scratch_np == np ? 3 : 2;
     }
     jobs[i] = j;
 }
@@ -399,7 +487,7 @@ __global__ void k_jobs_from_enc(const CblkDesc *__restrict__ cblks, const CblkOu
 __global__ void k_dstate_reset(DecState *d, long long n)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) { d[i].np_dec = 0; d[i].pad = 0; d[i].bad[0] = d[i].bad[1] = d[i].bad[2] = d[i].bad[3] = 0; }
+    if (i < n) { d[i].np_dec = 0; d[i].scratch_np = 0; d[i].bad[0] = d[i].bad[1] = d[i].bad[2] = d[i].bad[3] = 0; }
 }
 
 // Probe reconstruction: integer tier-1 output of "the first numpasses passes" for every sample, taken from the
@@ -427,7 +515,7 @@ __global__ void k_recon_dequant(const Plan *__restrict__ plan, const CblkOut *__
         const int k = bd.first_cblk + ((y - bd.offy) >> 6) * bd.cw + ((x - bd.offx) >> 6);
         const size_t bi = (size_t)frame * ncblks + k, si = (size_t)frame * n + i;
         int v;
-        if (jobs[bi].mode == 2) v = scratch[si];
+        if (jobs[bi].mode >= 2) v = scratch[si];
         else {
             const int np = cbout[bi].numpasses, npd = dstate[bi].np_dec;
             v = np > 0 ? iplane[si] : 0;            // a block that was never included has no recording
