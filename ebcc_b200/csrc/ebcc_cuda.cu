@@ -273,7 +273,6 @@ struct ebcc_cuda_ctx {
     size_t zstride;
     unsigned *d_zlen, *h_zlen, *d_zsrc_len, *h_zsrc_len;
     unsigned char *d_zin, *h_zin;   // [B][zstride] zstd frames to decode (decode path)
-    ZEncWork *d_zenc_work;
     unsigned char *d_zblk;
     unsigned *d_zblen;
     int zmaxchunks;
@@ -352,8 +351,8 @@ static void free_buffers(ebcc_cuda_ctx *c)
     cudaFree(c->sp.lis0); cudaFree(c->sp.lis1); cudaFree(c->sp.sign_pos); cudaFree(c->sp.lsp_idx); cudaFree(c->sp.bits);
     cudaFree(c->d_sp_img0); cudaFree(c->d_sp_img1); cudaFree(c->d_sp_info); cudaFree(c->d_sp_P); cudaFree(c->d_sp_budget);
     cudaFree(c->d_sp_active); cudaFree(c->d_sp_rmm); cudaFree(c->d_es2); cudaFree(c->d_zout); cudaFree(c->d_zlen); cudaFree(c->d_zsrc_len);
-    cudaFree(c->d_zin); cudaFree(c->d_zenc_work); cudaFree(c->d_zblk); cudaFree(c->d_zblen); c->d_zblk = NULL; c->d_zblen = NULL; cudaFree(c->d_zdec_work); cudaFree(c->d_zcap); cudaFreeHost(c->h_zcap);
-    c->d_zenc_work = NULL; c->d_zdec_work = NULL; c->d_zcap = NULL; c->h_zcap = NULL;
+    cudaFree(c->d_zin); cudaFree(c->d_zblk); cudaFree(c->d_zblen); c->d_zblk = NULL; c->d_zblen = NULL; cudaFree(c->d_zdec_work); cudaFree(c->d_zcap); cudaFreeHost(c->h_zcap);
+    c->d_zdec_work = NULL; c->d_zcap = NULL; c->h_zcap = NULL;
     cudaFreeHost(c->h_sp_info); cudaFreeHost(c->h_sp_P); cudaFreeHost(c->h_sp_budget); cudaFreeHost(c->h_sp_active);
     cudaFreeHost(c->h_sp_rmm); cudaFreeHost(c->h_es2); cudaFreeHost(c->h_zout); cudaFreeHost(c->h_zlen); cudaFreeHost(c->h_zsrc_len);
     cudaFreeHost(c->h_zin);
@@ -448,7 +447,7 @@ extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nf
         CK(cudaMalloc((void **)&c->d_zout, B * c->zstride)); CK(cudaMalloc((void **)&c->d_zlen, B * 4)); CK(cudaMalloc((void **)&c->d_zsrc_len, B * 4));
         CK(cudaMalloc((void **)&c->d_zin, B * c->zstride));
         c->zmaxchunks = (int)((c->sp.bits_words * 4 + Z_CHUNK - 1) / Z_CHUNK);
-        CK(cudaMalloc((void **)&c->d_zenc_work, B * c->zmaxchunks * sizeof(ZEncWork)));
+        CK(cudaFuncSetAttribute(k_zstd_compress_chunks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ZEncWork)));
         CK(cudaMalloc((void **)&c->d_zblk, B * c->zmaxchunks * (size_t)Z_BLK_STRIDE)); CK(cudaMalloc((void **)&c->d_zblen, B * c->zmaxchunks * 4)); CK(cudaMalloc((void **)&c->d_zdec_work, B * sizeof(ZDecWork)));
         CK(cudaMalloc((void **)&c->d_zcap, B * 4)); CK(cudaMallocHost((void **)&c->h_zcap, B * 4));
         CK(cudaMallocHost((void **)&c->h_sp_info, B * sizeof(SpInfo))); CK(cudaMallocHost((void **)&c->h_sp_P, B * 4)); CK(cudaMallocHost((void **)&c->h_sp_budget, B * 4));
@@ -788,8 +787,8 @@ extern "C" int ebcc_cuda_residual_pack(ebcc_cuda_ctx *c, size_t nframes, const s
     size_t maxn = 0;
     for (int i = 0; i < B; ++i) if (coeffs_size[i] > maxn) maxn = coeffs_size[i];
     const int nch = (int)((maxn + Z_CHUNK - 1) / Z_CHUNK);
-    EBCC_LAUNCH(k_zstd_compress_chunks, dim3((unsigned)nch, (unsigned)B), dim3(ZC_THREADS), 0, c->stream, (const unsigned char *)c->sp.bits,
-                c->sp.bits_words * 4, c->d_zsrc_len, c->d_zblk, c->d_zblen, c->zmaxchunks, c->d_zenc_work);
+    EBCC_LAUNCH(k_zstd_compress_chunks, dim3((unsigned)nch, (unsigned)B), dim3(ZC_THREADS), sizeof(ZEncWork), c->stream, (const unsigned char *)c->sp.bits,
+                c->sp.bits_words * 4, c->d_zsrc_len, c->d_zblk, c->d_zblen, c->zmaxchunks);
     EBCC_LAUNCH(k_zstd_assemble, dim3((unsigned)B), dim3(256), 0, c->stream, c->d_zblk, c->d_zblen, c->zmaxchunks, c->d_zsrc_len, c->d_zout,
                 c->zstride, c->d_zlen);
     c->launches++;

@@ -405,16 +405,24 @@ __device__ __forceinline__ int zw_close(ZBitW &b)
     return b.err ? -1 : b.pos;
 }
 
-struct ZSeq { unsigned ll, ml; };          // literal run length, match length (offset is always the repeat offset 1)
-
+// Working set of one block of the compressor, in shared memory (one warp per block).
 struct ZEncWork {
-    unsigned char lit[Z_CHUNK];
-    ZSeq seq[Z_CHUNK / 4 + 8];
+    unsigned char lit[Z_CHUNK + 16];     // the chunk, compacted in place to its literals
+    unsigned short sll[Z_CHUNK / 5 + 8]; // sequences: literal run length, match length (offset: always repeat offset 1)
+    unsigned short sml[Z_CHUNK / 5 + 8];
     ZFseEntry ll[64], ml[64], wt[64];
     unsigned hist[256];
+    unsigned key[256];                   // Huffman build: weight << 8 | symbol
+    unsigned short order[256];           // symbols by ascending weight
+    unsigned nwt[512];                   // node weights (leaves in sorted order, then internal nodes)
+    short parent[512];
+    unsigned char depth[512];
     unsigned char nbits[256];
     unsigned short code[256];
-    unsigned char tmp[2 * Z_CHUNK + 1024];
+    unsigned char weights[256];
+    unsigned char tmp[Z_CHUNK + 1024];   // tree description and the Huffman streams
+    unsigned char out[Z_CHUNK + 32];     // the block being built (header + body)
+    int v[16];                           // scalars handed from one phase to the next
 };
 
 // tANS encode step through the decoding table: find the entry of symbol s whose state interval contains x
@@ -449,31 +457,54 @@ __device__ __forceinline__ int z_ml_code(unsigned v)
     return c;
 }
 
-// Huffman code lengths (<= Z_HUF_MAXLOG) for hist[0..255]; returns number of used symbols.  Length limiting by
-// flattening the histogram and rebuilding keeps the code complete (Kraft sum exactly 1), which the implicit last
-// weight of the tree description relies on.
-__device__ int z_huf_lengths(const unsigned *hist, unsigned char *nbits)
+// Huffman code lengths (<= Z_HUF_MAXLOG) for w->hist[0..255] into w->nbits; returns number of used symbols.  Called by
+// the whole warp.  Symbols are rank-sorted by weight in parallel, lane 0 merges with the two-queue method.  Length
+// limiting by flattening the histogram and rebuilding keeps the code complete (Kraft sum exactly 1), which the
+// implicit last weight of the tree description relies on.
+__device__ int z_huf_lengths(ZEncWork *w, int lane)
 {
-    int parent[512]; unsigned wt[512]; unsigned char alive[512];
     int used = 0;
-    for (int s = 0; s < 256; ++s) { nbits[s] = 0; if (hist[s]) used++; }
+    for (int s = lane; s < 256; s += 32) { w->nbits[s] = 0; if (w->hist[s]) used++; }
+    for (int o = 16; o > 0; o >>= 1) used += __shfl_xor_sync(0xffffffffu, used, o);
     if (used < 2) return used;
     for (int shift = 0; shift < 32; ++shift) {
-        int n = 256;
-        for (int s = 0; s < 256; ++s) { unsigned v = hist[s] >> shift; wt[s] = hist[s] ? (v ? v : 1u) : 0u; alive[s] = hist[s] != 0; parent[s] = -1; }
-        for (int it = 0; it < used - 1; ++it) {
-            int a = -1, c = -1;
-            for (int i = 0; i < n; ++i)
-                if (alive[i]) {
-                    if (a < 0 || wt[i] < wt[a]) { c = a; a = i; }
-                    else if (c < 0 || wt[i] < wt[c]) c = i;
-                }
-            wt[n] = wt[a] + wt[c]; alive[n] = 1; parent[n] = -1; alive[a] = alive[c] = 0; parent[a] = parent[c] = n; n++;
+        for (int s = lane; s < 256; s += 32) {
+            const unsigned v = w->hist[s] >> shift;
+            w->key[s] = w->hist[s] ? ((v ? v : 1u) << 8) | (unsigned)s : 0xffffffffu;
         }
-        int maxlen = 0;
-        for (int s = 0; s < 256; ++s)
-            if (hist[s]) { int d = 0; for (int p = parent[s]; p >= 0; p = parent[p]) d++; nbits[s] = (unsigned char)d; if (d > maxlen) maxlen = d; }
-        if (maxlen <= Z_HUF_MAXLOG) break;
+        __syncwarp();
+        for (int s = lane; s < 256; s += 32) {
+            const unsigned k = w->key[s];
+            if (k == 0xffffffffu) continue;
+            int r = 0;
+            for (int t = 0; t < 256; ++t) r += w->key[t] < k;
+            w->order[r] = (unsigned short)s; w->nwt[r] = k >> 8;
+        }
+        __syncwarp();
+        if (lane == 0) {
+            // leaves 0..used-1 ascending, internal nodes used..2*used-2 are created in ascending weight order
+            int lf = 0, in = used, n = used;
+            for (int it = 0; it < used - 1; ++it) {
+                int pick[2];
+                for (int k = 0; k < 2; ++k) {
+                    if (lf < used && (in >= n || w->nwt[lf] <= w->nwt[in])) pick[k] = lf++; else pick[k] = in++;
+                }
+                w->nwt[n] = w->nwt[pick[0]] + w->nwt[pick[1]];
+                w->parent[pick[0]] = w->parent[pick[1]] = (short)n;
+                n++;
+            }
+            w->depth[n - 1] = 0;
+            int maxlen = 0;
+            for (int i = n - 2; i >= 0; --i) {
+                const int d = w->depth[w->parent[i]] + 1;
+                w->depth[i] = (unsigned char)d;
+                if (i < used) { w->nbits[w->order[i]] = (unsigned char)d; if (d > maxlen) maxlen = d; }
+            }
+            w->v[15] = maxlen;
+        }
+        __syncwarp();
+        if (w->v[15] <= Z_HUF_MAXLOG) break;
+        __syncwarp();
     }
     return used;
 }
@@ -565,153 +596,210 @@ __device__ int z_huf_write_tree(unsigned char *dst, int cap, const unsigned char
     return 1 + total;
 }
 
-// compress one block's literals; returns section bytes written or -1 when raw is better / not possible
-__device__ int z_write_literals(ZEncWork *w, unsigned char *dst, int cap, int nlit)
+// Literals section of the block into dst (called by the whole warp); returns bytes written or -1.
+__device__ int z_write_literals(ZEncWork *w, unsigned char *dst, int cap, int nlit, int lane)
 {
     const unsigned char *lit = w->lit;
-    int best_raw = nlit + (nlit < 32 ? 1 : (nlit < 4096 ? 2 : 3));
+    const int best_raw = nlit + (nlit < 32 ? 1 : (nlit < 4096 ? 2 : 3));
+    int written = -1;
     if (nlit >= 64) {
-        for (int i = 0; i < 256; ++i) w->hist[i] = 0;
-        for (int i = 0; i < nlit; ++i) w->hist[lit[i]]++;
-        const int used = z_huf_lengths(w->hist, w->nbits);
-        int maxsym = 255;
-        while (maxsym > 0 && !w->hist[maxsym]) maxsym--;
-        if (used >= 2) {
-            int maxlen = 0;
-            for (int s = 0; s < 256; ++s) if (w->nbits[s] > maxlen) maxlen = w->nbits[s];
-            // canonical codes (HUF_buildCTable): longest codes first from 0, within a length ascending symbol order
-            unsigned nper[Z_HUF_MAXLOG + 2], val[Z_HUF_MAXLOG + 2];
-            for (int k = 0; k <= Z_HUF_MAXLOG + 1; ++k) nper[k] = 0;
-            for (int s = 0; s <= maxsym; ++s) nper[w->nbits[s]]++;
-            unsigned mn = 0;
-            for (int k = maxlen; k >= 1; --k) { val[k] = mn; mn += nper[k]; mn >>= 1; }
-            for (int s = 0; s <= maxsym; ++s) if (w->nbits[s]) w->code[s] = (unsigned short)val[w->nbits[s]]++;
-            unsigned char weights[256];
-            for (int s = 0; s <= maxsym; ++s) weights[s] = w->nbits[s] ? (unsigned char)(maxlen + 1 - w->nbits[s]) : 0;
-            unsigned char *t = w->tmp;
-            int tl = z_huf_write_tree(t, 512, weights, maxsym, w->wt);
-            if (tl > 0) {
-                int pos = tl, ok = 1;
-                const int streams = nlit < 1024 ? 1 : 4;
-                if (streams == 1) {
-                    const int sl = z_huf_enc_stream(t + pos, 2 * Z_CHUNK + 1024 - pos, lit, nlit, w->code, w->nbits);
-                    if (sl < 0) ok = 0; else pos += sl;
-                } else {
-                    const int seg = (nlit + 3) / 4;
-                    int jt = pos; pos += 6;
-                    for (int k = 0; k < 4 && ok; ++k) {
-                        const int a = k * seg, len = k < 3 ? seg : nlit - 3 * seg;
-                        const int sl = z_huf_enc_stream(t + pos, 2 * Z_CHUNK + 1024 - pos, lit + a, len, w->code, w->nbits);
-                        if (sl < 0 || sl > 65535) { ok = 0; break; }
-                        if (k < 3) { t[jt + 2 * k] = (unsigned char)sl; t[jt + 2 * k + 1] = (unsigned char)(sl >> 8); }
+        for (int i = lane; i < 256; i += 32) w->hist[i] = 0;
+        __syncwarp();
+        for (int i = lane; i < nlit; i += 32) atomicAdd(&w->hist[lit[i]], 1u);
+        __syncwarp();
+        const int used = z_huf_lengths(w, lane);
+        unsigned char *t = w->tmp;
+        if (lane == 0) {
+            w->v[0] = 0;                                     // tree length, 0 = no Huffman coding
+            int maxsym = 255;
+            while (maxsym > 0 && !w->hist[maxsym]) maxsym--;
+            if (used >= 2) {
+                int maxlen = 0;
+                unsigned long long bits = 0;
+                for (int s = 0; s < 256; ++s) { if (w->nbits[s] > maxlen) maxlen = w->nbits[s]; bits += (unsigned long long)w->hist[s] * w->nbits[s]; }
+                // worth trying only if the streams alone already beat raw
+                if ((long long)(bits >> 3) + 16 < nlit) {
+                    // canonical codes (HUF_buildCTable): longest codes first from 0, within a length ascending symbol order
+                    unsigned nper[Z_HUF_MAXLOG + 2], val[Z_HUF_MAXLOG + 2];
+                    for (int k = 0; k <= Z_HUF_MAXLOG + 1; ++k) nper[k] = 0;
+                    for (int s = 0; s <= maxsym; ++s) nper[w->nbits[s]]++;
+                    unsigned mn = 0;
+                    for (int k = maxlen; k >= 1; --k) { val[k] = mn; mn += nper[k]; mn >>= 1; }
+                    for (int s = 0; s <= maxsym; ++s) if (w->nbits[s]) w->code[s] = (unsigned short)val[w->nbits[s]]++;
+                    for (int s = 0; s <= maxsym; ++s) w->weights[s] = w->nbits[s] ? (unsigned char)(maxlen + 1 - w->nbits[s]) : 0;
+                    const int tl = z_huf_write_tree(t, 512, w->weights, maxsym, w->wt);
+                    if (tl > 0) w->v[0] = tl;
+                }
+            }
+        }
+        __syncwarp();
+        const int tl = w->v[0];
+        if (tl > 0) {
+            // streams 0..3 (or one) are coded by one lane each into their own quarter of tmp
+            const int streams = nlit < 1024 ? 1 : 4;
+            const int seg = (nlit + 3) / 4, scap = (Z_CHUNK + 1024 - 512) / 4;
+            if (lane < streams) {
+                const int a = streams == 1 ? 0 : lane * seg, len = streams == 1 ? nlit : (lane < 3 ? seg : nlit - 3 * seg);
+                w->v[1 + lane] = z_huf_enc_stream(t + 512 + lane * scap, streams == 1 ? 4 * scap : scap, lit + a, len, w->code, w->nbits);
+            }
+            __syncwarp();
+            int ok = 1, csize = tl + (streams == 4 ? 6 : 0);
+            for (int k = 0; k < streams; ++k) { const int sl = w->v[1 + k]; if (sl < 0 || sl > 65535) ok = 0; else csize += sl; }
+            if (ok) {
+                int hdr; unsigned long long hv;
+                if (streams == 1) { hdr = 3; hv = 2ull | (0ull << 2) | ((unsigned long long)nlit << 4) | ((unsigned long long)csize << 14); }
+                else if (nlit < 1024 && csize < 1024) { hdr = 3; hv = 2ull | (1ull << 2) | ((unsigned long long)nlit << 4) | ((unsigned long long)csize << 14); }
+                else if (nlit < 16384 && csize < 16384) { hdr = 4; hv = 2ull | (2ull << 2) | ((unsigned long long)nlit << 4) | ((unsigned long long)csize << 18); }
+                else { hdr = 5; hv = 2ull | (3ull << 2) | ((unsigned long long)nlit << 4) | ((unsigned long long)csize << 22); }
+                if (hdr + csize < best_raw && hdr + csize <= cap) {
+                    int pos = 0;
+                    if (lane == 0) for (int k = 0; k < hdr; ++k) dst[k] = (unsigned char)(hv >> (8 * k));
+                    pos = hdr;
+                    for (int k = lane; k < tl; k += 32) dst[pos + k] = t[k];
+                    pos += tl;
+                    if (streams == 4) {
+                        if (lane < 3) { const int sl = w->v[1 + lane]; dst[pos + 2 * lane] = (unsigned char)sl; dst[pos + 2 * lane + 1] = (unsigned char)(sl >> 8); }
+                        pos += 6;
+                    }
+                    for (int k = 0; k < streams; ++k) {
+                        const int sl = w->v[1 + k];
+                        const unsigned char *sp = t + 512 + k * scap;
+                        for (int i = lane; i < sl; i += 32) dst[pos + i] = sp[i];
                         pos += sl;
                     }
-                }
-                if (ok) {
-                    const int csize = pos;
-                    int hdr; unsigned long long hv;
-                    if (streams == 1) { hdr = 3; hv = 2ull | (0ull << 2) | ((unsigned long long)nlit << 4) | ((unsigned long long)csize << 14); }
-                    else if (nlit < 1024 && csize < 1024) { hdr = 3; hv = 2ull | (1ull << 2) | ((unsigned long long)nlit << 4) | ((unsigned long long)csize << 14); }
-                    else if (nlit < 16384 && csize < 16384) { hdr = 4; hv = 2ull | (2ull << 2) | ((unsigned long long)nlit << 4) | ((unsigned long long)csize << 18); }
-                    else { hdr = 5; hv = 2ull | (3ull << 2) | ((unsigned long long)nlit << 4) | ((unsigned long long)csize << 22); }
-                    if (hdr + csize < best_raw && hdr + csize <= cap) {
-                        for (int k = 0; k < hdr; ++k) dst[k] = (unsigned char)(hv >> (8 * k));
-                        for (int k = 0; k < csize; ++k) dst[hdr + k] = t[k];
-                        return hdr + csize;
-                    }
+                    written = pos;
                 }
             }
         }
     }
-    // raw literals
-    if (best_raw > cap) return -1;
-    int pos;
-    if (nlit < 32) { dst[0] = (unsigned char)(nlit << 3); pos = 1; }
-    else if (nlit < 4096) { dst[0] = (unsigned char)((1 << 2) | ((nlit & 15) << 4)); dst[1] = (unsigned char)(nlit >> 4); pos = 2; }
-    else { dst[0] = (unsigned char)((3 << 2) | ((nlit & 15) << 4)); dst[1] = (unsigned char)(nlit >> 4); dst[2] = (unsigned char)(nlit >> 12); pos = 3; }
-    for (int i = 0; i < nlit; ++i) dst[pos + i] = lit[i];
-    return pos + nlit;
+    if (written < 0) {
+        // raw literals
+        if (best_raw > cap) return -1;
+        int pos;
+        if (nlit < 32) { if (lane == 0) dst[0] = (unsigned char)(nlit << 3); pos = 1; }
+        else if (nlit < 4096) { if (lane == 0) { dst[0] = (unsigned char)((1 << 2) | ((nlit & 15) << 4)); dst[1] = (unsigned char)(nlit >> 4); } pos = 2; }
+        else { if (lane == 0) { dst[0] = (unsigned char)((3 << 2) | ((nlit & 15) << 4)); dst[1] = (unsigned char)(nlit >> 4); dst[2] = (unsigned char)(nlit >> 12); } pos = 3; }
+        for (int i = lane; i < nlit; i += 32) dst[pos + i] = lit[i];
+        written = pos + nlit;
+    }
+    __syncwarp();
+    return written;
 }
 
-// one compressed block from src[0..n); returns bytes written or -1 if the block should be stored raw
-__device__ int z_compress_block(ZEncWork *w, const unsigned char *src, int n, unsigned char *dst, int cap)
+// one compressed block from w->lit[0..n) (called by the whole warp); returns bytes written or -1 if the block
+// should be stored raw
+__device__ int z_compress_block(ZEncWork *w, int n, unsigned char *dst, int cap, int lane)
 {
-    // ---- parse: runs of >= 5 equal bytes become (1 literal, match of run-1 at offset 1) ----
-    int nlit = 0, nseq = 0, i = 0, pending = 0;
-    while (i < n) {
-        int j = i + 1;
-        while (j < n && src[j] == src[i]) j++;
-        const int run = j - i;
-        if (run >= 5) {
-            w->lit[nlit++] = src[i];
-            w->seq[nseq].ll = (unsigned)(pending + 1); w->seq[nseq].ml = (unsigned)(run - 1); nseq++;
-            pending = 0;
-        } else {
-            for (int k = i; k < j; ++k) w->lit[nlit++] = src[k];
-            pending += run;
-        }
-        i = j;
+    // ---- does the chunk hold a run of >= 5 equal bytes at all?  (high-entropy chunks do not) ----
+    int hit = 0;
+    for (int i = lane; i + 4 < n; i += 32) {
+        const unsigned char c = w->lit[i];
+        if (w->lit[i + 1] == c && w->lit[i + 2] == c && w->lit[i + 3] == c && w->lit[i + 4] == c) { hit = 1; break; }
     }
-    int pos = z_write_literals(w, dst, cap, nlit);
+    hit = __any_sync(0xffffffffu, hit);
+    // ---- parse: runs of >= 5 equal bytes become (1 literal, match of run-1 at offset 1) ----
+    if (lane == 0) {
+        int nlit = n, nseq = 0;
+        if (hit) {
+            unsigned char *src = w->lit;
+            int i = 0, pending = 0;
+            nlit = 0;
+            while (i < n) {
+                const unsigned char c = src[i];
+                int j = i + 1;
+                while (j < n && src[j] == c) j++;
+                const int run = j - i;
+                if (run >= 5) {
+                    src[nlit++] = c;
+                    w->sll[nseq] = (unsigned short)(pending + 1); w->sml[nseq] = (unsigned short)(run - 1); nseq++;
+                    pending = 0;
+                } else {
+                    for (int k = 0; k < run; ++k) src[nlit++] = c;
+                    pending += run;
+                }
+                i = j;
+            }
+        }
+        w->v[8] = nlit; w->v[9] = nseq;
+    }
+    __syncwarp();
+    const int nlit = w->v[8], nseq = w->v[9];
+    int pos = z_write_literals(w, dst, cap, nlit, lane);
     if (pos < 0) return -1;
     // ---- sequences ----
-    if (pos + 4 > cap) return -1;
-    if (nseq == 0) { dst[pos++] = 0; return pos; }
-    if (nseq < 128) dst[pos++] = (unsigned char)nseq;
-    else if (nseq < 0x7f00) { dst[pos++] = (unsigned char)((nseq >> 8) + 128); dst[pos++] = (unsigned char)nseq; }
-    else { dst[pos++] = 255; dst[pos++] = (unsigned char)(nseq - 0x7f00); dst[pos++] = (unsigned char)((nseq - 0x7f00) >> 8); }
-    dst[pos++] = (unsigned char)((0 << 6) | (1 << 4) | (0 << 2));     // LL predefined, OF RLE, ML predefined
-    dst[pos++] = 0;                                                     // the single offset code: 0 = repeat offset 1
-    z_fse_build(w->ll, 6, z_ll_default, 36);
-    z_fse_build(w->ml, 6, z_ml_default, 53);
-    ZBitW b; zw_init(b, dst + pos, cap - pos);
-    unsigned sl, sm;
-    {
-        const ZSeq &q = w->seq[nseq - 1];
-        const int lc = z_ll_code(q.ll), mc = z_ml_code(q.ml);
-        sm = z_fse_first(w->ml, 64, mc); sl = z_fse_first(w->ll, 64, lc);
-        zw_add(b, q.ll - z_ll_base[lc], z_ll_bits[lc]);
-        zw_add(b, q.ml - z_ml_base[mc], z_ml_bits[mc]);
+    if (lane == 0) {
+        int r = -1;
+        do {
+            if (pos + 4 > cap) break;
+            if (nseq == 0) { dst[pos++] = 0; r = pos; break; }
+            if (nseq < 128) dst[pos++] = (unsigned char)nseq;
+            else if (nseq < 0x7f00) { dst[pos++] = (unsigned char)((nseq >> 8) + 128); dst[pos++] = (unsigned char)nseq; }
+            else { dst[pos++] = 255; dst[pos++] = (unsigned char)(nseq - 0x7f00); dst[pos++] = (unsigned char)((nseq - 0x7f00) >> 8); }
+            dst[pos++] = (unsigned char)((0 << 6) | (1 << 4) | (0 << 2));     // LL predefined, OF RLE, ML predefined
+            dst[pos++] = 0;                                                     // the single offset code: 0 = repeat offset 1
+            z_fse_build(w->ll, 6, z_ll_default, 36);
+            z_fse_build(w->ml, 6, z_ml_default, 53);
+            ZBitW b; zw_init(b, dst + pos, cap - pos);
+            unsigned sl, sm;
+            {
+                const unsigned ql = w->sll[nseq - 1], qm = w->sml[nseq - 1];
+                const int lc = z_ll_code(ql), mc = z_ml_code(qm);
+                sm = z_fse_first(w->ml, 64, mc); sl = z_fse_first(w->ll, 64, lc);
+                zw_add(b, ql - z_ll_base[lc], z_ll_bits[lc]);
+                zw_add(b, qm - z_ml_base[mc], z_ml_bits[mc]);
+            }
+            for (int k = nseq - 2; k >= 0; --k) {
+                const unsigned ql = w->sll[k], qm = w->sml[k];
+                const int lc = z_ll_code(ql), mc = z_ml_code(qm);
+                // (offset state: RLE table, no bits)
+                sm = z_fse_enc(b, w->ml, 64, sm, mc);
+                sl = z_fse_enc(b, w->ll, 64, sl, lc);
+                zw_add(b, ql - z_ll_base[lc], z_ll_bits[lc]);
+                zw_add(b, qm - z_ml_base[mc], z_ml_bits[mc]);
+            }
+            zw_add(b, sm, 6);
+            zw_add(b, sl, 6);
+            const int sl_bytes = zw_close(b);
+            if (sl_bytes >= 0) r = pos + sl_bytes;
+        } while (0);
+        w->v[10] = r;
     }
-    for (int k = nseq - 2; k >= 0; --k) {
-        const ZSeq &q = w->seq[k];
-        const int lc = z_ll_code(q.ll), mc = z_ml_code(q.ml);
-        // (offset state: RLE table, no bits)
-        sm = z_fse_enc(b, w->ml, 64, sm, mc);
-        sl = z_fse_enc(b, w->ll, 64, sl, lc);
-        zw_add(b, q.ll - z_ll_base[lc], z_ll_bits[lc]);
-        zw_add(b, q.ml - z_ml_base[mc], z_ml_bits[mc]);
-    }
-    zw_add(b, sm, 6);
-    zw_add(b, sl, 6);
-    const int sl_bytes = zw_close(b);
-    if (sl_bytes < 0) return -1;
-    return pos + sl_bytes;
+    __syncwarp();
+    return w->v[10];
 }
 
-// Compressor, stage 1: grid = (maxchunks, nframes), block = ZC_THREADS (thread 0 works).  Chunk j of frame i
-// (Z_CHUNK bytes of in[i]) becomes one zstd block (3-byte header + body) in blk[i][j]; blen[i][j] = its size.
+// Compressor, stage 1: grid = (maxchunks, nframes), one warp per block, working set in shared memory.  Chunk j of
+// frame i (Z_CHUNK bytes of in[i]) becomes one zstd block (3-byte header + body) in blk[i][j]; blen[i][j] = its size.
 // Blocks of a frame are independent: every block carries its own Huffman table, sequences use predefined tables
 // and only the repeat offset 1, which no block ever changes.
 #define Z_BLK_STRIDE (Z_CHUNK + 16)
-__global__ void k_zstd_compress_chunks(const unsigned char *__restrict__ in, size_t in_stride, const unsigned *__restrict__ in_len,
-                                       unsigned char *blk, unsigned *blen, int maxchunks, ZEncWork *work)
+__global__ void __launch_bounds__(ZC_THREADS)
+k_zstd_compress_chunks(const unsigned char *__restrict__ in, size_t in_stride, const unsigned *__restrict__ in_len,
+                       unsigned char *blk, unsigned *blen, int maxchunks)
 {
-    const int frame = blockIdx.y, j = blockIdx.x;
-    if (threadIdx.x != 0) return;
+    EBCC_DYN_SMEM(ZEncWork, w);
+    const int frame = blockIdx.y, j = blockIdx.x, lane = threadIdx.x;
     const int n = (int)in_len[frame], a = j * Z_CHUNK;
     unsigned *bl = blen + (size_t)frame * maxchunks + j;
-    if (a >= n) { *bl = 0; return; }
+    if (a >= n) { if (lane == 0) *bl = 0; return; }
     const unsigned char *src = in + (size_t)frame * in_stride + a;
     unsigned char *dst = blk + ((size_t)frame * maxchunks + j) * Z_BLK_STRIDE;
-    ZEncWork *w = work + (size_t)frame * maxchunks + j;
     const int len = n - a < Z_CHUNK ? n - a : Z_CHUNK, last = a + len >= n;
-    int cs = z_compress_block(w, src, len, dst + 3, len - 1);
+    for (int i = lane; i < (len + 3) / 4; i += 32) ((unsigned *)w->lit)[i] = ((const unsigned *)src)[i];
+    __syncwarp();
+    int cs = z_compress_block(w, len, w->out, len - 1, lane);
     unsigned bh;
-    if (cs > 0 && cs < len) bh = (unsigned)last | (2u << 1) | ((unsigned)cs << 3);
-    else { cs = len; bh = (unsigned)last | (0u << 1) | ((unsigned)len << 3); for (int k = 0; k < len; ++k) dst[3 + k] = src[k]; }
-    dst[0] = (unsigned char)bh; dst[1] = (unsigned char)(bh >> 8); dst[2] = (unsigned char)(bh >> 16);
-    *bl = (unsigned)(3 + cs);
+    if (cs > 0 && cs < len) {
+        bh = (unsigned)last | (2u << 1) | ((unsigned)cs << 3);
+        for (int k = lane; k < cs; k += 32) dst[3 + k] = w->out[k];
+    } else {
+        cs = len; bh = (unsigned)last | (0u << 1) | ((unsigned)len << 3);
+        for (int k = lane; k < len; k += 32) dst[3 + k] = src[k];
+    }
+    if (lane == 0) {
+        dst[0] = (unsigned char)bh; dst[1] = (unsigned char)(bh >> 8); dst[2] = (unsigned char)(bh >> 16);
+        *bl = (unsigned)(3 + cs);
+    }
 }
 
 // stage 2: grid = nframes, block = 256: frame header + the blocks at their prefix-summed offsets
