@@ -108,22 +108,63 @@ static int dims_are_valid(const size_t dims[NDIMS])
            dims[NDIMS - 1] >= EBCC_MIN_INTERNAL_IMAGE_DIM && dims[NDIMS - 1] <= EBCC_MAX_INTERNAL_IMAGE_DIM;
 }
 
-/* ---- process-wide device context, created lazily and re-created after fork ------------------------- */
+/* ---- process-wide pool of device pipelines (context + stream each), created lazily and re-created after fork.
+ * Every encode / decode call (and every worker of a multi-batch call) owns one pipeline while it runs, so callers on
+ * several threads -- or several batches of one call -- are in flight on the device at the same time: the kernels of
+ * one batch fill the issue slots the latency-bound tier-1 coder of another leaves idle.  EBCC_PIPELINES (1..8,
+ * default 2) bounds how many. */
+#define EBCC_MAX_PIPELINES 8
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
-static ebcc_cuda_ctx *g_ctx = NULL;
+static pthread_cond_t g_cv = PTHREAD_COND_INITIALIZER;
+static ebcc_cuda_ctx *g_pool[EBCC_MAX_PIPELINES];
+static int g_busy[EBCC_MAX_PIPELINES];
 static pid_t g_ctx_pid = 0;
 
-static ebcc_cuda_ctx *get_ctx_locked(void)
+static int n_pipelines(void)
 {
-    pid_t me = getpid();
-    if (g_ctx && g_ctx_pid == me) return g_ctx;
-    int dev = 0;
-    const char *env = getenv("EBCC_CUDA_DEVICE");
-    if (env) dev = atoi(env);
-    g_ctx = ebcc_cuda_ctx_create(dev);   /* a context inherited through fork is abandoned, not reused */
-    g_ctx_pid = me;
-    if (!g_ctx) ebcc_log(LOG_FATAL, "no usable CUDA device: this build of EBCC has no CPU code path");
-    return g_ctx;
+    const char *env = getenv("EBCC_PIPELINES");
+    long v = env ? atol(env) : 2;
+    return v < 1 ? 1 : (v > EBCC_MAX_PIPELINES ? EBCC_MAX_PIPELINES : (int)v);
+}
+
+/* blocks until a pipeline is free; NULL when no CUDA device is usable */
+static ebcc_cuda_ctx *acquire_ctx(void)
+{
+    const int np = n_pipelines();
+    pthread_mutex_lock(&g_mu);
+    const pid_t me = getpid();
+    if (g_ctx_pid != me) {               /* contexts inherited through fork are abandoned, not reused */
+        for (int k = 0; k < EBCC_MAX_PIPELINES; ++k) { g_pool[k] = NULL; g_busy[k] = 0; }
+        g_ctx_pid = me;
+    }
+    for (;;) {
+        for (int k = 0; k < np; ++k) {
+            if (g_busy[k]) continue;
+            if (!g_pool[k]) {
+                int dev = 0;
+                const char *env = getenv("EBCC_CUDA_DEVICE");
+                if (env) dev = atoi(env);
+                g_pool[k] = ebcc_cuda_ctx_create(dev);
+                if (!g_pool[k]) {
+                    pthread_mutex_unlock(&g_mu);
+                    ebcc_log(LOG_FATAL, "no usable CUDA device: this build of EBCC has no CPU code path");
+                    return NULL;
+                }
+            }
+            g_busy[k] = 1;
+            pthread_mutex_unlock(&g_mu);
+            return g_pool[k];
+        }
+        pthread_cond_wait(&g_cv, &g_mu);
+    }
+}
+
+static void release_ctx(ebcc_cuda_ctx *ctx)
+{
+    pthread_mutex_lock(&g_mu);
+    for (int k = 0; k < EBCC_MAX_PIPELINES; ++k) if (g_pool[k] == ctx) g_busy[k] = 0;
+    pthread_cond_signal(&g_cv);
+    pthread_mutex_unlock(&g_mu);
 }
 
 static size_t max_batch_frames(void)
@@ -475,6 +516,39 @@ out:
     return rc;
 }
 
+/* batches of one call are handed to up to EBCC_PIPELINES workers, each on its own device pipeline */
+typedef struct {
+    const float *frames; size_t nframes; const codec_config_t *config; uint8_t **outs; size_t *sizes;
+    size_t N, maxb, next, done;
+    int failed;
+    pthread_mutex_t mu;
+} enc_job_t;
+
+static void *enc_worker(void *arg)
+{
+    enc_job_t *j = (enc_job_t *)arg;
+    ebcc_cuda_ctx *ctx = acquire_ctx();
+    if (!ctx) { pthread_mutex_lock(&j->mu); j->failed = 1; pthread_mutex_unlock(&j->mu); return NULL; }
+    for (;;) {
+        pthread_mutex_lock(&j->mu);
+        const size_t base = j->next;
+        const int stop = j->failed || base >= j->nframes;
+        if (!stop) j->next = base + j->maxb;
+        pthread_mutex_unlock(&j->mu);
+        if (stop) break;
+        const size_t nb = j->nframes - base < j->maxb ? j->nframes - base : j->maxb;
+        size_t done = 0;
+        const int rc = encode_chunk(ctx, j->frames + base * j->N, nb, base, j->config, j->outs, j->sizes, &done);
+        pthread_mutex_lock(&j->mu);
+        j->done += done;
+        if (rc) j->failed = 1;
+        pthread_mutex_unlock(&j->mu);
+        if (rc) { ebcc_log(LOG_FATAL, "CUDA encode of frames %lu..%lu failed", base, base + nb - 1); break; }
+    }
+    release_ctx(ctx);
+    return NULL;
+}
+
 size_t ebcc_encode_batch(const float *frames, size_t nframes, const codec_config_t *config, uint8_t **outs, size_t *sizes)
 {
     log_set_level_from_env();
@@ -492,21 +566,20 @@ size_t ebcc_encode_batch(const float *frames, size_t nframes, const codec_config
         ebcc_log(LOG_FATAL, "unknown residual compression type %d", (int)config->residual_compression_type);
         return 0;
     }
-    const size_t N = config->dims[1] * config->dims[2];
-    const size_t maxb = max_batch_frames();
-    size_t done = 0;
-    pthread_mutex_lock(&g_mu);
-    ebcc_cuda_ctx *ctx = get_ctx_locked();
-    if (!ctx) { pthread_mutex_unlock(&g_mu); return 0; }
-    for (size_t base = 0; base < nframes; base += maxb) {
-        const size_t nb = nframes - base < maxb ? nframes - base : maxb;
-        if (encode_chunk(ctx, frames + base * N, nb, base, config, outs, sizes, &done)) {
-            ebcc_log(LOG_FATAL, "CUDA encode of frames %lu..%lu failed", base, base + nb - 1);
-            break;
-        }
-    }
-    pthread_mutex_unlock(&g_mu);
-    return done;
+    enc_job_t job;
+    job.frames = frames; job.nframes = nframes; job.config = config; job.outs = outs; job.sizes = sizes;
+    job.N = config->dims[1] * config->dims[2]; job.maxb = max_batch_frames(); job.next = 0; job.done = 0; job.failed = 0;
+    pthread_mutex_init(&job.mu, NULL);
+    const size_t nbatches = (nframes + job.maxb - 1) / job.maxb;
+    int nworkers = n_pipelines();
+    if ((size_t)nworkers > nbatches) nworkers = (int)nbatches;
+    pthread_t th[EBCC_MAX_PIPELINES];
+    int started = 0;
+    for (int k = 1; k < nworkers; ++k) if (pthread_create(&th[started], NULL, enc_worker, &job) == 0) started++;
+    enc_worker(&job);                      /* the calling thread is worker 0 */
+    for (int k = 0; k < started; ++k) pthread_join(th[k], NULL);
+    pthread_mutex_destroy(&job.mu);
+    return job.done;
 }
 
 size_t ebcc_encode(float *data, codec_config_t *config, uint8_t **out_buffer)
@@ -597,7 +670,6 @@ size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, si
     float *mn = (float *)malloc(sizeof(float) * maxb), *mx = (float *)malloc(sizeof(float) * maxb);
     float **dst = (float **)malloc(sizeof(float *) * maxb);
     ebcc_residual_in *rs = (ebcc_residual_in *)calloc(maxb, sizeof(*rs));
-    pthread_mutex_lock(&g_mu);
     ebcc_cuda_ctx *ctx = NULL;
     size_t i = 0;
     while (i < nframes) {
@@ -619,7 +691,7 @@ size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, si
             nb++;
         }
         if (nb) {
-            if (!ctx) ctx = get_ctx_locked();
+            if (!ctx) ctx = acquire_ctx();
             int rc = ctx ? ebcc_cuda_decode_batch(ctx, js, jn, nb, H, W, mn, mx, rs, dst) : -1;
             for (size_t k = 0; k < nb; ++k) {
                 if (rc == 0) { counts[idx[k]] = H * W; done++; }
@@ -629,7 +701,7 @@ size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, si
         }
         i = j;
     }
-    pthread_mutex_unlock(&g_mu);
+    if (ctx) release_ctx(ctx);
     free(js); free(jn); free(idx); free(mn); free(mx); free(dst); free(rs); free(ps); free(owned);
     return done;
 }

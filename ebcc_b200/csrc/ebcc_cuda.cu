@@ -1023,3 +1023,44 @@ extern "C" int ebcc_cuda_bench_resident(ebcc_cuda_ctx *c, size_t nframes, float 
     if (flush) cudaFree(flush);
     return 0;
 }
+
+// Several resident batches in flight: step it runs on ctxs[it % nctx], every context on its own stream, so that the
+// tier-1 context-modelling kernel of one batch overlaps the (latency-bound) MQ kernel of another.  All launches are
+// issued by the calling thread; the timed region is bracketed by events on a timing stream that every context
+// stream waits on / is waited for.  flush_bytes > 0 writes a scratch buffer of that size before every step (inside
+// the timed region).  total_ms: device time of the `steps` timed steps.
+extern "C" int ebcc_cuda_bench_resident_pipelined(ebcc_cuda_ctx **ctxs, int nctx, size_t nframes, float base_cr, int steps, int warmup,
+                                                  size_t flush_bytes, float *total_ms)
+{
+    if (!ctxs || nctx <= 0 || nctx > 8 || steps <= 0) return -1;
+    CK(cudaSetDevice(ctxs[0]->device));
+    void *flush[8] = {0};
+    cudaStream_t ts;
+    cudaEvent_t e0, e1, done[8];
+    CK(cudaStreamCreateWithFlags(&ts, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    for (int k = 0; k < nctx; ++k) {
+        CK(cudaEventCreateWithFlags(&done[k], cudaEventDisableTiming));
+        if (flush_bytes) CK(cudaMalloc(&flush[k], flush_bytes));
+    }
+    int rc = 0;
+    for (int phase = 0; phase < 2 && !rc; ++phase) {
+        const int n = phase == 0 ? warmup : steps;
+        if (phase == 1) {
+            CK(cudaEventRecord(e0, ts));
+            for (int k = 0; k < nctx; ++k) CK(cudaStreamWaitEvent(ctxs[k]->stream, e0, 0));
+        }
+        for (int it = 0; it < n && !rc; ++it) {
+            ebcc_cuda_ctx *c = ctxs[it % nctx];
+            if (flush[it % nctx]) CK(cudaMemsetAsync(flush[it % nctx], it & 0xff, flush_bytes, c->stream));
+            rc = ebcc_cuda_j2k_encode_resident(c, nframes, base_cr);
+        }
+        for (int k = 0; k < nctx; ++k) { CK(cudaEventRecord(done[k], ctxs[k]->stream)); CK(cudaStreamWaitEvent(ts, done[k], 0)); }
+        if (phase == 1) CK(cudaEventRecord(e1, ts));
+        CK(cudaStreamSynchronize(ts));
+    }
+    if (!rc) CK(cudaEventElapsedTime(total_ms, e0, e1));
+    for (int k = 0; k < nctx; ++k) { cudaEventDestroy(done[k]); if (flush[k]) cudaFree(flush[k]); }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(ts);
+    return rc;
+}

@@ -17,8 +17,10 @@
 #pragma once
 #include "common.cuh"
 
+#ifndef T1_THREADS
 #define T1_THREADS 256
-#define T1_CPT 4                    // stripe columns per thread
+#endif
+#define T1_CPT (1024 / T1_THREADS)  // stripe columns per thread
 #define T1_SW 66                    // state row stride: 64 + border
 #define T1_NSTATE (18 * T1_SW)      // 16 stripes + border
 #define T1_SYMBUF 10240             // max symbols per pass: 1024 stripe columns x 10
@@ -211,6 +213,13 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
                 if (sidx[k] < 0) continue;
                 const int p = sidx[k];
                 const unsigned cw = st[p];
+                {
+                    // columns with nothing to code in this pass need no neighbourhood window
+                    const unsigned rows = (1u << lim[k]) - 1u;
+                    if (passtype == 1) { if ((ST_SIG(cw) & ~ST_PI(cw) & rows) == 0) continue; }
+                    else if (passtype == 0) { if ((~ST_SIG(cw) & rows) == 0) { if (nw[p]) { nw[p] = 0; changed = 1; } continue; } }
+                    else if (((ST_SIG(cw) | ST_PI(cw)) & rows) == rows) { upd_sig[k] = nw[p]; continue; }
+                }
                 T1Win w;
                 {
                     unsigned lo = t1_six(ST_SIG(st[p - T1_SW - 1]), ST_SIG(st[p - 1]), ST_SIG(st[p + T1_SW - 1]));

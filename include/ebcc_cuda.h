@@ -110,6 +110,12 @@ unsigned long long ebcc_cuda_launch_count(ebcc_cuda_ctx *ctx);
 int ebcc_cuda_bench_resident(ebcc_cuda_ctx *ctx, size_t nframes, float base_cr, int steps, int warmup,
                              size_t flush_bytes, float *total_ms, float *stage_ms_sum);
 
+/* Same measurement with several resident batches in flight: step i runs on ctxs[i % nctx], each context on its own
+ * stream (the per-batch hot path is unchanged; kernels of different batches overlap).  The flush buffer is written
+ * before every step inside the timed region.  total_ms: device time of all `steps` timed steps. */
+int ebcc_cuda_bench_resident_pipelined(ebcc_cuda_ctx **ctxs, int nctx, size_t nframes, float base_cr, int steps, int warmup,
+                                       size_t flush_bytes, float *total_ms);
+
 /* debug/test taps on the resident batch (device -> host copies of intermediates) */
 int ebcc_cuda_debug_coef(ebcc_cuda_ctx *ctx, size_t frame, float *dst);
 int ebcc_cuda_debug_spiht_stream(ebcc_cuda_ctx *ctx, size_t frame, uint8_t *dst, size_t cap, size_t *len);

@@ -11,7 +11,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "libh5z_ebcc_ref.so")
 ORC_SO = os.path.join(ROOT, "oracle", "libebcc_oracle.so")
-PROD_SO = os.path.join(ROOT, "ebcc_b200", "libh5z_ebcc.so")
+PROD_SO = os.environ.get("EBCC_PROD_SO", os.path.join(ROOT, "ebcc_b200", "libh5z_ebcc.so"))
 
 NONE, MAX_ERROR, RELATIVE_ERROR = 0, 1, 2
 
