@@ -538,17 +538,20 @@ extern "C" int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *c, size_t nframes)
 
     mark(c, EBCC_ST_T1_CM);
     EBCC_LAUNCH(k_t1_cm, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
-                c->d_coef, c->d_cblks, c->d_bands, c->d_luts, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks, pl->sym_stride);
+                c->d_coef, c->d_cblks, c->d_bands, c->d_luts, (const unsigned char *)c->d_declut, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks,
+                pl->sym_stride);
     mark(c, EBCC_ST_T1_MQ);
     {
         const long long jobs = (long long)pl->ncblks * B;
-        const char *el = getenv("EBCC_MQ_LANES");                // code-blocks per warp: 1, 2, 4 or 8
-        const int lanes = el ? atoi(el) : MQ_DEFAULT_LANES;
-        const long long per_cta = (long long)MQ_WARPS * (lanes == 8 ? 8 : lanes == 4 ? 4 : lanes == 2 ? 2 : 1);
-        const dim3 grid((unsigned)((jobs + per_cta - 1) / per_cta)), block(MQ_THREADS);
+        const char *el = getenv("EBCC_MQ_LANES");                // code-blocks per warp: 1, 2, 4, 8, 16 or 32
+        int lanes = el ? atoi(el) : MQ_DEFAULT_LANES;
+        if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8 && lanes != 16 && lanes != 32) lanes = MQ_DEFAULT_LANES;
+        const long long per_cta = (long long)MQ_WARPS(lanes) * lanes;
+        const dim3 grid((unsigned)((jobs + per_cta - 1) / per_cta)), block(MQ_THREADS(lanes));
 #define MQ_GO(LL) EBCC_LAUNCH(k_t1_mq<LL>, grid, block, 0, c->stream, c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, \
                               c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride)
-        if (lanes == 8) MQ_GO(8); else if (lanes == 4) MQ_GO(4); else if (lanes == 2) MQ_GO(2); else MQ_GO(1);
+        if (lanes == 32) MQ_GO(32); else if (lanes == 16) MQ_GO(16); else if (lanes == 8) MQ_GO(8); else if (lanes == 4) MQ_GO(4);
+        else if (lanes == 2) MQ_GO(2); else MQ_GO(1);
 #undef MQ_GO
     }
     c->launches += 2;

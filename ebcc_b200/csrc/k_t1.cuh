@@ -3,12 +3,15 @@
 //   k_t1_cm : one CTA per 64x64 code-block.  Quantises the block (t1.c:2397-2425), then runs the
 //             bit-plane passes (cleanup / significance propagation / magnitude refinement) in
 //             PARALLEL over stripe columns and emits the (context, decision) symbol stream in
-//             scan order through a CTA-wide prefix sum.  The scan-order dependence of the
-//             significance state is resolved analytically: a neighbour counts as significant
-//             if it was before the pass, or becomes so in this pass AND precedes the sample in
-//             scan order.  For the cleanup pass "becomes significant" is known a priori
-//             (insignificant, not visited, bit set); for the significance-propagation pass it is
-//             the least fixed point of a monotone map, reached by iterating to convergence.
+//             scan order through a CTA-wide prefix sum.  Every stripe column owns one flag word
+//             holding the significance of its whole 3x6 neighbourhood (kept current by atomicOr
+//             scatter), so a context is one shift + mask + table look-up.  The scan-order
+//             dependence of the significance state is resolved analytically: a neighbour counts
+//             as significant if it was before the pass, or becomes so in this pass AND precedes
+//             the sample in scan order.  For the cleanup pass "becomes significant" is known a
+//             priori (insignificant, not visited, bit set); for the significance-propagation pass
+//             it is the least fixed point of a monotone map, reached by cheap sweeps that emit
+//             nothing, followed by one emitting sweep.
 //   k_t1_mq : one code-block per warp.  The warp stages the symbol stream through shared memory, lane 0
 //             runs the serial MQ arithmetic coder (mqc.c / mqc_inl.h) over it, pass rates as
 //             opj_t1_encode_cblk computes them (t1.c:2655-2723).
@@ -18,7 +21,7 @@
 #include "common.cuh"
 
 #ifndef T1_THREADS
-#define T1_THREADS 256
+#define T1_THREADS 512
 #endif
 #define T1_CPT (1024 / T1_THREADS)  // stripe columns per thread
 #define T1_SW 66                    // state row stride: 64 + border
@@ -66,15 +69,6 @@ __device__ __forceinline__ int t1_contrib(int sa, int na, int sb, int nb)
     return pos - neg;
 }
 
-// window of one stripe column: significance of rows -1..4 (bit r+1) for W / own / E columns and
-// sign bits in the same layout
-struct T1Win { unsigned L, C, R, gL, gC, gR; };
-
-__device__ __forceinline__ unsigned t1_six(unsigned up, unsigned mid, unsigned dn)
-{
-    return ((up >> 3) & 1u) | ((mid & 0xfu) << 1) | ((dn & 1u) << 5);
-}
-
 struct T1Sym { unsigned long long bits; int cnt; };
 __device__ __forceinline__ void t1_put(T1Sym &s, int ctx, int d)
 {
@@ -82,47 +76,86 @@ __device__ __forceinline__ void t1_put(T1Sym &s, int ctx, int d)
     s.cnt++;
 }
 
-// zero-coding context of row j given window w (L/C/R hold time-correct significance)
-__device__ __forceinline__ int t1_zc_of(const T1Win &w, int j, int orient)
-{
-    int h = ((w.L >> (j + 1)) & 1) + ((w.R >> (j + 1)) & 1);
-    int v = ((w.C >> j) & 1) + ((w.C >> (j + 2)) & 1);
-    int d = ((w.L >> j) & 1) + ((w.L >> (j + 2)) & 1) + ((w.R >> j) & 1) + ((w.R >> (j + 2)) & 1);
-    return CTX_ZC + t1_zc_ctx(orient, h, v, d);
-}
-__device__ __forceinline__ int t1_has_nb(const T1Win &w, int j)
-{
-    unsigned m3 = 7u << j;
-    return ((w.L & m3) | (w.R & m3) | (w.C & (5u << j))) != 0;
-}
-// sign coding of row j: emits (ctx, sign ^ spb)
-__device__ __forceinline__ void t1_sign(T1Sym &s, const T1Win &w, int j, int neg)
-{
-    int hc = t1_contrib((w.R >> (j + 1)) & 1, (w.gR >> (j + 1)) & 1, (w.L >> (j + 1)) & 1, (w.gL >> (j + 1)) & 1);
-    int vc = t1_contrib((w.C >> j) & 1, (w.gC >> j) & 1, (w.C >> (j + 2)) & 1, (w.gC >> (j + 2)) & 1);
-    int e = t1_sc_lut(hc, vc);
-    t1_put(s, CTX_SC + (e & 7), neg ^ (e >> 3));
-}
-
 __device__ __forceinline__ int t1_nm_sig(const T1Luts *l, unsigned x, int bpno)
 { return bpno > 0 ? l->sig[(x >> bpno) & 127] : l->sig0[x & 127]; }
 __device__ __forceinline__ int t1_nm_ref(const T1Luts *l, unsigned x, int bpno)
 { return bpno > 0 ? l->ref[(x >> bpno) & 127] : l->ref0[x & 127]; }
 
-// state word per stripe column: bits 0-3 significant, 4-7 visited-in-sigpass (pi), 8-11 refined (mu)
-#define ST_SIG(w) ((w) & 0xfu)
-#define ST_PI(w) (((w) >> 4) & 0xfu)
-#define ST_MU(w) (((w) >> 8) & 0xfu)
+// Flag word of one stripe column (the layout of OPJ's opj_flag_t and of the decoder's DF_* word): bits 0-17
+// significance of the 3x6 neighbourhood (bit (r+1)*3 + (dx+1), r = -1..4, dx = -1..1; the column's own rows are
+// dx = 0, r = 0..3), bits 24-27 pi (coded in the significance pass), bits 28-31 mu (already refined).
+#define CF_W 66
+#define CF_WORDS (18 * CF_W)
+#define CF_SIG(ci) (1u << ((ci) * 3 + 4))
+#define CF_NB(ci) (0x1efu << ((ci) * 3))
+#define CF_PI(ci) (1u << (24 + (ci)))
+#define CF_MU(ci) (1u << (28 + (ci)))
+// neighbours of a column that precede ALL of its rows in scan order: column to the west rows -1..3, row -1 of the
+// own and the eastern column.  (Own rows above the current one are tracked in registers while a column is coded.)
+#define CF_EARLY 0x124fu
+
+__device__ __forceinline__ unsigned cf_own4(unsigned f) { return ((f >> 4) & 1u) | ((f >> 6) & 2u) | ((f >> 8) & 4u) | ((f >> 10) & 8u); }
+
+// rows b4 of column p become significant: set the bits every neighbouring word sees
+__device__ __forceinline__ void cf_scatter(unsigned *N, int p, unsigned b4)
+{
+    unsigned own = 0, we = 0;
+#pragma unroll
+    for (int ci = 0; ci < 4; ++ci)
+        if ((b4 >> ci) & 1u) { own |= CF_SIG(ci); we |= 1u << ((ci + 1) * 3); }
+    atomicOr(&N[p], own);
+    atomicOr(&N[p - 1], we << 2);
+    atomicOr(&N[p + 1], we);
+    if (b4 & 1u) { atomicOr(&N[p - CF_W], 1u << 16); atomicOr(&N[p - CF_W - 1], 1u << 17); atomicOr(&N[p - CF_W + 1], 1u << 15); }
+    if (b4 & 8u) { atomicOr(&N[p + CF_W], 1u << 1); atomicOr(&N[p + CF_W - 1], 1u << 2); atomicOr(&N[p + CF_W + 1], 1u << 0); }
+}
+
+// sign coding of row j of column p; t = time-correct significance window, static signs in SG (rows -1..4 of a column
+// at bits 0..5)
+__device__ __forceinline__ void cf_sign(T1Sym &s, unsigned t, const unsigned *SG, int p, int j, int neg)
+{
+    const unsigned gc = SG[p], gw = SG[p - 1], ge = SG[p + 1];
+    const int hc = t1_contrib((t >> ((j + 1) * 3 + 2)) & 1, (ge >> (j + 1)) & 1, (t >> ((j + 1) * 3)) & 1, (gw >> (j + 1)) & 1);
+    const int vc = t1_contrib((t >> (j * 3 + 1)) & 1, (gc >> j) & 1, (t >> ((j + 2) * 3 + 1)) & 1, (gc >> (j + 2)) & 1);
+    const int e = t1_sc_lut(hc, vc);
+    t1_put(s, CTX_SC + (e & 7), neg ^ (e >> 3));
+}
+
+// One column of a significance-propagation pass (t1.c:363-410, 479-580).  Returns the rows that become significant;
+// EMIT adds the symbols, the rows coded (pi) and the distortion estimate.
+template <bool EMIT>
+__device__ __forceinline__ unsigned cf_sigpass_col(unsigned f, unsigned n, const unsigned *mag, unsigned one, int lim, unsigned sgn4,
+                                                    const unsigned char *zc, const unsigned *SG, int p, const T1Luts *luts, int bpno,
+                                                    T1Sym &sy, unsigned &coded, int &nmsedec)
+{
+    unsigned t = f | (n & CF_EARLY), fresh = 0;
+    if ((t & 0x3ffffu) == 0) return 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        if (j >= lim) break;
+        if (!(f & CF_SIG(j)) && (t & CF_NB(j))) {
+            const int v = (mag[j] & one) ? 1 : 0;
+            if (EMIT) { t1_put(sy, CTX_ZC + zc[(t >> (j * 3)) & 0x1ffu], v); coded |= 1u << j; }
+            if (v) {
+                if (EMIT) { cf_sign(sy, t, SG, p, j, (sgn4 >> j) & 1); nmsedec += t1_nm_sig(luts, mag[j], bpno); }
+                fresh |= 1u << j;
+                t |= CF_SIG(j);
+            }
+        }
+    }
+    return fresh;
+}
 
 __global__ void __launch_bounds__(T1_THREADS)
 k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, const BandDesc *__restrict__ bands,
-        const T1Luts *__restrict__ g_luts, CblkOut *cbout, unsigned char *sym_pool,
+        const T1Luts *__restrict__ g_luts, const unsigned char *__restrict__ zc_lut, CblkOut *cbout, unsigned char *sym_pool,
         int W, int H, int ncblks, size_t sym_stride)
 {
-    __shared__ unsigned st[T1_NSTATE];      // state words
-    __shared__ unsigned sg[T1_NSTATE];      // sign nibbles (static)
-    __shared__ unsigned nw[T1_NSTATE];      // newly significant in the running pass
+    __shared__ unsigned F[CF_WORDS];        // flag words
+    __shared__ unsigned N[CF_WORDS];        // significance gained in the running pass, same neighbourhood layout
+    __shared__ unsigned SG[CF_WORDS];       // static: sign of rows -1..4 of the column (bits 0..5)
     __shared__ unsigned char symbuf[T1_SYMBUF + 64];
+    __shared__ unsigned char zc[512];
     __shared__ T1Luts luts;
     __shared__ int warp_sum[T1_THREADS / 32];
     __shared__ int s_max, s_nmsedec, s_total;
@@ -136,8 +169,9 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
     CblkOut *out = cbout + (size_t)frame * ncblks + cbi;
     unsigned char *sym = sym_pool + (size_t)frame * sym_stride + cb.sym_off;
 
-    for (int i = tid; i < T1_NSTATE; i += T1_THREADS) { st[i] = 0; sg[i] = 0; nw[i] = 0; }
+    for (int i = tid; i < CF_WORDS; i += T1_THREADS) { F[i] = 0; N[i] = 0; SG[i] = 0; }
     for (int i = tid; i < (int)(sizeof(T1Luts) / 2); i += T1_THREADS) ((short *)&luts)[i] = ((const short *)g_luts)[i];
+    for (int i = tid; i < 512; i += T1_THREADS) zc[i] = zc_lut[orient * 512 + i];
     if (tid == 0) { s_max = 0; s_nmsedec = 0; }
     __syncthreads();
 
@@ -156,7 +190,7 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
         for (int j = 0; j < 4; ++j) mag[k][j] = 0;
         if (q < nsc) {
             int s = q / bw, x = q - s * bw;
-            sidx[k] = (s + 1) * T1_SW + x + 1;
+            sidx[k] = (s + 1) * CF_W + x + 1;
             lim[k] = min(4, bh - 4 * s);
 #pragma unroll
             for (int j = 0; j < 4; ++j)
@@ -168,141 +202,130 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
                     if (v < 0) sgn4[k] |= 1u << j;
                     mymax = max(mymax, a);
                 }
-            sg[sidx[k]] = sgn4[k];
+            N[sidx[k]] = sgn4[k];          // staging for SG
         }
     }
     for (int o = 16; o > 0; o >>= 1) mymax = max(mymax, __shfl_xor_sync(0xffffffffu, mymax, o));
     if ((tid & 31) == 0) atomicMax(&s_max, mymax);
     __syncthreads();
+#pragma unroll
+    for (int k = 0; k < T1_CPT; ++k)
+        if (sidx[k] >= 0) SG[sidx[k]] = ((N[sidx[k] - CF_W] >> 3) & 1u) | (sgn4[k] << 1) | ((N[sidx[k] + CF_W] & 1u) << 5);
     const int maxv = s_max;
     const int numbps = maxv ? (32 - __clz(maxv)) - 6 : 0;     // floorlog2(max)+1-T1_NMSEDEC_FRACBITS
     if (tid == 0) { out->numbps = numbps; out->totalpasses = 0; out->datalen = 0; out->numpasses = 0; }
     if (numbps <= 0) return;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < T1_CPT; ++k) if (sidx[k] >= 0) N[sidx[k]] = 0;
+    __syncthreads();
 
     unsigned total_syms = 0;
     int passno = 0;
     for (int bpno = numbps - 1, passtype = 2; bpno >= 0; ++passno) {
         const unsigned one = 1u << (bpno + 6);
         T1Sym sy[T1_CPT];
-        unsigned upd_sig[T1_CPT], upd_pi[T1_CPT], upd_mu[T1_CPT];
+        unsigned upd_pi[T1_CPT], upd_mu[T1_CPT];
         int nmsedec = 0;
+#pragma unroll
+        for (int k = 0; k < T1_CPT; ++k) { sy[k].bits = 0; sy[k].cnt = 0; upd_pi[k] = 0; upd_mu[k] = 0; }
 
-        // ---- pass-specific preparation of nw[] ---------------------------------------------------
-        if (passtype == 2) {
+        if (passtype == 0) {
+            // ---- significance propagation: least fixed point of "becomes significant", then one emitting sweep ----
+            unsigned acc[T1_CPT];
 #pragma unroll
-            for (int k = 0; k < T1_CPT; ++k)
-                if (sidx[k] >= 0) {
-                    unsigned w = st[sidx[k]], bits = 0;
+            for (int k = 0; k < T1_CPT; ++k) acc[k] = 0;
+            for (;;) {
+                int changed = 0;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) bits |= ((mag[k][j] & one) ? 1u : 0u) << j;
-                    nw[sidx[k]] = ~ST_SIG(w) & ~ST_PI(w) & bits & 0xfu;
+                for (int k = 0; k < T1_CPT; ++k) {
+                    if (sidx[k] < 0) continue;
+                    const int p = sidx[k];
+                    const unsigned f = F[p];
+                    if ((~cf_own4(f) & ((1u << lim[k]) - 1u)) == 0) continue;
+                    unsigned dummy_c = 0; int dummy_n = 0;
+                    const unsigned fr = cf_sigpass_col<false>(f, N[p], mag[k], one, lim[k], sgn4[k], zc, SG, p, &luts, bpno, sy[k], dummy_c, dummy_n);
+                    const unsigned delta = fr & ~acc[k];
+                    if (delta) { cf_scatter(N, p, delta); acc[k] |= delta; changed = 1; }
                 }
-            __syncthreads();
-        } else if (passtype == 0) {
-#pragma unroll
-            for (int k = 0; k < T1_CPT; ++k) if (sidx[k] >= 0) nw[sidx[k]] = 0;
-            __syncthreads();
-        }
-
-        // ---- evaluate (sigpass iterates to the fixed point; the last sweep emits) ------------------
-        for (;;) {
-            int changed = 0;
+                if (!__syncthreads_or(changed)) break;
+            }
 #pragma unroll
             for (int k = 0; k < T1_CPT; ++k) {
-                sy[k].bits = 0; sy[k].cnt = 0; upd_sig[k] = 0; upd_pi[k] = 0; upd_mu[k] = 0;
                 if (sidx[k] < 0) continue;
                 const int p = sidx[k];
-                const unsigned cw = st[p];
-                {
-                    // columns with nothing to code in this pass need no neighbourhood window
-                    const unsigned rows = (1u << lim[k]) - 1u;
-                    if (passtype == 1) { if ((ST_SIG(cw) & ~ST_PI(cw) & rows) == 0) continue; }
-                    else if (passtype == 0) { if ((~ST_SIG(cw) & rows) == 0) { if (nw[p]) { nw[p] = 0; changed = 1; } continue; } }
-                    else if (((ST_SIG(cw) | ST_PI(cw)) & rows) == rows) { upd_sig[k] = nw[p]; continue; }
-                }
-                T1Win w;
-                {
-                    unsigned lo = t1_six(ST_SIG(st[p - T1_SW - 1]), ST_SIG(st[p - 1]), ST_SIG(st[p + T1_SW - 1]));
-                    unsigned co = t1_six(ST_SIG(st[p - T1_SW]), ST_SIG(cw), ST_SIG(st[p + T1_SW]));
-                    unsigned ro = t1_six(ST_SIG(st[p - T1_SW + 1]), ST_SIG(st[p + 1]), ST_SIG(st[p + T1_SW + 1]));
-                    if (passtype != 1) {
-                        unsigned ln = t1_six(nw[p - T1_SW - 1], nw[p - 1], nw[p + T1_SW - 1]);
-                        unsigned cn = t1_six(nw[p - T1_SW], 0, 0);
-                        unsigned rn = t1_six(nw[p - T1_SW + 1], 0, 0);
-                        lo |= ln & 0x1fu; co |= cn & 1u; ro |= rn & 1u;
-                    }
-                    w.L = lo; w.C = co; w.R = ro;
-                    w.gL = t1_six(sg[p - T1_SW - 1], sg[p - 1], sg[p + T1_SW - 1]);
-                    w.gC = t1_six(sg[p - T1_SW], sgn4[k], sg[p + T1_SW]);
-                    w.gR = t1_six(sg[p - T1_SW + 1], sg[p + 1], sg[p + T1_SW + 1]);
-                }
-                const unsigned sig = ST_SIG(cw), pi = ST_PI(cw), mu = ST_MU(cw);
-                if (passtype == 0) {
-                    // significance propagation (t1.c:363-410, 479-580)
-                    unsigned coded = 0, fresh = 0;
+                const unsigned f = F[p];
+                if ((~cf_own4(f) & ((1u << lim[k]) - 1u)) == 0) continue;
+                cf_sigpass_col<true>(f, N[p], mag[k], one, lim[k], sgn4[k], zc, SG, p, &luts, bpno, sy[k], upd_pi[k], nmsedec);
+            }
+        } else if (passtype == 1) {
+            // ---- magnitude refinement (t1.c:743-765, 814-922) ----
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        if (j >= lim[k]) break;
-                        if (!((sig >> j) & 1) && t1_has_nb(w, j)) {
-                            int v = (mag[k][j] & one) ? 1 : 0;
-                            t1_put(sy[k], t1_zc_of(w, j, orient), v);
-                            if (v) {
-                                t1_sign(sy[k], w, j, (sgn4[k] >> j) & 1);
-                                nmsedec += t1_nm_sig(&luts, mag[k][j], bpno);
-                                fresh |= 1u << j;
-                                w.C |= 1u << (j + 1);
-                            }
-                            coded |= 1u << j;
-                        }
-                    }
-                    if (fresh != nw[p]) { nw[p] = fresh; changed = 1; }
-                    upd_sig[k] = fresh; upd_pi[k] = coded;
-                } else if (passtype == 1) {
-                    // magnitude refinement (t1.c:743-765, 814-922)
+            for (int k = 0; k < T1_CPT; ++k) {
+                if (sidx[k] < 0) continue;
+                const unsigned f = F[sidx[k]];
+                const unsigned sig = cf_own4(f), pi = (f >> 24) & 15u;
+                if ((sig & ~pi & ((1u << lim[k]) - 1u)) == 0) continue;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        if (j >= lim[k]) break;
-                        if (((sig >> j) & 1) && !((pi >> j) & 1)) {
-                            int ctx = ((mu >> j) & 1) ? CTX_MAG + 2 : (t1_has_nb(w, j) ? CTX_MAG + 1 : CTX_MAG);
-                            nmsedec += t1_nm_ref(&luts, mag[k][j], bpno);
-                            t1_put(sy[k], ctx, (mag[k][j] & one) ? 1 : 0);
-                            upd_mu[k] |= 1u << j;
-                        }
+                for (int j = 0; j < 4; ++j) {
+                    if (j >= lim[k]) break;
+                    if (((sig >> j) & 1) && !((pi >> j) & 1)) {
+                        const int ctx = (f & CF_MU(j)) ? CTX_MAG + 2 : ((f & CF_NB(j)) ? CTX_MAG + 1 : CTX_MAG);
+                        nmsedec += t1_nm_ref(&luts, mag[k][j], bpno);
+                        t1_put(sy[k], ctx, (mag[k][j] & one) ? 1 : 0);
+                        upd_mu[k] |= 1u << j;
                     }
-                } else {
-                    // cleanup with run-length mode (t1.c:1051-1116, 1163-1256)
-                    int runlen = 0, agg = 0;
-                    if (lim[k] == 4 && (sig | pi) == 0 && (w.L | w.C | w.R) == 0) {
-                        agg = 1;
-                        const unsigned fresh = nw[p];
-                        runlen = fresh ? (__ffs((int)fresh) - 1) : 4;
-                        t1_put(sy[k], CTX_AGG, runlen != 4);
-                        if (runlen != 4) { t1_put(sy[k], CTX_UNI, runlen >> 1); t1_put(sy[k], CTX_UNI, runlen & 1); }
-                    }
-                    if (runlen < 4) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            if (j >= lim[k]) break;
-                            if (j < runlen) continue;
-                            int v;
-                            if (agg && j == runlen) v = 1;
-                            else if (!(((sig | pi) >> j) & 1)) {
-                                v = (mag[k][j] & one) ? 1 : 0;
-                                t1_put(sy[k], t1_zc_of(w, j, orient), v);
-                            } else v = 0;
-                            if (v) {
-                                t1_sign(sy[k], w, j, (sgn4[k] >> j) & 1);
-                                nmsedec += t1_nm_sig(&luts, mag[k][j], bpno);
-                                w.C |= 1u << (j + 1);
-                            }
-                        }
-                    }
-                    upd_sig[k] = nw[p];
                 }
             }
-            if (passtype != 0) break;
-            if (!__syncthreads_or(changed)) break;
-            nmsedec = 0;
+        } else {
+            // ---- cleanup with run-length mode (t1.c:1051-1116, 1163-1256): what becomes significant is known up front ----
+            unsigned fresh[T1_CPT];
+#pragma unroll
+            for (int k = 0; k < T1_CPT; ++k) {
+                fresh[k] = 0;
+                if (sidx[k] < 0) continue;
+                const unsigned f = F[sidx[k]];
+                unsigned bits = 0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) bits |= ((mag[k][j] & one) ? 1u : 0u) << j;
+                fresh[k] = ~cf_own4(f) & ~(f >> 24) & bits & ((1u << lim[k]) - 1u);
+                if (fresh[k]) cf_scatter(N, sidx[k], fresh[k]);
+            }
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < T1_CPT; ++k) {
+                if (sidx[k] < 0) continue;
+                const int p = sidx[k];
+                const unsigned f = F[p];
+                const unsigned sig = cf_own4(f), pi = (f >> 24) & 15u, rows = (1u << lim[k]) - 1u;
+                if (((sig | pi) & rows) == rows) continue;
+                unsigned t = f | (N[p] & CF_EARLY);
+                int runlen = 0, agg = 0;
+                if (lim[k] == 4 && (t & 0x0f03ffffu) == 0) {
+                    agg = 1;
+                    runlen = fresh[k] ? (__ffs((int)fresh[k]) - 1) : 4;
+                    t1_put(sy[k], CTX_AGG, runlen != 4);
+                    if (runlen != 4) { t1_put(sy[k], CTX_UNI, runlen >> 1); t1_put(sy[k], CTX_UNI, runlen & 1); }
+                }
+                if (runlen < 4) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        if (j >= lim[k]) break;
+                        if (j < runlen) continue;
+                        int v;
+                        if (agg && j == runlen) v = 1;
+                        else if (!(((sig | pi) >> j) & 1)) {
+                            v = (mag[k][j] & one) ? 1 : 0;
+                            t1_put(sy[k], CTX_ZC + zc[(t >> (j * 3)) & 0x1ffu], v);
+                        } else v = 0;
+                        if (v) {
+                            cf_sign(sy[k], t, SG, p, j, (sgn4[k] >> j) & 1);
+                            nmsedec += t1_nm_sig(&luts, mag[k][j], bpno);
+                            t |= CF_SIG(j);
+                        }
+                    }
+                }
+            }
         }
 
         // ---- CTA-wide exclusive scan of symbol counts, staged write of the symbol bytes ------------
@@ -314,6 +337,18 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
         if ((tid & 31) == 31) warp_sum[tid >> 5] = incl;
         for (int o = 16; o > 0; o >>= 1) nmsedec += __shfl_xor_sync(0xffffffffu, nmsedec, o);
         if ((tid & 31) == 0 && nmsedec) atomicAdd(&s_nmsedec, nmsedec);
+        // ---- state update: every word absorbs what its neighbourhood gained; own pi / mu ---------------
+#pragma unroll
+        for (int k = 0; k < T1_CPT; ++k)
+            if (sidx[k] >= 0) {
+                const int p = sidx[k];
+                unsigned w = F[p];
+                if (passtype == 2) w = (w | N[p]) & ~(0xfu << 24);                // new significance, clear pi
+                else if (passtype == 0) w |= N[p] | (upd_pi[k] << 24);
+                else w |= upd_mu[k] << 28;
+                F[p] = w;
+                if (passtype != 1) N[p] = 0;
+            }
         __syncthreads();
         int off = incl - mycnt;
         for (int wi = 0; wi < (tid >> 5); ++wi) off += warp_sum[wi];
@@ -323,16 +358,6 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
             unsigned long long b = sy[k].bits;
             for (int i = 0; i < sy[k].cnt; ++i) { symbuf[off++] = (unsigned char)(((b & 62) << 1) | (b & 1)); b >>= 6; }
         }
-        // ---- state update ---------------------------------------------------------------------------
-#pragma unroll
-        for (int k = 0; k < T1_CPT; ++k)
-            if (sidx[k] >= 0) {
-                unsigned w = st[sidx[k]];
-                if (passtype == 2) w = (w | upd_sig[k]) & ~0xf0u;                 // new significance, clear pi
-                else if (passtype == 0) w |= upd_sig[k] | (upd_pi[k] << 4);
-                else w |= upd_mu[k] << 8;
-                st[sidx[k]] = w;
-            }
         __syncthreads();
         const int total = s_total;
         for (int i = tid; i < total; i += T1_THREADS) sym[total_syms + i] = symbuf[i];
@@ -366,10 +391,9 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
 // successors of the new state are fetched off the critical path.  The symbol byte is ctx << 2 | decision.
 struct MqTable { unsigned e[47]; };
 
-#define MQ_WARPS 4
-#define MQ_THREADS (MQ_WARPS * 32)
+#define MQ_WARPS(L) ((L) >= 32 ? 2 : 4)       // warps per CTA (static shared memory stays below 48 KB)
+#define MQ_THREADS(L) (MQ_WARPS(L) * 32)
 #define MQ_DEFAULT_LANES 4
-#define MQ_CHUNK 512                 // symbol bytes staged in shared memory per refill (16 per lane)
 
 // shared-memory accesses of the serial chain by 32-bit shared address: one LDS / STS each, no generic
 // address arithmetic (the host-side emulation build uses plain pointers)
@@ -443,35 +467,37 @@ __device__ __forceinline__ void mq_pass_end(MqEnc &q, CblkOut *out, int p, int n
     }
 }
 
-// L code-blocks per warp (L = 1, 2, 4, 8).  The 32 / L lanes of a group move their block's symbol stream
-// HBM -> registers -> shared memory in 512-byte refills (the next refill is in flight while the current one
+// L code-blocks per warp (L = 1, 2, 4, ... 32).  The 32 / L lanes of a group move their block's symbol stream
+// HBM -> registers -> shared memory in refills of up to 512 bytes (the next refill is in flight while the current one
 // is coded); the first lane of each group runs the serial MQ chain out of shared memory.  The coding lanes
 // advance in lock step: every stretch of symbols up to the nearest pass end of any of them has a uniform
 // trip count, the common step (MPS, interval still normalised) is shared by all lanes, and the state
 // update + renormalisation is one predicated region so that only byte output really diverges.
 template <int L>
-__global__ void __launch_bounds__(MQ_THREADS)
+__global__ void __launch_bounds__(MQ_THREADS(L))
 k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char *__restrict__ sym_pool,
         unsigned char *mq_pool, const MqTable *__restrict__ g_tab, int ncblks, int nframes,
         size_t sym_stride, size_t mq_stride)
 {
     constexpr int G = 32 / L;                     // lanes per code-block
-    constexpr int R = MQ_CHUNK / (16 * G);        // 16-byte loads per lane and refill
-    constexpr unsigned CM = L == 1 ? 0x1u : (L == 2 ? 0x00010001u : (L == 4 ? 0x01010101u : 0x11111111u));
+    constexpr int R = L < 8 ? L : 8;              // 16-byte loads per lane and refill
+    constexpr int CH = 16 * G * R;                // symbol bytes per refill and block: 512 (L <= 8), 256, 128
+    constexpr unsigned CM = L == 1 ? 0x1u : (L == 2 ? 0x00010001u : (L == 4 ? 0x01010101u : (L == 8 ? 0x11111111u :
+                            (L == 16 ? 0x55555555u : 0xffffffffu))));
     __shared__ __align__(16) uint2 tabn[96];      // pair -> {word after MPS, word after LPS}
-    __shared__ __align__(16) uint4 ctxs[MQ_WARPS * L][20];
-    __shared__ __align__(16) unsigned char stage[MQ_WARPS * L][MQ_CHUNK + 16];
+    __shared__ __align__(16) uint4 ctxs[MQ_WARPS(L) * L][20];
+    __shared__ __align__(16) unsigned char stage[MQ_WARPS(L) * L][CH + 16];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     auto word = [&](unsigned pr) { return ((g_tab->e[pr >> 1] & 0xffffu) << 16) | (pr << 3) | (pr & 1u); };
     auto succ = [&](unsigned pr) {
         const unsigned e = g_tab->e[pr >> 1], m = pr & 1u;
         return make_uint2(word(((e >> 16) & 63u) * 2u + m), word(((e >> 22) & 63u) * 2u + (m ^ ((e >> 28) & 1u))));
     };
-    if (tid < 94) tabn[tid] = succ(tid);
+    for (int i = tid; i < 94; i += MQ_THREADS(L)) tabn[i] = succ((unsigned)i);
     __syncthreads();
     const int g = lane / G, gl = lane - g * G, blk = wid * L + g;
     const bool coder = gl == 0;
-    const long long job = ((long long)blockIdx.x * MQ_WARPS + wid) * L + g;
+    const long long job = ((long long)blockIdx.x * MQ_WARPS(L) + wid) * L + g;
     const bool valid = job < (long long)ncblks * nframes;
     // frame varies fastest: the lanes of a warp code the same code-block position of different frames, whose
     // symbol counts are similar
@@ -490,7 +516,7 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
         const uint2 nx = tabn[pr];
         cx[k] = make_uint4(word(pr), nx.x, nx.y, 0);
     }
-    for (int k = gl; k < 16; k += G) stage[blk][MQ_CHUNK + k] = 0;       // look-ahead slack behind the refill
+    for (int k = gl; k < 16; k += G) stage[blk][CH + k] = 0;       // look-ahead slack behind the refill
 
     MqEnc q;
     q.a = 0x8000; q.c = 0; q.ct = 12; q.pos = -1; q.pend = 0;
@@ -506,18 +532,18 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
         const unsigned o = (gl + r * G) * 16u;
         pre[r] = o < total ? *(const uint4 *)(sym + o) : make_uint4(0, 0, 0, 0);
     }
-    for (unsigned cbeg = 0; cbeg < maxtotal; cbeg += MQ_CHUNK) {
+    for (unsigned cbeg = 0; cbeg < maxtotal; cbeg += CH) {
         __syncwarp();
 #pragma unroll
         for (int r = 0; r < R; ++r) *(uint4 *)(stg + (gl + r * G) * 16) = pre[r];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const unsigned o = cbeg + MQ_CHUNK + (gl + r * G) * 16u;
+            const unsigned o = cbeg + CH + (gl + r * G) * 16u;
             if (o < total) pre[r] = *(const uint4 *)(sym + o);
         }
         __syncwarp();
         if (!coder) continue;
-        const unsigned cend = min(cbeg + MQ_CHUNK, total);
+        const unsigned cend = min(cbeg + CH, total);
         for (;;) {
             const bool act = i < cend;
             const unsigned m = __ballot_sync(CM, act);
