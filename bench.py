@@ -36,7 +36,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import harness as H  # noqa: E402
 
 FRAMES, HH, WW, BASE_CR = 24, 721, 1440, 30.0
-PIPES = 3
+PIPES = 6
 NSAMP = HH * WW
 STAGES = ["h2d", "minmax", "dwt", "t1_cm", "t1_mq", "pcrd_t2", "bodies", "d2h"]
 METRIC = "compress throughput, GB/s of f32 input (mode NONE, 24x721x1440, base_cr 30)"
@@ -168,6 +168,10 @@ def run_ours(args):
     os.environ.setdefault("EBCC_PIPELINES", str(PIPES))
     frames = make_frames(rank)
     in_bytes = frames.nbytes
+    # the caller's input buffer is pinned host memory (base contract: H2D "from pinned host memory")
+    import torch
+    pinned = torch.from_numpy(frames).pin_memory()
+    frames = pinned.numpy()
 
     # ---- device-resident pass (value) ----
     ctx = C.c_void_p(lib.ebcc_cuda_ctx_create(local))
@@ -247,24 +251,29 @@ def run_ours(args):
     if world == 1:
         lib.ebcc_decode_batch.restype = C.c_size_t
 
+        dec_buf = torch.empty((FRAMES, NSAMP), dtype=torch.float32).pin_memory()   # caller-owned, pinned output frames
+        dec_np = dec_buf.numpy()
+
         def time_mode(mode, err, label):
             c2 = H.CodecConfig(); c2.dims[:] = [1, HH, WW]; c2.base_cr = BASE_CR; c2.mode = mode; c2.error = err
             best_e = best_d = 1e9
-            for _ in range(2):
+            for _ in range(3):
                 t0 = time.perf_counter()
                 n = lib.ebcc_encode_batch(frames.ctypes.data_as(C.c_void_p), C.c_size_t(FRAMES), C.byref(c2), outs, osz)
                 best_e = min(best_e, time.perf_counter() - t0)
                 assert n == FRAMES
                 ptrs = (C.c_void_p * FRAMES)(*[C.cast(outs[i], C.c_void_p).value for i in range(FRAMES)])
                 douts, cnts = (C.POINTER(C.c_float) * FRAMES)(), (C.c_size_t * FRAMES)()
+                for i in range(FRAMES):
+                    douts[i] = C.cast(dec_buf[i].data_ptr(), C.POINTER(C.c_float))
                 t0 = time.perf_counter()
                 n = lib.ebcc_decode_batch(ptrs, osz, C.c_size_t(FRAMES), douts, cnts)
                 best_d = min(best_d, time.perf_counter() - t0)
                 assert n == FRAMES
-                worst = max(float(np.abs(np.ctypeslib.as_array(douts[i], shape=(cnts[i],)) - frames[i].ravel()).max()) for i in range(FRAMES))
+                worst = max(float(np.abs(dec_np[i] - frames[i].ravel()).max()) for i in range(FRAMES))
                 tot = sum(osz)
                 for i in range(FRAMES):
-                    lib.free_buffer(outs[i]); lib.free_buffer(douts[i])
+                    lib.free_buffer(outs[i])
             modes[label] = {"compress_GBps_e2e": in_bytes / best_e / 1e9, "decompress_GBps_e2e": in_bytes / best_d / 1e9,
                             "cr": in_bytes / tot, "max_abs_err": worst}
         time_mode(H.NONE, 0.0, "none")

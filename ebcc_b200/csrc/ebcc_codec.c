@@ -112,7 +112,7 @@ static int dims_are_valid(const size_t dims[NDIMS])
  * Every encode / decode call (and every worker of a multi-batch call) owns one pipeline while it runs, so callers on
  * several threads -- or several batches of one call -- are in flight on the device at the same time: the kernels of
  * one batch fill the issue slots the latency-bound tier-1 coder of another leaves idle.  EBCC_PIPELINES (1..8,
- * default 2) bounds how many. */
+ * default 4) bounds how many. */
 #define EBCC_MAX_PIPELINES 8
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
 static pthread_cond_t g_cv = PTHREAD_COND_INITIALIZER;
@@ -123,7 +123,7 @@ static pid_t g_ctx_pid = 0;
 static int n_pipelines(void)
 {
     const char *env = getenv("EBCC_PIPELINES");
-    long v = env ? atol(env) : 2;
+    long v = env ? atol(env) : 4;
     return v < 1 ? 1 : (v > EBCC_MAX_PIPELINES ? EBCC_MAX_PIPELINES : (int)v);
 }
 

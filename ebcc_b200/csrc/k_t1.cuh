@@ -393,7 +393,7 @@ struct MqTable { unsigned e[47]; };
 
 #define MQ_WARPS(L) ((L) >= 32 ? 2 : 4)       // warps per CTA (static shared memory stays below 48 KB)
 #define MQ_THREADS(L) (MQ_WARPS(L) * 32)
-#define MQ_DEFAULT_LANES 4
+#define MQ_DEFAULT_LANES 32
 
 // shared-memory accesses of the serial chain by 32-bit shared address: one LDS / STS each, no generic
 // address arithmetic (the host-side emulation build uses plain pointers)
