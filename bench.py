@@ -191,6 +191,8 @@ def run_ours(args):
     sizes = (C.c_size_t * FRAMES)()
     lib.ebcc_cuda_download(ctx, C.c_size_t(FRAMES), None, sizes, None, None, None)
     out_bytes = sum(sizes)
+    nsym, mqb = C.c_ulonglong(), C.c_ulonglong()
+    assert lib.ebcc_cuda_t1_totals(ctx, C.c_size_t(FRAMES), C.byref(nsym), C.byref(mqb)) == 0
     # ---- the same step with PIPES batches in flight (value) ----
     ctxs = [ctx]
     for _ in range(PIPES - 1):
@@ -293,9 +295,14 @@ def run_ours(args):
     peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
     stage = {n: st[i] / args.steps for i, n in enumerate(STAGES)}
     dom = max(("t1_cm", "t1_mq", "dwt", "pcrd_t2"), key=lambda k: stage[k])
-    alg = {"t1_mq": FRAMES * NSAMP * 4 + out_bytes, "t1_cm": FRAMES * NSAMP * 4 + out_bytes,
+    # algorithmic bytes per launch (kernel table): k_t1_cm reads the coefficients and writes one byte per EBCOT
+    # symbol; k_t1_mq reads the symbols and writes the MQ bytes; the DWT reads/writes every level twice
+    alg = {"t1_mq": nsym.value + mqb.value, "t1_cm": FRAMES * NSAMP * 4 + nsym.value,
            "dwt": FRAMES * NSAMP * 4 * (1 + 2 * (4 / 3)), "pcrd_t2": out_bytes}[dom]
     achieved = alg / (stage[dom] * 1e-3) / 1e9
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture of this workload
+    # (profiles/r01_ncu_t1_enc_summary.md)
+    traffic = {"t1_mq": 347.6e6, "t1_cm": 348.4e6}.get(dom)
     line = {
         "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -310,8 +317,11 @@ def run_ours(args):
         "stage_ms": stage,
         "modes": modes,
         "roofline": {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None,
-                     "note": "tier-1 is integer-issue/latency bound; the HBM fraction is reported for completeness"},
+                     "frac": achieved / peak, "traffic": traffic,
+                     "algorithmic_bytes": int(alg), "ebcot_symbols_per_step": int(nsym.value), "mq_bytes_per_step": int(mqb.value),
+                     "note": "tier-1 is integer-issue/latency bound (serial MQ chain per code-block), not HBM bound; the HBM "
+                             "fraction is reported for completeness.  Timed alone on one stream; with batches in flight the "
+                             "kernel overlaps other batches' kernels"},
         "clocks": sampler.summary(),
     }
     if world == 1 and H.have_ref() and not args.no_cpu:

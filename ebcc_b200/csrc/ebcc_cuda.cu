@@ -981,6 +981,24 @@ extern "C" int ebcc_cuda_debug_cblk(ebcc_cuda_ctx *c, size_t frame, size_t cblk,
     return 0;
 }
 
+// measurement tap: what tier-1 moved for the resident batch -- EBCOT symbols (1 byte each, written by k_t1_cm, read by
+// k_t1_mq) and MQ-coded bytes (written by k_t1_mq), summed over all code-blocks of the first nframes frames
+extern "C" int ebcc_cuda_t1_totals(ebcc_cuda_ctx *c, size_t nframes, unsigned long long *symbols, unsigned long long *mq_bytes)
+{
+    if (!c || nframes > c->cap_frames) return -1;
+    const size_t n = nframes * (size_t)c->plan.ncblks;
+    CblkOut *h = (CblkOut *)malloc(n * sizeof(CblkOut));
+    if (!h) return -1;
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaMemcpy(h, c->d_cbout, n * sizeof(CblkOut), cudaMemcpyDeviceToHost));
+    unsigned long long s = 0, b = 0;
+    for (size_t i = 0; i < n; ++i)
+        if (h[i].totalpasses > 0) { s += h[i].nsym_end[h[i].totalpasses - 1]; b += (unsigned long long)h[i].datalen; }
+    free(h);
+    *symbols = s; *mq_bytes = b;
+    return 0;
+}
+
 // test tap: SPIHT bitstream of a frame after ebcc_cuda_residual_encode
 extern "C" int ebcc_cuda_debug_spiht_stream(ebcc_cuda_ctx *c, size_t frame, uint8_t *dst, size_t cap, size_t *len)
 {

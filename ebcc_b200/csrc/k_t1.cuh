@@ -154,7 +154,7 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
     __shared__ unsigned F[CF_WORDS];        // flag words
     __shared__ unsigned N[CF_WORDS];        // significance gained in the running pass, same neighbourhood layout
     __shared__ unsigned SG[CF_WORDS];       // static: sign of rows -1..4 of the column (bits 0..5)
-    __shared__ unsigned char symbuf[T1_SYMBUF + 64];
+    __shared__ __align__(16) unsigned char symbuf[T1_SYMBUF + 64];
     __shared__ unsigned char zc[512];
     __shared__ T1Luts luts;
     __shared__ int warp_sum[T1_THREADS / 32];
@@ -350,9 +350,17 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
                 if (passtype != 1) N[p] = 0;
             }
         __syncthreads();
-        int off = incl - mycnt;
-        for (int wi = 0; wi < (tid >> 5); ++wi) off += warp_sum[wi];
-        if (tid == T1_THREADS - 1) s_total = off + mycnt;
+        // symbols are staged behind the still unwritten tail of the previous pass (head bytes), so that shared and
+        // global memory are 16-byte co-aligned and the copy moves whole 16-byte blocks
+        const int head = (int)(total_syms & 15u);
+        int off = incl - mycnt + head;
+        {
+            const int nw = T1_THREADS / 32, wv = (tid & 31) < nw ? warp_sum[tid & 31] : 0;
+            int ex = wv;
+            for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, ex, o); if ((tid & 31) >= o) ex += t; }
+            off += __shfl_sync(0xffffffffu, ex - wv, tid >> 5);
+        }
+        if (tid == T1_THREADS - 1) s_total = off + mycnt - head;
 #pragma unroll
         for (int k = 0; k < T1_CPT; ++k) {
             unsigned long long b = sy[k].bits;
@@ -360,10 +368,19 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
         }
         __syncthreads();
         const int total = s_total;
-        for (int i = tid; i < total; i += T1_THREADS) sym[total_syms + i] = symbuf[i];
+        {
+            const int nblk = (head + total + 15) >> 4;
+            uint4 *dst = (uint4 *)(sym + (total_syms & ~15u));
+            for (int i = tid; i < nblk; i += T1_THREADS) dst[i] = ((const uint4 *)symbuf)[i];
+        }
         total_syms += (unsigned)total;
         if (tid == 0) { out->nsym_end[passno] = total_syms; out->nmsedec[passno] = s_nmsedec; s_nmsedec = 0; }
         __syncthreads();
+        // the partial last block stays staged for the next pass
+        uint4 tailv = make_uint4(0, 0, 0, 0);
+        if (tid == 0) tailv = ((const uint4 *)symbuf)[(head + total) >> 4];
+        __syncthreads();
+        if (tid == 0) ((uint4 *)symbuf)[0] = tailv;
         if (++passtype == 3) { passtype = 0; bpno--; }
     }
 

@@ -116,6 +116,10 @@ int ebcc_cuda_bench_resident(ebcc_cuda_ctx *ctx, size_t nframes, float base_cr, 
 int ebcc_cuda_bench_resident_pipelined(ebcc_cuda_ctx **ctxs, int nctx, size_t nframes, float base_cr, int steps, int warmup,
                                        size_t flush_bytes, float *total_ms);
 
+/* measurement tap: EBCOT symbols (one byte each, k_t1_cm -> k_t1_mq) and MQ-coded bytes tier-1 produced for the first
+ * nframes frames of the resident batch -- the algorithmic traffic of the tier-1 kernels */
+int ebcc_cuda_t1_totals(ebcc_cuda_ctx *ctx, size_t nframes, unsigned long long *symbols, unsigned long long *mq_bytes);
+
 /* debug/test taps on the resident batch (device -> host copies of intermediates) */
 int ebcc_cuda_debug_coef(ebcc_cuda_ctx *ctx, size_t frame, float *dst);
 int ebcc_cuda_debug_spiht_stream(ebcc_cuda_ctx *ctx, size_t frame, uint8_t *dst, size_t cap, size_t *len);
