@@ -129,8 +129,15 @@ def barrier(dist):
         torch.cuda.synchronize()
 
 
+def dist_teardown(dist):
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def run_reference(args):
     rank, world, local, dist = dist_setup(args.gpus)
+    dist_teardown(dist)
     if rank != 0:
         return
     if not H.have_ref():
@@ -282,6 +289,7 @@ def run_ours(args):
         time_mode(H.MAX_ERROR, 0.5, "max_error_0.5")
         time_mode(H.MAX_ERROR, 0.1, "max_error_0.1")
     sampler.stop_flag = True; sampler.join(timeout=2)
+    dist_teardown(dist)
 
     if rank != 0:
         return
