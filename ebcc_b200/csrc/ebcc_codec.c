@@ -603,27 +603,57 @@ typedef struct {
 
 static uint32_t be32(const uint8_t *p) { return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]; }
 
+static int legacy_take(const uint8_t **it, const uint8_t *end, void *dst, size_t nb)
+{
+    if ((size_t)(end - *it) < nb) return 0;
+    memcpy(dst, *it, nb);
+    *it += nb;
+    return 1;
+}
+
+/* header-less streams of older EBCC releases (reference ebcc_decode_legacy, src/ebcc_codec.c:1147-1213):
+ * f32 min, f32 max, u64 coeffs_size, f32 rmin, f32 rmax, u64 zstd_size, zstd payload, then u64 count (constant
+ * field, min == max) or the JPEG 2000 codestream */
+static int parse_legacy_prefix(const uint8_t *data, size_t n, parsed_stream_t *ps)
+{
+    const uint8_t *it = data, *end = data + n;
+    uint64_t cs = 0, zs = 0;
+    if (!legacy_take(&it, end, &ps->minval, 4) || !legacy_take(&it, end, &ps->maxval, 4) || !legacy_take(&it, end, &cs, 8) ||
+        !legacy_take(&it, end, &ps->rmin, 4) || !legacy_take(&it, end, &ps->rmax, 4) || !legacy_take(&it, end, &zs, 8)) {
+        ebcc_log(LOG_FATAL, "Invalid legacy encoded data: truncated header");
+        return 0;
+    }
+    if ((uint64_t)(end - it) < zs) { ebcc_log(LOG_FATAL, "Invalid legacy encoded data: truncated residual payload"); return 0; }
+    ps->coeffs_size = (size_t)cs; ps->zstd_size = (size_t)zs;
+    ps->zstd = it; it += zs;
+    ps->tail = it; ps->tail_size = (size_t)(end - it);
+    ps->const_field = ps->minval == ps->maxval;
+    if (ps->const_field && ps->tail_size < sizeof(uint64_t)) { ebcc_log(LOG_FATAL, "Invalid legacy encoded data: missing const-field length"); return 0; }
+    if (ps->const_field) ps->tail_size = sizeof(uint64_t);
+    return 1;
+}
+
 static int parse_stream(const uint8_t *data, size_t n, parsed_stream_t *ps)
 {
     memset(ps, 0, sizeof(*ps));
     if (n < sizeof(ebcc_header_t) || memcmp(data, EBCC_HEADER_MAGIC, 4) != 0) {
-        ebcc_log(LOG_FATAL, "legacy (header-less) EBCC streams are not supported by the CUDA codec");
-        return 0;
+        if (!parse_legacy_prefix(data, n, ps)) return 0;
+    } else {
+        ebcc_header_t h;
+        memcpy(&h, data, sizeof(h));
+        if (h.version != EBCC_HEADER_VERSION) { ebcc_log(LOG_FATAL, "Unsupported EBCC header version: %u", h.version); return 0; }
+        size_t used = sizeof(h);
+        if (h.compressed_size > n - used) { ebcc_log(LOG_FATAL, "Invalid encoded data: truncated payload"); return 0; }
+        used += (size_t)h.compressed_size;
+        if (h.tail_size > n - used) { ebcc_log(LOG_FATAL, "Invalid encoded data: truncated payload"); return 0; }
+        used += (size_t)h.tail_size;
+        if (used != n) { ebcc_log(LOG_FATAL, "Invalid encoded data: payload size mismatch"); return 0; }
+        ps->minval = bits_to_float(h.minval_bits); ps->maxval = bits_to_float(h.maxval_bits);
+        ps->rmin = bits_to_float(h.residual_minval_bits); ps->rmax = bits_to_float(h.residual_maxval_bits);
+        ps->coeffs_size = (size_t)h.coeffs_size; ps->zstd_size = (size_t)h.compressed_size; ps->tail_size = (size_t)h.tail_size;
+        ps->zstd = data + sizeof(h); ps->tail = ps->zstd + ps->zstd_size;
+        ps->const_field = (h.flags & EBCC_HEADER_FLAG_CONST_FIELD) != 0;
     }
-    ebcc_header_t h;
-    memcpy(&h, data, sizeof(h));
-    if (h.version != EBCC_HEADER_VERSION) { ebcc_log(LOG_FATAL, "Unsupported EBCC header version: %u", h.version); return 0; }
-    size_t used = sizeof(h);
-    if (h.compressed_size > n - used) { ebcc_log(LOG_FATAL, "Invalid encoded data: truncated payload"); return 0; }
-    used += (size_t)h.compressed_size;
-    if (h.tail_size > n - used) { ebcc_log(LOG_FATAL, "Invalid encoded data: truncated payload"); return 0; }
-    used += (size_t)h.tail_size;
-    if (used != n) { ebcc_log(LOG_FATAL, "Invalid encoded data: payload size mismatch"); return 0; }
-    ps->minval = bits_to_float(h.minval_bits); ps->maxval = bits_to_float(h.maxval_bits);
-    ps->rmin = bits_to_float(h.residual_minval_bits); ps->rmax = bits_to_float(h.residual_maxval_bits);
-    ps->coeffs_size = (size_t)h.coeffs_size; ps->zstd_size = (size_t)h.compressed_size; ps->tail_size = (size_t)h.tail_size;
-    ps->zstd = data + sizeof(h); ps->tail = ps->zstd + ps->zstd_size;
-    ps->const_field = (h.flags & EBCC_HEADER_FLAG_CONST_FIELD) != 0;
     if (ps->const_field) {
         if (ps->tail_size != sizeof(uint64_t)) { ebcc_log(LOG_FATAL, "Invalid encoded data: const-field payload must contain uint64_t length"); return 0; }
         uint64_t t; memcpy(&t, ps->tail, sizeof(t));

@@ -83,3 +83,33 @@ def test_chunked_container_round_trip(built):
     d = H.decode(lib, s, fn="ebcc_decode_chunking")
     assert d is not None and d.size == data.size
     assert np.allclose(d.reshape(data.shape), data, atol=0.02)       # tolerance of the reference's tests/test_c_api.py:168-171
+
+
+def _to_legacy(stream):
+    """Re-serialise a current stream in the header-less layout of older EBCC releases (reference
+    ebcc_decode_legacy, src/ebcc_codec.c:1147-1213)."""
+    import struct
+    magic, ver, flags, _r, mn, mx, coeffs, rmn, rmx, zsize, tsize = struct.unpack("<4sBBHIIQIIQQ", stream[:48])
+    assert magic == b"EBCC"
+    z, tail = stream[48:48 + zsize], stream[48 + zsize:48 + zsize + tsize]
+    return struct.pack("<IIQIIQ", mn, mx, coeffs, rmn, rmx, zsize) + z + tail
+
+
+@pytest.mark.parametrize("mode,err", [(H.NONE, 0.0), (H.MAX_ERROR, 0.2)])
+def test_legacy_streams_decode(built, mode, err):
+    lib = H.prod_lib()
+    f = H.synth_stack(1, 150, 210)[0]
+    s = H.encode(lib, f, (1, 150, 210), 15.0, mode, err)
+    want = H.decode(lib, s)
+    leg = _to_legacy(s)
+    got = H.decode(lib, leg)
+    assert got is not None and np.array_equal(got, want)
+    if H.have_ref():
+        assert np.array_equal(H.decode(H.ref_lib(), leg), got)
+    # constant field in the legacy layout: min == max, then the element count
+    c = np.full((40, 50), 3.25, dtype=np.float32)
+    sc = H.encode(lib, c, (1, 40, 50), 10.0)
+    gc = H.decode(lib, _to_legacy(sc))
+    assert gc is not None and gc.size == 2000 and np.all(gc == np.float32(3.25))
+    # truncated legacy header fails cleanly
+    assert H.decode(lib, leg[:20]) is None
