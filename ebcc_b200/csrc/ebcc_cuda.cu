@@ -218,7 +218,7 @@ static void fill_dec_luts(DecLuts *d, const MqTable *t)
     for (int st = 0; st < 47; ++st)
         for (int mps = 0; mps < 2; ++mps) {
             const unsigned e = t->e[st], qe = e & 0xffffu, nm = (e >> 16) & 63u, nl = (e >> 22) & 63u, sw = (e >> 28) & 1u;
-            d->mq[st * 2 + mps] = qe | ((nm * 2 + (unsigned)mps) << 16) | ((nl * 2 + ((unsigned)mps ^ sw)) << 24);
+            d->mq[st * 2 + mps] = qe | ((nm * 2 + (unsigned)mps) << 16) | ((nl * 2 + ((unsigned)mps ^ sw)) << 23) | ((unsigned)mps << 30);
         }
 }
 
@@ -230,6 +230,7 @@ struct ebcc_cuda_ctx {
     CblkDesc *h_cblks;
     Plan *d_plan;
     CblkDesc *d_cblks;
+    int *d_order;              // code-block indices by descending area: long decode chains start first
     BandDesc *d_bands;
     T1Luts *d_luts;
     MqTable *d_mqtab;
@@ -336,7 +337,7 @@ extern "C" ebcc_cuda_ctx *ebcc_cuda_ctx_create(int device)
 
 static void free_buffers(ebcc_cuda_ctx *c)
 {
-    cudaFree(c->d_plan); cudaFree(c->d_cblks); cudaFree(c->d_in); cudaFree(c->d_coef); cudaFree(c->d_stat);
+    cudaFree(c->d_plan); cudaFree(c->d_cblks); cudaFree(c->d_order); c->d_order = NULL; cudaFree(c->d_in); cudaFree(c->d_coef); cudaFree(c->d_stat);
     cudaFree(c->d_sym); cudaFree(c->d_mq); cudaFree(c->d_out); cudaFree(c->d_packed); cudaFree(c->d_cbout);
     cudaFree(c->d_maxlen); cudaFree(c->d_body_off); cudaFree(c->d_pout); cudaFree(c->d_offs);
     cudaFreeHost(c->h_pout); cudaFreeHost(c->h_stat); cudaFreeHost(c->h_offs); cudaFreeHost(c->h_maxlen);
@@ -395,6 +396,21 @@ extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nf
     CK(cudaMalloc((void **)&c->d_cblks, sizeof(CblkDesc) * pl->ncblks));
     CK(cudaMemcpy(c->d_plan, pl, sizeof(Plan), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(c->d_cblks, c->h_cblks, sizeof(CblkDesc) * pl->ncblks, cudaMemcpyHostToDevice));
+    {
+        // longest-processing-time-first launch order for the one-block-per-warp decoder: when the grid does not fit
+        // the GPU in one wave, the blocks left for the tail are the small ones
+        int *ord = (int *)malloc(sizeof(int) * pl->ncblks);
+        for (int i = 0; i < pl->ncblks; ++i) ord[i] = i;
+        for (int i = 1; i < pl->ncblks; ++i) {              // insertion sort, stable, by area descending
+            const int v = ord[i], a = c->h_cblks[v].w * c->h_cblks[v].h;
+            int j = i - 1;
+            while (j >= 0 && c->h_cblks[ord[j]].w * c->h_cblks[ord[j]].h < a) { ord[j + 1] = ord[j]; --j; }
+            ord[j + 1] = v;
+        }
+        CK(cudaMalloc((void **)&c->d_order, sizeof(int) * pl->ncblks));
+        CK(cudaMemcpy(c->d_order, ord, sizeof(int) * pl->ncblks, cudaMemcpyHostToDevice));
+        free(ord);
+    }
     c->d_bands = (BandDesc *)((char *)c->d_plan + offsetof(Plan, bands));
     CK(cudaMalloc((void **)&c->d_in, B * N * sizeof(float)));
     CK(cudaMalloc((void **)&c->d_coef, B * N * sizeof(float)));
@@ -602,7 +618,7 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
     const long long njobs = (long long)pl->ncblks * B;
     const bool probe = orig != NULL;         // probe of the CR search: jobs come from the encoder, the recording is used
     EBCC_LAUNCH(k_t1_dec, dim3((unsigned)((njobs + DEC_WARPS - 1) / DEC_WARPS)), dim3(DEC_WARPS * 32), 0, c->stream,
-                c->d_cblks, c->d_jobs, pool, pool_stride, c->d_declut, c->d_iplane, probe ? c->d_spass : (unsigned char *)NULL, c->d_scratch,
+                c->d_cblks, c->d_order, c->d_jobs, pool, pool_stride, c->d_declut, c->d_iplane, probe ? c->d_spass : (unsigned char *)NULL, c->d_scratch,
                 probe ? (const CblkOut *)c->d_cbout : (const CblkOut *)NULL, probe ? c->d_dstate : (DecState *)NULL,
                 probe ? c->d_decsave : (unsigned *)NULL, W, H, pl->ncblks, B);
     if (probe)

@@ -39,7 +39,7 @@ struct DecState { int np_dec; int scratch_np; unsigned bad[4]; };
 // the same Annex-D rule the encoder evaluates arithmetically (t1_zc_ctx)
 struct DecLuts {
     unsigned char zc[4 * 512];
-    unsigned mq[94];           // per (state, mps): qe | next-if-mps << 16 | next-if-lps << 24
+    unsigned mq[94];           // per (state, mps) pair: qe | pair after an MPS << 16 | pair after an LPS << 23 | mps << 30
 };
 
 #define DEC_FW 66
@@ -83,52 +83,115 @@ __device__ __forceinline__ void mqc_shift(MqCore &k, const unsigned char *data, 
     }
 }
 
+// Truncation shadows (compression-ratio search only), one set per warp in shared memory: shadow j replays the
+// byte-consuming half of the decoder on the segment cut at trunc[j] = rate[pass + j]; it forks from the main decoder the
+// first time a byte at or beyond the cut is read.  Everything that touches them is out of line, so the per-symbol code
+// of the (eight times inlined) decoder stays small: the kernel is bound by instruction fetch otherwise.
+struct MqShadows {
+    MqCore sh[DEC_NSHADOW];
+    int trunc[DEC_NSHADOW];        // cut length of slot j, < 0: slot unused
+    unsigned sh_bad;               // bit j: slot j diverged (or could not be verified)
+};
+
 struct MqDec {
     unsigned a;
     MqCore m;                      // the decoder proper
     const unsigned char *data;
-    // truncation shadows (compression-ratio search only): shadow j replays the decoder on the segment cut at
-    // trunc[j] = rate[tp + j]; it forks from the main decoder the first time a byte at or beyond the cut is read
-    MqCore sh[DEC_NSHADOW];
-    int trunc[DEC_NSHADOW];        // cut length of slot j, < 0: slot unused
-    unsigned sh_on, sh_bad;        // bit j: slot j forked / diverged (or could not be verified)
+    MqShadows *sw;                 // nullptr: plain decode
+    unsigned sh_on;                // bit j: slot j forked
+    int fork_at;                   // smallest armed cut that has not forked yet (INT_MAX: none)
     int maxread;                   // highest byte index the main decoder has looked at
 };
 
+__device__ __forceinline__ int mqd_next_fork(const MqShadows *sw, unsigned sh_on)
+{
+    int f = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < DEC_NSHADOW; ++j)
+        if (sw->trunc[j] >= 0 && !((sh_on >> j) & 1u) && sw->trunc[j] < f) f = sw->trunc[j];
+    return f;
+}
+
+// the main decoder (state m, about to read byte idx) reaches one or more cuts: fork their shadows.
 // nrem: renormalisation shifts of the current symbol still to be applied (a shadow forked in the middle of a
-// renormalisation has to finish it on its own)
+// renormalisation has to finish it on its own).  Returns the new sh_on.
+__device__ __noinline__ unsigned mqd_fork(MqShadows *sw, unsigned sh_on, MqCore m, const unsigned char *data, int idx, int nrem)
+{
+#pragma unroll
+    for (int j = 0; j < DEC_NSHADOW; ++j)
+        if (sw->trunc[j] >= 0 && !((sh_on >> j) & 1u) && idx >= sw->trunc[j]) {
+            MqCore k = m;
+            k.len = sw->trunc[j]; sh_on |= 1u << j;
+            // the shadow's current byte may already lie beyond its cut (a cut inside the decoder's look-ahead)
+            if (k.bp >= sw->trunc[j]) sw->sh_bad |= 1u << j;
+            mqc_bytein(k, data);
+            mqc_shift(k, data, nrem);
+            sw->sh[j] = k;
+        }
+    return sh_on;
+}
+
+// one decision of the main decoder replayed on every forked shadow
+__device__ __noinline__ void mqd_shadow_step(MqShadows *sw, unsigned sh_on, unsigned qe, unsigned a0, unsigned mps, unsigned d,
+                                             int nshift, const unsigned char *data)
+{
+#pragma unroll
+    for (int j = 0; j < DEC_NSHADOW; ++j)
+        if ((sh_on >> j) & 1u) {
+            MqCore k = sw->sh[j];
+            unsigned ds;
+            if ((k.c >> 16) < qe) ds = (a0 < qe) ? mps : (mps ^ 1u);
+            else { k.c -= qe << 16; ds = ((a0 & 0x8000u) == 0) ? ((a0 < qe) ? (mps ^ 1u) : mps) : mps; }
+            if (ds != d) sw->sh_bad |= 1u << j;
+            else if (!((sw->sh_bad >> j) & 1u)) mqc_shift(k, data, nshift);
+            sw->sh[j] = k;
+        }
+}
+
+// end of pass p: slot 0 holds the verdict of "stop after pass p" (not forked => the decoder never looked beyond the
+// cut); retire it, shift the others down, arm a new last slot with cut tn (< 0: none).  Returns the verdict (1 = bad).
+__device__ __noinline__ unsigned mqd_retire(MqShadows *sw, unsigned &sh_on, int tn, int maxread)
+{
+    const unsigned bad = sw->sh_bad & 1u;
+#pragma unroll
+    for (int j = 0; j + 1 < DEC_NSHADOW; ++j) { sw->sh[j] = sw->sh[j + 1]; sw->trunc[j] = sw->trunc[j + 1]; }
+    sh_on >>= 1; sw->sh_bad >>= 1;
+    sw->trunc[DEC_NSHADOW - 1] = tn;
+    if (tn >= 0 && tn <= maxread) { sh_on |= 1u << (DEC_NSHADOW - 1); sw->sh_bad |= 1u << (DEC_NSHADOW - 1); }
+    return bad;
+}
+
 __device__ __forceinline__ void mqd_main_bytein(MqDec &q, int nrem)
 {
     const int idx = q.m.bp + 1;
     if (idx > q.maxread) q.maxread = idx;
-#pragma unroll
-    for (int j = 0; j < DEC_NSHADOW; ++j)
-        if (q.trunc[j] >= 0 && !((q.sh_on >> j) & 1u) && idx >= q.trunc[j]) {
-            q.sh[j] = q.m; q.sh[j].len = q.trunc[j]; q.sh_on |= 1u << j;
-            // the shadow's current byte may already lie beyond its cut (a cut inside the decoder's look-ahead)
-            if (q.sh[j].bp >= q.trunc[j]) q.sh_bad |= 1u << j;
-            mqc_bytein(q.sh[j], q.data);
-            mqc_shift(q.sh[j], q.data, nrem);
-        }
+    if (idx >= q.fork_at) {
+        q.sh_on = mqd_fork(q.sw, q.sh_on, q.m, q.data, idx, nrem);
+        q.fork_at = mqd_next_fork(q.sw, q.sh_on);
+    }
     mqc_bytein(q.m, q.data);
 }
 
-__device__ __forceinline__ void mqd_init(MqDec &q, const unsigned char *data, int len)
+__device__ __forceinline__ void mqd_init(MqDec &q, const unsigned char *data, int len, MqShadows *sw)
 {
     q.data = data; q.m.len = len; q.m.bp = 0;
     q.m.cur = mqc_byte(q.m, data, 0);
     q.m.c = q.m.cur << 16;
     q.m.ct = 0;
-    q.sh_on = 0; q.sh_bad = 0; q.maxread = 1;
+    q.sw = sw; q.sh_on = 0; q.fork_at = 0x7fffffff; q.maxread = 1;
+    if (sw) {
+        sw->sh_bad = 0;
 #pragma unroll
-    for (int j = 0; j < DEC_NSHADOW; ++j) q.trunc[j] = -1;
+        for (int j = 0; j < DEC_NSHADOW; ++j) sw->trunc[j] = -1;
+    }
     mqc_bytein(q.m, data);
     q.m.c <<= 7; q.m.ct -= 7; q.a = 0x8000u;
 }
 
-__device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned char *ctx, const unsigned *tab)
+// a context is a copy of its pair's table word, so one shared-memory load brings qe, mps and both successors
+__device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned *ctx, const unsigned *tab)
 {
-    const unsigned st = *ctx, e = tab[st], qe = e & 0xffffu, mps = st & 1u;
+    const unsigned e = *ctx, qe = e & 0xffffu, mps = e >> 30;
     const unsigned a0 = q.a - qe;
     unsigned d, a1 = a0;
     bool ren;
@@ -141,20 +204,9 @@ __device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned char *ctx, con
         else { d = mps; ren = false; }
     }
     const int nshift = ren ? __clz((int)a1) - 16 : 0;
-    if (q.sh_on) {
-#pragma unroll
-        for (int j = 0; j < DEC_NSHADOW; ++j)
-            if ((q.sh_on >> j) & 1u) {
-                MqCore &k = q.sh[j];
-                unsigned ds;
-                if ((k.c >> 16) < qe) ds = (a0 < qe) ? mps : (mps ^ 1u);
-                else { k.c -= qe << 16; ds = ((a0 & 0x8000u) == 0) ? ((a0 < qe) ? (mps ^ 1u) : mps) : mps; }
-                if (ds != d) q.sh_bad |= 1u << j;
-                else if (!((q.sh_bad >> j) & 1u)) mqc_shift(k, q.data, nshift);
-            }
-    }
+    if (q.sh_on) mqd_shadow_step(q.sw, q.sh_on, qe, a0, mps, d, nshift, q.data);
     if (ren) {
-        *ctx = (unsigned char)((d == mps) ? ((e >> 16) & 0xffu) : (e >> 24));
+        *ctx = tab[(d == mps) ? ((e >> 16) & 127u) : ((e >> 23) & 127u)];
         // main decoder: shifts with fork checks at every byte read
         int n = nshift;
         while (n > 0) {
@@ -169,7 +221,7 @@ __device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned char *ctx, con
 
 struct T1DecState {
     unsigned *F;                 // flag words of this block
-    unsigned char *cx;           // 19 context states
+    unsigned *cx;                // 19 contexts (table words)
     const unsigned char *zc;     // zero-coding LUT of this orientation
     const unsigned *tab;
     int *plane;                  // top-left of the block inside the integer coefficient plane
@@ -308,44 +360,39 @@ __device__ void t1d_passes(T1DecState &S, MqDec &q, int w, int h, int numbps, in
         else if (passtype == 1) t1d_refpass(S, q, w, h, bpno);
         else t1d_clnpass(S, q, w, h, bpno);
         if (rates) {
-            // verdict for "stop after pass p": slot 0.  Not forked => the decoder never looked beyond the cut.
-            if ((q.sh_bad & 1u) && p < 128) ds.bad[p >> 5] |= 1u << (p & 31);
-            // retire slot 0, shift the others down, arm a new last slot
-#pragma unroll
-            for (int j = 0; j + 1 < DEC_NSHADOW; ++j) { q.sh[j] = q.sh[j + 1]; q.trunc[j] = q.trunc[j + 1]; }
-            q.sh_on >>= 1; q.sh_bad >>= 1;
             const int pn = p + DEC_NSHADOW;
-            const int tn = pn < nrates ? rates[pn] : -1;
-            q.trunc[DEC_NSHADOW - 1] = tn;
-            if (tn >= 0 && tn <= q.maxread) { q.sh_on |= 1u << (DEC_NSHADOW - 1); q.sh_bad |= 1u << (DEC_NSHADOW - 1); }
+            if (mqd_retire(q.sw, q.sh_on, pn < nrates ? rates[pn] : -1, q.maxread) && p < 128) ds.bad[p >> 5] |= 1u << (p & 31);
+            q.fork_at = mqd_next_fork(q.sw, q.sh_on);
         }
     }
 }
 
 // serial decoder registers <-> save area
-__device__ __forceinline__ void mqd_save(const MqDec &q, const unsigned char *cx, unsigned *o)
+__device__ __noinline__ void mqd_save(const MqDec &q, const unsigned *cx, unsigned *o)
 {
     int k = 0;
     o[k++] = q.a; o[k++] = q.m.c; o[k++] = q.m.ct; o[k++] = (unsigned)q.m.bp; o[k++] = (unsigned)q.m.len; o[k++] = q.m.cur;
-#pragma unroll
     for (int j = 0; j < DEC_NSHADOW; ++j) {
-        o[k++] = q.sh[j].c; o[k++] = q.sh[j].ct; o[k++] = (unsigned)q.sh[j].bp; o[k++] = (unsigned)q.sh[j].len; o[k++] = q.sh[j].cur;
-        o[k++] = (unsigned)q.trunc[j];
+        const MqCore &h = q.sw->sh[j];
+        o[k++] = h.c; o[k++] = h.ct; o[k++] = (unsigned)h.bp; o[k++] = (unsigned)h.len; o[k++] = h.cur;
+        o[k++] = (unsigned)q.sw->trunc[j];
     }
-    o[k++] = q.sh_on; o[k++] = q.sh_bad; o[k++] = (unsigned)q.maxread;
-    for (int i = 0; i < 20; i += 4) o[k++] = cx[i] | (cx[i + 1] << 8) | (cx[i + 2] << 16) | ((unsigned)cx[i + 3] << 24);
+    o[k++] = q.sh_on; o[k++] = q.sw->sh_bad; o[k++] = (unsigned)q.maxread;
+    for (int i = 0; i < 19; ++i) o[k++] = cx[i];
 }
-__device__ __forceinline__ void mqd_load(MqDec &q, unsigned char *cx, const unsigned *o)
+__device__ __noinline__ void mqd_load(MqDec &q, unsigned *cx, const unsigned *o, MqShadows *sw)
 {
     int k = 0;
     q.a = o[k++]; q.m.c = o[k++]; q.m.ct = o[k++]; q.m.bp = (int)o[k++]; q.m.len = (int)o[k++]; q.m.cur = o[k++];
-#pragma unroll
+    q.sw = sw;
     for (int j = 0; j < DEC_NSHADOW; ++j) {
-        q.sh[j].c = o[k++]; q.sh[j].ct = o[k++]; q.sh[j].bp = (int)o[k++]; q.sh[j].len = (int)o[k++]; q.sh[j].cur = o[k++];
-        q.trunc[j] = (int)o[k++];
+        MqCore &h = sw->sh[j];
+        h.c = o[k++]; h.ct = o[k++]; h.bp = (int)o[k++]; h.len = (int)o[k++]; h.cur = o[k++];
+        sw->trunc[j] = (int)o[k++];
     }
-    q.sh_on = o[k++]; q.sh_bad = o[k++]; q.maxread = (int)o[k++];
-    for (int i = 0; i < 20; i += 4) { const unsigned v = o[k++]; cx[i] = v & 0xff; cx[i + 1] = (v >> 8) & 0xff; cx[i + 2] = (v >> 16) & 0xff; cx[i + 3] = v >> 24; }
+    q.sh_on = o[k++]; sw->sh_bad = o[k++]; q.maxread = (int)o[k++];
+    q.fork_at = mqd_next_fork(sw, q.sh_on);
+    for (int i = 0; i < 19; ++i) cx[i] = o[k++];
 }
 
 // grid = ceil(ncblks * nframes / DEC_WARPS) CTAs of DEC_WARPS warps; lane 0 of a warp decodes, the warp moves state.
@@ -355,12 +402,13 @@ __device__ __forceinline__ void mqd_load(MqDec &q, unsigned char *cx, const unsi
 //   decodes the truncated segment for real into the scratch plane right away (job becomes mode 2).  Mode 2 does only
 //   that.  The block region of a plane is cleared before a decode that starts at pass 0.
 __global__ void __launch_bounds__(DEC_WARPS * 32)
-k_t1_dec(const CblkDesc *__restrict__ cblks, DecJob *jobs, const unsigned char *__restrict__ pool,
+k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJob *jobs, const unsigned char *__restrict__ pool,
          size_t pool_stride, const DecLuts *__restrict__ g_luts, int *iplane, unsigned char *spass, int *scratch,
          const CblkOut *__restrict__ cbout, DecState *dstate, unsigned *save, int W, int H, int ncblks, int nframes)
 {
     __shared__ unsigned F[DEC_WARPS][DEC_FWORDS];
-    __shared__ unsigned char cxs[DEC_WARPS][32];
+    __shared__ unsigned cxs[DEC_WARPS][20];
+    __shared__ MqShadows shw[DEC_WARPS];
     __shared__ unsigned tab[94];
     __shared__ unsigned char zc[4 * 512];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -370,7 +418,8 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, DecJob *jobs, const unsigned char *
     const long long job = (long long)blockIdx.x * DEC_WARPS + warp;
     if (job >= (long long)ncblks * nframes) return;
     // frame varies fastest so that the warps of a CTA (and neighbouring CTAs) hold blocks of similar length
-    const int cbi = (int)(job / nframes), frame = (int)(job - (long long)cbi * nframes);
+    const int slot = (int)(job / nframes), frame = (int)(job - (long long)slot * nframes);
+    const int cbi = order[slot];               // largest blocks first
     const size_t bi = (size_t)frame * ncblks + cbi;
     const DecJob jb = jobs[bi];
     if (jb.mode != 1 && jb.mode != 2) return;
@@ -381,7 +430,7 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, DecJob *jobs, const unsigned char *
     unsigned *sv = search ? save + bi * DEC_SAVE_WORDS : nullptr;
     const size_t o = (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx;
     const unsigned char *seg = pool + (size_t)frame * pool_stride + jb.off;
-    unsigned char *cx = cxs[warp];
+    unsigned *cx = cxs[warp];
     T1DecState S;
     S.F = F[warp]; S.cx = cx; S.zc = zc + cb.orient * 512; S.tab = tab; S.W = W; S.pass = 0;
     int mode = jb.mode;
@@ -404,18 +453,19 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, DecJob *jobs, const unsigned char *
             MqDec q;
             const int *rates = search ? cbout[bi].rate : nullptr;
             const int nrates = search ? cbout[bi].totalpasses : 0;
-            if (resume) { mqd_load(q, cx, sv + DEC_SAVE_MQ); q.data = seg; }
+            if (resume) { mqd_load(q, cx, sv + DEC_SAVE_MQ, &shw[warp]); q.data = seg; }
             else {
-                for (int i = 0; i < 20; ++i) cx[i] = 0;
-                cx[CTX_UNI] = 46 << 1; cx[CTX_AGG] = 3 << 1; cx[CTX_ZC] = 4 << 1;
-                mqd_init(q, seg, jb.len);
+                for (int i = 0; i < 19; ++i) cx[i] = tab[0];
+                cx[CTX_UNI] = tab[46 << 1]; cx[CTX_AGG] = tab[3 << 1]; cx[CTX_ZC] = tab[4 << 1];
+                mqd_init(q, seg, jb.len, rates ? &shw[warp] : (MqShadows *)nullptr);
                 if (rates) {
-#pragma unroll
                     for (int j = 0; j < DEC_NSHADOW; ++j) {
-                        q.trunc[j] = j < nrates ? rates[j] : -1;
+                        const int tn = j < nrates ? rates[j] : -1;
+                        shw[warp].trunc[j] = tn;
                         // cuts inside the two bytes the decoder reads while initialising cannot fork any more
-                        if (q.trunc[j] >= 0 && q.trunc[j] <= q.maxread) { q.sh_on |= 1u << j; q.sh_bad |= 1u << j; }
+                        if (tn >= 0 && tn <= q.maxread) { q.sh_on |= 1u << j; shw[warp].sh_bad |= 1u << j; }
                     }
+                    q.fork_at = mqd_next_fork(&shw[warp], q.sh_on);
                 }
             }
             t1d_passes(S, q, cb.w, cb.h, jb.numbps, ds.np_dec, jb.np, rates, nrates, ds);
@@ -447,11 +497,11 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, DecJob *jobs, const unsigned char *
     __syncwarp();
     if (lane != 0) return;
     if (jb.np > 0 && jb.numbps > 0) {
-        for (int i = 0; i < 20; ++i) cx[i] = 0;
-        cx[CTX_UNI] = 46 << 1; cx[CTX_AGG] = 3 << 1; cx[CTX_ZC] = 4 << 1;
+        for (int i = 0; i < 19; ++i) cx[i] = tab[0];
+        cx[CTX_UNI] = tab[46 << 1]; cx[CTX_AGG] = tab[3 << 1]; cx[CTX_ZC] = tab[4 << 1];
         S.plane = scratch + o; S.spass = nullptr;
         MqDec q;
-        mqd_init(q, seg, search ? cbout[bi].rate[jb.np - 1] : jb.len);
+        mqd_init(q, seg, search ? cbout[bi].rate[jb.np - 1] : jb.len, nullptr);
         DecState dummy = ds;
         t1d_passes(S, q, cb.w, cb.h, jb.numbps, 0, jb.np, nullptr, 0, dummy);
     }
