@@ -677,6 +677,61 @@ static int parse_stream(const uint8_t *data, size_t n, parsed_stream_t *ps)
     return 1;
 }
 
+typedef struct {
+    parsed_stream_t *ps; float **outs; size_t *counts; int *owned;
+    size_t nframes, maxb, ngroups, next, done;
+    size_t *starts, *ends;
+    pthread_mutex_t mu;
+} dec_job_t;
+
+static void *dec_worker(void *arg)
+{
+    dec_job_t *jb = (dec_job_t *)arg;
+    const size_t maxb = jb->maxb;
+    parsed_stream_t *ps = jb->ps;
+    const uint8_t **js = (const uint8_t **)malloc(sizeof(*js) * maxb);
+    size_t *jn = (size_t *)malloc(sizeof(size_t) * maxb), *idx = (size_t *)malloc(sizeof(size_t) * maxb);
+    float *mn = (float *)malloc(sizeof(float) * maxb), *mx = (float *)malloc(sizeof(float) * maxb);
+    float **dst = (float **)malloc(sizeof(float *) * maxb);
+    ebcc_residual_in *rs = (ebcc_residual_in *)calloc(maxb, sizeof(*rs));
+    ebcc_cuda_ctx *ctx = NULL;
+    for (;;) {
+        pthread_mutex_lock(&jb->mu);
+        const size_t g = jb->next < jb->ngroups ? jb->next++ : (size_t)-1;
+        pthread_mutex_unlock(&jb->mu);
+        if (g == (size_t)-1) break;
+        const size_t i = jb->starts[g], H = ps[i].H, W = ps[i].W;
+        size_t nb = 0;
+        for (size_t j = i; j < jb->ends[g]; ++j) {
+            if (!ps[j].ok || ps[j].const_field) continue;
+            if (!jb->outs[j]) { jb->outs[j] = (float *)malloc(H * W * sizeof(float)); jb->owned[j] = 1; }
+            if (!jb->outs[j]) { ps[j].ok = 0; continue; }
+            js[nb] = ps[j].tail; jn[nb] = ps[j].tail_size; mn[nb] = ps[j].minval; mx[nb] = ps[j].maxval; dst[nb] = jb->outs[j]; idx[nb] = j;
+            memset(&rs[nb], 0, sizeof(rs[nb]));
+            if (ps[j].zstd_size > 0 && ps[j].coeffs_size > 0) {
+                rs[nb].zstd = ps[j].zstd; rs[nb].zstd_size = ps[j].zstd_size; rs[nb].coeffs_size = ps[j].coeffs_size;
+                rs[nb].rmin = ps[j].rmin; rs[nb].rmax = ps[j].rmax;
+            }
+            nb++;
+        }
+        if (!nb) continue;
+        if (!ctx) ctx = acquire_ctx();
+        const int rc = ctx ? ebcc_cuda_decode_batch(ctx, js, jn, nb, H, W, mn, mx, rs, dst) : -1;
+        size_t ok = 0;
+        for (size_t k = 0; k < nb; ++k) {
+            if (rc == 0) { jb->counts[idx[k]] = H * W; ok++; }
+            else if (jb->owned[idx[k]]) { free(jb->outs[idx[k]]); jb->outs[idx[k]] = NULL; }
+        }
+        if (rc) ebcc_log(LOG_FATAL, "CUDA decode of %lu frame(s) failed", nb);
+        pthread_mutex_lock(&jb->mu);
+        jb->done += ok;
+        pthread_mutex_unlock(&jb->mu);
+    }
+    if (ctx) release_ctx(ctx);
+    free(js); free(jn); free(idx); free(mn); free(mx); free(dst); free(rs);
+    return NULL;
+}
+
 size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, size_t nframes, float **outs, size_t *counts)
 {
     log_set_level_from_env();
@@ -694,45 +749,34 @@ size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, si
             outs[i] = o; counts[i] = ps[i].tot_size; done++;
         }
     }
-    const size_t maxb = max_batch_frames();
-    const uint8_t **js = (const uint8_t **)malloc(sizeof(*js) * maxb);
-    size_t *jn = (size_t *)malloc(sizeof(size_t) * maxb), *idx = (size_t *)malloc(sizeof(size_t) * maxb);
-    float *mn = (float *)malloc(sizeof(float) * maxb), *mx = (float *)malloc(sizeof(float) * maxb);
-    float **dst = (float **)malloc(sizeof(float *) * maxb);
-    ebcc_residual_in *rs = (ebcc_residual_in *)calloc(maxb, sizeof(*rs));
-    ebcc_cuda_ctx *ctx = NULL;
-    size_t i = 0;
-    while (i < nframes) {
+    /* runs of frames with the same geometry, at most EBCC_BATCH_FRAMES each, become the jobs of the workers */
+    dec_job_t job;
+    memset(&job, 0, sizeof(job));
+    job.ps = ps; job.outs = outs; job.counts = counts; job.owned = owned; job.nframes = nframes; job.maxb = max_batch_frames();
+    job.starts = (size_t *)malloc(sizeof(size_t) * (nframes ? nframes : 1));
+    job.ends = (size_t *)malloc(sizeof(size_t) * (nframes ? nframes : 1));
+    for (size_t i = 0; i < nframes;) {
         if (!ps[i].ok || ps[i].const_field) { ++i; continue; }
-        /* gather a run of frames with the same geometry */
-        const size_t H = ps[i].H, W = ps[i].W;
         size_t nb = 0, j = i;
-        for (; j < nframes && nb < maxb; ++j) {
+        for (; j < nframes && nb < job.maxb; ++j) {
             if (!ps[j].ok || ps[j].const_field) continue;
-            if (ps[j].H != H || ps[j].W != W) break;
-            if (!outs[j]) { outs[j] = (float *)malloc(H * W * sizeof(float)); owned[j] = 1; }
-            if (!outs[j]) { ps[j].ok = 0; continue; }
-            js[nb] = ps[j].tail; jn[nb] = ps[j].tail_size; mn[nb] = ps[j].minval; mx[nb] = ps[j].maxval; dst[nb] = outs[j]; idx[nb] = j;
-            memset(&rs[nb], 0, sizeof(rs[nb]));
-            if (ps[j].zstd_size > 0 && ps[j].coeffs_size > 0) {
-                rs[nb].zstd = ps[j].zstd; rs[nb].zstd_size = ps[j].zstd_size; rs[nb].coeffs_size = ps[j].coeffs_size;
-                rs[nb].rmin = ps[j].rmin; rs[nb].rmax = ps[j].rmax;
-            }
+            if (ps[j].H != ps[i].H || ps[j].W != ps[i].W) break;
             nb++;
         }
-        if (nb) {
-            if (!ctx) ctx = acquire_ctx();
-            int rc = ctx ? ebcc_cuda_decode_batch(ctx, js, jn, nb, H, W, mn, mx, rs, dst) : -1;
-            for (size_t k = 0; k < nb; ++k) {
-                if (rc == 0) { counts[idx[k]] = H * W; done++; }
-                else if (owned[idx[k]]) { free(outs[idx[k]]); outs[idx[k]] = NULL; }
-            }
-            if (rc) ebcc_log(LOG_FATAL, "CUDA decode of %lu frame(s) failed", nb);
-        }
+        job.starts[job.ngroups] = i; job.ends[job.ngroups] = j; job.ngroups++;
         i = j;
     }
-    if (ctx) release_ctx(ctx);
-    free(js); free(jn); free(idx); free(mn); free(mx); free(dst); free(rs); free(ps); free(owned);
+    pthread_mutex_init(&job.mu, NULL);
+    int nworkers = n_pipelines();
+    if ((size_t)nworkers > job.ngroups) nworkers = (int)job.ngroups;
+    pthread_t th[EBCC_MAX_PIPELINES];
+    int started = 0;
+    for (int k = 1; k < nworkers; ++k) if (pthread_create(&th[started], NULL, dec_worker, &job) == 0) started++;
+    if (job.ngroups) dec_worker(&job);
+    for (int k = 0; k < started; ++k) pthread_join(th[k], NULL);
+    pthread_mutex_destroy(&job.mu);
+    done += job.done;
+    free(job.starts); free(job.ends); free(ps); free(owned);
     return done;
 }
 

@@ -64,6 +64,20 @@ def test_multi_batch_call_uses_pipelines(built, env_guard):
     os.environ["EBCC_PIPELINES"] = "3"
     many = _encode_batch(lib, frames, 160, 224, 12.0, H.MAX_ERROR, 0.3)
     assert one == many
+    # one decode call over all 13 streams: 4 batches on 3 pipelines, results equal the single-stream decodes
+    lib.ebcc_decode_batch.restype = C.c_size_t
+    n = len(many)
+    bufs = [C.create_string_buffer(s, len(s)) for s in many]
+    ptrs = (C.c_void_p * n)(*[C.addressof(b) for b in bufs])
+    sizes = (C.c_size_t * n)(*[len(s) for s in many])
+    douts, cnts = (C.POINTER(C.c_float) * n)(), (C.c_size_t * n)()
+    assert lib.ebcc_decode_batch(ptrs, sizes, C.c_size_t(n), douts, cnts) == n
+    os.environ["EBCC_PIPELINES"] = "1"
+    for t in range(n):
+        got = np.ctypeslib.as_array(douts[t], shape=(cnts[t],)).copy()
+        lib.free_buffer(douts[t])
+        assert np.array_equal(got, H.decode(lib, many[t]))
+        assert float(np.abs(got - frames[t].ravel()).max()) <= 0.3 * 1.01 + 1e-6
 
 
 def test_concurrent_callers(built, env_guard):
