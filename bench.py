@@ -260,31 +260,37 @@ def run_ours(args):
     if world == 1:
         lib.ebcc_decode_batch.restype = C.c_size_t
 
-        dec_buf = torch.empty((FRAMES, NSAMP), dtype=torch.float32).pin_memory()   # caller-owned, pinned output frames
+        # one call = PIPES batches of 24 frames (EBCC_BATCH_FRAMES=24): the library spreads them over its pipelines
+        os.environ["EBCC_BATCH_FRAMES"] = str(FRAMES)
+        NF = FRAMES * PIPES
+        big = torch.from_numpy(np.ascontiguousarray(np.concatenate([frames] * PIPES, axis=0))).pin_memory()
+        big_np = big.numpy()
+        dec_buf = torch.empty((NF, NSAMP), dtype=torch.float32).pin_memory()   # caller-owned, pinned output frames
         dec_np = dec_buf.numpy()
+        bouts, bosz = (C.POINTER(C.c_uint8) * NF)(), (C.c_size_t * NF)()
 
         def time_mode(mode, err, label):
             c2 = H.CodecConfig(); c2.dims[:] = [1, HH, WW]; c2.base_cr = BASE_CR; c2.mode = mode; c2.error = err
             best_e = best_d = 1e9
             for _ in range(3):
                 t0 = time.perf_counter()
-                n = lib.ebcc_encode_batch(frames.ctypes.data_as(C.c_void_p), C.c_size_t(FRAMES), C.byref(c2), outs, osz)
+                n = lib.ebcc_encode_batch(big_np.ctypes.data_as(C.c_void_p), C.c_size_t(NF), C.byref(c2), bouts, bosz)
                 best_e = min(best_e, time.perf_counter() - t0)
-                assert n == FRAMES
-                ptrs = (C.c_void_p * FRAMES)(*[C.cast(outs[i], C.c_void_p).value for i in range(FRAMES)])
-                douts, cnts = (C.POINTER(C.c_float) * FRAMES)(), (C.c_size_t * FRAMES)()
-                for i in range(FRAMES):
+                assert n == NF
+                ptrs = (C.c_void_p * NF)(*[C.cast(bouts[i], C.c_void_p).value for i in range(NF)])
+                douts, cnts = (C.POINTER(C.c_float) * NF)(), (C.c_size_t * NF)()
+                for i in range(NF):
                     douts[i] = C.cast(dec_buf[i].data_ptr(), C.POINTER(C.c_float))
                 t0 = time.perf_counter()
-                n = lib.ebcc_decode_batch(ptrs, osz, C.c_size_t(FRAMES), douts, cnts)
+                n = lib.ebcc_decode_batch(ptrs, bosz, C.c_size_t(NF), douts, cnts)
                 best_d = min(best_d, time.perf_counter() - t0)
-                assert n == FRAMES
-                worst = max(float(np.abs(dec_np[i] - frames[i].ravel()).max()) for i in range(FRAMES))
-                tot = sum(osz)
-                for i in range(FRAMES):
-                    lib.free_buffer(outs[i])
-            modes[label] = {"compress_GBps_e2e": in_bytes / best_e / 1e9, "decompress_GBps_e2e": in_bytes / best_d / 1e9,
-                            "cr": in_bytes / tot, "max_abs_err": worst}
+                assert n == NF
+                worst = max(float(np.abs(dec_np[i] - big_np[i].ravel()).max()) for i in range(0, NF, 5))
+                tot = sum(bosz)
+                for i in range(NF):
+                    lib.free_buffer(bouts[i])
+            modes[label] = {"frames_per_call": NF, "compress_GBps_e2e": big_np.nbytes / best_e / 1e9,
+                            "decompress_GBps_e2e": big_np.nbytes / best_d / 1e9, "cr": big_np.nbytes / tot, "max_abs_err": worst}
         time_mode(H.NONE, 0.0, "none")
         time_mode(H.MAX_ERROR, 0.5, "max_error_0.5")
         time_mode(H.MAX_ERROR, 0.1, "max_error_0.1")
