@@ -173,6 +173,8 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device visible; the EBCC B200 path has no CPU fallback")
     os.environ["EBCC_CUDA_DEVICE"] = str(local)
     os.environ.setdefault("EBCC_PIPELINES", str(PIPES))
+    # waiting pipeline threads spin while there is a host core for each of them, else they sleep on blocking-sync events
+    os.environ.setdefault("EBCC_SPIN_SYNC", "1" if world * PIPES <= (os.cpu_count() or 1) else "0")
     frames = make_frames(rank)
     in_bytes = frames.nbytes
     # the caller's input buffer is pinned host memory (base contract: H2D "from pinned host memory")

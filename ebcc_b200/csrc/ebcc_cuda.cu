@@ -290,10 +290,23 @@ struct ebcc_cuda_ctx {
     size_t h_stage_cap;
     int profiling;
     cudaEvent_t ev[EBCC_ST_COUNT + 1];
+    cudaEvent_t ev_sync;       // blocking-sync event: a host thread waiting for its pipeline sleeps instead of spinning
+    int spin_sync;
     float stage_ms[EBCC_ST_COUNT];
     int ev_valid;
     unsigned long long launches;
 };
+
+// Wait for the pipeline's stream.  Several pipelines (and, on a multi-GPU box, several ranks) share the host cores:
+// the waiting thread sleeps on a blocking-sync event unless EBCC_SPIN_SYNC=1 asks for the lower-latency spin wait.
+static cudaError_t ctx_sync(ebcc_cuda_ctx *c)
+{
+    if (c->spin_sync) return cudaStreamSynchronize(c->stream);
+    cudaError_t e = cudaEventRecord(c->ev_sync, c->stream);
+    if (e != cudaSuccess) return e;
+    return cudaEventSynchronize(c->ev_sync);
+}
+
 
 extern "C" int ebcc_cuda_device_count(void)
 {
@@ -314,6 +327,8 @@ extern "C" ebcc_cuda_ctx *ebcc_cuda_ctx_create(int device)
     c->device = device;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { free(c); return NULL; }
     for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventCreate(&c->ev[i]);
+    cudaEventCreateWithFlags(&c->ev_sync, cudaEventBlockingSync | cudaEventDisableTiming);
+    { const char *sp = getenv("EBCC_SPIN_SYNC"); c->spin_sync = sp && sp[0] == '1'; }
     T1Luts luts; MqTable tab;
     fill_luts(&luts, &tab);
     if (cudaMalloc((void **)&c->d_luts, sizeof(luts)) != cudaSuccess || cudaMalloc((void **)&c->d_mqtab, sizeof(tab)) != cudaSuccess) { free(c); return NULL; }
@@ -374,7 +389,7 @@ extern "C" void ebcc_cuda_ctx_destroy(ebcc_cuda_ctx *c)
 {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
+    ctx_sync(c);
     free_buffers(c);
     cudaFree(c->d_luts); cudaFree(c->d_mqtab); cudaFree(c->d_declut); cudaFree(c->d_step_tab);
     for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventDestroy(c->ev[i]);
@@ -387,7 +402,7 @@ extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nf
     if (!c || H < 32 || W < 32 || H > 2047 || W > 2047 || nframes == 0) return -1;
     CK(cudaSetDevice(c->device));
     if (c->cap_frames >= nframes && c->plan.H == (int)H && c->plan.W == (int)W) return 0;
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     free_buffers(c);
     build_plan((int)H, (int)W, &c->plan, &c->h_cblks);
     const Plan *pl = &c->plan;
@@ -668,7 +683,7 @@ extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const floa
     if (run_decode_stage(c, B, c->d_mq, pl->mq_stride, c->d_in)) return -1;
     CK(cudaMemcpyAsync(c->h_es, c->d_es, sizeof(ErrStat) * B, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaMemcpyAsync(c->h_pout, c->d_pout, sizeof(ProbeOut) * B, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     for (int i = 0; i < B; ++i) {
         const ErrStat &e = c->h_es[i];
         res[i].n_over = e.n_over;
@@ -732,7 +747,7 @@ extern "C" int ebcc_cuda_residual_encode(ebcc_cuda_ctx *c, size_t nframes, const
     EBCC_LAUNCH(k_sp_encode, dim3((unsigned)B), dim3(SP_THREADS), 0, c->stream, c->sp, c->d_sp_info, g, c->d_step_tab);
     c->launches += 5;
     CK(cudaMemcpyAsync(c->h_sp_info, c->d_sp_info, sizeof(SpInfo) * B, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     CK(cudaGetLastError());
     for (int i = 0; i < B; ++i) if (active[i]) coeffs_size[i] = c->h_sp_info[i].nbytes;
     return 0;
@@ -782,7 +797,7 @@ extern "C" int ebcc_cuda_residual_probe(ebcc_cuda_ctx *c, size_t nframes, const 
     EBCC_LAUNCH(k_sp_errstat, ge, dim3(256), 0, c->stream, c->d_sp_img0, c->d_in, c->d_dec, c->d_sp_info, c->d_sp_P, c->d_es2, g);
     c->launches += 2;
     CK(cudaMemcpyAsync(c->h_es2, c->d_es2, sizeof(ErrStat) * B, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     CK(cudaGetLastError());
     for (int i = 0; i < B; ++i) {
         if (!active[i]) continue;
@@ -813,10 +828,10 @@ extern "C" int ebcc_cuda_residual_pack(ebcc_cuda_ctx *c, size_t nframes, const s
     c->launches++;
     c->launches++;
     CK(cudaMemcpyAsync(c->h_zlen, c->d_zlen, 4 * B, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     for (int i = 0; i < B; ++i)
         if (c->h_zlen[i]) CK(cudaMemcpyAsync(c->h_zout + (size_t)i * c->zstride, c->d_zout + (size_t)i * c->zstride, c->h_zlen[i], cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     CK(cudaGetLastError());
     for (int i = 0; i < B; ++i) { frames[i] = c->h_zout + (size_t)i * c->zstride; sizes[i] = c->h_zlen[i]; }
     return 0;
@@ -835,7 +850,7 @@ extern "C" int ebcc_cuda_frame_stats(ebcc_cuda_ctx *c, size_t nframes, float *mi
     if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
     CK(cudaSetDevice(c->device));
     CK(cudaMemcpyAsync(c->h_stat, c->d_stat, sizeof(FrameStat) * nframes, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     for (size_t i = 0; i < nframes; ++i) { minv[i] = c->h_stat[i].minv; maxv[i] = c->h_stat[i].maxv; flags[i] = c->h_stat[i].flags; }
     return 0;
 }
@@ -915,7 +930,7 @@ extern "C" int ebcc_cuda_decode_batch(ebcc_cuda_ctx *c, const uint8_t *const *st
     CK(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
     for (int i = 0; i < B; ++i)
         CK(cudaMemcpyAsync(outs[i], c->d_dec + (size_t)i * N, N * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     int bad = 0;
     for (int i = 0; i < B; ++i) if (c->h_status[i] != PARSE_OK) { fprintf(stderr, "[ebcc-cuda] malformed JPEG 2000 codestream in frame %d\n", i); bad = 1; }
     for (int i = 0; any_res && i < B; ++i)
@@ -934,7 +949,7 @@ extern "C" int ebcc_cuda_download(ebcc_cuda_ctx *c, size_t nframes, const uint8_
     CK(cudaMemcpyAsync(c->h_pout, c->d_pout, sizeof(ProbeOut) * B, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaMemcpyAsync(c->h_stat, c->d_stat, sizeof(FrameStat) * B, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaMemcpyAsync(c->h_offs, c->d_offs, sizeof(unsigned long long) * (B + 1), cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     const size_t total = (size_t)c->h_offs[B];
     if (total > c->h_packed_cap) {
         cudaFreeHost(c->h_packed);
@@ -943,7 +958,7 @@ extern "C" int ebcc_cuda_download(ebcc_cuda_ctx *c, size_t nframes, const uint8_
     }
     if (total) CK(cudaMemcpyAsync(c->h_packed, c->d_packed, total, cudaMemcpyDeviceToHost, c->stream));
     if (c->profiling) cudaEventRecord(c->ev[EBCC_ST_COUNT], c->stream);
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     for (int i = 0; i < B; ++i) {
         if (streams) streams[i] = c->h_packed + c->h_offs[i];
         if (sizes) sizes[i] = (size_t)c->h_pout[i].stream_bytes;
@@ -973,14 +988,14 @@ extern "C" int ebcc_cuda_j2k_encode_batch(ebcc_cuda_ctx *c, const float *frames,
 
 extern "C" void ebcc_cuda_set_profiling(ebcc_cuda_ctx *c, int enabled) { if (c) c->profiling = enabled; }
 extern "C" float ebcc_cuda_stage_ms(ebcc_cuda_ctx *c, int stage) { return (c && stage >= 0 && stage < EBCC_ST_COUNT) ? c->stage_ms[stage] : -1.0f; }
-extern "C" int ebcc_cuda_sync(ebcc_cuda_ctx *c) { if (!c) return -1; CK(cudaSetDevice(c->device)); CK(cudaStreamSynchronize(c->stream)); return 0; }
+extern "C" int ebcc_cuda_sync(ebcc_cuda_ctx *c) { if (!c) return -1; CK(cudaSetDevice(c->device)); CK(ctx_sync(c)); return 0; }
 extern "C" unsigned long long ebcc_cuda_launch_count(ebcc_cuda_ctx *c) { return c ? c->launches : 0; }
 
 extern "C" int ebcc_cuda_debug_coef(ebcc_cuda_ctx *c, size_t frame, float *dst)
 {
     if (!c || frame >= c->cap_frames) return -1;
     const size_t N = (size_t)c->plan.H * c->plan.W;
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     CK(cudaMemcpy(dst, c->d_coef + frame * N, N * sizeof(float), cudaMemcpyDeviceToHost));
     return 0;
 }
@@ -990,7 +1005,7 @@ extern "C" int ebcc_cuda_debug_cblk(ebcc_cuda_ctx *c, size_t frame, size_t cblk,
 {
     if (!c || frame >= c->cap_frames || cblk >= (size_t)c->plan.ncblks) return -1;
     CblkOut o;
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     CK(cudaMemcpy(&o, c->d_cbout + frame * c->plan.ncblks + cblk, sizeof(o), cudaMemcpyDeviceToHost));
     *numbps = o.numbps; *totalpasses = o.totalpasses; *numpasses = o.numpasses;
     for (int i = 0; i < o.totalpasses && i < J2K_MAXPASSES; ++i) { rates[i] = o.rate[i]; dists[i] = o.dist[i]; }
@@ -1005,7 +1020,7 @@ extern "C" int ebcc_cuda_t1_totals(ebcc_cuda_ctx *c, size_t nframes, unsigned lo
     const size_t n = nframes * (size_t)c->plan.ncblks;
     CblkOut *h = (CblkOut *)malloc(n * sizeof(CblkOut));
     if (!h) return -1;
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     CK(cudaMemcpy(h, c->d_cbout, n * sizeof(CblkOut), cudaMemcpyDeviceToHost));
     unsigned long long s = 0, b = 0;
     for (size_t i = 0; i < n; ++i)
@@ -1019,7 +1034,7 @@ extern "C" int ebcc_cuda_t1_totals(ebcc_cuda_ctx *c, size_t nframes, unsigned lo
 extern "C" int ebcc_cuda_debug_spiht_stream(ebcc_cuda_ctx *c, size_t frame, uint8_t *dst, size_t cap, size_t *len)
 {
     if (!c || frame >= c->cap_frames) return -1;
-    CK(cudaStreamSynchronize(c->stream));
+    CK(ctx_sync(c));
     const size_t n = c->h_sp_info[frame].nbytes;
     *len = n;
     if (n > cap) return -1;
@@ -1045,7 +1060,7 @@ extern "C" int ebcc_cuda_bench_resident(ebcc_cuda_ctx *c, size_t nframes, float 
     for (int it = 0; it < warmup + steps; ++it) {
         if (flush) CK(cudaMemsetAsync(flush, it & 0xff, flush_bytes, c->stream));
         if (ebcc_cuda_j2k_encode_resident(c, nframes, base_cr)) { cudaFree(flush); return -1; }
-        CK(cudaStreamSynchronize(c->stream));
+        CK(ctx_sync(c));
         if (it >= warmup) {
             float ms = 0;
             CK(cudaEventElapsedTime(&ms, c->ev[EBCC_ST_MINMAX], c->ev[EBCC_ST_D2H]));
