@@ -36,7 +36,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import harness as H  # noqa: E402
 
 FRAMES, HH, WW, BASE_CR = 24, 721, 1440, 30.0
-PIPES = 6
+PIPES = int(os.environ.get("EBCC_BENCH_PIPES", "8"))
 NSAMP = HH * WW
 STAGES = ["h2d", "minmax", "dwt", "t1_cm", "t1_mq", "pcrd_t2", "bodies", "d2h"]
 METRIC = "compress throughput, GB/s of f32 input (mode NONE, 24x721x1440, base_cr 30)"
