@@ -146,7 +146,11 @@ __device__ __forceinline__ unsigned cf_sigpass_col(unsigned f, unsigned n, const
     return fresh;
 }
 
-__global__ void __launch_bounds__(T1_THREADS)
+// 3 CTAs per SM caps the kernel at 40 registers: room for the long-lived MQ CTAs of other batches in flight
+#ifndef T1_MIN_CTAS
+#define T1_MIN_CTAS 3
+#endif
+__global__ void __launch_bounds__(T1_THREADS, T1_MIN_CTAS)
 k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, const BandDesc *__restrict__ bands,
         const T1Luts *__restrict__ g_luts, const unsigned char *__restrict__ zc_lut, CblkOut *cbout, unsigned char *sym_pool,
         int W, int H, int ncblks, size_t sym_stride)
@@ -490,8 +494,11 @@ __device__ __forceinline__ void mq_pass_end(MqEnc &q, CblkOut *out, int p, int n
 // advance in lock step: every stretch of symbols up to the nearest pass end of any of them has a uniform
 // trip count, the common step (MPS, interval still normalised) is shared by all lanes, and the state
 // update + renormalisation is one predicated region so that only byte output really diverges.
+#ifndef MQ_MIN_CTAS
+#define MQ_MIN_CTAS 1
+#endif
 template <int L>
-__global__ void __launch_bounds__(MQ_THREADS(L))
+__global__ void __launch_bounds__(MQ_THREADS(L), MQ_MIN_CTAS)
 k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char *__restrict__ sym_pool,
         unsigned char *mq_pool, const MqTable *__restrict__ g_tab, int ncblks, int nframes,
         size_t sym_stride, size_t mq_stride)
