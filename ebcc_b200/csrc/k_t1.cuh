@@ -26,7 +26,9 @@
 #define T1_CPT (1024 / T1_THREADS)  // stripe columns per thread
 #define T1_SW 66                    // state row stride: 64 + border
 #define T1_NSTATE (18 * T1_SW)      // 16 stripes + border
-#define T1_SYMBUF 10240             // max symbols per pass: 1024 stripe columns x 10
+// private symbol slot of a thread: 3 passes x T1_CPT columns x 10 symbols, padded to an odd number of words so that
+// the 32 lanes of a warp hit 32 different banks
+#define T1_SLOT (((30 * T1_CPT + 3) / 4 | 1) * 4)
 
 #define CTX_ZC 0
 #define CTX_SC 9
@@ -69,11 +71,11 @@ __device__ __forceinline__ int t1_contrib(int sa, int na, int sb, int nb)
     return pos - neg;
 }
 
-struct T1Sym { unsigned long long bits; int cnt; };
+// symbols of one coding pass go straight into the thread's private slot of shared memory as ctx << 2 | decision
+struct T1Sym { unsigned char *p; int cnt; };
 __device__ __forceinline__ void t1_put(T1Sym &s, int ctx, int d)
 {
-    s.bits |= (unsigned long long)((ctx << 1) | d) << (6 * s.cnt);
-    s.cnt++;
+    s.p[s.cnt++] = (unsigned char)((ctx << 2) | d);
 }
 
 __device__ __forceinline__ int t1_nm_sig(const T1Luts *l, unsigned x, int bpno)
@@ -158,11 +160,11 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
     __shared__ unsigned F[CF_WORDS];        // flag words
     __shared__ unsigned N[CF_WORDS];        // significance gained in the running pass, same neighbourhood layout
     __shared__ unsigned SG[CF_WORDS];       // static: sign of rows -1..4 of the column (bits 0..5)
-    __shared__ __align__(16) unsigned char symbuf[T1_SYMBUF + 64];
+    __shared__ unsigned char priv[T1_THREADS * T1_SLOT];   // per thread: 3 passes x T1_CPT columns x 10 symbols (+ pad)
     __shared__ unsigned char zc[512];
     __shared__ T1Luts luts;
-    __shared__ int warp_sum[T1_THREADS / 32];
-    __shared__ int s_max, s_nmsedec, s_total;
+    __shared__ unsigned long long warp_sum[T1_THREADS / 32];
+    __shared__ int s_max, s_nmsedec[3];
 
     const int tid = threadIdx.x;
     const int cbi = blockIdx.x, frame = blockIdx.y;
@@ -176,7 +178,7 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
     for (int i = tid; i < CF_WORDS; i += T1_THREADS) { F[i] = 0; N[i] = 0; SG[i] = 0; }
     for (int i = tid; i < (int)(sizeof(T1Luts) / 2); i += T1_THREADS) ((short *)&luts)[i] = ((const short *)g_luts)[i];
     for (int i = tid; i < 512; i += T1_THREADS) zc[i] = zc_lut[orient * 512 + i];
-    if (tid == 0) { s_max = 0; s_nmsedec = 0; }
+    if (tid == 0) { s_max = 0; s_nmsedec[0] = s_nmsedec[1] = s_nmsedec[2] = 0; }
     __syncthreads();
 
     // ---- quantise: lrintf((coef / stepsize) * 64) ------------------------------------------------
@@ -224,17 +226,20 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
     for (int k = 0; k < T1_CPT; ++k) if (sidx[k] >= 0) N[sidx[k]] = 0;
     __syncthreads();
 
+    // ---- bit-planes.  The (up to) three passes of a plane run back to back, each thread writing its symbols into
+    // its private slot; ONE packed prefix sum per plane then places the three symbol runs in the stream. -----------
     unsigned total_syms = 0;
     int passno = 0;
-    for (int bpno = numbps - 1, passtype = 2; bpno >= 0; ++passno) {
+    unsigned char *slot = priv + tid * T1_SLOT;
+    for (int bpno = numbps - 1; bpno >= 0; --bpno) {
+        const bool first = bpno == numbps - 1;          // the top plane has a clean-up pass only
         const unsigned one = 1u << (bpno + 6);
-        T1Sym sy[T1_CPT];
-        unsigned upd_pi[T1_CPT], upd_mu[T1_CPT];
-        int nmsedec = 0;
+        T1Sym sq[3];
+        int nm[3] = {0, 0, 0};
 #pragma unroll
-        for (int k = 0; k < T1_CPT; ++k) { sy[k].bits = 0; sy[k].cnt = 0; upd_pi[k] = 0; upd_mu[k] = 0; }
+        for (int q = 0; q < 3; ++q) { sq[q].p = slot + q * (10 * T1_CPT); sq[q].cnt = 0; }
 
-        if (passtype == 0) {
+        if (!first) {
             // ---- significance propagation: least fixed point of "becomes significant", then one emitting sweep ----
             unsigned acc[T1_CPT];
 #pragma unroll
@@ -248,7 +253,7 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
                     const unsigned f = F[p];
                     if ((~cf_own4(f) & ((1u << lim[k]) - 1u)) == 0) continue;
                     unsigned dummy_c = 0; int dummy_n = 0;
-                    const unsigned fr = cf_sigpass_col<false>(f, N[p], mag[k], one, lim[k], sgn4[k], zc, SG, p, &luts, bpno, sy[k], dummy_c, dummy_n);
+                    const unsigned fr = cf_sigpass_col<false>(f, N[p], mag[k], one, lim[k], sgn4[k], zc, SG, p, &luts, bpno, sq[0], dummy_c, dummy_n);
                     const unsigned delta = fr & ~acc[k];
                     if (delta) { cf_scatter(N, p, delta); acc[k] |= delta; changed = 1; }
                 }
@@ -259,29 +264,33 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
                 if (sidx[k] < 0) continue;
                 const int p = sidx[k];
                 const unsigned f = F[p];
-                if ((~cf_own4(f) & ((1u << lim[k]) - 1u)) == 0) continue;
-                cf_sigpass_col<true>(f, N[p], mag[k], one, lim[k], sgn4[k], zc, SG, p, &luts, bpno, sy[k], upd_pi[k], nmsedec);
-            }
-        } else if (passtype == 1) {
-            // ---- magnitude refinement (t1.c:743-765, 814-922) ----
-#pragma unroll
-            for (int k = 0; k < T1_CPT; ++k) {
-                if (sidx[k] < 0) continue;
-                const unsigned f = F[sidx[k]];
-                const unsigned sig = cf_own4(f), pi = (f >> 24) & 15u;
+                unsigned coded = 0;
+                if ((~cf_own4(f) & ((1u << lim[k]) - 1u)) != 0)
+                    cf_sigpass_col<true>(f, N[p], mag[k], one, lim[k], sgn4[k], zc, SG, p, &luts, bpno, sq[0], coded, nm[0]);
+                // state: the word absorbs what its neighbourhood gained, rows coded here are marked pi
+                const unsigned w = f | N[p] | (coded << 24);
+                F[p] = w;
+                N[p] = 0;
+                // ---- magnitude refinement (t1.c:743-765, 814-922): needs nothing but the own word ----
+                const unsigned sig = cf_own4(w), pi = (w >> 24) & 15u;
                 if ((sig & ~pi & ((1u << lim[k]) - 1u)) == 0) continue;
+                unsigned mu = 0;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     if (j >= lim[k]) break;
                     if (((sig >> j) & 1) && !((pi >> j) & 1)) {
-                        const int ctx = (f & CF_MU(j)) ? CTX_MAG + 2 : ((f & CF_NB(j)) ? CTX_MAG + 1 : CTX_MAG);
-                        nmsedec += t1_nm_ref(&luts, mag[k][j], bpno);
-                        t1_put(sy[k], ctx, (mag[k][j] & one) ? 1 : 0);
-                        upd_mu[k] |= 1u << j;
+                        const int ctx = (w & CF_MU(j)) ? CTX_MAG + 2 : ((w & CF_NB(j)) ? CTX_MAG + 1 : CTX_MAG);
+                        nm[1] += t1_nm_ref(&luts, mag[k][j], bpno);
+                        t1_put(sq[1], ctx, (mag[k][j] & one) ? 1 : 0);
+                        mu |= 1u << j;
                     }
                 }
+                F[p] = w | (mu << 28);
             }
-        } else {
+            __syncthreads();            // every N word is zero again before the clean-up pass scatters into it
+        }
+
+        {
             // ---- cleanup with run-length mode (t1.c:1051-1116, 1163-1256): what becomes significant is known up front ----
             unsigned fresh[T1_CPT];
 #pragma unroll
@@ -289,10 +298,12 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
                 fresh[k] = 0;
                 if (sidx[k] < 0) continue;
                 const unsigned f = F[sidx[k]];
+                const unsigned cand = ~cf_own4(f) & ~(f >> 24) & ((1u << lim[k]) - 1u);
+                if (!cand) continue;
                 unsigned bits = 0;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) bits |= ((mag[k][j] & one) ? 1u : 0u) << j;
-                fresh[k] = ~cf_own4(f) & ~(f >> 24) & bits & ((1u << lim[k]) - 1u);
+                fresh[k] = cand & bits;
                 if (fresh[k]) cf_scatter(N, sidx[k], fresh[k]);
             }
             __syncthreads();
@@ -302,90 +313,77 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
                 const int p = sidx[k];
                 const unsigned f = F[p];
                 const unsigned sig = cf_own4(f), pi = (f >> 24) & 15u, rows = (1u << lim[k]) - 1u;
-                if (((sig | pi) & rows) == rows) continue;
-                unsigned t = f | (N[p] & CF_EARLY);
-                int runlen = 0, agg = 0;
-                if (lim[k] == 4 && (t & 0x0f03ffffu) == 0) {
-                    agg = 1;
-                    runlen = fresh[k] ? (__ffs((int)fresh[k]) - 1) : 4;
-                    t1_put(sy[k], CTX_AGG, runlen != 4);
-                    if (runlen != 4) { t1_put(sy[k], CTX_UNI, runlen >> 1); t1_put(sy[k], CTX_UNI, runlen & 1); }
-                }
-                if (runlen < 4) {
+                if (((sig | pi) & rows) != rows) {
+                    unsigned t = f | (N[p] & CF_EARLY);
+                    int runlen = 0, agg = 0;
+                    if (lim[k] == 4 && (t & 0x0f03ffffu) == 0) {
+                        agg = 1;
+                        runlen = fresh[k] ? (__ffs((int)fresh[k]) - 1) : 4;
+                        t1_put(sq[2], CTX_AGG, runlen != 4);
+                        if (runlen != 4) { t1_put(sq[2], CTX_UNI, runlen >> 1); t1_put(sq[2], CTX_UNI, runlen & 1); }
+                    }
+                    if (runlen < 4) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        if (j >= lim[k]) break;
-                        if (j < runlen) continue;
-                        int v;
-                        if (agg && j == runlen) v = 1;
-                        else if (!(((sig | pi) >> j) & 1)) {
-                            v = (mag[k][j] & one) ? 1 : 0;
-                            t1_put(sy[k], CTX_ZC + zc[(t >> (j * 3)) & 0x1ffu], v);
-                        } else v = 0;
-                        if (v) {
-                            cf_sign(sy[k], t, SG, p, j, (sgn4[k] >> j) & 1);
-                            nmsedec += t1_nm_sig(&luts, mag[k][j], bpno);
-                            t |= CF_SIG(j);
+                        for (int j = 0; j < 4; ++j) {
+                            if (j >= lim[k]) break;
+                            if (j < runlen) continue;
+                            int v;
+                            if (agg && j == runlen) v = 1;
+                            else if (!(((sig | pi) >> j) & 1)) {
+                                v = (mag[k][j] & one) ? 1 : 0;
+                                t1_put(sq[2], CTX_ZC + zc[(t >> (j * 3)) & 0x1ffu], v);
+                            } else v = 0;
+                            if (v) {
+                                cf_sign(sq[2], t, SG, p, j, (sgn4[k] >> j) & 1);
+                                nm[2] += t1_nm_sig(&luts, mag[k][j], bpno);
+                                t |= CF_SIG(j);
+                            }
                         }
                     }
                 }
+                F[p] = (f | N[p]) & ~(0xfu << 24);                // new significance, clear pi
+                N[p] = 0;
             }
         }
 
-        // ---- CTA-wide exclusive scan of symbol counts, staged write of the symbol bytes ------------
-        int mycnt = 0;
-#pragma unroll
-        for (int k = 0; k < T1_CPT; ++k) mycnt += sy[k].cnt;
-        int incl = mycnt;
-        for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, o); if ((tid & 31) >= o) incl += t; }
+        // ---- one CTA-wide exclusive scan of the three symbol counts (21-bit fields of a 64-bit word) ----
+        const unsigned long long mine = (unsigned long long)sq[0].cnt | ((unsigned long long)sq[1].cnt << 21) | ((unsigned long long)sq[2].cnt << 42);
+        unsigned long long incl = mine;
+        for (int o = 1; o < 32; o <<= 1) { unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o); if ((tid & 31) >= o) incl += t; }
         if ((tid & 31) == 31) warp_sum[tid >> 5] = incl;
-        for (int o = 16; o > 0; o >>= 1) nmsedec += __shfl_xor_sync(0xffffffffu, nmsedec, o);
-        if ((tid & 31) == 0 && nmsedec) atomicAdd(&s_nmsedec, nmsedec);
-        // ---- state update: every word absorbs what its neighbourhood gained; own pi / mu ---------------
 #pragma unroll
-        for (int k = 0; k < T1_CPT; ++k)
-            if (sidx[k] >= 0) {
-                const int p = sidx[k];
-                unsigned w = F[p];
-                if (passtype == 2) w = (w | N[p]) & ~(0xfu << 24);                // new significance, clear pi
-                else if (passtype == 0) w |= N[p] | (upd_pi[k] << 24);
-                else w |= upd_mu[k] << 28;
-                F[p] = w;
-                if (passtype != 1) N[p] = 0;
+        for (int q = 0; q < 3; ++q) {
+            int v = nm[q];
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if ((tid & 31) == 0 && v) atomicAdd(&s_nmsedec[q], v);
+        }
+        __syncthreads();
+        unsigned long long excl = incl - mine, total3;
+        {
+            const int nw = T1_THREADS / 32;
+            const unsigned long long wv = (tid & 31) < nw ? warp_sum[tid & 31] : 0ull;
+            unsigned long long ex = wv;
+            for (int o = 1; o < 32; o <<= 1) { unsigned long long t = __shfl_up_sync(0xffffffffu, ex, o); if ((tid & 31) >= o) ex += t; }
+            excl += __shfl_sync(0xffffffffu, ex - wv, tid >> 5);
+            total3 = __shfl_sync(0xffffffffu, ex, nw - 1);
+        }
+        // ---- the runs leave for the stream: pass q starts where pass q-1 ended ----
+        unsigned base = total_syms;
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const unsigned tot = (unsigned)(total3 >> (21 * q)) & 0x1fffffu, off = (unsigned)(excl >> (21 * q)) & 0x1fffffu;
+            unsigned char *dst = sym + base + off;
+            for (int i = 0; i < sq[q].cnt; ++i) dst[i] = sq[q].p[i];
+            base += tot;
+            if (tid == 0 && (q == 2 || !first)) {
+                const int pn = first ? passno : passno + q;
+                out->nsym_end[pn] = base; out->nmsedec[pn] = s_nmsedec[q];
             }
-        __syncthreads();
-        // symbols are staged behind the still unwritten tail of the previous pass (head bytes), so that shared and
-        // global memory are 16-byte co-aligned and the copy moves whole 16-byte blocks
-        const int head = (int)(total_syms & 15u);
-        int off = incl - mycnt + head;
-        {
-            const int nw = T1_THREADS / 32, wv = (tid & 31) < nw ? warp_sum[tid & 31] : 0;
-            int ex = wv;
-            for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, ex, o); if ((tid & 31) >= o) ex += t; }
-            off += __shfl_sync(0xffffffffu, ex - wv, tid >> 5);
         }
-        if (tid == T1_THREADS - 1) s_total = off + mycnt - head;
-#pragma unroll
-        for (int k = 0; k < T1_CPT; ++k) {
-            unsigned long long b = sy[k].bits;
-            for (int i = 0; i < sy[k].cnt; ++i) { symbuf[off++] = (unsigned char)(((b & 62) << 1) | (b & 1)); b >>= 6; }
-        }
+        total_syms = base;
+        passno += first ? 1 : 3;
         __syncthreads();
-        const int total = s_total;
-        {
-            const int nblk = (head + total + 15) >> 4;
-            uint4 *dst = (uint4 *)(sym + (total_syms & ~15u));
-            for (int i = tid; i < nblk; i += T1_THREADS) dst[i] = ((const uint4 *)symbuf)[i];
-        }
-        total_syms += (unsigned)total;
-        if (tid == 0) { out->nsym_end[passno] = total_syms; out->nmsedec[passno] = s_nmsedec; s_nmsedec = 0; }
-        __syncthreads();
-        // the partial last block stays staged for the next pass
-        uint4 tailv = make_uint4(0, 0, 0, 0);
-        if (tid == 0) tailv = ((const uint4 *)symbuf)[(head + total) >> 4];
-        __syncthreads();
-        if (tid == 0) ((uint4 *)symbuf)[0] = tailv;
-        if (++passtype == 3) { passtype = 0; bpno--; }
+        if (tid < 3) s_nmsedec[tid] = 0;
     }
 
     // ---- distortion per pass: opj_t1_getwmsedec, accumulated in pass order (t1.c:1416-1449, 2655) --
