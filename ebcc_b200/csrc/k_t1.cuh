@@ -85,7 +85,8 @@ __device__ __forceinline__ int t1_nm_ref(const T1Luts *l, unsigned x, int bpno)
 
 // Flag word of one stripe column (the layout of OPJ's opj_flag_t and of the decoder's DF_* word): bits 0-17
 // significance of the 3x6 neighbourhood (bit (r+1)*3 + (dx+1), r = -1..4, dx = -1..1; the column's own rows are
-// dx = 0, r = 0..3), bits 24-27 pi (coded in the significance pass), bits 28-31 mu (already refined).
+// dx = 0, r = 0..3), bits 18-21 the own rows again as a nibble, bits 24-27 pi (coded in the significance pass),
+// bits 28-31 mu (already refined).
 #define CF_W 66
 #define CF_WORDS (18 * CF_W)
 #define CF_SIG(ci) (1u << ((ci) * 3 + 4))
@@ -96,7 +97,8 @@ __device__ __forceinline__ int t1_nm_ref(const T1Luts *l, unsigned x, int bpno)
 // own and the eastern column.  (Own rows above the current one are tracked in registers while a column is coded.)
 #define CF_EARLY 0x124fu
 
-__device__ __forceinline__ unsigned cf_own4(unsigned f) { return ((f >> 4) & 1u) | ((f >> 6) & 2u) | ((f >> 8) & 4u) | ((f >> 10) & 8u); }
+// bits 18-21 repeat the significance of the column's own rows 0..3 as a nibble
+__device__ __forceinline__ unsigned cf_own4(unsigned f) { return (f >> 18) & 15u; }
 
 // rows b4 of column p become significant: set the bits every neighbouring word sees
 __device__ __forceinline__ void cf_scatter(unsigned *N, int p, unsigned b4)
@@ -105,7 +107,7 @@ __device__ __forceinline__ void cf_scatter(unsigned *N, int p, unsigned b4)
 #pragma unroll
     for (int ci = 0; ci < 4; ++ci)
         if ((b4 >> ci) & 1u) { own |= CF_SIG(ci); we |= 1u << ((ci + 1) * 3); }
-    atomicOr(&N[p], own);
+    atomicOr(&N[p], own | (b4 << 18));
     atomicOr(&N[p - 1], we << 2);
     atomicOr(&N[p + 1], we);
     if (b4 & 1u) { atomicOr(&N[p - CF_W], 1u << 16); atomicOr(&N[p - CF_W - 1], 1u << 17); atomicOr(&N[p - CF_W + 1], 1u << 15); }
@@ -241,21 +243,29 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
 
         if (!first) {
             // ---- significance propagation: least fixed point of "becomes significant", then one emitting sweep ----
-            unsigned acc[T1_CPT];
+            // todo[k]: insignificant rows whose bit is set in this plane and that are not fresh yet -- the only rows a
+            // sweep can still change; columns without any skip the sweeps altogether
+            unsigned acc[T1_CPT], todo[T1_CPT];
 #pragma unroll
-            for (int k = 0; k < T1_CPT; ++k) acc[k] = 0;
+            for (int k = 0; k < T1_CPT; ++k) {
+                acc[k] = 0; todo[k] = 0;
+                if (sidx[k] < 0) continue;
+                unsigned bits = 0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) bits |= ((mag[k][j] & one) ? 1u : 0u) << j;
+                todo[k] = ~cf_own4(F[sidx[k]]) & bits & ((1u << lim[k]) - 1u);
+            }
             for (;;) {
                 int changed = 0;
 #pragma unroll
                 for (int k = 0; k < T1_CPT; ++k) {
-                    if (sidx[k] < 0) continue;
+                    if (!todo[k]) continue;
                     const int p = sidx[k];
                     const unsigned f = F[p];
-                    if ((~cf_own4(f) & ((1u << lim[k]) - 1u)) == 0) continue;
                     unsigned dummy_c = 0; int dummy_n = 0;
                     const unsigned fr = cf_sigpass_col<false>(f, N[p], mag[k], one, lim[k], sgn4[k], zc, SG, p, &luts, bpno, sq[0], dummy_c, dummy_n);
                     const unsigned delta = fr & ~acc[k];
-                    if (delta) { cf_scatter(N, p, delta); acc[k] |= delta; changed = 1; }
+                    if (delta) { cf_scatter(N, p, delta); acc[k] |= delta; todo[k] &= ~delta; changed = 1; }
                 }
                 if (!__syncthreads_or(changed)) break;
             }
