@@ -632,10 +632,19 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
     const int W = pl->W, H = pl->H, N = W * H;
     const long long njobs = (long long)pl->ncblks * B;
     const bool probe = orig != NULL;         // probe of the CR search: jobs come from the encoder, the recording is used
-    EBCC_LAUNCH(k_t1_dec, dim3((unsigned)((njobs + DEC_WARPS - 1) / DEC_WARPS)), dim3(DEC_WARPS * 32), 0, c->stream,
-                c->d_cblks, c->d_order, c->d_jobs, pool, pool_stride, c->d_declut, c->d_iplane, probe ? c->d_spass : (unsigned char *)NULL, c->d_scratch,
-                probe ? (const CblkOut *)c->d_cbout : (const CblkOut *)NULL, probe ? c->d_dstate : (DecState *)NULL,
-                probe ? c->d_decsave : (unsigned *)NULL, W, H, pl->ncblks, B);
+    {
+        const char *el = getenv("EBCC_DEC_LANES");              // code-blocks per warp of the tier-1 decoder: 1, 2, 4 or 8
+        int lanes = el ? atoi(el) : DEC_DEFAULT_LANES;
+        if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8) lanes = DEC_DEFAULT_LANES;
+        const long long per_cta = (long long)DEC_WPC(lanes) * lanes;
+        const dim3 grid((unsigned)((njobs + per_cta - 1) / per_cta)), block((unsigned)(DEC_WPC(lanes) * 32));
+#define DEC_GO(LL) EBCC_LAUNCH(k_t1_dec<LL>, grid, block, 0, c->stream, c->d_cblks, c->d_order, c->d_jobs, pool, pool_stride, c->d_declut, \
+                               c->d_iplane, probe ? c->d_spass : (unsigned char *)NULL, c->d_scratch,                                  \
+                               probe ? (const CblkOut *)c->d_cbout : (const CblkOut *)NULL, probe ? c->d_dstate : (DecState *)NULL,   \
+                               probe ? c->d_decsave : (unsigned *)NULL, W, H, pl->ncblks, B)
+        if (lanes == 8) DEC_GO(8); else if (lanes == 4) DEC_GO(4); else if (lanes == 2) DEC_GO(2); else DEC_GO(1);
+#undef DEC_GO
+    }
     if (probe)
         EBCC_LAUNCH(k_recon_dequant, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_plan, c->d_cbout, c->d_dstate, c->d_jobs,
                     c->d_iplane, c->d_spass, c->d_scratch, c->d_dcoef);

@@ -45,7 +45,7 @@ struct DecLuts {
 #define DEC_FW 66
 #define DEC_FWORDS (18 * DEC_FW)
 #define DEC_FWORDS_C (18 * 66)
-#define DEC_WARPS 4
+#define DEC_DEFAULT_LANES 2
 #define DEC_NSHADOW 3
 
 // flag word of one stripe column: bits 0-17 significance of the 3x6 neighbourhood
@@ -395,118 +395,171 @@ __device__ __noinline__ void mqd_load(MqDec &q, unsigned *cx, const unsigned *o,
     for (int i = 0; i < 19; ++i) cx[i] = o[k++];
 }
 
-// grid = ceil(ncblks * nframes / DEC_WARPS) CTAs of DEC_WARPS warps; lane 0 of a warp decodes, the warp moves state.
+// One decode job as the kernel sees it (every lane can rebuild any job of its warp from the job index).
+struct DecView {
+    int cbi, frame, mode;
+    size_t bi, o;              // block index in the [frame][cblk] tables; offset of the block's top-left sample in a plane
+    DecJob jb;
+    CblkDesc cb;
+};
+
+__device__ __forceinline__ bool dec_view(DecView &v, long long job, const CblkDesc *cblks, const int *order, const DecJob *jobs,
+                                         int W, int H, int ncblks, int nframes)
+{
+    v.mode = 0;
+    if (job >= (long long)ncblks * nframes) return false;
+    // frame varies fastest so that the blocks of a warp (and of neighbouring warps) are of similar length
+    const int slot = (int)(job / nframes);
+    v.frame = (int)(job - (long long)slot * nframes);
+    v.cbi = order[slot];                       // largest blocks first
+    v.bi = (size_t)v.frame * ncblks + v.cbi;
+    v.jb = jobs[v.bi];
+    v.mode = (v.jb.mode == 1 || v.jb.mode == 2) ? v.jb.mode : 0;
+    v.cb = cblks[v.cbi];
+    v.o = (size_t)v.frame * H * W + (size_t)v.cb.ty * W + v.cb.tx;
+    return v.mode != 0;
+}
+
+// Warps per CTA for L blocks per warp: 8 blocks (39 KB of flag words) per CTA from L = 2 on.
+#define DEC_WPC(L) ((L) == 1 ? 4 : 8 / (L))
+
+// grid = ceil(ncblks * nframes / (DEC_WPC(L) * L)) CTAs.  A warp owns L code-blocks; lanes 0 .. L-1 decode one each
+// (SIMT: they share every instruction they have in common, which trades a longer serial chain per block for fewer
+// issued instructions -- worth it when other batches are in flight), all 32 lanes move state.
 //   plain decode (ebcc_decode; cbout == nullptr): mode-1 jobs from k_t2_parse, decoded into iplane.
 //   CR search (cbout, dstate, save given): mode 1 continues the block's recording from the complete segment up to
-//   jb.np passes with truncation shadows; if the cut this probe needs turns out not to be reproducible the warp
+//   jb.np passes with truncation shadows; if the cut this probe needs turns out not to be reproducible the lane
 //   decodes the truncated segment for real into the scratch plane right away (job becomes mode 2).  Mode 2 does only
 //   that.  The block region of a plane is cleared before a decode that starts at pass 0.
-__global__ void __launch_bounds__(DEC_WARPS * 32)
+template <int L>
+__global__ void __launch_bounds__(DEC_WPC(L) * 32)
 k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJob *jobs, const unsigned char *__restrict__ pool,
          size_t pool_stride, const DecLuts *__restrict__ g_luts, int *iplane, unsigned char *spass, int *scratch,
          const CblkOut *__restrict__ cbout, DecState *dstate, unsigned *save, int W, int H, int ncblks, int nframes)
 {
-    __shared__ unsigned F[DEC_WARPS][DEC_FWORDS];
-    __shared__ unsigned cxs[DEC_WARPS][20];
-    __shared__ MqShadows shw[DEC_WARPS];
+    constexpr int NB = DEC_WPC(L) * L;          // blocks per CTA
+    __shared__ unsigned F[NB][DEC_FWORDS];
+    __shared__ unsigned cxs[NB][20];
+    __shared__ MqShadows shw[NB];
+    __shared__ int need2[NB];
     __shared__ unsigned tab[94];
     __shared__ unsigned char zc[4 * 512];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int i = tid; i < 94; i += blockDim.x) tab[i] = g_luts->mq[i];
     for (int i = tid; i < 4 * 512; i += blockDim.x) zc[i] = g_luts->zc[i];
     __syncthreads();
-    const long long job = (long long)blockIdx.x * DEC_WARPS + warp;
-    if (job >= (long long)ncblks * nframes) return;
-    // frame varies fastest so that the warps of a CTA (and neighbouring CTAs) hold blocks of similar length
-    const int slot = (int)(job / nframes), frame = (int)(job - (long long)slot * nframes);
-    const int cbi = order[slot];               // largest blocks first
-    const size_t bi = (size_t)frame * ncblks + cbi;
-    const DecJob jb = jobs[bi];
-    if (jb.mode != 1 && jb.mode != 2) return;
-    const CblkDesc cb = cblks[cbi];
+    const long long job0 = ((long long)blockIdx.x * DEC_WPC(L) + warp) * L;
     const bool search = cbout != nullptr && dstate != nullptr && save != nullptr;
-    DecState ds; ds.np_dec = 0; ds.scratch_np = 0; ds.bad[0] = ds.bad[1] = ds.bad[2] = ds.bad[3] = 0;
-    if (search) ds = dstate[bi];
-    unsigned *sv = search ? save + bi * DEC_SAVE_WORDS : nullptr;
-    const size_t o = (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx;
-    const unsigned char *seg = pool + (size_t)frame * pool_stride + jb.off;
-    unsigned *cx = cxs[warp];
-    T1DecState S;
-    S.F = F[warp]; S.cx = cx; S.zc = zc + cb.orient * 512; S.tab = tab; S.W = W; S.pass = 0;
-    int mode = jb.mode;
 
-    if (mode == 1) {
-        const bool resume = search && ds.np_dec > 0;
+    // ---- all lanes: bring every block of the warp to its starting state ----
+    for (int sb = 0; sb < L; ++sb) {
+        DecView v;
+        if (!dec_view(v, job0 + sb, cblks, order, jobs, W, H, ncblks, nframes)) continue;
+        unsigned *Fb = F[warp * L + sb];
+        const bool resume = v.mode == 1 && search && dstate[v.bi].np_dec > 0;
         if (resume) {
-            for (int i = lane; i < DEC_FWORDS; i += 32) F[warp][i] = sv[i];
+            const unsigned *sv = save + v.bi * DEC_SAVE_WORDS;
+            for (int i = lane; i < DEC_FWORDS; i += 32) Fb[i] = sv[i];
         } else {
-            for (int i = lane; i < DEC_FWORDS; i += 32) F[warp][i] = 0;
-            for (int i = lane; i < cb.w * cb.h; i += 32) {
-                const int y = i / cb.w, x = i - y * cb.w;
-                iplane[o + (size_t)y * W + x] = 0;
-                if (spass) spass[o + (size_t)y * W + x] = 255;
+            for (int i = lane; i < DEC_FWORDS; i += 32) Fb[i] = 0;
+            int *dst = (v.mode == 1 ? iplane : scratch) + v.o;
+            unsigned char *sp = (v.mode == 1 && spass) ? spass + v.o : nullptr;
+            for (int i = lane; i < v.cb.w * v.cb.h; i += 32) {
+                const int y = i / v.cb.w, x = i - y * v.cb.w;
+                dst[(size_t)y * W + x] = 0;
+                if (sp) sp[(size_t)y * W + x] = 255;
             }
         }
-        __syncwarp();
-        if (lane == 0 && jb.np > 0 && jb.numbps > 0) {
-            S.plane = iplane + o; S.spass = spass ? spass + o : nullptr;
-            MqDec q;
-            const int *rates = search ? cbout[bi].rate : nullptr;
-            const int nrates = search ? cbout[bi].totalpasses : 0;
-            if (resume) { mqd_load(q, cx, sv + DEC_SAVE_MQ, &shw[warp]); q.data = seg; }
-            else {
-                for (int i = 0; i < 19; ++i) cx[i] = tab[0];
-                cx[CTX_UNI] = tab[46 << 1]; cx[CTX_AGG] = tab[3 << 1]; cx[CTX_ZC] = tab[4 << 1];
-                mqd_init(q, seg, jb.len, rates ? &shw[warp] : (MqShadows *)nullptr);
-                if (rates) {
-                    for (int j = 0; j < DEC_NSHADOW; ++j) {
-                        const int tn = j < nrates ? rates[j] : -1;
-                        shw[warp].trunc[j] = tn;
-                        // cuts inside the two bytes the decoder reads while initialising cannot fork any more
-                        if (tn >= 0 && tn <= q.maxread) { q.sh_on |= 1u << j; shw[warp].sh_bad |= 1u << j; }
-                    }
-                    q.fork_at = mqd_next_fork(&shw[warp], q.sh_on);
-                }
-            }
-            t1d_passes(S, q, cb.w, cb.h, jb.numbps, ds.np_dec, jb.np, rates, nrates, ds);
-            ds.np_dec = jb.np;
-            if (search) mqd_save(q, cx, sv + DEC_SAVE_MQ);
-        }
-        __syncwarp();
-        if (!search) return;
-        for (int i = lane; i < DEC_FWORDS; i += 32) sv[i] = F[warp][i];
-        // the cut this probe needs: rate[np - 1]
-        int need = 0;
-        if (lane == 0) {
-            const int pc = jb.np - 1;
-            need = jb.np > 0 && (pc >= 128 || ((ds.bad[pc >> 5] >> (pc & 31)) & 1u));
-            if (need && ds.scratch_np == jb.np) { need = 0; jobs[bi].mode = 3; }
-        }
-        need = __shfl_sync(0xffffffffu, need, 0);
-        if (!need) { if (lane == 0) dstate[bi] = ds; return; }
-        mode = 2;
-        __syncwarp();
     }
+    if (lane < L) need2[warp * L + lane] = 0;
+    __syncwarp();
 
-    // mode 2: real decode of the segment cut at rate[np - 1] into the scratch plane
-    for (int i = lane; i < DEC_FWORDS; i += 32) F[warp][i] = 0;
-    for (int i = lane; i < cb.w * cb.h; i += 32) {
-        const int y = i / cb.w, x = i - y * cb.w;
-        scratch[o + (size_t)y * W + x] = 0;
+    // ---- lanes 0 .. L-1: decode ----
+    DecView v;
+    const bool mine = lane < L && dec_view(v, job0 + lane, cblks, order, jobs, W, H, ncblks, nframes);
+    const int blk = warp * L + (lane < L ? lane : 0);
+    T1DecState S;
+    S.F = F[blk]; S.cx = cxs[blk]; S.tab = tab; S.W = W; S.pass = 0;
+    DecState ds; ds.np_dec = 0; ds.scratch_np = 0; ds.bad[0] = ds.bad[1] = ds.bad[2] = ds.bad[3] = 0;
+    if (mine) {
+        S.zc = zc + v.cb.orient * 512;
+        if (search) ds = dstate[v.bi];
+        const unsigned char *seg = pool + (size_t)v.frame * pool_stride + v.jb.off;
+        unsigned *cx = cxs[blk];
+        if (v.mode == 1) {
+            unsigned *sv = search ? save + v.bi * DEC_SAVE_WORDS : nullptr;
+            const bool resume = search && ds.np_dec > 0;
+            if (v.jb.np > 0 && v.jb.numbps > 0) {
+                S.plane = iplane + v.o; S.spass = spass ? spass + v.o : nullptr;
+                MqDec q;
+                const int *rates = search ? cbout[v.bi].rate : nullptr;
+                const int nrates = search ? cbout[v.bi].totalpasses : 0;
+                if (resume) { mqd_load(q, cx, sv + DEC_SAVE_MQ, &shw[blk]); q.data = seg; }
+                else {
+                    for (int i = 0; i < 19; ++i) cx[i] = tab[0];
+                    cx[CTX_UNI] = tab[46 << 1]; cx[CTX_AGG] = tab[3 << 1]; cx[CTX_ZC] = tab[4 << 1];
+                    mqd_init(q, seg, v.jb.len, rates ? &shw[blk] : (MqShadows *)nullptr);
+                    if (rates) {
+                        for (int j = 0; j < DEC_NSHADOW; ++j) {
+                            const int tn = j < nrates ? rates[j] : -1;
+                            shw[blk].trunc[j] = tn;
+                            // cuts inside the two bytes the decoder reads while initialising cannot fork any more
+                            if (tn >= 0 && tn <= q.maxread) { q.sh_on |= 1u << j; shw[blk].sh_bad |= 1u << j; }
+                        }
+                        q.fork_at = mqd_next_fork(&shw[blk], q.sh_on);
+                    }
+                }
+                t1d_passes(S, q, v.cb.w, v.cb.h, v.jb.numbps, ds.np_dec, v.jb.np, rates, nrates, ds);
+                ds.np_dec = v.jb.np;
+                if (search) mqd_save(q, cx, sv + DEC_SAVE_MQ);
+            }
+            if (search) {
+                // the cut this probe needs: rate[np - 1]
+                const int pc = v.jb.np - 1;
+                int need = v.jb.np > 0 && (pc >= 128 || ((ds.bad[pc >> 5] >> (pc & 31)) & 1u));
+                if (need && ds.scratch_np == v.jb.np) { need = 0; jobs[v.bi].mode = 3; }
+                need2[blk] = need ? 1 : 0;
+                if (!need) dstate[v.bi] = ds;
+            }
+        } else need2[blk] = 1;
     }
     __syncwarp();
-    if (lane != 0) return;
-    if (jb.np > 0 && jb.numbps > 0) {
-        for (int i = 0; i < 19; ++i) cx[i] = tab[0];
-        cx[CTX_UNI] = tab[46 << 1]; cx[CTX_AGG] = tab[3 << 1]; cx[CTX_ZC] = tab[4 << 1];
-        S.plane = scratch + o; S.spass = nullptr;
-        MqDec q;
-        mqd_init(q, seg, search ? cbout[bi].rate[jb.np - 1] : jb.len, nullptr);
-        DecState dummy = ds;
-        t1d_passes(S, q, cb.w, cb.h, jb.numbps, 0, jb.np, nullptr, 0, dummy);
+
+    // ---- all lanes: save the recordings' flag words; clear what a real truncated decode needs ----
+    for (int sb = 0; sb < L; ++sb) {
+        DecView u;
+        if (!dec_view(u, job0 + sb, cblks, order, jobs, W, H, ncblks, nframes)) continue;
+        unsigned *Fb = F[warp * L + sb];
+        if (u.mode == 1 && search) {
+            unsigned *sv = save + u.bi * DEC_SAVE_WORDS;
+            for (int i = lane; i < DEC_FWORDS; i += 32) sv[i] = Fb[i];
+        }
+        if (need2[warp * L + sb] && (u.mode == 2 ? false : true)) {
+            // recording just made, cut not reproducible: the scratch decode starts from a clean block
+            for (int i = lane; i < DEC_FWORDS; i += 32) Fb[i] = 0;
+            for (int i = lane; i < u.cb.w * u.cb.h; i += 32) {
+                const int y = i / u.cb.w, x = i - y * u.cb.w;
+                scratch[u.o + (size_t)y * W + x] = 0;
+            }
+        }
     }
-    if (search) { ds.scratch_np = jb.np; dstate[bi] = ds; }
-    if (jb.mode == 1) jobs[bi].mode = 2;
+    __syncwarp();
+
+    // ---- lanes 0 .. L-1: real decode of the segment cut at rate[np - 1] into the scratch plane ----
+    if (mine && need2[blk]) {
+        if (v.jb.np > 0 && v.jb.numbps > 0) {
+            unsigned *cx = cxs[blk];
+            for (int i = 0; i < 19; ++i) cx[i] = tab[0];
+            cx[CTX_UNI] = tab[46 << 1]; cx[CTX_AGG] = tab[3 << 1]; cx[CTX_ZC] = tab[4 << 1];
+            S.plane = scratch + v.o; S.spass = nullptr;
+            MqDec q;
+            mqd_init(q, pool + (size_t)v.frame * pool_stride + v.jb.off, search ? cbout[v.bi].rate[v.jb.np - 1] : v.jb.len, nullptr);
+            DecState dummy = ds;
+            t1d_passes(S, q, v.cb.w, v.cb.h, v.jb.numbps, 0, v.jb.np, nullptr, 0, dummy);
+        }
+        if (search) { ds.scratch_np = v.jb.np; dstate[v.bi] = ds; }
+        if (v.jb.mode == 1) jobs[v.bi].mode = 2;
+    }
 }
 
 // decode jobs for the encoder's own allocation (compression-ratio search).  Block k is recorded (mode 1) when the

@@ -33,7 +33,7 @@ def _encode_batch(lib, frames, h, w, cr, mode=H.NONE, err=0.0):
 
 @pytest.fixture
 def env_guard():
-    keys = ("EBCC_MQ_LANES", "EBCC_BATCH_FRAMES", "EBCC_PIPELINES")
+    keys = ("EBCC_MQ_LANES", "EBCC_DEC_LANES", "EBCC_BATCH_FRAMES", "EBCC_PIPELINES")
     saved = {k: os.environ.get(k) for k in keys}
     yield
     for k, v in saved.items():
@@ -52,6 +52,33 @@ def test_mq_lanes_are_byte_identical(built, env_guard):
         got = _encode_batch(lib, frames, 200, 300, 6.0)
         for t in range(5):
             assert got[t][48:] == want[t], "lanes %d frame %d" % (lanes, t)
+
+
+def test_decoder_lanes_are_byte_identical(built, env_guard):
+    """The tier-1 decoder runs 1, 2, 4 or 8 code-blocks per warp; the CR search and the decode do not depend on it."""
+    lib = H.prod_lib()
+    lib.ebcc_decode_batch.restype = C.c_size_t
+    frames = H.synth_stack(5, 200, 300)
+    ref_streams, ref_dec = None, None
+    for lanes in (1, 2, 4, 8):
+        os.environ["EBCC_DEC_LANES"] = str(lanes)
+        got = _encode_batch(lib, frames, 200, 300, 20.0, H.MAX_ERROR, 0.25)
+        n = len(got)
+        bufs = [C.create_string_buffer(s, len(s)) for s in got]
+        ptrs = (C.c_void_p * n)(*[C.addressof(b) for b in bufs])
+        sizes = (C.c_size_t * n)(*[len(s) for s in got])
+        douts, cnts = (C.POINTER(C.c_float) * n)(), (C.c_size_t * n)()
+        assert lib.ebcc_decode_batch(ptrs, sizes, C.c_size_t(n), douts, cnts) == n
+        dec = [np.ctypeslib.as_array(douts[t], shape=(cnts[t],)).copy() for t in range(n)]
+        for t in range(n):
+            lib.free_buffer(douts[t])
+            assert float(np.abs(dec[t] - frames[t].ravel()).max()) <= 0.25
+        if ref_streams is None:
+            ref_streams, ref_dec = got, dec
+        else:
+            assert got == ref_streams, "lanes %d" % lanes
+            for t in range(n):
+                assert np.array_equal(dec[t], ref_dec[t]), "lanes %d frame %d" % (lanes, t)
 
 
 def test_multi_batch_call_uses_pipelines(built, env_guard):
