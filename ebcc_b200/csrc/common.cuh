@@ -71,6 +71,10 @@ struct CblkOut {
 
 struct Plan {
     int H, W, nbands, ncblks;
+    // tile of a multi-tile image (src/ebcc_codec.c:105-123: dims[0] tiles of dims[1] x dims[2] stacked vertically):
+    // canvas row of the tile's first line, its index (Isot) and the tile count; a single-tile image is {0, 0, 1}
+    int y0, tile_index, ntiles;
+    int cas_v[J2K_NRES];              // row parity of each resolution's origin on the canvas (dwt.c:1986-1987, 3575)
     int res_w[J2K_NRES], res_h[J2K_NRES];
     BandDesc bands[J2K_MAXBANDS];
     int nnodes;                       // tag-tree nodes over all bands

@@ -316,7 +316,8 @@ static int search_batch(ebcc_cuda_ctx *ctx, size_t nb, const int *run, const flo
 static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size_t base, const codec_config_t *config,
                         uint8_t **outs, size_t *sizes, size_t *done)
 {
-    const size_t H = config->dims[1], W = config->dims[2], N = H * W;
+    /* dims[0] tiles of dims[1] x dims[2] per image (reference j2k_encode_internal, src/ebcc_codec.c:105-123) */
+    const size_t T = config->dims[0], H = config->dims[1], W = config->dims[2], N = T * H * W;
     const residual_t mode = config->residual_compression_type;
     int rc = -1;
     double base_error_quantile = 1e-6;
@@ -350,7 +351,7 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
 
     g_profile = getenv("EBCC_PROFILE") != NULL;
     if (g_profile) { memset(g_tm, 0, sizeof(g_tm)); memset(g_tm_calls, 0, sizeof(g_tm_calls)); }
-    if (ebcc_cuda_reserve(ctx, H, W, nb)) goto out;
+    if (ebcc_cuda_reserve_tiled(ctx, T, H, W, nb)) goto out;
     if (TIMED(TM_ANALYZE, ebcc_cuda_upload(ctx, frames, nb) || ebcc_cuda_analyze_resident(ctx, nb) || ebcc_cuda_sync(ctx))) goto out;
     for (size_t i = 0; i < nb; ++i) { cr[i] = config->base_cr; tgt[i] = 0; }
 
@@ -558,17 +559,13 @@ size_t ebcc_encode_batch(const float *frames, size_t nframes, const codec_config
                  NDIMS - 2, NDIMS - 1, EBCC_MIN_INTERNAL_IMAGE_DIM, EBCC_MAX_INTERNAL_IMAGE_DIM);
         return 0;
     }
-    if (config->dims[0] != 1) {
-        ebcc_log(LOG_FATAL, "multi-tile internal images (dims[0]=%lu > 1) are not implemented on the CUDA path yet", config->dims[0]);
-        return 0;
-    }
     if ((unsigned)config->residual_compression_type > RELATIVE_ERROR) {
         ebcc_log(LOG_FATAL, "unknown residual compression type %d", (int)config->residual_compression_type);
         return 0;
     }
     enc_job_t job;
     job.frames = frames; job.nframes = nframes; job.config = config; job.outs = outs; job.sizes = sizes;
-    job.N = config->dims[1] * config->dims[2]; job.maxb = max_batch_frames(); job.next = 0; job.done = 0; job.failed = 0;
+    job.N = config->dims[0] * config->dims[1] * config->dims[2]; job.maxb = max_batch_frames(); job.next = 0; job.done = 0; job.failed = 0;
     pthread_mutex_init(&job.mu, NULL);
     const size_t nbatches = (nframes + job.maxb - 1) / job.maxb;
     int nworkers = n_pipelines();
@@ -598,7 +595,7 @@ typedef struct {
     float minval, maxval, rmin, rmax;
     size_t coeffs_size, zstd_size, tail_size, tot_size;
     const uint8_t *zstd, *tail;
-    size_t H, W;
+    size_t H, W, T;              /* tile height, width, tiles per image */
 } parsed_stream_t;
 
 static uint32_t be32(const uint8_t *p) { return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]; }
@@ -665,11 +662,12 @@ static int parse_stream(const uint8_t *data, size_t n, parsed_stream_t *ps)
             ebcc_log(LOG_FATAL, "Invalid encoded data: no JPEG 2000 codestream"); return 0;
         }
         const size_t X = be32(ps->tail + 8), Y = be32(ps->tail + 12), XT = be32(ps->tail + 24), YT = be32(ps->tail + 28);
-        if (be32(ps->tail + 16) || be32(ps->tail + 20) || X != XT || Y != YT) {
-            ebcc_log(LOG_FATAL, "multi-tile codestreams (dims[0] > 1) are not implemented on the CUDA path yet"); return 0;
+        /* one column of tiles, all of the same height (what j2k_encode_internal writes for dims[0] > 1) */
+        if (be32(ps->tail + 16) || be32(ps->tail + 20) || be32(ps->tail + 32) || be32(ps->tail + 36) || X != XT || YT == 0 || Y % YT != 0) {
+            ebcc_log(LOG_FATAL, "Invalid encoded data: unsupported JPEG 2000 tiling"); return 0;
         }
-        ps->W = X; ps->H = Y; ps->tot_size = X * Y;
-        if (X < EBCC_MIN_INTERNAL_IMAGE_DIM || X > EBCC_MAX_INTERNAL_IMAGE_DIM || Y < EBCC_MIN_INTERNAL_IMAGE_DIM || Y > EBCC_MAX_INTERNAL_IMAGE_DIM) {
+        ps->W = X; ps->H = YT; ps->T = Y / YT; ps->tot_size = X * Y;
+        if (X < EBCC_MIN_INTERNAL_IMAGE_DIM || X > EBCC_MAX_INTERNAL_IMAGE_DIM || YT < EBCC_MIN_INTERNAL_IMAGE_DIM || Y > EBCC_MAX_INTERNAL_IMAGE_DIM) {
             ebcc_log(LOG_FATAL, "Invalid encoded data: image size %lu x %lu out of range", Y, X); return 0;
         }
     }
@@ -700,11 +698,11 @@ static void *dec_worker(void *arg)
         const size_t g = jb->next < jb->ngroups ? jb->next++ : (size_t)-1;
         pthread_mutex_unlock(&jb->mu);
         if (g == (size_t)-1) break;
-        const size_t i = jb->starts[g], H = ps[i].H, W = ps[i].W;
+        const size_t i = jb->starts[g], H = ps[i].H, W = ps[i].W, T = ps[i].T;
         size_t nb = 0;
         for (size_t j = i; j < jb->ends[g]; ++j) {
             if (!ps[j].ok || ps[j].const_field) continue;
-            if (!jb->outs[j]) { jb->outs[j] = (float *)malloc(H * W * sizeof(float)); jb->owned[j] = 1; }
+            if (!jb->outs[j]) { jb->outs[j] = (float *)malloc(T * H * W * sizeof(float)); jb->owned[j] = 1; }
             if (!jb->outs[j]) { ps[j].ok = 0; continue; }
             js[nb] = ps[j].tail; jn[nb] = ps[j].tail_size; mn[nb] = ps[j].minval; mx[nb] = ps[j].maxval; dst[nb] = jb->outs[j]; idx[nb] = j;
             memset(&rs[nb], 0, sizeof(rs[nb]));
@@ -716,10 +714,10 @@ static void *dec_worker(void *arg)
         }
         if (!nb) continue;
         if (!ctx) ctx = acquire_ctx();
-        const int rc = ctx ? ebcc_cuda_decode_batch(ctx, js, jn, nb, H, W, mn, mx, rs, dst) : -1;
+        const int rc = ctx ? ebcc_cuda_decode_batch_tiled(ctx, js, jn, nb, T, H, W, mn, mx, rs, dst) : -1;
         size_t ok = 0;
         for (size_t k = 0; k < nb; ++k) {
-            if (rc == 0) { jb->counts[idx[k]] = H * W; ok++; }
+            if (rc == 0) { jb->counts[idx[k]] = T * H * W; ok++; }
             else if (jb->owned[idx[k]]) { free(jb->outs[idx[k]]); jb->outs[idx[k]] = NULL; }
         }
         if (rc) ebcc_log(LOG_FATAL, "CUDA decode of %lu frame(s) failed", nb);
@@ -760,7 +758,7 @@ size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, si
         size_t nb = 0, j = i;
         for (; j < nframes && nb < job.maxb; ++j) {
             if (!ps[j].ok || ps[j].const_field) continue;
-            if (ps[j].H != ps[i].H || ps[j].W != ps[i].W) break;
+            if (ps[j].H != ps[i].H || ps[j].W != ps[i].W || ps[j].T != ps[i].T) break;
             nb++;
         }
         job.starts[job.ngroups] = i; job.ends[job.ngroups] = j; job.ngroups++;

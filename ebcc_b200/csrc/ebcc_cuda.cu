@@ -47,7 +47,37 @@ __global__ void k_compact(const unsigned char *__restrict__ out_pool, const Prob
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += gridDim.x * blockDim.x) dst[i] = src[i];
 }
 
-// ---- host-side geometry (tcd.c:961-1264 for one tile at the canvas origin) ------------------------
+// ---- multi-tile codestream assembly ---------------------------------------------------------------------------------
+// Every tile context writes "main header | SOT(Isot = t) SOD packets | EOC" for its tile; the image's codestream is
+// the main header, the tile-parts in tile order and one EOC (opj_j2k_write_tile per tile + opj_end_compress,
+// src/ebcc_codec.c:166-176).  grid = (ntiles, nframes).
+#define EBCC_MAX_TILES 64
+struct TileSrc { const unsigned char *out; const ProbeOut *pout; size_t stride; };
+
+__global__ void k_assemble_tiles(const TileSrc *__restrict__ src, int ntiles, int hl, unsigned char *out, size_t out_stride, ProbeOut *pout)
+{
+    const int t = blockIdx.x, frame = blockIdx.y;
+    const int sb = src[t].pout[frame].stream_bytes;
+    if (sb == 0) {                                   // constant image: no codestream
+        if (t == 0 && threadIdx.x == 0) { pout[frame].stream_bytes = 0; pout[frame].total_bytes = 0; }
+        return;
+    }
+    int off = hl;
+    for (int k = 0; k < t; ++k) off += src[k].pout[frame].stream_bytes - hl - 2;
+    const int len = sb - hl - 2;
+    const unsigned char *s = src[t].out + (size_t)frame * src[t].stride;
+    unsigned char *o = out + (size_t)frame * out_stride;
+    for (int i = threadIdx.x; i < len; i += blockDim.x) o[off + i] = s[hl + i];
+    if (t == 0) for (int i = threadIdx.x; i < hl; i += blockDim.x) o[i] = s[i];
+    if (t == ntiles - 1 && threadIdx.x == 0) {
+        o[off + len] = 0xff; o[off + len + 1] = 0xd9;
+        pout[frame].stream_bytes = off + len + 2;
+        pout[frame].total_bytes = off + len - hl;
+        pout[frame].iters = 0; pout[frame].thresh = 0.0;
+    }
+}
+
+// ---- host-side geometry (tcd.c:961-1264) ---------------------------------------------------------------------------
 static int h_ceildivpow2(int a, int b) { return (int)(((long long)a + (1ll << b) - 1) >> b); }
 static int h_floorlog2(int a) { int l = 0; while (a > 1) { a >>= 1; l++; } return l; }
 
@@ -60,15 +90,23 @@ static const double h_norms97[4][10] = {
 static void put16(unsigned char *&p, unsigned v) { *p++ = (unsigned char)(v >> 8); *p++ = (unsigned char)v; }
 static void put32(unsigned char *&p, unsigned v) { put16(p, v >> 16); put16(p, v & 0xffff); }
 
-static void build_plan(int H, int W, Plan *pl, CblkDesc **cblks_out)
+// Geometry of one tile of H x W whose first line is canvas row y0 (tile tile_index of ntiles; the image is Himg lines
+// high).  Tiles below the first one start at a non-zero canvas row: resolutions and bands are the canvas rectangles of
+// tcd.c:961-1055 (ceil-divisions of y0 and y0 + H), the row parity of a resolution's origin decides which lines are
+// low-pass (dwt.c:1986-1987), and the code-block grid stays anchored to multiples of 64 of the band's canvas
+// coordinates (tcd.c:1122-1230), so the first block row of a band can be a partial one.
+static void build_plan(int H, int W, int y0, int tile_index, int ntiles, int Himg, Plan *pl, CblkDesc **cblks_out)
 {
     memset(pl, 0, sizeof(*pl));
-    pl->H = H; pl->W = W;
+    pl->H = H; pl->W = W; pl->y0 = y0; pl->tile_index = tile_index; pl->ntiles = ntiles;
     for (int r = 0; r < J2K_NRES; ++r) {
-        pl->res_w[r] = h_ceildivpow2(W, J2K_NRES - 1 - r);
-        pl->res_h[r] = h_ceildivpow2(H, J2K_NRES - 1 - r);
+        const int lvl = J2K_NRES - 1 - r, ry0 = h_ceildivpow2(y0, lvl);
+        pl->res_w[r] = h_ceildivpow2(W, lvl);
+        pl->res_h[r] = h_ceildivpow2(y0 + H, lvl) - ry0;
+        pl->cas_v[r] = ry0 & 1;
     }
     int nb = 0, ncb = 0, nnodes = 0;
+    int band_y0[J2K_MAXBANDS];                       // canvas row of each band's first line
     for (int r = 0; r < J2K_NRES; ++r) {
         const int lvl = J2K_NRES - 1 - r;
         pl->res_first[r] = ncb;
@@ -77,11 +115,13 @@ static void build_plan(int H, int W, Plan *pl, CblkDesc **cblks_out)
             const int orient = r == 0 ? 0 : bi + 1;
             b->resno = r; b->orient = orient; b->level = lvl;
             if (r == 0) {
-                b->bw = h_ceildivpow2(W, lvl); b->bh = h_ceildivpow2(H, lvl);
+                b->bw = h_ceildivpow2(W, lvl); b->bh = pl->res_h[0];
+                band_y0[nb] = h_ceildivpow2(y0, lvl);
             } else {
                 const int x0b = orient & 1, y0b = orient >> 1;
                 b->bw = h_ceildivpow2(W - (x0b << lvl), lvl + 1);
-                b->bh = h_ceildivpow2(H - (y0b << lvl), lvl + 1);
+                band_y0[nb] = h_ceildivpow2(y0 - (y0b << lvl), lvl + 1);
+                b->bh = h_ceildivpow2(y0 + H - (y0b << lvl), lvl + 1) - band_y0[nb];
                 b->offx = x0b ? pl->res_w[r - 1] : 0;
                 b->offy = y0b ? pl->res_h[r - 1] : 0;
             }
@@ -104,7 +144,7 @@ static void build_plan(int H, int W, Plan *pl, CblkDesc **cblks_out)
             }
             const bool empty = b->bw <= 0 || b->bh <= 0;
             b->cw = empty ? 0 : (b->bw + 63) / 64;
-            b->ch = empty ? 0 : (b->bh + 63) / 64;
+            b->ch = empty ? 0 : (band_y0[nb] + b->bh + 63) / 64 - band_y0[nb] / 64;
             b->first_cblk = ncb;
             ncb += b->cw * b->ch;
             // tag tree shape
@@ -133,8 +173,11 @@ static void build_plan(int H, int W, Plan *pl, CblkDesc **cblks_out)
                 CblkDesc *c = &cb[b->first_cblk + gy * b->cw + gx];
                 c->band = bi; c->gx = gx; c->gy = gy; c->orient = b->orient;
                 c->w = (gx * 64 + 64 <= b->bw ? 64 : b->bw - gx * 64);
-                c->h = (gy * 64 + 64 <= b->bh ? 64 : b->bh - gy * 64);
-                c->tx = b->offx + gx * 64; c->ty = b->offy + gy * 64;
+                // rows of the band relative to its first line: grid row gy of a grid anchored at canvas multiples of 64
+                const int by0 = band_y0[bi], gr0 = (by0 / 64 + gy) * 64 - by0;
+                const int r0 = gr0 < 0 ? 0 : gr0, r1 = gr0 + 64 < b->bh ? gr0 + 64 : b->bh;
+                c->h = r1 - r0;
+                c->tx = b->offx + gx * 64; c->ty = b->offy + r0;
                 // symbols: <= 1.5 per sample per bit-plane (zero coding / refinement / run mode) + one sign
                 size_t cap = (size_t)c->w * c->h * (3 * (size_t)b->numbps / 2 + 2) + 32;
                 cap = (cap + 15) & ~(size_t)15;
@@ -149,7 +192,7 @@ static void build_plan(int H, int W, Plan *pl, CblkDesc **cblks_out)
     unsigned char *p = pl->main_header;
     put16(p, 0xFF4F);
     put16(p, 0xFF51); put16(p, 41); put16(p, 0);
-    put32(p, (unsigned)W); put32(p, (unsigned)H); put32(p, 0); put32(p, 0);
+    put32(p, (unsigned)W); put32(p, (unsigned)Himg); put32(p, 0); put32(p, 0);
     put32(p, (unsigned)W); put32(p, (unsigned)H); put32(p, 0); put32(p, 0);
     put16(p, 1); *p++ = 15; *p++ = 1; *p++ = 1;
     put16(p, 0xFF52); put16(p, 12); *p++ = 0; *p++ = 0; put16(p, 1); *p++ = 0;
@@ -160,18 +203,19 @@ static void build_plan(int H, int W, Plan *pl, CblkDesc **cblks_out)
     put16(p, 0xFF64); put16(p, (unsigned)(4 + sizeof(com) - 1)); put16(p, 1);
     memcpy(p, com, sizeof(com) - 1); p += sizeof(com) - 1;
     pl->main_header_len = (int)(p - pl->main_header);
-    size_t os = (size_t)((double)((unsigned long long)W * H * 16) * 1.4 / 8) + 500 + 256 + (size_t)pl->main_header_len;
+    // room for every tile-part of a multi-tile image when this plan is the image-level one (Himg == H, ntiles > 1)
+    size_t os = (size_t)((double)((unsigned long long)W * H * 16) * 1.4 / 8) + 500 + 256 + (size_t)pl->main_header_len + 520 * (size_t)ntiles;
     pl->out_stride = (os + 255) & ~(size_t)255;
     *cblks_out = cb;
 }
 
 // per-tile byte budget in f32 exactly as opj_j2k_update_rates (j2k.c:5376-5408); < 0 => all passes
-static int tile_maxlen(int H, int W, float base_cr, int main_header_bytes)
+static int tile_maxlen(int H, int W, float base_cr, int main_header_bytes, int ntiles)
 {
     float rate = base_cr / 2;                            // src/ebcc_codec.c:116
     if (rate <= 1.0) return -1;                          // j2k.c:8159-8162
     float r = (float)(((double)16 * (unsigned)W * (unsigned)H) / (rate * (float)8)) - 0.0f;
-    r -= (float)main_header_bytes / (float)1;
+    r -= (float)main_header_bytes / (float)(unsigned)ntiles;     // l_sot_remove, j2k.c:5351-5352
     if (r < 30.0f) r = 30.0f;
     unsigned long long tile_size = (unsigned long long)((double)((unsigned long long)W * H * 16) * 1.4 / 8) + 500;
     unsigned len = (unsigned)tile_size - 12 - 4;
@@ -295,6 +339,13 @@ struct ebcc_cuda_ctx {
     float stage_ms[EBCC_ST_COUNT];
     int ev_valid;
     unsigned long long launches;
+    // multi-tile images (dims[0] > 1, src/ebcc_codec.c:105-180): this context holds the image-level data (input,
+    // min/max, decoded image, residual layer, assembled codestreams); tile t of every image of the batch is coded by
+    // tile[t], a light context with the tile's own geometry that shares this context's stream and look-up tables
+    int ntiles;
+    ebcc_cuda_ctx *tile[EBCC_MAX_TILES];
+    ebcc_cuda_ctx *parent;
+    TileSrc *d_tile_src;
 };
 
 // Wait for the pipeline's stream.  Several pipelines (and, on a multi-GPU box, several ranks) share the host cores:
@@ -324,7 +375,7 @@ extern "C" ebcc_cuda_ctx *ebcc_cuda_ctx_create(int device)
     }
     if (cudaSetDevice(device) != cudaSuccess) return NULL;
     ebcc_cuda_ctx *c = (ebcc_cuda_ctx *)calloc(1, sizeof(*c));
-    c->device = device;
+    c->device = device; c->ntiles = 1;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { free(c); return NULL; }
     for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventCreate(&c->ev[i]);
     cudaEventCreateWithFlags(&c->ev_sync, cudaEventBlockingSync | cudaEventDisableTiming);
@@ -348,6 +399,34 @@ extern "C" ebcc_cuda_ctx *ebcc_cuda_ctx_create(int device)
         cudaMemcpy(c->d_step_tab, tab, sizeof(tab), cudaMemcpyHostToDevice);
     }
     return c;
+}
+
+// light context of one tile: shares the parent's stream and tables, owns its geometry and work buffers
+static ebcc_cuda_ctx *ctx_create_tile(ebcc_cuda_ctx *parent)
+{
+    ebcc_cuda_ctx *c = (ebcc_cuda_ctx *)calloc(1, sizeof(*c));
+    if (!c) return NULL;
+    c->device = parent->device; c->stream = parent->stream; c->parent = parent; c->spin_sync = parent->spin_sync;
+    c->d_luts = parent->d_luts; c->d_mqtab = parent->d_mqtab; c->d_declut = parent->d_declut; c->d_step_tab = parent->d_step_tab;
+    for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventCreate(&c->ev[i]);
+    cudaEventCreateWithFlags(&c->ev_sync, cudaEventBlockingSync | cudaEventDisableTiming);
+    return c;
+}
+
+static void free_buffers(ebcc_cuda_ctx *c);
+static void drop_tiles(ebcc_cuda_ctx *c)
+{
+    for (int t = 0; t < EBCC_MAX_TILES; ++t) {
+        ebcc_cuda_ctx *s = c->tile[t];
+        if (!s) continue;
+        free_buffers(s);
+        for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventDestroy(s->ev[i]);
+        cudaEventDestroy(s->ev_sync);
+        free(s);
+        c->tile[t] = NULL;
+    }
+    cudaFree(c->d_tile_src); c->d_tile_src = NULL;
+    c->ntiles = 1;
 }
 
 static void free_buffers(ebcc_cuda_ctx *c)
@@ -390,6 +469,7 @@ extern "C" void ebcc_cuda_ctx_destroy(ebcc_cuda_ctx *c)
     if (!c) return;
     cudaSetDevice(c->device);
     ctx_sync(c);
+    drop_tiles(c);
     free_buffers(c);
     cudaFree(c->d_luts); cudaFree(c->d_mqtab); cudaFree(c->d_declut); cudaFree(c->d_step_tab);
     for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventDestroy(c->ev[i]);
@@ -397,14 +477,17 @@ extern "C" void ebcc_cuda_ctx_destroy(ebcc_cuda_ctx *c)
     free(c);
 }
 
-extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes)
+// work buffers of one context for nframes tiles of H x W at canvas row y0 (tile_index of ntiles, image height Himg);
+// light: no residual-layer buffers (tile contexts of a multi-tile image)
+static int reserve_impl(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes, int y0, int tile_index, int ntiles, int Himg, int light)
 {
     if (!c || H < 32 || W < 32 || H > 2047 || W > 2047 || nframes == 0) return -1;
     CK(cudaSetDevice(c->device));
-    if (c->cap_frames >= nframes && c->plan.H == (int)H && c->plan.W == (int)W) return 0;
+    if (c->cap_frames >= nframes && c->plan.H == (int)H && c->plan.W == (int)W && c->plan.y0 == y0 && c->plan.tile_index == tile_index &&
+        c->plan.ntiles == ntiles) return 0;
     CK(ctx_sync(c));
     free_buffers(c);
-    build_plan((int)H, (int)W, &c->plan, &c->h_cblks);
+    build_plan((int)H, (int)W, y0, tile_index, ntiles, Himg, &c->plan, &c->h_cblks);
     const Plan *pl = &c->plan;
     const size_t B = nframes, N = H * W;
     CK(cudaMalloc((void **)&c->d_plan, sizeof(Plan)));
@@ -461,7 +544,7 @@ extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nf
     CK(cudaMallocHost((void **)&c->h_slens, B * sizeof(int)));
     CK(cudaMallocHost((void **)&c->h_targets, B * sizeof(float)));
     CK(cudaMallocHost((void **)&c->h_streams, B * pl->out_stride));
-    {   // residual layer
+    if (!light) {   // residual layer
         SpGeom &g = c->sg;
         g.W = (int)W; g.H = (int)H; g.Wp = ((int)W + 15) & ~15; g.Hp = ((int)H + 15) & ~15; g.lx = g.Wp >> SP_STAGES; g.ly = g.Hp >> SP_STAGES;
         const size_t Np = (size_t)g.Wp * g.Hp;
@@ -502,6 +585,37 @@ extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nf
     return 0;
 }
 
+extern "C" int ebcc_cuda_reserve_tiled(ebcc_cuda_ctx *c, size_t ntiles, size_t H, size_t W, size_t nframes)
+{
+    if (!c || c->parent || ntiles == 0 || ntiles > EBCC_MAX_TILES || ntiles * H > 2047) return -1;
+    CK(cudaSetDevice(c->device));
+    if (ntiles == 1) {
+        if (c->ntiles > 1) { CK(ctx_sync(c)); drop_tiles(c); }
+        c->ntiles = 1;
+        return reserve_impl(c, H, W, nframes, 0, 0, 1, (int)H, 0);
+    }
+    const int T = (int)ntiles, Himg = (int)(ntiles * H);
+    if (c->ntiles != T) { CK(ctx_sync(c)); drop_tiles(c); }
+    // image-level context: input, statistics, decoded image, residual layer and the assembled codestreams
+    if (reserve_impl(c, (size_t)Himg, W, nframes, 0, 0, T, Himg, 0)) return -1;
+    c->ntiles = T;
+    TileSrc src[EBCC_MAX_TILES];
+    for (int t = 0; t < T; ++t) {
+        if (!c->tile[t] && !(c->tile[t] = ctx_create_tile(c))) return -1;
+        if (reserve_impl(c->tile[t], H, W, nframes, t * (int)H, t, T, Himg, 1)) return -1;
+        src[t].out = c->tile[t]->d_out; src[t].pout = c->tile[t]->d_pout; src[t].stride = c->tile[t]->plan.out_stride;
+    }
+    if (!c->d_tile_src) CK(cudaMalloc((void **)&c->d_tile_src, sizeof(TileSrc) * EBCC_MAX_TILES));
+    CK(cudaMemcpyAsync(c->d_tile_src, src, sizeof(TileSrc) * T, cudaMemcpyHostToDevice, c->stream));
+    CK(ctx_sync(c));
+    return 0;
+}
+
+extern "C" int ebcc_cuda_reserve(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes)
+{
+    return ebcc_cuda_reserve_tiled(c, 1, H, W, nframes);
+}
+
 static void mark(ebcc_cuda_ctx *c, int i)
 {
     if (c->profiling) cudaEventRecord(c->ev[i], c->stream);
@@ -530,9 +644,9 @@ static int launch_dwt(ebcc_cuda_ctx *c, int B)
         dim3 gv((unsigned)((rw + CW - 1) / CW), (unsigned)B);
         size_t sv = (size_t)rh * CW * sizeof(float);
         if (r == J2K_NRES - 1)
-            EBCC_LAUNCH(k_dwt_v<true>, gv, bv, sv, c->stream, c->d_in, c->d_coef, c->d_stat, W, H, rw, rh, pl->res_h[r - 1]);
+            EBCC_LAUNCH(k_dwt_v<true>, gv, bv, sv, c->stream, c->d_in, c->d_coef, c->d_stat, W, H, rw, rh, pl->res_h[r - 1], pl->cas_v[r]);
         else
-            EBCC_LAUNCH(k_dwt_v<false>, gv, bv, sv, c->stream, c->d_in, c->d_coef, c->d_stat, W, H, rw, rh, pl->res_h[r - 1]);
+            EBCC_LAUNCH(k_dwt_v<false>, gv, bv, sv, c->stream, c->d_in, c->d_coef, c->d_stat, W, H, rw, rh, pl->res_h[r - 1], pl->cas_v[r]);
         // horizontal: RH full rows per CTA
         int RH = 4;
         while ((size_t)rw * RH * sizeof(float) > 64 * 1024 && RH > 1) RH >>= 1;
@@ -544,13 +658,52 @@ static int launch_dwt(ebcc_cuda_ctx *c, int B)
     return 0;
 }
 
+static int launch_minmax(ebcc_cuda_ctx *c, int B)
+{
+    const int N = c->plan.H * c->plan.W;
+    EBCC_LAUNCH(k_stat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_stat, B);
+    EBCC_LAUNCH(k_minmax, dim3(74, (unsigned)B), dim3(256), 0, c->stream, c->d_in, c->d_stat, N);
+    EBCC_LAUNCH(k_minmax_final, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_in, c->d_stat, N, B);
+    c->launches += 3;
+    return 0;
+}
+
+static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax);
+
+// multi-tile image: min/max over the whole image (src/ebcc_codec.c:676-689 scales the image, not the tile), then
+// every tile context transforms and codes its tile of every image
+static int analyze_tiled(ebcc_cuda_ctx *c, size_t nframes)
+{
+    const int B = (int)nframes, T = c->ntiles;
+    mark(c, EBCC_ST_MINMAX);
+    if (launch_minmax(c, B)) return -1;
+    mark(c, EBCC_ST_DWT);
+    for (int t = 0; t < T; ++t) {
+        ebcc_cuda_ctx *s = c->tile[t];
+        const size_t Nt = (size_t)s->plan.H * s->plan.W;
+        CK(cudaMemcpyAsync(s->d_stat, c->d_stat, sizeof(FrameStat) * B, cudaMemcpyDeviceToDevice, c->stream));
+        CK(cudaMemcpy2DAsync(s->d_in, Nt * sizeof(float), c->d_in + (size_t)t * Nt, (size_t)T * Nt * sizeof(float), Nt * sizeof(float),
+                             (size_t)B, cudaMemcpyDeviceToDevice, c->stream));
+        if (analyze_impl(s, nframes, 0)) return -1;
+    }
+    mark(c, EBCC_ST_T1_CM);
+    mark(c, EBCC_ST_T1_MQ);
+    return 0;
+}
+
 // stage 1 of the encoder: everything that does not depend on the compression ratio
 extern "C" int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *c, size_t nframes)
 {
     if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
     CK(cudaSetDevice(c->device));
+    if (c->ntiles > 1) return analyze_tiled(c, nframes);
+    return analyze_impl(c, nframes, 1);
+}
+
+static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax)
+{
     const Plan *pl = &c->plan;
-    const int B = (int)nframes, N = pl->H * pl->W;
+    const int B = (int)nframes;
     {
         const char *nr = getenv("EBCC_NO_RECORDING");   // debugging aid: every probe decodes every block for real
         c->use_recording = !(nr && nr[0] == '1');
@@ -559,10 +712,7 @@ extern "C" int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *c, size_t nframes)
         c->launches++;
     }
     mark(c, EBCC_ST_MINMAX);
-    EBCC_LAUNCH(k_stat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_stat, B);
-    EBCC_LAUNCH(k_minmax, dim3(74, (unsigned)B), dim3(256), 0, c->stream, c->d_in, c->d_stat, N);
-    EBCC_LAUNCH(k_minmax_final, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_in, c->d_stat, N, B);
-    c->launches += 3;
+    if (with_minmax && launch_minmax(c, B)) return -1;
 
     mark(c, EBCC_ST_DWT);
     if (launch_dwt(c, B)) return -1;
@@ -594,7 +744,24 @@ extern "C" int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *c, size_t nframes)
 static int launch_rate_stage(ebcc_cuda_ctx *c, int B, const float *cr, int with_bodies)
 {
     const Plan *pl = &c->plan;
-    for (int i = 0; i < B; ++i) c->h_maxlen[i] = tile_maxlen(pl->H, pl->W, cr[i], pl->main_header_len);
+    if (c->ntiles > 1) {
+        // per-tile rate allocation (opj_j2k_update_rates splits the budget per tile, j2k.c:5361-5408), then the
+        // tile-parts are gathered behind one main header
+        mark(c, EBCC_ST_PCRD_T2);
+        for (int t = 0; t < c->ntiles; ++t) if (launch_rate_stage(c->tile[t], B, cr, with_bodies)) return -1;
+        mark(c, EBCC_ST_BODIES);
+        if (with_bodies) {
+            EBCC_LAUNCH(k_assemble_tiles, dim3((unsigned)c->ntiles, (unsigned)B), dim3(256), 0, c->stream, c->d_tile_src, c->ntiles,
+                        c->tile[0]->plan.main_header_len, c->d_out, pl->out_stride, c->d_pout);
+            EBCC_LAUNCH(k_offsets, dim3(1), dim3(32), 0, c->stream, c->d_pout, c->d_offs, B);
+            EBCC_LAUNCH(k_compact, dim3(8, (unsigned)B), dim3(256), 0, c->stream, c->d_out, c->d_pout, c->d_offs, c->d_packed, pl->out_stride);
+            c->launches += 3;
+        }
+        mark(c, EBCC_ST_D2H);
+        CK(cudaGetLastError());
+        return 0;
+    }
+    for (int i = 0; i < B; ++i) c->h_maxlen[i] = tile_maxlen(pl->H, pl->W, cr[i], pl->main_header_len, pl->ntiles);
     CK(cudaMemcpyAsync(c->d_maxlen, c->h_maxlen, sizeof(int) * B, cudaMemcpyHostToDevice, c->stream));
     mark(c, EBCC_ST_PCRD_T2);
     EBCC_LAUNCH(k_pcrd_t2, dim3((unsigned)B), dim3(T2_THREADS), t2_smem_bytes(pl->ncblks, pl->nnodes), c->stream,
@@ -660,7 +827,7 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
         int CW = 32;
         while ((size_t)rh * CW * sizeof(float) > 96 * 1024 && CW > 4) CW >>= 1;
         EBCC_LAUNCH(k_idwt_v, dim3((unsigned)((rw + CW - 1) / CW), (unsigned)B), dim3((unsigned)CW, (unsigned)(512 / CW)),
-                    (size_t)rh * CW * sizeof(float), c->stream, c->d_dcoef, W, H, rw, rh, pl->res_h[r - 1]);
+                    (size_t)rh * CW * sizeof(float), c->stream, c->d_dcoef, W, H, rw, rh, pl->res_h[r - 1], pl->cas_v[r]);
         c->launches += 2;
     }
     if (orig) { EBCC_LAUNCH(k_errstat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_es, B); c->launches++; }
@@ -675,14 +842,10 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
 // One probe of the compression-ratio search (emulate_j2k_compression, src/ebcc_codec.c:535-543) for every frame of
 // the resident batch: rate allocation at cr[i], real tier-1 decode of the truncated segments, IDWT, and the error
 // statistics against the original frame.  Synchronous; res[i] is filled for every frame.
-extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const float *cr, const float *targets,
-                                    int with_streams, ebcc_probe_result *res)
+// device work of one probe on one (tile) context; the statistics land in the context's pinned h_es / h_pout
+static int probe_launch(ebcc_cuda_ctx *c, int B, const float *targets)
 {
-    if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
-    CK(cudaSetDevice(c->device));
     const Plan *pl = &c->plan;
-    const int B = (int)nframes;
-    if (launch_rate_stage(c, B, cr, with_streams)) return -1;
     for (int i = 0; i < B; ++i) c->h_targets[i] = targets[i];
     CK(cudaMemcpyAsync(c->d_targets, c->h_targets, sizeof(float) * B, cudaMemcpyHostToDevice, c->stream));
     const long long njobs = (long long)pl->ncblks * B;
@@ -692,7 +855,53 @@ extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const floa
     if (run_decode_stage(c, B, c->d_mq, pl->mq_stride, c->d_in)) return -1;
     CK(cudaMemcpyAsync(c->h_es, c->d_es, sizeof(ErrStat) * B, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaMemcpyAsync(c->h_pout, c->d_pout, sizeof(ProbeOut) * B, cudaMemcpyDeviceToHost, c->stream));
-    CK(ctx_sync(c));
+    return 0;
+}
+
+// tile t's decoded lines of every image -> their place in the image-level plane
+static int gather_tiles(ebcc_cuda_ctx *c, int B)
+{
+    const int T = c->ntiles;
+    for (int t = 0; t < T; ++t) {
+        ebcc_cuda_ctx *s = c->tile[t];
+        const size_t Nt = (size_t)s->plan.H * s->plan.W;
+        CK(cudaMemcpy2DAsync(c->d_dec + (size_t)t * Nt, (size_t)T * Nt * sizeof(float), s->d_dec, Nt * sizeof(float), Nt * sizeof(float),
+                             (size_t)B, cudaMemcpyDeviceToDevice, c->stream));
+    }
+    return 0;
+}
+
+extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const float *cr, const float *targets,
+                                    int with_streams, ebcc_probe_result *res)
+{
+    if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
+    CK(cudaSetDevice(c->device));
+    const int B = (int)nframes;
+    if (launch_rate_stage(c, B, cr, with_streams)) return -1;
+    if (c->ntiles > 1) {
+        const int T = c->ntiles, hl = c->tile[0]->plan.main_header_len;
+        for (int t = 0; t < T; ++t) if (probe_launch(c->tile[t], B, targets)) return -1;
+        if (gather_tiles(c, B)) return -1;
+        CK(ctx_sync(c));
+        // image-level statistics: the samples of an image are the samples of its tiles
+        for (int i = 0; i < B; ++i) {
+            ErrStat e = c->tile[0]->h_es[i];
+            int bytes = c->tile[0]->h_pout[i].stream_bytes;
+            for (int t = 1; t < T; ++t) {
+                const ErrStat &x = c->tile[t]->h_es[i];
+                e.n_over += x.n_over; e.sum_err += x.sum_err;
+                if (x.max_err_bits > e.max_err_bits) e.max_err_bits = x.max_err_bits;
+                if (x.rmin_key < e.rmin_key) e.rmin_key = x.rmin_key;
+                if (x.rmax_key > e.rmax_key) e.rmax_key = x.rmax_key;
+                if (bytes) bytes += c->tile[t]->h_pout[i].stream_bytes - hl - 2;
+            }
+            c->h_es[i] = e;
+            c->h_pout[i].stream_bytes = bytes;
+        }
+    } else {
+        if (probe_launch(c, B, targets)) return -1;
+        CK(ctx_sync(c));
+    }
     for (int i = 0; i < B; ++i) {
         const ErrStat &e = c->h_es[i];
         res[i].n_over = e.n_over;
@@ -870,11 +1079,11 @@ __global__ void k_set_stat(FrameStat *stat, const float *mm, int n)
     if (i < n) { stat[i].minv = mm[2 * i]; stat[i].maxv = mm[2 * i + 1]; stat[i].flags = 0; }
 }
 
-extern "C" int ebcc_cuda_decode_batch(ebcc_cuda_ctx *c, const uint8_t *const *streams, const size_t *sizes, size_t nframes,
-                                      size_t H, size_t W, const float *minv, const float *maxv, const ebcc_residual_in *res,
-                                      float *const *outs)
+extern "C" int ebcc_cuda_decode_batch_tiled(ebcc_cuda_ctx *c, const uint8_t *const *streams, const size_t *sizes, size_t nframes,
+                                            size_t ntiles, size_t H, size_t W, const float *minv, const float *maxv,
+                                            const ebcc_residual_in *res, float *const *outs)
 {
-    if (ebcc_cuda_reserve(c, H, W, nframes)) return -1;
+    if (ebcc_cuda_reserve_tiled(c, ntiles, H, W, nframes)) return -1;
     int any_res = 0;
     for (size_t i = 0; res && i < nframes; ++i)
         if (res[i].zstd_size) {
@@ -884,8 +1093,8 @@ extern "C" int ebcc_cuda_decode_batch(ebcc_cuda_ctx *c, const uint8_t *const *st
             }
         }
     const Plan *pl = &c->plan;
-    const int B = (int)nframes;
-    const size_t N = H * W;
+    const int B = (int)nframes, T = c->ntiles;
+    const size_t N = (size_t)T * H * W;
     for (int i = 0; i < B; ++i) {
         if (sizes[i] > pl->out_stride) { fprintf(stderr, "[ebcc-cuda] codestream %d too large (%zu bytes)\n", i, sizes[i]); return -1; }
         memcpy(c->h_streams + (size_t)i * pl->out_stride, streams[i], sizes[i]);
@@ -900,10 +1109,25 @@ extern "C" int ebcc_cuda_decode_batch(ebcc_cuda_ctx *c, const uint8_t *const *st
     CK(cudaMemcpyAsync(c->d_slens, c->h_slens, sizeof(int) * B, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(c->d_es, mm, sizeof(float) * 2 * B, cudaMemcpyHostToDevice, c->stream));
     EBCC_LAUNCH(k_set_stat, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_stat, (const float *)c->d_es, B);
-    EBCC_LAUNCH(k_t2_parse, dim3((unsigned)B), dim3(32), (size_t)pl->nnodes * 4 * sizeof(int), c->stream,
-                c->d_plan, c->d_cblks, c->d_streams, pl->out_stride, c->d_slens, c->d_jobs, c->d_status);
-    c->launches += 2;
-    if (run_decode_stage(c, B, c->d_streams, pl->out_stride, NULL)) return -1;
+    c->launches++;
+    if (T == 1) {
+        EBCC_LAUNCH(k_t2_parse, dim3((unsigned)B), dim3(32), (size_t)pl->nnodes * 4 * sizeof(int), c->stream,
+                    c->d_plan, c->d_cblks, c->d_streams, pl->out_stride, c->d_slens, c->d_jobs, c->d_status);
+        c->launches++;
+        if (run_decode_stage(c, B, c->d_streams, pl->out_stride, NULL)) return -1;
+    } else {
+        // every tile context finds its own tile-part in the image's codestream and decodes it
+        for (int t = 0; t < T; ++t) {
+            ebcc_cuda_ctx *s = c->tile[t];
+            CK(cudaMemcpyAsync(s->d_stat, c->d_stat, sizeof(FrameStat) * B, cudaMemcpyDeviceToDevice, c->stream));
+            EBCC_LAUNCH(k_t2_parse, dim3((unsigned)B), dim3(32), (size_t)s->plan.nnodes * 4 * sizeof(int), c->stream,
+                        s->d_plan, s->d_cblks, c->d_streams, pl->out_stride, c->d_slens, s->d_jobs, s->d_status);
+            s->launches++;
+            if (run_decode_stage(s, B, c->d_streams, pl->out_stride, NULL)) return -1;
+            CK(cudaMemcpyAsync(s->h_status, s->d_status, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
+        }
+        if (gather_tiles(c, B)) return -1;
+    }
     if (any_res) {
         // residual layer: zstd frame -> SPIHT stream -> coefficient plane -> inverse transform -> add (src/ebcc_codec.c:1294-1312)
         const SpGeom g = c->sg;
@@ -936,17 +1160,29 @@ extern "C" int ebcc_cuda_decode_batch(ebcc_cuda_ctx *c, const uint8_t *const *st
         CK(cudaMemcpyAsync(c->h_zlen, c->d_zlen, 4 * B, cudaMemcpyDeviceToHost, c->stream));
         CK(cudaMemcpyAsync(c->h_maxlen, c->d_maxlen, 4 * B, cudaMemcpyDeviceToHost, c->stream));
     }
-    CK(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
+    if (T == 1) CK(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
     for (int i = 0; i < B; ++i)
         CK(cudaMemcpyAsync(outs[i], c->d_dec + (size_t)i * N, N * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
     CK(ctx_sync(c));
     int bad = 0;
+    for (int t = 0; T > 1 && t < T; ++t)
+        for (int i = 0; i < B; ++i) {
+            if (t == 0) c->h_status[i] = PARSE_OK;
+            if (c->tile[t]->h_status[i] != PARSE_OK) c->h_status[i] = c->tile[t]->h_status[i];
+        }
     for (int i = 0; i < B; ++i) if (c->h_status[i] != PARSE_OK) { fprintf(stderr, "[ebcc-cuda] malformed JPEG 2000 codestream in frame %d\n", i); bad = 1; }
     for (int i = 0; any_res && i < B; ++i)
         if (res[i].zstd_size && (c->h_zlen[i] == 0xffffffffu || c->h_maxlen[i] != 0)) {
             fprintf(stderr, "[ebcc-cuda] malformed residual layer (%s) in frame %d\n", c->h_zlen[i] == 0xffffffffu ? "zstd frame" : "SPIHT header", i); bad = 1;
         }
     return bad ? -2 : 0;
+}
+
+extern "C" int ebcc_cuda_decode_batch(ebcc_cuda_ctx *c, const uint8_t *const *streams, const size_t *sizes, size_t nframes,
+                                      size_t H, size_t W, const float *minv, const float *maxv, const ebcc_residual_in *res,
+                                      float *const *outs)
+{
+    return ebcc_cuda_decode_batch_tiled(c, streams, sizes, nframes, 1, H, W, minv, maxv, res, outs);
 }
 
 extern "C" int ebcc_cuda_download(ebcc_cuda_ctx *c, size_t nframes, const uint8_t **streams, size_t *sizes,

@@ -711,11 +711,19 @@ __global__ void k_t2_parse(const Plan *__restrict__ plan, const CblkDesc *__rest
         if (s[pos + 1] == 0x90) break;
         pos += 2 + ((s[pos + 2] << 8) | s[pos + 3]);
     }
-    if (pos + 14 > n) return;
-    const unsigned psot = ((unsigned)s[pos + 6] << 24) | ((unsigned)s[pos + 7] << 16) | ((unsigned)s[pos + 8] << 8) | s[pos + 9];
-    if (s[pos + 4] != 0 || s[pos + 5] != 0) return;             // single tile
-    int tp_end = psot ? pos + (int)psot : n - 2;
-    if (tp_end > n) return;
+    // tile-parts follow one another (SOT .. data, Psot bytes each); find the one of this plan's tile
+    int tp_end;
+    for (;;) {
+        if (pos + 14 > n || s[pos] != 0xff || s[pos + 1] != 0x90) return;
+        const unsigned psot = ((unsigned)s[pos + 6] << 24) | ((unsigned)s[pos + 7] << 16) | ((unsigned)s[pos + 8] << 8) | s[pos + 9];
+        const int isot = (s[pos + 4] << 8) | s[pos + 5];
+        tp_end = psot ? pos + (int)psot : n - 2;
+        if (psot != 0 && psot < 14) return;
+        if (tp_end > n || tp_end < pos) return;
+        if (isot == plan->tile_index) break;
+        if (!psot) return;
+        pos = tp_end;
+    }
     pos += 12;
     if (s[pos] != 0xff || s[pos + 1] != 0x93) return;
     pos += 2;

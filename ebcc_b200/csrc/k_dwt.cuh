@@ -74,6 +74,10 @@ __global__ void k_minmax_final(const float *__restrict__ in, FrameStat *stat, in
 #define DWT_K (1.230174105f)
 #define DWT_INVK ((float)(1.0 / 1.230174105))
 
+// The lifting helpers are written for an interleaved line with ne even-indexed and no odd-indexed samples
+// (parameters sn = ne, dn = no).  For a line whose origin has even parity (cas 0) the even samples are the low-pass
+// ones; for odd parity (cas 1, rows of a tile that starts at an odd canvas row of this resolution) they are the
+// high-pass ones and the four steps swap roles (opj_dwt_encode_1_real with a = 1, b = 0, dwt.c:1251-1300).
 // d[i] += (s[i] + s[i+1]) * c ; the last d of an even-length line mirrors: (2 * s[i]) * c
 __device__ __forceinline__ void lift_d(float *x, int es, int sn, int dn, float c, int i0, int istr)
 {
@@ -101,10 +105,10 @@ __device__ __forceinline__ void lift_s(float *x, int es, int sn, int dn, float c
     }
 }
 
-__device__ __forceinline__ void lift_scale(float *x, int es, int n, int i0, int istr)
+__device__ __forceinline__ void lift_scale(float *x, int es, int n, int i0, int istr, int cas = 0)
 {
     for (int i = i0; i < n; i += istr)
-        x[i * es] = __fmul_rn(x[i * es], (i & 1) ? DWT_K : DWT_INVK);
+        x[i * es] = __fmul_rn(x[i * es], ((i ^ cas) & 1) ? DWT_K : DWT_INVK);
 }
 
 // the raw sample as OpenJPEG sees it: u16 scaling (src/ebcc_codec.c:686-689) then DC shift (tcd.c:2469-2508)
@@ -119,7 +123,7 @@ __device__ __forceinline__ float scale_shift(float d, float mn, float range)
 // FIRST: source is the raw frame (scaled on the fly), else the coefficient buffer (in place).
 template <bool FIRST>
 __global__ void k_dwt_v(const float *__restrict__ in, float *coef, const FrameStat *__restrict__ stat,
-                        int W, int H, int rw, int rh, int sn)
+                        int W, int H, int rw, int rh, int sn, int cas)
 {
     EBCC_DYN_SMEM(float, x);
     const int CW = blockDim.x, c = threadIdx.x, ty = threadIdx.y, TY = blockDim.y;
@@ -138,21 +142,31 @@ __global__ void k_dwt_v(const float *__restrict__ in, float *coef, const FrameSt
     if (rh > 1) {
         const int dn = rh - sn;
         float *xc = x + c;
-        if (active) lift_d(xc, CW, sn, dn, DWT_ALPHA, ty, TY);
+        if (cas == 0) {
+            if (active) lift_d(xc, CW, sn, dn, DWT_ALPHA, ty, TY);
+            __syncthreads();
+            if (active) lift_s(xc, CW, sn, dn, DWT_BETA, ty, TY);
+            __syncthreads();
+            if (active) lift_d(xc, CW, sn, dn, DWT_GAMMA, ty, TY);
+            __syncthreads();
+            if (active) lift_s(xc, CW, sn, dn, DWT_DELTA, ty, TY);
+        } else {
+            if (active) lift_s(xc, CW, dn, sn, DWT_ALPHA, ty, TY);
+            __syncthreads();
+            if (active) lift_d(xc, CW, dn, sn, DWT_BETA, ty, TY);
+            __syncthreads();
+            if (active) lift_s(xc, CW, dn, sn, DWT_GAMMA, ty, TY);
+            __syncthreads();
+            if (active) lift_d(xc, CW, dn, sn, DWT_DELTA, ty, TY);
+        }
         __syncthreads();
-        if (active) lift_s(xc, CW, sn, dn, DWT_BETA, ty, TY);
-        __syncthreads();
-        if (active) lift_d(xc, CW, sn, dn, DWT_GAMMA, ty, TY);
-        __syncthreads();
-        if (active) lift_s(xc, CW, sn, dn, DWT_DELTA, ty, TY);
-        __syncthreads();
-        if (active) lift_scale(xc, CW, rh, ty, TY);
+        if (active) lift_scale(xc, CW, rh, ty, TY, cas);
         __syncthreads();
     }
     if (active) {
         if (rh > 1) {
             for (int i = ty; i < rh; i += TY) {
-                int dst = (i & 1) ? sn + (i >> 1) : (i >> 1);
+                int dst = ((i ^ cas) & 1) ? sn + (i >> 1) : (i >> 1);
                 coef[base + (size_t)dst * W + col] = x[i * CW + c];
             }
         } else if (FIRST) {

@@ -36,9 +36,9 @@ __global__ void k_dequant(const int *__restrict__ iplane, float *coef, const Pla
 }
 
 // x holds one interleaved line (element stride es): evens = low-pass, odds = high-pass
-__device__ __forceinline__ void ilift_scale(float *x, int es, int n, int i0, int istr)
+__device__ __forceinline__ void ilift_scale(float *x, int es, int n, int i0, int istr, int cas = 0)
 {
-    for (int i = i0; i < n; i += istr) x[i * es] = __fmul_rn(x[i * es], (i & 1) ? IDWT_TWO_INVK : DWT_K);
+    for (int i = i0; i < n; i += istr) x[i * es] = __fmul_rn(x[i * es], ((i ^ cas) & 1) ? IDWT_TWO_INVK : DWT_K);
 }
 // even[i] += (odd[i-1] + odd[i]) * c ; even[0] uses odd[0] twice ; trailing even of an odd-length line: (c+c) * odd[i-1]
 __device__ __forceinline__ void ilift_s(float *x, int es, int sn, int dn, float c, int i0, int istr)
@@ -90,8 +90,10 @@ __global__ void k_idwt_h(float *coef, int W, int H, int rw, int rh, int sn)
     if (active) for (int j = tx; j < rw; j += TX) g[j] = line[j];
 }
 
-// vertical synthesis of a strip of CW columns; block = (CW, TY); grid = (ceil(rw/CW), B)
-__global__ void k_idwt_v(float *coef, int W, int H, int rw, int rh, int sn)
+// vertical synthesis of a strip of CW columns; block = (CW, TY); grid = (ceil(rw/CW), B).  cas = row parity of the
+// resolution's canvas origin: with cas 1 the low-pass lines are the odd ones and the steps swap roles
+// (opj_v8dwt_decode with a = 1, b = 0, dwt.c:3353-3428; interleave dwt.c:3575-3600).
+__global__ void k_idwt_v(float *coef, int W, int H, int rw, int rh, int sn, int cas)
 {
     EBCC_DYN_SMEM(float, x);
     const int CW = blockDim.x, c = threadIdx.x, ty = threadIdx.y, TY = blockDim.y;
@@ -100,19 +102,29 @@ __global__ void k_idwt_v(float *coef, int W, int H, int rw, int rh, int sn)
     const size_t base = (size_t)frame * H * W;
     const int dn = rh - sn;
     if (active)
-        for (int i = ty; i < rh; i += TY) x[((i < sn) ? 2 * i : 2 * (i - sn) + 1) * CW + c] = coef[base + (size_t)i * W + col];
+        for (int i = ty; i < rh; i += TY) x[((i < sn) ? 2 * i + cas : 2 * (i - sn) + 1 - cas) * CW + c] = coef[base + (size_t)i * W + col];
     __syncthreads();
     float *xc = x + c;
-    if (dn > 0 || sn > 1) {
-        if (active) ilift_scale(xc, CW, rh, ty, TY);
+    if (cas == 0 ? (dn > 0 || sn > 1) : (sn > 0 || dn > 1)) {
+        if (active) ilift_scale(xc, CW, rh, ty, TY, cas);
         __syncthreads();
-        if (active) ilift_s(xc, CW, sn, dn, -DWT_DELTA, ty, TY);
-        __syncthreads();
-        if (active) ilift_d(xc, CW, sn, dn, -DWT_GAMMA, ty, TY);
-        __syncthreads();
-        if (active) ilift_s(xc, CW, sn, dn, -DWT_BETA, ty, TY);
-        __syncthreads();
-        if (active) ilift_d(xc, CW, sn, dn, -DWT_ALPHA, ty, TY);
+        if (cas == 0) {
+            if (active) ilift_s(xc, CW, sn, dn, -DWT_DELTA, ty, TY);
+            __syncthreads();
+            if (active) ilift_d(xc, CW, sn, dn, -DWT_GAMMA, ty, TY);
+            __syncthreads();
+            if (active) ilift_s(xc, CW, sn, dn, -DWT_BETA, ty, TY);
+            __syncthreads();
+            if (active) ilift_d(xc, CW, sn, dn, -DWT_ALPHA, ty, TY);
+        } else {
+            if (active) ilift_d(xc, CW, dn, sn, -DWT_DELTA, ty, TY);
+            __syncthreads();
+            if (active) ilift_s(xc, CW, dn, sn, -DWT_GAMMA, ty, TY);
+            __syncthreads();
+            if (active) ilift_d(xc, CW, dn, sn, -DWT_BETA, ty, TY);
+            __syncthreads();
+            if (active) ilift_s(xc, CW, dn, sn, -DWT_ALPHA, ty, TY);
+        }
         __syncthreads();
     }
     if (active) for (int i = ty; i < rh; i += TY) coef[base + (size_t)i * W + col] = x[i * CW + c];

@@ -379,7 +379,7 @@ k_pcrd_t2(const Plan *__restrict__ plan, const CblkDesc *__restrict__ cblks, Cbl
     if (tid == 0) {
         unsigned char *t = o + hl;
         unsigned psot = (unsigned)total + 14u;
-        t[0] = 0xff; t[1] = 0x90; t[2] = 0; t[3] = 10; t[4] = 0; t[5] = 0;
+        t[0] = 0xff; t[1] = 0x90; t[2] = 0; t[3] = 10; t[4] = (unsigned char)(plan->tile_index >> 8); t[5] = (unsigned char)plan->tile_index;
         t[6] = (unsigned char)(psot >> 24); t[7] = (unsigned char)(psot >> 16); t[8] = (unsigned char)(psot >> 8); t[9] = (unsigned char)psot;
         t[10] = 0; t[11] = 1; t[12] = 0xff; t[13] = 0x93;
         t[14 + total] = 0xff; t[15 + total] = 0xd9;

@@ -37,6 +37,12 @@ void ebcc_cuda_ctx_destroy(ebcc_cuda_ctx *ctx);
 /* size the work buffers for batches of up to nframes frames of height x width samples */
 int ebcc_cuda_reserve(ebcc_cuda_ctx *ctx, size_t height, size_t width, size_t nframes);
 
+/* multi-tile internal images (dims[0] > 1; j2k_encode_internal with n_tiles > 1, src/ebcc_codec.c:105-180): every
+ * frame of the batch is an image of ntiles tiles of height x width stacked vertically, (ntiles * height) x width
+ * samples; upload / analyze / rate_probe / residual_* / download then work on whole images, each tile being coded
+ * with the geometry of its canvas position.  ntiles == 1 is ebcc_cuda_reserve. */
+int ebcc_cuda_reserve_tiled(ebcc_cuda_ctx *ctx, size_t ntiles, size_t height, size_t width, size_t nframes);
+
 /* host -> device copy of nframes frames (float32, C-contiguous) into the context's input buffer */
 int ebcc_cuda_upload(ebcc_cuda_ctx *ctx, const float *frames, size_t nframes);
 
@@ -95,6 +101,11 @@ typedef struct {
 int ebcc_cuda_decode_batch(ebcc_cuda_ctx *ctx, const uint8_t *const *j2k, const size_t *j2k_sizes, size_t nframes,
                            size_t height, size_t width, const float *minv, const float *maxv,
                            const ebcc_residual_in *res, float *const *outs);
+
+/* the same for multi-tile codestreams: ntiles tiles of height x width per image, outs[i] holds ntiles * height * width floats */
+int ebcc_cuda_decode_batch_tiled(ebcc_cuda_ctx *ctx, const uint8_t *const *j2k, const size_t *j2k_sizes, size_t nframes,
+                                 size_t ntiles, size_t height, size_t width, const float *minv, const float *maxv,
+                                 const ebcc_residual_in *res, float *const *outs);
 
 /* profiling: when enabled, CUDA events bracket every stage on the context's stream */
 void ebcc_cuda_set_profiling(ebcc_cuda_ctx *ctx, int enabled);

@@ -149,6 +149,11 @@ static inline cudaError_t cudaHostAlloc(void **p, size_t n, unsigned) { *p = mal
 static inline cudaError_t cudaFreeHost(void *p) { free(p); return 0; }
 static inline cudaError_t cudaMemcpy(void *d, const void *s, size_t n, cudaMemcpyKind) { memmove(d, s, n); return 0; }
 static inline cudaError_t cudaMemcpyAsync(void *d, const void *s, size_t n, cudaMemcpyKind, cudaStream_t = 0) { memmove(d, s, n); return 0; }
+static inline cudaError_t cudaMemcpy2DAsync(void *d, size_t dp, const void *s, size_t sp, size_t w, size_t h, cudaMemcpyKind, cudaStream_t = 0)
+{
+    for (size_t r = 0; r < h; ++r) memmove((char *)d + r * dp, (const char *)s + r * sp, w);
+    return 0;
+}
 static inline cudaError_t cudaMemset(void *d, int v, size_t n) { memset(d, v, n); return 0; }
 static inline cudaError_t cudaMemsetAsync(void *d, int v, size_t n, cudaStream_t = 0) { memset(d, v, n); return 0; }
 static inline cudaError_t cudaStreamCreate(cudaStream_t *s) { *s = 0; return 0; }
