@@ -111,9 +111,9 @@ static int dims_are_valid(const size_t dims[NDIMS])
 /* ---- process-wide pool of device pipelines (context + stream each), created lazily and re-created after fork.
  * Every encode / decode call (and every worker of a multi-batch call) owns one pipeline while it runs, so callers on
  * several threads -- or several batches of one call -- are in flight on the device at the same time: the kernels of
- * one batch fill the issue slots the latency-bound tier-1 coder of another leaves idle.  EBCC_PIPELINES (1..8,
+ * one batch fill the issue slots the latency-bound tier-1 coder of another leaves idle.  EBCC_PIPELINES (1..16,
  * default 4) bounds how many. */
-#define EBCC_MAX_PIPELINES 8
+#define EBCC_MAX_PIPELINES 16
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
 static pthread_cond_t g_cv = PTHREAD_COND_INITIALIZER;
 static ebcc_cuda_ctx *g_pool[EBCC_MAX_PIPELINES];

@@ -1329,11 +1329,11 @@ extern "C" int ebcc_cuda_bench_resident(ebcc_cuda_ctx *c, size_t nframes, float 
 extern "C" int ebcc_cuda_bench_resident_pipelined(ebcc_cuda_ctx **ctxs, int nctx, size_t nframes, float base_cr, int steps, int warmup,
                                                   size_t flush_bytes, float *total_ms)
 {
-    if (!ctxs || nctx <= 0 || nctx > 8 || steps <= 0) return -1;
+    if (!ctxs || nctx <= 0 || nctx > 16 || steps <= 0) return -1;
     CK(cudaSetDevice(ctxs[0]->device));
-    void *flush[8] = {0};
+    void *flush[16] = {0};
     cudaStream_t ts;
-    cudaEvent_t e0, e1, done[8];
+    cudaEvent_t e0, e1, done[16];
     CK(cudaStreamCreateWithFlags(&ts, cudaStreamNonBlocking));
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     for (int k = 0; k < nctx; ++k) {
