@@ -740,11 +740,17 @@ size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, si
         counts[i] = 0;
         if (!parse_stream(streams[i], stream_sizes[i], &ps[i])) continue;
         if (ps[i].const_field) {
-            /* constant field: the stream carries one value and a count (reference :1265-1281, always mallocs) */
+            /* constant field: the stream carries one value and a count (reference :1265-1281) */
             float *o = (float *)malloc(ps[i].tot_size * sizeof(float));
             if (!o) { ps[i].ok = 0; continue; }
             for (size_t k = 0; k < ps[i].tot_size; ++k) o[k] = ps[i].minval;
-            outs[i] = o; counts[i] = ps[i].tot_size; done++;
+            if (outs[i]) {
+                /* caller-provided destination (host or device memory): written in place like every other frame */
+                const int rc = ebcc_cuda_copy_out(outs[i], o, ps[i].tot_size * sizeof(float));
+                free(o);
+                if (rc) { ps[i].ok = 0; continue; }
+            } else outs[i] = o;
+            counts[i] = ps[i].tot_size; done++;
         }
     }
     /* runs of frames with the same geometry, at most EBCC_BATCH_FRAMES each, become the jobs of the workers */
@@ -780,9 +786,14 @@ size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, si
 
 size_t ebcc_decode(uint8_t *data, size_t data_size, float **out_buffer)
 {
+    /* like the reference (src/ebcc_codec.c:1215-1320) the result is always a fresh malloc'ed buffer: whatever
+     * *out_buffer held on entry is ignored (callers pass uninitialised pointers) */
     size_t count = 0;
     uint8_t *s[1] = {data};
-    if (ebcc_decode_batch(s, &data_size, 1, out_buffer, &count) != 1) return 0;
+    float *o = NULL;
+    *out_buffer = NULL;
+    if (ebcc_decode_batch(s, &data_size, 1, &o, &count) != 1) return 0;
+    *out_buffer = o;
     return count;
 }
 

@@ -627,7 +627,9 @@ extern "C" int ebcc_cuda_upload(ebcc_cuda_ctx *c, const float *frames, size_t nf
     CK(cudaSetDevice(c->device));
     const size_t bytes = nframes * (size_t)c->plan.H * c->plan.W * sizeof(float);
     mark(c, EBCC_ST_H2D);
-    CK(cudaMemcpyAsync(c->d_in, frames, bytes, cudaMemcpyHostToDevice, c->stream));
+    // cudaMemcpyDefault: frames may be host memory (pinned or pageable) or a device buffer of any GPU of the process
+    // (unified virtual addressing), e.g. a tensor produced on the device -- then no H2D copy happens at all
+    CK(cudaMemcpyAsync(c->d_in, frames, bytes, cudaMemcpyDefault, c->stream));
     return 0;
 }
 
@@ -1162,7 +1164,7 @@ extern "C" int ebcc_cuda_decode_batch_tiled(ebcc_cuda_ctx *c, const uint8_t *con
     }
     if (T == 1) CK(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
     for (int i = 0; i < B; ++i)
-        CK(cudaMemcpyAsync(outs[i], c->d_dec + (size_t)i * N, N * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaMemcpyAsync(outs[i], c->d_dec + (size_t)i * N, N * sizeof(float), cudaMemcpyDefault, c->stream));   // host or device destination
     CK(ctx_sync(c));
     int bad = 0;
     for (int t = 0; T > 1 && t < T; ++t)
@@ -1229,6 +1231,13 @@ extern "C" int ebcc_cuda_j2k_encode_batch(ebcc_cuda_ctx *c, const float *frames,
     if (ebcc_cuda_upload(c, frames, nframes)) return -1;
     if (ebcc_cuda_j2k_encode_resident(c, nframes, base_cr)) return -1;
     return ebcc_cuda_download(c, nframes, streams, sizes, minv, maxv, flags);
+}
+
+// bytes from host memory to a caller-provided destination that may be host or device memory
+extern "C" int ebcc_cuda_copy_out(void *dst, const void *src, size_t bytes)
+{
+    CK(cudaMemcpy(dst, src, bytes, cudaMemcpyDefault));
+    return 0;
 }
 
 extern "C" void ebcc_cuda_set_profiling(ebcc_cuda_ctx *c, int enabled) { if (c) c->profiling = enabled; }

@@ -34,13 +34,24 @@ class EBCCZarrFilter(Codec):
         lib.ebcc_decode.restype = ctypes.c_size_t
         lib.ebcc_decode.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.POINTER(ctypes.POINTER(ctypes.c_float))]
         lib.free_buffer.argtypes = [ctypes.c_void_p]
+        lib.ebcc_decode_batch.restype = ctypes.c_size_t
+        lib.ebcc_decode_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
         self.lib = lib
 
     def encode(self, buf):
-        buf = np.ascontiguousarray(buf, dtype=np.float32).ravel()
         cfg, out = CodecConfigT(), ctypes.POINTER(ctypes.c_ubyte)()
-        self.lib.populate_config(ctypes.byref(cfg), len(self.arglist), self.arglist.ctypes.data, buf.nbytes)
-        n = self.lib.ebcc_encode(buf.ctypes.data, ctypes.byref(cfg), ctypes.byref(out))
+        cai = getattr(buf, "__cuda_array_interface__", None)
+        if cai is not None and cai["typestr"].endswith("f4") and cai.get("strides") is None:
+            # chunk already in GPU memory (torch / cupy): the C ABI takes the device pointer, no host round trip
+            addr, nbytes = int(cai["data"][0]), 4 * int(np.prod(cai["shape"]))
+            if hasattr(buf, "is_cuda"):
+                import torch
+                torch.cuda.current_stream(buf.device).synchronize()
+        else:
+            buf = np.ascontiguousarray(buf, dtype=np.float32).ravel()
+            addr, nbytes = buf.ctypes.data, buf.nbytes
+        self.lib.populate_config(ctypes.byref(cfg), len(self.arglist), self.arglist.ctypes.data, nbytes)
+        n = self.lib.ebcc_encode(ctypes.c_void_p(addr), ctypes.byref(cfg), ctypes.byref(out))
         if n == 0:
             raise RuntimeError("ebcc_encode failed")
         data = ctypes.string_at(out, n)
@@ -49,13 +60,21 @@ class EBCCZarrFilter(Codec):
 
     def decode(self, buf, out=None):
         buf = bytes(buf)
-        ptr = out.ctypes.data_as(ctypes.POINTER(ctypes.c_float)) if out is not None else ctypes.POINTER(ctypes.c_float)()
         src = (ctypes.c_ubyte * len(buf)).from_buffer_copy(buf)
+        if out is not None:
+            # in place: host numpy array or a device array (torch / cupy, __cuda_array_interface__)
+            cai = getattr(out, "__cuda_array_interface__", None)
+            addr = int(cai["data"][0]) if cai is not None else out.ctypes.data
+            srcs = (ctypes.c_void_p * 1)(ctypes.addressof(src))
+            lens, cnts = (ctypes.c_size_t * 1)(len(buf)), (ctypes.c_size_t * 1)()
+            outs = (ctypes.c_void_p * 1)(addr)
+            if self.lib.ebcc_decode_batch(srcs, lens, ctypes.c_size_t(1), outs, cnts) != 1:
+                raise RuntimeError("ebcc_decode failed")
+            return out
+        ptr = ctypes.POINTER(ctypes.c_float)()
         n = self.lib.ebcc_decode(src, len(buf), ctypes.byref(ptr))
         if n == 0:
             raise RuntimeError("ebcc_decode failed")
-        if out is not None:
-            return out
         arr = np.ctypeslib.as_array(ptr, shape=(n,)).copy()
         self.lib.free_buffer(ptr)
         return arr

@@ -60,7 +60,10 @@ EBCC_API void print_config(codec_config_t *config);
 EBCC_API void log_set_level_from_env(void);
 EBCC_API void populate_config(codec_config_t *config, size_t cd_nelmts, const unsigned int cd_values[], size_t buf_size);
 
-/* Batched entry points.  frames: nframes contiguous frames of prod(config->dims) floats each.
+/* Batched entry points.  frames: nframes contiguous frames of prod(config->dims) floats each; a host pointer or a
+ * CUDA device pointer (unified virtual addressing: frames produced on the GPU are compressed without a host round
+ * trip; the work producing them must have completed, the codec runs on its own streams).  The same holds for
+ * ebcc_encode's data and for caller-provided outs[i] of ebcc_decode_batch.
  * outs[i] receives a malloc'ed stream (free with free_buffer), sizes[i] its length (0 = failure).
  * Returns the number of frames encoded successfully. */
 EBCC_API size_t ebcc_encode_batch(const float *frames, size_t nframes, const codec_config_t *config,

@@ -107,6 +107,9 @@ int ebcc_cuda_decode_batch_tiled(ebcc_cuda_ctx *ctx, const uint8_t *const *j2k, 
                                  size_t ntiles, size_t height, size_t width, const float *minv, const float *maxv,
                                  const ebcc_residual_in *res, float *const *outs);
 
+/* copies bytes from host memory to dst, which may be host or device memory (caller-provided decode destinations) */
+int ebcc_cuda_copy_out(void *dst, const void *src, size_t bytes);
+
 /* profiling: when enabled, CUDA events bracket every stage on the context's stream */
 void ebcc_cuda_set_profiling(ebcc_cuda_ctx *ctx, int enabled);
 /* milliseconds spent in a stage during the last pass (valid after ebcc_cuda_sync) */
