@@ -265,18 +265,20 @@ def run_ours(args):
             lib.free_buffer(o[i])
         return tot
 
-    def e2e_thread(t, nsteps):
+    def e2e_thread(t, nsteps, gate):
         o, z = (C.POINTER(C.c_uint8) * FRAMES)(), (C.c_size_t * FRAMES)()
+        gate.wait()      # all callers start together (in the warm-up round this makes every one of them build its own pipeline)
         for k in range(t, nsteps, PIPES):
             d2h_box[0] = one_e2e(o, z)
 
     def e2e_round(nsteps):
-        th = [threading.Thread(target=e2e_thread, args=(t, nsteps)) for t in range(PIPES)]
+        gate = threading.Barrier(PIPES)
+        th = [threading.Thread(target=e2e_thread, args=(t, nsteps, gate)) for t in range(PIPES)]
         for t in th:
             t.start()
         for t in th:
             t.join()
-    e2e_round(max(args.warmup, PIPES))
+    e2e_round(max(args.warmup, 2 * PIPES))
     barrier(dist)
     t0 = time.perf_counter()
     e2e_round(args.steps)

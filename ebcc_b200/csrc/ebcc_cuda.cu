@@ -342,6 +342,7 @@ struct ebcc_cuda_ctx {
     // multi-tile images (dims[0] > 1, src/ebcc_codec.c:105-180): this context holds the image-level data (input,
     // min/max, decoded image, residual layer, assembled codestreams); tile t of every image of the batch is coded by
     // tile[t], a light context with the tile's own geometry that shares this context's stream and look-up tables
+    int crowd;                 // pipelines at work on this device (hint from the host codec), see mq_lanes()
     int ntiles;
     ebcc_cuda_ctx *tile[EBCC_MAX_TILES];
     ebcc_cuda_ctx *parent;
@@ -660,6 +661,30 @@ static int launch_dwt(ebcc_cuda_ctx *c, int B)
     return 0;
 }
 
+// Code-blocks per warp of the two serial tier-1 coders.  A warp that steps L blocks in lock step issues about 1/L of the
+// instructions but every block's chain gets longer (lanes diverge), so the best L depends on what else runs: alone on
+// the GPU a short chain wins (measured on B200, k_t1_mq alone: 1 frame L=1 5.0 ms / L=32 12.2 ms; 24 frames L=4 8.4 ms /
+// L=32 12.6 ms), with several pipelines in flight the issue slots are the scarce resource and L = 32 wins.
+// EBCC_MQ_LANES / EBCC_DEC_LANES override.
+static int ctx_crowd(const ebcc_cuda_ctx *c) { const ebcc_cuda_ctx *r = c->parent ? c->parent : c; return r->crowd > 0 ? r->crowd : 1; }
+static int mq_lanes(const ebcc_cuda_ctx *c, long long jobs)
+{
+    const char *el = getenv("EBCC_MQ_LANES");
+    if (el) { const int l = atoi(el); if (l == 1 || l == 2 || l == 4 || l == 8 || l == 16 || l == 32) return l; }
+    const int crowd = ctx_crowd(c);
+    if (crowd >= 3) return MQ_DEFAULT_LANES;
+    if (crowd == 2) return 8;
+    return jobs <= 1600 ? 1 : (jobs <= 3600 ? 2 : 4);
+}
+static int dec_lanes(const ebcc_cuda_ctx *c)
+{
+    const char *el = getenv("EBCC_DEC_LANES");
+    if (el) { const int l = atoi(el); if (l == 1 || l == 2 || l == 4 || l == 8) return l; }
+    return ctx_crowd(c) >= 3 ? DEC_DEFAULT_LANES : 1;
+}
+
+extern "C" void ebcc_cuda_set_crowd(ebcc_cuda_ctx *c, int pipelines_at_work) { if (c) c->crowd = pipelines_at_work; }
+
 static int launch_minmax(ebcc_cuda_ctx *c, int B)
 {
     const int N = c->plan.H * c->plan.W;
@@ -726,9 +751,8 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax)
     mark(c, EBCC_ST_T1_MQ);
     {
         const long long jobs = (long long)pl->ncblks * B;
-        const char *el = getenv("EBCC_MQ_LANES");                // code-blocks per warp: 1, 2, 4, 8, 16 or 32
-        int lanes = el ? atoi(el) : MQ_DEFAULT_LANES;
-        if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8 && lanes != 16 && lanes != 32) lanes = MQ_DEFAULT_LANES;
+        const int lanes = mq_lanes(c, jobs);                     // code-blocks per warp: 1, 2, 4, 8, 16 or 32
+        if (getenv("EBCC_DEBUG_LANES")) fprintf(stderr, "[ebcc-cuda] mq lanes %d (crowd %d, jobs %lld)\n", lanes, ctx_crowd(c), jobs);
         const long long per_cta = (long long)MQ_WARPS(lanes) * lanes;
         const dim3 grid((unsigned)((jobs + per_cta - 1) / per_cta)), block(MQ_THREADS(lanes));
 #define MQ_GO(LL) EBCC_LAUNCH(k_t1_mq<LL>, grid, block, 0, c->stream, c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, \
@@ -802,9 +826,7 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
     const long long njobs = (long long)pl->ncblks * B;
     const bool probe = orig != NULL;         // probe of the CR search: jobs come from the encoder, the recording is used
     {
-        const char *el = getenv("EBCC_DEC_LANES");              // code-blocks per warp of the tier-1 decoder: 1, 2, 4 or 8
-        int lanes = el ? atoi(el) : DEC_DEFAULT_LANES;
-        if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8) lanes = DEC_DEFAULT_LANES;
+        const int lanes = dec_lanes(c);                         // code-blocks per warp of the tier-1 decoder: 1, 2, 4 or 8
         const long long per_cta = (long long)DEC_WPC(lanes) * lanes;
         const dim3 grid((unsigned)((njobs + per_cta - 1) / per_cta)), block((unsigned)(DEC_WPC(lanes) * 32));
 #define DEC_GO(LL) EBCC_LAUNCH(k_t1_dec<LL>, grid, block, 0, c->stream, c->d_cblks, c->d_order, c->d_jobs, pool, pool_stride, c->d_declut, \
@@ -1340,6 +1362,7 @@ extern "C" int ebcc_cuda_bench_resident_pipelined(ebcc_cuda_ctx **ctxs, int nctx
 {
     if (!ctxs || nctx <= 0 || nctx > 16 || steps <= 0) return -1;
     CK(cudaSetDevice(ctxs[0]->device));
+    for (int k = 0; k < nctx; ++k) ctxs[k]->crowd = nctx;
     void *flush[16] = {0};
     cudaStream_t ts;
     cudaEvent_t e0, e1, done[16];

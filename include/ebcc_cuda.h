@@ -107,6 +107,11 @@ int ebcc_cuda_decode_batch_tiled(ebcc_cuda_ctx *ctx, const uint8_t *const *j2k, 
                                  size_t ntiles, size_t height, size_t width, const float *minv, const float *maxv,
                                  const ebcc_residual_in *res, float *const *outs);
 
+/* hint from the host codec: how many pipelines (contexts) are at work on this device right now.  The serial tier-1
+ * coders step more code-blocks per warp when the device is shared (fewer instructions) and fewer when a call has the
+ * GPU to itself (shorter chains); results do not depend on it. */
+void ebcc_cuda_set_crowd(ebcc_cuda_ctx *ctx, int pipelines_at_work);
+
 /* copies bytes from host memory to dst, which may be host or device memory (caller-provided decode destinations) */
 int ebcc_cuda_copy_out(void *dst, const void *src, size_t bytes);
 
