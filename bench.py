@@ -371,8 +371,8 @@ def run_ours(args):
            "dwt": FRAMES * NSAMP * 4 * (1 + 2 * (4 / 3)), "pcrd_t2": out_bytes}[dom]
     achieved = alg / (stage[dom] * 1e-3) / 1e9
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture of this workload
-    # (profiles/r01_ncu_t1_enc_summary.md)
-    traffic = {"t1_mq": 347.6e6, "t1_cm": 348.4e6}.get(dom)
+    # (profiles/r01b_ncu_t1_enc_summary.md: the single-stream step the roofline kernel is timed in runs k_t1_mq<4>)
+    traffic = {"t1_mq": 346.6e6, "t1_cm": 349.6e6}.get(dom)
     line = {
         "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
