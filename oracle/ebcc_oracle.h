@@ -56,6 +56,8 @@ typedef struct {
 
 typedef struct {
     int w, h;
+    int y0;                  /* canvas row of the tile's first line (tile t of a multi-tile image: t * h) */
+    int cas_v[ORC_NRES];     /* row parity of each resolution's canvas origin (dwt.c:1986-1987) */
     int nbands, ncblks;
     int res_w[ORC_NRES], res_h[ORC_NRES];
     orc_band_t bands[3 * ORC_NRES - 2];
@@ -69,14 +71,21 @@ void orc_scale_u16(const float *d, size_t n, float mn, float mx, uint16_t *out);
 
 /* --- JPEG 2000 encoder as EBCC configures OpenJPEG --- */
 orc_tile_t *orc_tile_create(int h, int w);
+/* tile of h x w lines whose first line is canvas row y0 (tcd.c:961-1264 with a non-zero tile origin) */
+orc_tile_t *orc_tile_create_at(int h, int w, int y0);
 void orc_tile_destroy(orc_tile_t *t);
 void orc_dwt97_forward(orc_tile_t *t, const uint16_t *img);   /* DC shift + 5-level 9/7 */
 void orc_t1_encode_all(orc_tile_t *t);                         /* quantise + EBCOT tier-1 */
 double orc_rate_allocate(orc_tile_t *t, float base_cr, int main_header_bytes); /* PCRD; returns threshold */
+double orc_rate_allocate_tiled(orc_tile_t *t, float base_cr, int main_header_bytes, int ntiles);
 size_t orc_t2_encode(orc_tile_t *t, uint8_t *dst, size_t cap, int dry_run);
 size_t orc_main_header(int h, int w, uint8_t *dst);
 /* whole J2K encode: returns malloc'ed codestream */
 size_t orc_j2k_encode(const uint16_t *img, int h, int w, float base_cr, uint8_t **out);
+/* multi-tile image (j2k_encode_internal with n_tiles > 1, src/ebcc_codec.c:105-180): ntiles tiles of h x w stacked
+ * vertically, img holds ntiles * h * w samples; main header | one tile-part per tile | EOC */
+size_t orc_main_header_tiled(int himg, int h, int w, uint8_t *dst);
+size_t orc_j2k_encode_tiled(const uint16_t *img, int ntiles, int h, int w, float base_cr, uint8_t **out);
 
 /* test helpers */
 void orc_get_luts(uint8_t *zc /*2048*/, uint8_t *sc /*256*/, uint8_t *spb /*256*/,

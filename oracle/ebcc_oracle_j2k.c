@@ -60,15 +60,20 @@ static double getnorm97(int level, int orient)
     return norms97[orient][level];
 }
 
-/* tcd.c:961-1264 for a single tile anchored at the canvas origin */
-orc_tile_t *orc_tile_create(int h, int w)
+orc_tile_t *orc_tile_create(int h, int w) { return orc_tile_create_at(h, w, 0); }
+
+/* tcd.c:961-1264 for one tile whose first line is canvas row y0 (x origin 0): resolution and band rectangles are
+ * ceil-divisions of the canvas coordinates y0 and y0 + h (tcd.c:961-1055); the code-block grid is anchored at
+ * multiples of 64 of the band's canvas rows (tcd.c:1122-1230), so the first block row of a band may be partial */
+orc_tile_t *orc_tile_create_at(int h, int w, int y0)
 {
     orc_tile_t *t = (orc_tile_t *)calloc(1, sizeof(*t));
-    t->w = w; t->h = h;
+    t->w = w; t->h = h; t->y0 = y0;
     for (int r = 0; r < ORC_NRES; ++r) {
         int lvl = ORC_NRES - 1 - r;
         t->res_w[r] = ceildivpow2(w, lvl);
-        t->res_h[r] = ceildivpow2(h, lvl);
+        t->res_h[r] = ceildivpow2(y0 + h, lvl) - ceildivpow2(y0, lvl);
+        t->cas_v[r] = ceildivpow2(y0, lvl) & 1;
     }
     int nb = 0, ncb = 0;
     for (int r = 0; r < ORC_NRES; ++r) {
@@ -79,14 +84,14 @@ orc_tile_t *orc_tile_create(int h, int w)
             int orient = r == 0 ? 0 : bi + 1;
             b->resno = r; b->orient = orient; b->level = lvl;
             if (r == 0) {
-                b->x0 = 0; b->y0 = 0;
-                b->x1 = ceildivpow2(w, lvl); b->y1 = ceildivpow2(h, lvl);
+                b->x0 = 0; b->y0 = ceildivpow2(y0, lvl);
+                b->x1 = ceildivpow2(w, lvl); b->y1 = ceildivpow2(y0 + h, lvl);
                 b->offx = 0; b->offy = 0;
             } else {
                 int x0b = orient & 1, y0b = orient >> 1;
-                b->x0 = 0; b->y0 = 0;
+                b->x0 = 0; b->y0 = ceildivpow2(y0 - (y0b << lvl), lvl + 1);
                 b->x1 = ceildivpow2(w - (x0b << lvl), lvl + 1);
-                b->y1 = ceildivpow2(h - (y0b << lvl), lvl + 1);
+                b->y1 = ceildivpow2(y0 + h - (y0b << lvl), lvl + 1);
                 b->offx = x0b ? t->res_w[r - 1] : 0;
                 b->offy = y0b ? t->res_h[r - 1] : 0;
             }
@@ -108,7 +113,7 @@ orc_tile_t *orc_tile_create(int h, int w)
             }
             int bw = b->x1 - b->x0, bh = b->y1 - b->y0;
             b->cw = bw > 0 && bh > 0 ? (bw + 63) / 64 : 0;
-            b->ch = bw > 0 && bh > 0 ? (bh + 63) / 64 : 0;
+            b->ch = bw > 0 && bh > 0 ? (b->y1 + 63) / 64 - b->y0 / 64 : 0;
             b->first_cblk = ncb;
             ncb += b->cw * b->ch;
             nb++;
@@ -122,10 +127,10 @@ orc_tile_t *orc_tile_create(int h, int w)
             for (int cx = 0; cx < b->cw; ++cx) {
                 orc_cblk_t *c = &t->cblks[b->first_cblk + cy * b->cw + cx];
                 c->band = bi;
-                c->x0 = cx * 64; c->y0 = cy * 64;
-                c->x1 = imin(c->x0 + 64, b->x1); c->y1 = imin(c->y0 + 64, b->y1);
+                c->x0 = cx * 64; c->y0 = imax((b->y0 / 64 + cy) * 64, b->y0);
+                c->x1 = imin(c->x0 + 64, b->x1); c->y1 = imin((b->y0 / 64 + cy + 1) * 64, b->y1);
                 c->w = c->x1 - c->x0; c->h = c->y1 - c->y0;
-                c->tx = b->offx + c->x0; c->ty = b->offy + c->y0;
+                c->tx = b->offx + c->x0; c->ty = b->offy + (c->y0 - b->y0);
                 c->data = (uint8_t *)calloc((size_t)(74 + c->w * c->h * 4), 1);
             }
     }
@@ -180,6 +185,23 @@ static void fwd97_line(float *x, int n)
     for (int i = 0; i < dn; ++i) x[2 * i + 1] *= kK;
 }
 
+/* the same line when its first sample has odd parity on the canvas (cas = 1; opj_dwt_encode_1_real with a = 1, b = 0,
+ * dwt.c:1251-1300, and opj_dwt_encode_and_deinterleave_v_real :1860-1924): the even-indexed samples are the dn
+ * high-pass ones, the odd-indexed the sn low-pass ones, and the lifting steps swap shapes.  lift_d / lift_s are
+ * "update the odd samples from their even neighbours" / "update the even samples from their odd neighbours" for a line
+ * with (first argument) even-indexed and (second argument) odd-indexed samples. */
+static void fwd97_line_odd(float *x, int n, int sn)
+{
+    if (n == 1) return;
+    int dn = n - sn;
+    lift_s(x, dn, sn, kAlpha);
+    lift_d(x, dn, sn, kBeta);
+    lift_s(x, dn, sn, kGamma);
+    lift_d(x, dn, sn, kDelta);
+    for (int i = 0; i < dn; ++i) x[2 * i] *= kK;
+    for (int i = 0; i < sn; ++i) x[2 * i + 1] *= kInvK;
+}
+
 void orc_dwt97_forward(orc_tile_t *t, const uint16_t *img)
 {
     const int w = t->w, h = t->h;
@@ -194,10 +216,11 @@ void orc_dwt97_forward(orc_tile_t *t, const uint16_t *img)
         sn = t->res_h[r - 1];
         if (rh > 1)
             for (int x = 0; x < rw; ++x) {
+                const int cas = t->cas_v[r];
                 for (int y = 0; y < rh; ++y) line[y] = a[(size_t)y * w + x];
-                fwd97_line(line, rh);
-                for (int i = 0; i < sn; ++i) a[(size_t)i * w + x] = line[2 * i];
-                for (int i = 0; i < rh - sn; ++i) a[(size_t)(sn + i) * w + x] = line[2 * i + 1];
+                if (cas == 0) fwd97_line(line, rh); else fwd97_line_odd(line, rh, sn);
+                for (int i = 0; i < sn; ++i) a[(size_t)i * w + x] = line[2 * i + cas];
+                for (int i = 0; i < rh - sn; ++i) a[(size_t)(sn + i) * w + x] = line[2 * i + 1 - cas];
             }
         /* then horizontal */
         sn = t->res_w[r - 1];
@@ -751,17 +774,24 @@ static int makelayer(orc_tile_t *t, double thresh)
 }
 
 /* per-tile byte budget exactly as opj_j2k_update_rates computes it in f32 */
-static float tile_budget(int h, int w, float base_cr, int main_header_bytes)
+static float tile_budget(int h, int w, float base_cr, int main_header_bytes, int ntiles)
 {
     float rate = base_cr / 2;                       /* src/ebcc_codec.c:116 */
     if (rate <= 1.0) return 0.0f;                   /* j2k.c:8159-8162 force lossless */
     float r = (float)(((double)16 * (uint32_t)w * (uint32_t)h) / (rate * (float)8)) - 0.0f;
-    r -= (float)main_header_bytes / (float)1;
+    r -= (float)main_header_bytes / (float)(uint32_t)ntiles;   /* l_sot_remove = stream position / (th * tw), j2k.c:5351 */
     if (r < 30.0f) r = 30.0f;
     return r;
 }
 
 double orc_rate_allocate(orc_tile_t *t, float base_cr, int main_header_bytes)
+{
+    return orc_rate_allocate_tiled(t, base_cr, main_header_bytes, 1);
+}
+
+/* opj_tcd_rateallocate runs per tile; opj_j2k_update_rates gives every tile the budget of its own area minus its
+ * share of the main header (j2k.c:5361-5408) */
+double orc_rate_allocate_tiled(orc_tile_t *t, float base_cr, int main_header_bytes, int ntiles)
 {
     double min = DBL_MAX, max = 0;
     for (int i = 0; i < t->ncblks; ++i) {
@@ -777,7 +807,7 @@ double orc_rate_allocate(orc_tile_t *t, float base_cr, int main_header_bytes)
             if (s > max) max = s;
         }
     }
-    float rates0 = tile_budget(t->h, t->w, base_cr, main_header_bytes);
+    float rates0 = tile_budget(t->h, t->w, base_cr, main_header_bytes, ntiles);
     /* tile buffer: j2k.c:5439-5470 (1.4*bits/8 + 500 + specific headers), minus SOT(12), SOD(2)+EOC room(2) */
     uint64_t tile_size = (uint64_t)((double)((uint64_t)t->w * t->h * 16) * 1.4 / 8) + 500;
     uint32_t len = (uint32_t)tile_size - 12 - 4;
@@ -810,13 +840,16 @@ double orc_rate_allocate(orc_tile_t *t, float base_cr, int main_header_bytes)
 static uint8_t *put16(uint8_t *p, uint32_t v) { p[0] = (uint8_t)(v >> 8); p[1] = (uint8_t)v; return p + 2; }
 static uint8_t *put32(uint8_t *p, uint32_t v) { p = put16(p, v >> 16); return put16(p, v & 0xffff); }
 
-size_t orc_main_header(int h, int w, uint8_t *dst)
+size_t orc_main_header(int h, int w, uint8_t *dst) { return orc_main_header_tiled(h, h, w, dst); }
+
+/* SIZ carries the image size (Xsiz, Ysiz) and the tile size (XTsiz, YTsiz); everything else is the single-tile header */
+size_t orc_main_header_tiled(int himg, int h, int w, uint8_t *dst)
 {
     uint8_t *p = dst;
     orc_tile_t *t = orc_tile_create(h, w);
     p = put16(p, 0xFF4F);
     p = put16(p, 0xFF51); p = put16(p, 41); p = put16(p, 0);
-    p = put32(p, (uint32_t)w); p = put32(p, (uint32_t)h); p = put32(p, 0); p = put32(p, 0);
+    p = put32(p, (uint32_t)w); p = put32(p, (uint32_t)himg); p = put32(p, 0); p = put32(p, 0);
     p = put32(p, (uint32_t)w); p = put32(p, (uint32_t)h); p = put32(p, 0); p = put32(p, 0);
     p = put16(p, 1); *p++ = 15; *p++ = 1; *p++ = 1;
     p = put16(p, 0xFF52); p = put16(p, 12); *p++ = 0; *p++ = 0; p = put16(p, 1); *p++ = 0;
@@ -849,4 +882,32 @@ size_t orc_j2k_encode(const uint16_t *img, int h, int w, float base_cr, uint8_t 
     *out = buf;
     orc_tile_destroy(t);
     return hdr + 14 + body + 2;
+}
+
+/* opj_write_tile per tile then opj_end_compress (src/ebcc_codec.c:166-176): each tile-part is SOT (Isot = tile index,
+ * Psot, TPsot 0, TNsot 1) SOD packets, coded with the geometry of the tile's canvas position and its own byte budget */
+size_t orc_j2k_encode_tiled(const uint16_t *img, int ntiles, int h, int w, float base_cr, uint8_t **out)
+{
+    if (ntiles <= 1) return orc_j2k_encode(img, h, w, base_cr, out);
+    const size_t tile_cap = (size_t)((double)((uint64_t)w * h * 16) * 1.4 / 8) + 1024;
+    uint8_t *buf = (uint8_t *)malloc(256 + tile_cap * (size_t)ntiles);
+    size_t pos = orc_main_header_tiled(ntiles * h, h, w, buf);
+    const int hdr = (int)pos;
+    for (int ti = 0; ti < ntiles; ++ti) {
+        orc_tile_t *t = orc_tile_create_at(h, w, ti * h);
+        orc_dwt97_forward(t, img + (size_t)ti * h * w);
+        orc_t1_encode_all(t);
+        orc_rate_allocate_tiled(t, base_cr, hdr, ntiles);
+        uint8_t *sot = buf + pos;
+        put16(sot, 0xFF90); put16(sot + 2, 10); put16(sot + 4, (uint32_t)ti); sot[10] = 0; sot[11] = 1;
+        put16(sot + 12, 0xFF93);
+        size_t body = orc_t2_encode(t, sot + 14, tile_cap - 14 - 2, 0);
+        if (body == (size_t)-1) body = 0;
+        put32(sot + 6, (uint32_t)(body + 14));
+        pos += 14 + body;
+        orc_tile_destroy(t);
+    }
+    put16(buf + pos, 0xFFD9);
+    *out = buf;
+    return pos + 2;
 }

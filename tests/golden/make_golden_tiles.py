@@ -46,6 +46,8 @@ def main():
         d = H.decode(lib, s)
         out[name + "_sha"] = np.frombuffer(hashlib.sha256(s).digest(), dtype=np.uint8)
         out[name + "_len"] = np.array([len(s)])
+        zsz = int.from_bytes(s[32:40], "little")                       # ebcc_header_t.compressed_size
+        out[name + "_j2k_sha"] = np.frombuffer(hashlib.sha256(s[48 + zsz:]).digest(), dtype=np.uint8)
         out[name + "_in_sha"] = np.frombuffer(hashlib.sha256(f.tobytes()).digest(), dtype=np.uint8)
         out[name + "_dec_sha"] = np.frombuffer(hashlib.sha256(d.tobytes()).digest(), dtype=np.uint8)
         out[name + "_maxerr"] = np.array([np.abs(d - f.ravel()).max()], dtype=np.float64)

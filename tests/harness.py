@@ -76,6 +76,8 @@ def orc_lib():
         lib = C.CDLL(ORC_SO)
         lib.orc_j2k_encode.restype = C.c_size_t
         lib.orc_j2k_encode.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.POINTER(C.POINTER(C.c_uint8))]
+        lib.orc_j2k_encode_tiled.restype = C.c_size_t
+        lib.orc_j2k_encode_tiled.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.POINTER(C.POINTER(C.c_uint8))]
         lib.orc_scale_u16.argtypes = [C.c_void_p, C.c_size_t, C.c_float, C.c_float, C.c_void_p]
         lib.orc_minmax.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         _cache["orc"] = lib
@@ -113,6 +115,19 @@ def orc_j2k_encode(u16, base_cr):
     h, w = u16.shape
     out = C.POINTER(C.c_uint8)()
     n = lib.orc_j2k_encode(u16.ctypes.data, h, w, C.c_float(base_cr), C.byref(out))
+    res = C.string_at(out, n)
+    _libc.free(out)
+    return res
+
+
+def orc_j2k_encode_tiled(u16, ntiles, base_cr):
+    """oracle restatement of a multi-tile image: u16 is (ntiles * h, w), tiles of h lines stacked vertically"""
+    lib = orc_lib()
+    u16 = np.ascontiguousarray(u16, dtype=np.uint16)
+    hh, w = u16.shape
+    assert hh % ntiles == 0
+    out = C.POINTER(C.c_uint8)()
+    n = lib.orc_j2k_encode_tiled(u16.ctypes.data, ntiles, hh // ntiles, w, C.c_float(base_cr), C.byref(out))
     res = C.string_at(out, n)
     _libc.free(out)
     return res

@@ -42,6 +42,7 @@ def test_none_streams_equal_golden(built, case):
     assert np.array_equal(sha(s), g[name + "_sha"])          # whole EBCC stream, byte for byte
     if name + "_stream" in g:
         assert s == g[name + "_stream"].tobytes()
+    assert s[48:] == H.orc_j2k_encode_tiled(H.scale_u16(f), t, cr)      # and the oracle restatement agrees
 
 
 @pytest.mark.parametrize("case", CASES, ids=lambda c: c[0])
