@@ -160,3 +160,38 @@ def test_reference_chunking_cases(built, shape, chunk):
         assert np.array_equal(dref.view(np.uint32), dec.view(np.uint32))
         assert np.array_equal(H.decode(lib, want, fn="ebcc_decode_chunking").view(np.uint32),
                               H.decode(H.ref_lib(), want, fn="ebcc_decode_chunking").view(np.uint32))
+
+
+def test_malformed_multi_tile_streams_fail_cleanly(built):
+    """the tile-part walk of the parser (Psot chain, Isot match) runs on untrusted bytes: every corruption must end in a
+    clean failure (ebcc_decode returns 0), never in a crash or a silently wrong image"""
+    lib = H.prod_lib()
+    f = H.synth_stack(1, 3 * 32, 48)[0]
+    s = H.encode(lib, f, (3, 32, 48), 6.0, H.NONE)
+    good = H.decode(lib, s)
+    assert good is not None and good.size == 3 * 32 * 48
+    j = 48                                   # start of the codestream inside the EBCC stream
+    sot0 = s.index(b"\xff\x90", j)           # first SOT: marker(2) Lsot(2) Isot(2) Psot(4) TPsot TNsot
+    assert s[sot0 + 4:sot0 + 6] == b"\x00\x00"
+    psot0 = int.from_bytes(s[sot0 + 6:sot0 + 10], "big")
+    sot1 = sot0 + psot0
+    assert s[sot1:sot1 + 2] == b"\xff\x90" and s[sot1 + 4:sot1 + 6] == b"\x00\x01"
+
+    def patched(off, val):
+        b = bytearray(s); b[off:off + len(val)] = val; return bytes(b)
+
+    cases = {
+        "Psot of tile 0 runs past the end": patched(sot0 + 6, (0x7fffff00).to_bytes(4, "big")),
+        "Psot of tile 0 shorter than a tile-part header": patched(sot0 + 6, (5).to_bytes(4, "big")),
+        "Psot of tile 0 is zero although tiles follow": patched(sot0 + 6, (0).to_bytes(4, "big")),
+        "Psot of tile 0 points into the middle of its packets": patched(sot0 + 6, (psot0 - 3).to_bytes(4, "big")),
+        "tile 1 carries a wrong Isot": patched(sot1 + 4, b"\x00\x07"),
+        "tile 0 appears twice, tile 1 never": patched(sot1 + 4, b"\x00\x00"),
+        "image height is not a multiple of the tile height": patched(j + 12, (3 * 32 + 1).to_bytes(4, "big")),
+        "tile height of zero": patched(j + 28, (0).to_bytes(4, "big")),
+        "tile offset not at the origin": patched(j + 36, (1).to_bytes(4, "big")),
+    }
+    for what, bad in cases.items():
+        assert H.decode(lib, bad) is None, what
+    # the library is still usable afterwards and the good stream still decodes to the same frame
+    assert np.array_equal(H.decode(lib, s), good)
