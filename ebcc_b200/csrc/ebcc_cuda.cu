@@ -689,7 +689,8 @@ static int launch_minmax(ebcc_cuda_ctx *c, int B)
 {
     const int N = c->plan.H * c->plan.W;
     EBCC_LAUNCH(k_stat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_stat, B);
-    EBCC_LAUNCH(k_minmax, dim3(74, (unsigned)B), dim3(256), 0, c->stream, c->d_in, c->d_stat, N);
+    // enough CTAs to keep every SM loading: 74 per frame for a batch, 296 for a handful of frames
+    EBCC_LAUNCH(k_minmax, dim3(B >= 8 ? 74u : 296u, (unsigned)B), dim3(256), 0, c->stream, c->d_in, c->d_stat, N);
     EBCC_LAUNCH(k_minmax_final, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_in, c->d_stat, N, B);
     c->launches += 3;
     return 0;

@@ -20,27 +20,50 @@ __device__ __forceinline__ unsigned f32_order_key(float f)
 }
 
 // findMinMaxf semantics: the FIRST element attaining the extremum wins (matters only for +-0).
-// key_min = (order << 32) | idx  -> atomicMin ; key_max = (order << 32) | ~idx -> atomicMax
-__global__ void k_minmax(const float *__restrict__ in, FrameStat *stat, int n)
+// A thread walks its elements in ascending index order and replaces its candidate only on a strict improvement of the
+// 32-bit order key, so it keeps the first occurrence; threads are merged with 64-bit keys
+// key_min = (order << 32) | idx  -> atomicMin ; key_max = (order << 32) | ~idx -> atomicMax.
+// 16-byte loads when the frame is 16-byte aligned (HBM-bound: 4N bytes read, nothing written).
+struct MinMaxAcc { unsigned kmin, kmax, imin, imax; int bad; };
+__device__ __forceinline__ void minmax_take(MinMaxAcc &a, float v, unsigned i)
+{
+    const unsigned b = __float_as_uint(v);
+    if ((b & 0x7f800000u) == 0x7f800000u) a.bad = 1;
+    const unsigned k = f32_order_key(v);
+    if (k < a.kmin) { a.kmin = k; a.imin = i; }
+    if (k > a.kmax) { a.kmax = k; a.imax = i; }
+}
+
+__global__ void __launch_bounds__(256) k_minmax(const float *__restrict__ in, FrameStat *stat, int n)
 {
     const int frame = blockIdx.y;
     const float *p = in + (size_t)frame * n;
-    unsigned long long kmin = ~0ull, kmax = 0ull;
-    int bad = 0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        float v = p[i];
-        unsigned b = __float_as_uint(v);
-        if ((b & 0x7f800000u) == 0x7f800000u) bad = 1;
-        unsigned long long k = (unsigned long long)f32_order_key(v) << 32;
-        unsigned long long k0 = k | (unsigned)i, k1 = k | (unsigned)(~(unsigned)i);
-        kmin = k0 < kmin ? k0 : kmin;
-        kmax = k1 > kmax ? k1 : kmax;
+    // "no element yet": the keys below are neutral for atomicMin / atomicMax once widened
+    MinMaxAcc a; a.kmin = 0xffffffffu; a.imin = 0xffffffffu; a.kmax = 0u; a.imax = 0xffffffffu; a.bad = 0;
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    const int n4 = (((size_t)p & 15) == 0) ? n >> 2 : 0;
+    const float4 *p4 = (const float4 *)p;
+    int j = gtid;
+    for (; j + stride < n4; j += 2 * stride) {          // two independent 16-byte loads in flight per thread
+        const float4 u = p4[j], v = p4[j + stride];
+        const unsigned i0 = 4u * (unsigned)j, i1 = 4u * (unsigned)(j + stride);
+        minmax_take(a, u.x, i0); minmax_take(a, u.y, i0 + 1); minmax_take(a, u.z, i0 + 2); minmax_take(a, u.w, i0 + 3);
+        minmax_take(a, v.x, i1); minmax_take(a, v.y, i1 + 1); minmax_take(a, v.z, i1 + 2); minmax_take(a, v.w, i1 + 3);
     }
+    if (j < n4) {
+        const float4 u = p4[j];
+        const unsigned i0 = 4u * (unsigned)j;
+        minmax_take(a, u.x, i0); minmax_take(a, u.y, i0 + 1); minmax_take(a, u.z, i0 + 2); minmax_take(a, u.w, i0 + 3);
+    }
+    for (int i = 4 * n4 + gtid; i < n; i += stride) minmax_take(a, p[i], (unsigned)i);   // tail / unaligned frame
+    unsigned long long kmin = ((unsigned long long)a.kmin << 32) | a.imin;
+    unsigned long long kmax = ((unsigned long long)a.kmax << 32) | (unsigned)(~a.imax);
+    int bad = a.bad;
     for (int o = 16; o > 0; o >>= 1) {
-        unsigned long long a = __shfl_xor_sync(0xffffffffu, kmin, o);
-        unsigned long long b = __shfl_xor_sync(0xffffffffu, kmax, o);
+        unsigned long long x = __shfl_xor_sync(0xffffffffu, kmin, o);
+        unsigned long long y = __shfl_xor_sync(0xffffffffu, kmax, o);
         int c = __shfl_xor_sync(0xffffffffu, bad, o);
-        kmin = a < kmin ? a : kmin; kmax = b > kmax ? b : kmax; bad |= c;
+        kmin = x < kmin ? x : kmin; kmax = y > kmax ? y : kmax; bad |= c;
     }
     if ((threadIdx.x & 31) == 0) {
         atomicMin(&stat[frame].minkey, kmin);

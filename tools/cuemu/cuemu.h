@@ -34,6 +34,7 @@ static const int warpSize = 32;
 
 struct uint2 { unsigned x, y; };
 static inline uint2 make_uint2(unsigned a, unsigned b) { uint2 r = {a, b}; return r; }
+struct float4 { float x, y, z, w; };
 struct uint4 { unsigned x, y, z, w; };
 static inline uint4 make_uint4(unsigned a, unsigned b, unsigned c, unsigned d) { uint4 r = {a, b, c, d}; return r; }
 
