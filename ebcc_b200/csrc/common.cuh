@@ -34,6 +34,7 @@ struct FrameStat {
 };
 #define STAT_CONST 1
 #define STAT_NANINF 2
+#define STAT_OVERFLOW 4    // a code-block outgrew its slice of the symbol or MQ pool: the frame fails loudly
 
 struct BandDesc {
     int resno, orient, level;
@@ -67,7 +68,16 @@ struct CblkOut {
     int nmsedec[J2K_MAXPASSES];
     int rate[J2K_MAXPASSES];            // cumulative bytes (after OPJ's fix-ups)
     double dist[J2K_MAXPASSES];         // cumulative distortion decrease
+    unsigned mqs[J2K_MAXPASSES][3];     // MQ coder at the end of each pass (compression-ratio search): c | ct << 28, a | pending byte << 16, index of the pending byte
 };
+
+// What the compression-ratio search knows about a code-block's truncation points.  The recording (value after all
+// passes + pass of significance per sample, written by k_t1_cm) covers np_dec passes.  Bit p of bad[] is set when
+// "decode only passes 0..p from the segment truncated at rate[p]" is NOT proven identical to the first p+1 passes of
+// a decode of the complete segment (OPJ truncates non-terminated MQ segments at numbytes+3, which is not always
+// enough; mq_cut_proven in k_t1.cuh).  scratch_np: pass count of the real truncated decode the scratch plane
+// currently holds for this block (0 = none).
+struct T1CutState { int np_dec; int scratch_np; unsigned bad[4]; };
 
 struct Plan {
     int H, W, nbands, ncblks;

@@ -256,7 +256,8 @@ static size_t assemble_frame(const frame_parts_t *p, uint8_t **out)
 #include <time.h>
 enum { TM_ANALYZE, TM_PROBE, TM_RESID_ENC, TM_RESID_PROBE, TM_PACK, TM_DOWNLOAD, TM_COUNT };
 static const char *const k_tm_names[TM_COUNT] = {"upload+analyze", "rate probes", "spiht encode", "spiht probes", "zstd pack", "download"};
-static double g_tm[TM_COUNT]; static int g_tm_calls[TM_COUNT]; static int g_profile = 0;
+/* per thread: every worker of a multi-batch call (and every concurrent caller) times its own batches */
+static _Thread_local double g_tm[TM_COUNT]; static _Thread_local int g_tm_calls[TM_COUNT]; static _Thread_local int g_profile = 0;
 static double now_ms(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return t.tv_sec * 1e3 + t.tv_nsec * 1e-6; }
 #define TIMED(slot, expr) ({ double t0_ = g_profile ? now_ms() : 0; int r_ = (expr); if (g_profile) { g_tm[slot] += now_ms() - t0_; g_tm_calls[slot]++; } r_; })
 
@@ -392,8 +393,8 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
     g_profile = getenv("EBCC_PROFILE") != NULL;
     if (g_profile) { memset(g_tm, 0, sizeof(g_tm)); memset(g_tm_calls, 0, sizeof(g_tm_calls)); }
     hint_crowd(ctx);
-    if (ebcc_cuda_reserve_tiled(ctx, T, H, W, nb)) goto out;
-    if (TIMED(TM_ANALYZE, ebcc_cuda_upload(ctx, frames, nb) || ebcc_cuda_analyze_resident(ctx, nb) || ebcc_cuda_sync(ctx))) goto out;
+    if (ebcc_cuda_reserve_tiled(ctx, T, H, W, nb)) { rc = -2; goto out; }     /* -2: the caller retries with fewer frames per batch */
+    if (TIMED(TM_ANALYZE, ebcc_cuda_upload(ctx, frames, nb) || ebcc_cuda_analyze(ctx, nb, mode != NONE) || ebcc_cuda_sync(ctx))) goto out;
     for (size_t i = 0; i < nb; ++i) { cr[i] = config->base_cr; tgt[i] = 0; }
 
     if (mode == NONE) {
@@ -416,6 +417,11 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
         }
         if (search_batch(ctx, nb, run, start, q0, base_quantile_target, tgt, N, memo, cr1, cr)) goto out;
         if (TIMED(TM_PROBE, ebcc_cuda_rate_probe(ctx, nb, cr1, tgt, 1, p1))) goto out;
+        for (size_t i = 0; i < nb; ++i) {
+            const double q = 1. - ((double)p1[i].n_over / N);
+            if (run[i] && q < base_quantile_target)      /* reference :591-593 */
+                ebcc_log(LOG_WARN, "Could not reach error target quantile of (1-%.2e) (1-%.2e instead).", 1 - base_quantile_target, 1 - q);
+        }
     }
     if (TIMED(TM_DOWNLOAD, ebcc_cuda_download(ctx, nb, streams, ssz, mn, mx, fl))) goto out;
     for (size_t i = 0; i < nb; ++i) {
@@ -450,7 +456,9 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
                 if (!resid[i]) continue;
                 if (perr[i] > tgt[i]) {
                     ebcc_log(LOG_INFO, "Could not reach error target of %f (%f instead). Retry with pure base compression.", tgt[i], perr[i]);
-                    resid[i] = 0; pure_required[i] = 1; coeffs_size[i] = 0;   /* coeffs_size stays coeffs_size_orig in the reference only until it is zeroed by the pure choice */
+                    /* like the reference (:752-758) the full-length residual stays in place: it is packed and written
+                     * unless the pure base-layer fallback below replaces it (which it does whenever it runs) */
+                    resid[i] = 0; pure_required[i] = 1;
                 } else {
                     best_err[i] = perr[i]; mean[i] = psum[i] / N;
                     thi[i] = (double)coeffs_size[i] * 8; tlo[i] = 112.0; best_trunc[i] = thi[i];
@@ -485,8 +493,8 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
             }
             for (size_t i = 0; i < nb; ++i) {
                 if (resid[i]) coeffs_size[i] = (size_t)(best_trunc[i] / 8.);
+                if (!resid[i] && !pure_required[i]) coeffs_size[i] = 0;
                 if (coeffs_size[i] <= 16) coeffs_size[i] = 0;
-                if (!resid[i]) coeffs_size[i] = 0;
             }
             /* zstd stage on the device (reference :813-817) */
             if (TIMED(TM_PACK, ebcc_cuda_residual_pack(ctx, nb, coeffs_size, zs, zn))) goto out;
@@ -536,6 +544,7 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
         } else {
             p.j2k = streams[i]; p.j2k_size = ssz[i];
         }
+        if (fl[i] & EBCC_FRAME_OVERFLOW) { ebcc_log(LOG_FATAL, "tier-1 work buffer overflow in frame %lu: no stream written", base + i); continue; }
         if (!p.const_field && p.j2k_size == 0) { ebcc_log(LOG_FATAL, "empty codestream for frame %lu", base + i); continue; }
         sizes[base + i] = assemble_frame(&p, &outs[base + i]);
         if (sizes[base + i]) {
@@ -566,6 +575,20 @@ typedef struct {
     pthread_mutex_t mu;
 } enc_job_t;
 
+/* one batch; when the device (or pinned host) memory for nb frames cannot be had, the batch is split in halves */
+static int encode_range(ebcc_cuda_ctx *ctx, enc_job_t *j, size_t base, size_t nb, size_t *done)
+{
+    const int rc = encode_chunk(ctx, j->frames + base * j->N, nb, base, j->config, j->outs, j->sizes, done);
+    if (rc != -2 || nb < 2) return rc;
+    ebcc_log(LOG_WARN, "work buffers for %lu frames could not be allocated: retrying with %lu", nb, nb / 2);
+    pthread_mutex_lock(&j->mu);
+    if (j->maxb > nb / 2) j->maxb = nb / 2;          /* later batches of this call start smaller right away */
+    pthread_mutex_unlock(&j->mu);
+    const int r1 = encode_range(ctx, j, base, nb / 2, done);
+    if (r1) return r1;
+    return encode_range(ctx, j, base + nb / 2, nb - nb / 2, done);
+}
+
 static void *enc_worker(void *arg)
 {
     enc_job_t *j = (enc_job_t *)arg;
@@ -575,12 +598,13 @@ static void *enc_worker(void *arg)
         pthread_mutex_lock(&j->mu);
         const size_t base = j->next;
         const int stop = j->failed || base >= j->nframes;
-        if (!stop) j->next = base + j->maxb;
+        const size_t maxb = j->maxb;
+        if (!stop) j->next = base + maxb;
         pthread_mutex_unlock(&j->mu);
         if (stop) break;
-        const size_t nb = j->nframes - base < j->maxb ? j->nframes - base : j->maxb;
+        const size_t nb = j->nframes - base < maxb ? j->nframes - base : maxb;
         size_t done = 0;
-        const int rc = encode_chunk(ctx, j->frames + base * j->N, nb, base, j->config, j->outs, j->sizes, &done);
+        const int rc = encode_range(ctx, j, base, nb, &done);
         pthread_mutex_lock(&j->mu);
         j->done += done;
         if (rc) j->failed = 1;
@@ -687,7 +711,8 @@ static int parse_stream(const uint8_t *data, size_t n, parsed_stream_t *ps)
         used += (size_t)h.compressed_size;
         if (h.tail_size > n - used) { ebcc_log(LOG_FATAL, "Invalid encoded data: truncated payload"); return 0; }
         used += (size_t)h.tail_size;
-        if (used != n) { ebcc_log(LOG_FATAL, "Invalid encoded data: payload size mismatch"); return 0; }
+        /* bytes beyond header + payload are tolerated like the reference does (its iterator check, :1314, only
+         * compares what it consumed with what the header announced): padded buffers, over-reported nbytes */
         ps->minval = bits_to_float(h.minval_bits); ps->maxval = bits_to_float(h.maxval_bits);
         ps->rmin = bits_to_float(h.residual_minval_bits); ps->rmax = bits_to_float(h.residual_maxval_bits);
         ps->coeffs_size = (size_t)h.coeffs_size; ps->zstd_size = (size_t)h.compressed_size; ps->tail_size = (size_t)h.tail_size;
@@ -697,6 +722,11 @@ static int parse_stream(const uint8_t *data, size_t n, parsed_stream_t *ps)
     if (ps->const_field) {
         if (ps->tail_size != sizeof(uint64_t)) { ebcc_log(LOG_FATAL, "Invalid encoded data: const-field payload must contain uint64_t length"); return 0; }
         uint64_t t; memcpy(&t, ps->tail, sizeof(t));
+        /* the largest frame the codec can write is 2047 x 2047 samples: anything else is a crafted or damaged stream
+         * (the count feeds a malloc and a fill loop; 2^62+1 would wrap the byte count) */
+        if (t == 0 || t > (uint64_t)EBCC_MAX_INTERNAL_IMAGE_DIM * EBCC_MAX_INTERNAL_IMAGE_DIM) {
+            ebcc_log(LOG_FATAL, "Invalid encoded data: const-field size %llu out of range", (unsigned long long)t); return 0;
+        }
         ps->tot_size = (size_t)t;
         if (ps->zstd_size > 0 && ps->coeffs_size > 0) { ebcc_log(LOG_FATAL, "Invalid encoded data: residual data cannot be applied to const field"); return 0; }
     } else {
@@ -774,7 +804,12 @@ static void *dec_worker(void *arg)
     return NULL;
 }
 
-size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, size_t nframes, float **outs, size_t *counts)
+/* const_inplace: constant fields are written into a caller-provided outs[i] (batch API, host or device memory); 0 =
+ * the reference's ebcc_decode, whose const-field branch always returns a fresh buffer (src/ebcc_codec.c:1278) while its
+ * JPEG 2000 branch writes into *out_buffer when that is non-NULL on entry (j2k_decode_internal, :1126-1128).
+ * expect_count != 0: every stream must announce exactly that many samples (chunk containers). */
+static size_t decode_batch_impl(uint8_t *const *streams, const size_t *stream_sizes, size_t nframes, float **outs, size_t *counts,
+                                int const_inplace, size_t expect_count)
 {
     log_set_level_from_env();
     size_t done = 0;
@@ -783,12 +818,17 @@ size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, si
     for (size_t i = 0; i < nframes; ++i) {
         counts[i] = 0;
         if (!parse_stream(streams[i], stream_sizes[i], &ps[i])) continue;
+        if (expect_count && ps[i].tot_size != expect_count) {
+            /* chunk containers know the size of every chunk: refuse before anything is allocated or decoded */
+            ebcc_log(LOG_FATAL, "chunk %lu holds %lu values, expected %lu", i, ps[i].tot_size, expect_count);
+            ps[i].ok = 0; continue;
+        }
         if (ps[i].const_field) {
             /* constant field: the stream carries one value and a count (reference :1265-1281) */
             float *o = (float *)malloc(ps[i].tot_size * sizeof(float));
             if (!o) { ps[i].ok = 0; continue; }
             for (size_t k = 0; k < ps[i].tot_size; ++k) o[k] = ps[i].minval;
-            if (outs[i]) {
+            if (outs[i] && const_inplace) {
                 /* caller-provided destination (host or device memory): written in place like every other frame */
                 const int rc = ebcc_cuda_copy_out(outs[i], o, ps[i].tot_size * sizeof(float));
                 free(o);
@@ -830,15 +870,21 @@ size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, si
     return done;
 }
 
+size_t ebcc_decode_batch(uint8_t *const *streams, const size_t *stream_sizes, size_t nframes, float **outs, size_t *counts)
+{
+    return decode_batch_impl(streams, stream_sizes, nframes, outs, counts, 1, 0);
+}
+
 size_t ebcc_decode(uint8_t *data, size_t data_size, float **out_buffer)
 {
-    /* like the reference (src/ebcc_codec.c:1215-1320) the result is always a fresh malloc'ed buffer: whatever
-     * *out_buffer held on entry is ignored (callers pass uninitialised pointers) */
+    /* Reference contract (src/ebcc_codec.c:1215-1320, :1126-1128): when *out_buffer is non-NULL on entry the frame is
+     * decoded INTO that buffer (the zarr codec's decode(buf, out=arr) relies on it, ebcc/zarr_filter.py:63-72) and the
+     * pointer is left unchanged; when it is NULL a fresh malloc'ed buffer is returned.  Constant-field streams always
+     * come back in a fresh buffer (:1278). */
     size_t count = 0;
     uint8_t *s[1] = {data};
-    float *o = NULL;
-    *out_buffer = NULL;
-    if (ebcc_decode_batch(s, &data_size, 1, &o, &count) != 1) return 0;
+    float *o = *out_buffer;
+    if (decode_batch_impl(s, &data_size, 1, &o, &count, 0, 0) != 1) return 0;
     *out_buffer = o;
     return count;
 }
@@ -1030,8 +1076,8 @@ size_t ebcc_decode_chunking(uint8_t *data, size_t data_size, float **out_buffer)
         return 0;
     }
     /* sequential scan of the length prefixes, then one batched decode */
-    uint8_t **streams = (uint8_t **)malloc(sizeof(*streams) * num_chunks);
-    size_t *ssz = (size_t *)malloc(sizeof(size_t) * num_chunks);
+    uint8_t **streams = (uint8_t **)calloc(num_chunks, sizeof(*streams));
+    size_t *ssz = (size_t *)calloc(num_chunks, sizeof(size_t));
     size_t *counts_out = (size_t *)calloc(num_chunks, sizeof(size_t));
     float **outs = (float **)calloc(num_chunks, sizeof(*outs));
     size_t off = sizeof(h), ok = 1;
@@ -1045,7 +1091,7 @@ size_t ebcc_decode_chunking(uint8_t *data, size_t data_size, float **out_buffer)
     float *out = NULL;
     size_t ret = 0;
     if (!ok) ebcc_log(LOG_FATAL, "Invalid chunked EBCC stream: truncated chunk table");
-    else if (ebcc_decode_batch(streams, ssz, num_chunks, outs, counts_out) == num_chunks) {
+    else if (decode_batch_impl(streams, ssz, num_chunks, outs, counts_out, 1, chunk_size) == num_chunks) {
         out = (float *)malloc(total * sizeof(float));
         for (size_t k = 0; k < num_chunks && out; ++k) {
             if (counts_out[k] != chunk_size) { ebcc_log(LOG_FATAL, "chunk %lu decoded to %lu values, expected %lu", k, counts_out[k], chunk_size); free(out); out = NULL; break; }

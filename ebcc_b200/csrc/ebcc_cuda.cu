@@ -22,6 +22,7 @@
         if (e_ != cudaSuccess) {                                                                     \
             fprintf(stderr, "[ebcc-cuda] %s failed at %s:%d: %s\n", #call, __FILE__, __LINE__,       \
                     cudaGetErrorString(e_));                                                         \
+            (void)cudaGetLastError();   /* a failed call must not poison the next check */            \
             return -1;                                                                               \
         }                                                                                            \
     } while (0)
@@ -266,6 +267,9 @@ static void fill_dec_luts(DecLuts *d, const MqTable *t)
         }
 }
 
+// sum of the errors of a frame as a double (fixed-point accumulator of the kernels, see ERR_FX_BITS)
+static double es_sum(const ErrStat &e) { return ldexp((double)e.sum_fx, e.sum_exp - ERR_FX_BITS); }
+
 // ---- context ---------------------------------------------------------------------------------------
 struct ebcc_cuda_ctx {
     int device;
@@ -296,7 +300,9 @@ struct ebcc_cuda_ctx {
     unsigned char *d_spass;    // [B][H][W] pass in which each sample became significant (recording)
     DecState *d_dstate;        // [B][ncblks]
     unsigned *d_decsave;       // [B][ncblks][DEC_SAVE_WORDS] decoder state of each block's recording (resumed by later probes)
-    int use_recording;
+    int use_recording;         // 0: every probe decodes every block for real (EBCC_NO_RECORDING=1)
+    int rec_from_encoder;      // recording + cut verdicts come from the encoder (k_t1_cm / k_t1_mq); 0: from k_t1_dec (EBCC_DECODER_RECORDING=1)
+    int for_search;            // the running analysis feeds a compression-ratio search
     float *d_dcoef;            // [B][H][W] dequantised coefficients / IDWT work plane
     float *d_dec;              // [B][H][W] decoded frames
     ErrStat *d_es;
@@ -343,11 +349,14 @@ struct ebcc_cuda_ctx {
     // min/max, decoded image, residual layer, assembled codestreams); tile t of every image of the batch is coded by
     // tile[t], a light context with the tile's own geometry that shares this context's stream and look-up tables
     int crowd;                 // pipelines at work on this device (hint from the host codec), see mq_lanes()
+    int env_mq_lanes, env_dec_lanes, env_no_recording, env_dec_recording, env_debug_lanes;   // tuning / debugging variables, read once per host call (read_env)
     int ntiles;
     ebcc_cuda_ctx *tile[EBCC_MAX_TILES];
     ebcc_cuda_ctx *parent;
     TileSrc *d_tile_src;
 };
+
+static void read_env(ebcc_cuda_ctx *c);
 
 // Wait for the pipeline's stream.  Several pipelines (and, on a multi-GPU box, several ranks) share the host cores:
 // the waiting thread sleeps on a blocking-sync event unless EBCC_SPIN_SYNC=1 asks for the lower-latency spin wait.
@@ -381,6 +390,7 @@ extern "C" ebcc_cuda_ctx *ebcc_cuda_ctx_create(int device)
     for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventCreate(&c->ev[i]);
     cudaEventCreateWithFlags(&c->ev_sync, cudaEventBlockingSync | cudaEventDisableTiming);
     { const char *sp = getenv("EBCC_SPIN_SYNC"); c->spin_sync = sp && sp[0] == '1'; }
+    read_env(c);
     T1Luts luts; MqTable tab;
     fill_luts(&luts, &tab);
     if (cudaMalloc((void **)&c->d_luts, sizeof(luts)) != cudaSuccess || cudaMalloc((void **)&c->d_mqtab, sizeof(tab)) != cudaSuccess) { free(c); return NULL; }
@@ -480,7 +490,19 @@ extern "C" void ebcc_cuda_ctx_destroy(ebcc_cuda_ctx *c)
 
 // work buffers of one context for nframes tiles of H x W at canvas row y0 (tile_index of ntiles, image height Himg);
 // light: no residual-layer buffers (tile contexts of a multi-tile image)
+static int reserve_alloc(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes, int y0, int tile_index, int ntiles, int Himg, int light);
 static int reserve_impl(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes, int y0, int tile_index, int ntiles, int Himg, int light)
+{
+    const int rc = reserve_alloc(c, H, W, nframes, y0, tile_index, ntiles, Himg, light);
+    if (rc && c) {            // out of device or pinned memory half way: give everything back, the caller may retry with fewer frames
+        cudaSetDevice(c->device);
+        free_buffers(c);
+        (void)cudaGetLastError();
+    }
+    return rc;
+}
+
+static int reserve_alloc(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes, int y0, int tile_index, int ntiles, int Himg, int light)
 {
     if (!c || H < 32 || W < 32 || H > 2047 || W > 2047 || nframes == 0) return -1;
     CK(cudaSetDevice(c->device));
@@ -666,11 +688,24 @@ static int launch_dwt(ebcc_cuda_ctx *c, int B)
 // the GPU a short chain wins (measured on B200, k_t1_mq alone: 1 frame L=1 5.0 ms / L=32 12.2 ms; 24 frames L=4 8.4 ms /
 // L=32 12.6 ms), with several pipelines in flight the issue slots are the scarce resource and L = 32 wins.
 // EBCC_MQ_LANES / EBCC_DEC_LANES override.
-static int ctx_crowd(const ebcc_cuda_ctx *c) { const ebcc_cuda_ctx *r = c->parent ? c->parent : c; return r->crowd > 0 ? r->crowd : 1; }
+static const ebcc_cuda_ctx *ctx_root(const ebcc_cuda_ctx *c) { return c->parent ? c->parent : c; }
+static int ctx_crowd(const ebcc_cuda_ctx *c) { const ebcc_cuda_ctx *r = ctx_root(c); return r->crowd > 0 ? r->crowd : 1; }
+// the environment is read when a context is created and at every ebcc_cuda_set_crowd (once per host-level call), not per launch
+static void read_env(ebcc_cuda_ctx *c)
+{
+    const char *e = getenv("EBCC_MQ_LANES");
+    c->env_mq_lanes = e ? atoi(e) : 0;
+    e = getenv("EBCC_DEC_LANES");
+    c->env_dec_lanes = e ? atoi(e) : 0;
+    e = getenv("EBCC_NO_RECORDING");                // debugging aid: every probe decodes every block for real
+    c->env_no_recording = e && e[0] == '1';
+    e = getenv("EBCC_DECODER_RECORDING");           // cross-check aid: recordings made by the tier-1 decoder (round-1 path)
+    c->env_dec_recording = e && e[0] == '1';
+    c->env_debug_lanes = getenv("EBCC_DEBUG_LANES") != NULL;
+}
 static int mq_lanes(const ebcc_cuda_ctx *c, long long jobs)
 {
-    const char *el = getenv("EBCC_MQ_LANES");
-    if (el) { const int l = atoi(el); if (l == 1 || l == 2 || l == 4 || l == 8 || l == 16 || l == 32) return l; }
+    { const int l = ctx_root(c)->env_mq_lanes; if (l == 1 || l == 2 || l == 4 || l == 8 || l == 16 || l == 32) return l; }
     const int crowd = ctx_crowd(c);
     if (crowd >= 3) return MQ_DEFAULT_LANES;
     if (crowd == 2) return 8;
@@ -678,12 +713,11 @@ static int mq_lanes(const ebcc_cuda_ctx *c, long long jobs)
 }
 static int dec_lanes(const ebcc_cuda_ctx *c)
 {
-    const char *el = getenv("EBCC_DEC_LANES");
-    if (el) { const int l = atoi(el); if (l == 1 || l == 2 || l == 4 || l == 8) return l; }
+    { const int l = ctx_root(c)->env_dec_lanes; if (l == 1 || l == 2 || l == 4 || l == 8) return l; }
     return ctx_crowd(c) >= 3 ? DEC_DEFAULT_LANES : 1;
 }
 
-extern "C" void ebcc_cuda_set_crowd(ebcc_cuda_ctx *c, int pipelines_at_work) { if (c) c->crowd = pipelines_at_work; }
+extern "C" void ebcc_cuda_set_crowd(ebcc_cuda_ctx *c, int pipelines_at_work) { if (c) { c->crowd = pipelines_at_work; read_env(c); } }
 
 static int launch_minmax(ebcc_cuda_ctx *c, int B)
 {
@@ -696,11 +730,11 @@ static int launch_minmax(ebcc_cuda_ctx *c, int B)
     return 0;
 }
 
-static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax);
+static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int for_search);
 
 // multi-tile image: min/max over the whole image (src/ebcc_codec.c:676-689 scales the image, not the tile), then
 // every tile context transforms and codes its tile of every image
-static int analyze_tiled(ebcc_cuda_ctx *c, size_t nframes)
+static int analyze_tiled(ebcc_cuda_ctx *c, size_t nframes, int for_search)
 {
     const int B = (int)nframes, T = c->ntiles;
     mark(c, EBCC_ST_MINMAX);
@@ -712,7 +746,7 @@ static int analyze_tiled(ebcc_cuda_ctx *c, size_t nframes)
         CK(cudaMemcpyAsync(s->d_stat, c->d_stat, sizeof(FrameStat) * B, cudaMemcpyDeviceToDevice, c->stream));
         CK(cudaMemcpy2DAsync(s->d_in, Nt * sizeof(float), c->d_in + (size_t)t * Nt, (size_t)T * Nt * sizeof(float), Nt * sizeof(float),
                              (size_t)B, cudaMemcpyDeviceToDevice, c->stream));
-        if (analyze_impl(s, nframes, 0)) return -1;
+        if (analyze_impl(s, nframes, 0, for_search)) return -1;
     }
     mark(c, EBCC_ST_T1_CM);
     mark(c, EBCC_ST_T1_MQ);
@@ -720,21 +754,24 @@ static int analyze_tiled(ebcc_cuda_ctx *c, size_t nframes)
 }
 
 // stage 1 of the encoder: everything that does not depend on the compression ratio
-extern "C" int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *c, size_t nframes)
+extern "C" int ebcc_cuda_analyze(ebcc_cuda_ctx *c, size_t nframes, int for_search)
 {
     if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
     CK(cudaSetDevice(c->device));
-    if (c->ntiles > 1) return analyze_tiled(c, nframes);
-    return analyze_impl(c, nframes, 1);
+    if (c->ntiles > 1) return analyze_tiled(c, nframes, for_search);
+    return analyze_impl(c, nframes, 1, for_search);
 }
 
-static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax)
+extern "C" int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *c, size_t nframes) { return ebcc_cuda_analyze(c, nframes, 1); }
+
+static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int for_search)
 {
     const Plan *pl = &c->plan;
     const int B = (int)nframes;
-    {
-        const char *nr = getenv("EBCC_NO_RECORDING");   // debugging aid: every probe decodes every block for real
-        c->use_recording = !(nr && nr[0] == '1');
+    c->for_search = for_search;
+    c->use_recording = !ctx_root(c)->env_no_recording;
+    c->rec_from_encoder = for_search && c->use_recording && !ctx_root(c)->env_dec_recording;
+    if (for_search && !c->rec_from_encoder) {
         const long long nb = (long long)pl->ncblks * B;
         EBCC_LAUNCH(k_dstate_reset, dim3((unsigned)((nb + 255) / 256)), dim3(256), 0, c->stream, c->d_dstate, nb);
         c->launches++;
@@ -746,18 +783,23 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax)
     if (launch_dwt(c, B)) return -1;
 
     mark(c, EBCC_ST_T1_CM);
-    EBCC_LAUNCH(k_t1_cm, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
-                c->d_coef, c->d_cblks, c->d_bands, c->d_luts, (const unsigned char *)c->d_declut, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks,
-                pl->sym_stride);
+    if (c->rec_from_encoder)
+        EBCC_LAUNCH(k_t1_cm<true>, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
+                    c->d_coef, c->d_cblks, c->d_bands, c->d_luts, (const unsigned char *)c->d_declut, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks,
+                    pl->sym_stride, c->d_iplane, c->d_spass, c->d_stat);
+    else
+        EBCC_LAUNCH(k_t1_cm<false>, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
+                    c->d_coef, c->d_cblks, c->d_bands, c->d_luts, (const unsigned char *)c->d_declut, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks,
+                    pl->sym_stride, (int *)NULL, (unsigned char *)NULL, c->d_stat);
     mark(c, EBCC_ST_T1_MQ);
     {
         const long long jobs = (long long)pl->ncblks * B;
         const int lanes = mq_lanes(c, jobs);                     // code-blocks per warp: 1, 2, 4, 8, 16 or 32
-        if (getenv("EBCC_DEBUG_LANES")) fprintf(stderr, "[ebcc-cuda] mq lanes %d (crowd %d, jobs %lld)\n", lanes, ctx_crowd(c), jobs);
+        if (ctx_root(c)->env_debug_lanes) fprintf(stderr, "[ebcc-cuda] mq lanes %d (crowd %d, jobs %lld)\n", lanes, ctx_crowd(c), jobs);
         const long long per_cta = (long long)MQ_WARPS(lanes) * lanes;
         const dim3 grid((unsigned)((jobs + per_cta - 1) / per_cta)), block(MQ_THREADS(lanes));
 #define MQ_GO(LL) EBCC_LAUNCH(k_t1_mq<LL>, grid, block, 0, c->stream, c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, \
-                              c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride)
+                              c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride, c->rec_from_encoder ? c->d_dstate : (T1CutState *)NULL, c->d_stat)
         if (lanes == 32) MQ_GO(32); else if (lanes == 16) MQ_GO(16); else if (lanes == 8) MQ_GO(8); else if (lanes == 4) MQ_GO(4);
         else if (lanes == 2) MQ_GO(2); else MQ_GO(1);
 #undef MQ_GO
@@ -809,7 +851,7 @@ static int launch_rate_stage(ebcc_cuda_ctx *c, int B, const float *cr, int with_
 
 extern "C" int ebcc_cuda_j2k_encode_resident(ebcc_cuda_ctx *c, size_t nframes, float base_cr)
 {
-    if (ebcc_cuda_analyze_resident(c, nframes)) return -1;
+    if (ebcc_cuda_analyze(c, nframes, 0)) return -1;
     float *cr = (float *)malloc(sizeof(float) * nframes);
     for (size_t i = 0; i < nframes; ++i) cr[i] = base_cr;
     int rc = launch_rate_stage(c, (int)nframes, cr, 1);
@@ -914,7 +956,7 @@ extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const floa
             int bytes = c->tile[0]->h_pout[i].stream_bytes;
             for (int t = 1; t < T; ++t) {
                 const ErrStat &x = c->tile[t]->h_es[i];
-                e.n_over += x.n_over; e.sum_err += x.sum_err;
+                e.n_over += x.n_over; e.sum_fx += x.sum_fx;       // same image range => same fixed-point unit in every tile
                 if (x.max_err_bits > e.max_err_bits) e.max_err_bits = x.max_err_bits;
                 if (x.rmin_key < e.rmin_key) e.rmin_key = x.rmin_key;
                 if (x.rmax_key > e.rmax_key) e.rmax_key = x.rmax_key;
@@ -933,7 +975,7 @@ extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const floa
         memcpy(&res[i].max_err, &e.max_err_bits, 4);
         unsigned k = e.rmin_key; k = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k; memcpy(&res[i].rmin, &k, 4);
         k = e.rmax_key; k = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k; memcpy(&res[i].rmax, &k, 4);
-        res[i].sum_err = e.sum_err;
+        res[i].sum_err = es_sum(e);
         res[i].stream_bytes = (size_t)c->h_pout[i].stream_bytes;
     }
     return 0;
@@ -1045,7 +1087,7 @@ extern "C" int ebcc_cuda_residual_probe(ebcc_cuda_ctx *c, size_t nframes, const 
     for (int i = 0; i < B; ++i) {
         if (!active[i]) continue;
         memcpy(&max_err[i], &c->h_es2[i].max_err_bits, 4);
-        sum_err[i] = c->h_es2[i].sum_err;
+        sum_err[i] = es_sum(c->h_es2[i]);
     }
     return 0;
 }
@@ -1304,6 +1346,41 @@ extern "C" int ebcc_cuda_t1_totals(ebcc_cuda_ctx *c, size_t nframes, unsigned lo
         if (h[i].totalpasses > 0) { s += h[i].nsym_end[h[i].totalpasses - 1]; b += (unsigned long long)h[i].datalen; }
     free(h);
     *symbols = s; *mq_bytes = b;
+    return 0;
+}
+
+// test tap: after ebcc_cuda_analyze(for_search = 1), checks EVERY truncation point of EVERY code-block of the first nframes
+// frames: the block is decoded for real from the segment cut at rate[np - 1] and compared with what the recording +
+// verdict would reconstruct.  counts[0] cuts checked, [1] flagged unproven, [2] flagged proven but different from the real
+// decode (must be 0), [3] flagged unproven although equal.  Leaves the PCRD allocation of the context clobbered.
+extern "C" int ebcc_cuda_debug_check_cuts(ebcc_cuda_ctx *c, size_t nframes, unsigned long long *counts)
+{
+    if (!c || nframes == 0 || nframes > c->cap_frames || c->ntiles > 1 || !c->for_search) return -1;
+    CK(cudaSetDevice(c->device));
+    const Plan *pl = &c->plan;
+    const int B = (int)nframes;
+    const long long njobs = (long long)pl->ncblks * B;
+    unsigned long long *d_cnt = NULL;
+    CK(cudaMalloc((void **)&d_cnt, 4 * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(d_cnt, 0, 4 * sizeof(unsigned long long), c->stream));
+    unsigned long long prev = 0;
+    for (int np = 1; np < J2K_MAXPASSES; ++np) {
+        EBCC_LAUNCH(k_dbg_force_np, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cbout, njobs, np);
+        EBCC_LAUNCH(k_jobs_from_enc, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cblks, c->d_cbout, c->d_dstate, c->d_jobs,
+                    pl->ncblks, B, 0);
+        const long long per_cta = (long long)DEC_WPC(1);
+        EBCC_LAUNCH(k_t1_dec<1>, dim3((unsigned)((njobs + per_cta - 1) / per_cta)), dim3((unsigned)(DEC_WPC(1) * 32)), 0, c->stream, c->d_cblks, c->d_order,
+                    c->d_jobs, c->d_mq, pl->mq_stride, c->d_declut, c->d_iplane, (unsigned char *)NULL, c->d_scratch, (const CblkOut *)c->d_cbout,
+                    c->d_dstate, c->d_decsave, pl->W, pl->H, pl->ncblks, B);
+        EBCC_LAUNCH(k_dbg_compare, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(128), 0, c->stream, c->d_cblks, c->d_cbout, c->d_dstate, c->d_iplane,
+                    c->d_spass, c->d_scratch, d_cnt, np, pl->W, pl->H, pl->ncblks);
+        CK(cudaMemcpyAsync(counts, d_cnt, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+        CK(ctx_sync(c));
+        if (counts[0] == prev) break;          // no block has this many passes
+        prev = counts[0];
+    }
+    cudaFree(d_cnt);
+    CK(cudaGetLastError());
     return 0;
 }
 

@@ -23,13 +23,10 @@
 //       3 = the scratch plane already holds exactly this decode (same block, same pass count)
 struct DecJob { int np; int numbps; unsigned off; int len; int mode; int pad; };
 
-// What the recording of a block holds (compression-ratio search): np_dec passes were decoded FROM THE COMPLETE
-// SEGMENT (all passes the encoder produced), so a later probe that needs more passes continues where the recording
-// stopped (decoder state in the save area).  Bit p of bad[] is set when "decode only passes 0..p from the segment
-// truncated at rate[p]" is NOT proven identical to the first p+1 passes of the recorded decode (OPJ truncates
-// non-terminated MQ segments at numbytes+3, which is not always enough).  scratch_np: pass count of the real
-// truncated decode the scratch plane currently holds for this block (0 = none).
-struct DecState { int np_dec; int scratch_np; unsigned bad[4]; };
+// T1CutState (common.cuh): what the recording of a block holds.  Two producers: the encoder itself (k_t1_cm writes the
+// recording, k_t1_mq the verdicts -- the product path) and, for cross-checking, this decoder reading the COMPLETE
+// segment with truncation shadows (mode 1 jobs, EBCC_DECODER_RECORDING=1).
+typedef T1CutState DecState;
 
 // per-block save area of a recording (32-bit words): flag words, then the serial decoder's registers
 #define DEC_SAVE_MQ DEC_FWORDS_C
@@ -598,6 +595,19 @@ __global__ void k_dstate_reset(DecState *d, long long n)
 // dequantised: (float)v * (0.5f * stepsize_dec)  (t1.c:1853-1865).
 //   decoder units: |v| = 2*M + 2^b, M = magnitude bits decoded down to plane b, 2^b the half-bit bias
 //   (t1.c:582-1140: oneplushalf on significance, +-poshalf per refinement)
+// value of a sample after the first np coding passes, from its recording (value v after npd >= np passes, pass of
+// significance ps)
+__device__ __forceinline__ int recon_value(int v, int ps, int np, int npd, int numbps)
+{
+    if (np == npd || v == 0) return v;
+    if (ps >= np) return 0;
+    const int kk = ps == 0 ? 0 : (ps + 2) / 3, kr = np / 3;
+    const int b = numbps - 1 - (kr > kk ? kr : kk);
+    const int a = v < 0 ? -v : v;
+    const int mag = ((((a >> 1) >> b) << b) << 1) + (1 << b);
+    return v < 0 ? -mag : mag;
+}
+
 __global__ void k_recon_dequant(const Plan *__restrict__ plan, const CblkOut *__restrict__ cbout, const DecState *__restrict__ dstate,
                                 const DecJob *__restrict__ jobs, const int *__restrict__ iplane, const unsigned char *__restrict__ spass,
                                 const int *__restrict__ scratch, float *coef)
@@ -620,20 +630,8 @@ __global__ void k_recon_dequant(const Plan *__restrict__ plan, const CblkOut *__
         int v;
         if (jobs[bi].mode >= 2) v = scratch[si];
         else {
-            const int np = cbout[bi].numpasses, npd = dstate[bi].np_dec;
-            v = np > 0 ? iplane[si] : 0;            // a block that was never included has no recording
-            if (np != npd && v != 0) {
-                const int ps = spass[si];
-                if (ps >= np) v = 0;
-                else {
-                    const int numbps = cbout[bi].numbps;
-                    const int kk = ps == 0 ? 0 : (ps + 2) / 3, kr = np / 3;
-                    const int b = numbps - 1 - (kr > kk ? kr : kk);
-                    const int a = v < 0 ? -v : v;
-                    const int mag = ((((a >> 1) >> b) << b) << 1) + (1 << b);
-                    v = v < 0 ? -mag : mag;
-                }
-            }
+            const int np = cbout[bi].numpasses;
+            v = np > 0 ? recon_value(iplane[si], spass[si], np, dstate[bi].np_dec, cbout[bi].numbps) : 0;   // a block that was never included has no recording
         }
         coef[si] = __fmul_rn((float)v, __fmul_rn(0.5f, bd.stepsize_dec));
     }
@@ -766,4 +764,38 @@ __global__ void k_t2_parse(const Plan *__restrict__ plan, const CblkDesc *__rest
         }
     }
     status[frame] = PARSE_OK;
+}
+
+// ---- test taps: every truncation point of every code-block checked against a real decode ------------------------------
+__global__ void k_dbg_force_np(CblkOut *cbout, long long n, int np)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) cbout[i].numpasses = cbout[i].totalpasses >= np ? np : 0;
+}
+
+// grid (ncblks, nframes): block k of a frame, cut after np passes: recording vs the real truncated decode in `scratch`.
+// cnt[0] cuts checked, [1] flagged unproven, [2] flagged proven but DIFFERENT (must stay 0), [3] flagged unproven but equal
+__global__ void k_dbg_compare(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cbout, const DecState *__restrict__ dstate,
+                              const int *__restrict__ iplane, const unsigned char *__restrict__ spass, const int *__restrict__ scratch,
+                              unsigned long long *cnt, int np, int W, int H, int ncblks)
+{
+    const int k = blockIdx.x, frame = blockIdx.y;
+    const size_t bi = (size_t)frame * ncblks + k;
+    if (cbout[bi].numpasses != np || np <= 0) return;
+    const CblkDesc cb = cblks[k];
+    const int npd = dstate[bi].np_dec, numbps = cbout[bi].numbps;
+    int diff = 0;
+    for (int i = threadIdx.x; i < cb.w * cb.h; i += blockDim.x) {
+        const int y = i / cb.w, x = i - y * cb.w;
+        const size_t si = (size_t)frame * W * H + (size_t)(cb.ty + y) * W + cb.tx + x;
+        if (recon_value(iplane[si], spass[si], np, npd, numbps) != scratch[si]) diff = 1;
+    }
+    diff = __syncthreads_or(diff);
+    if (threadIdx.x == 0) {
+        const int bad = (np - 1) >= 128 || ((dstate[bi].bad[(np - 1) >> 5] >> ((np - 1) & 31)) & 1u);
+        atomicAdd(&cnt[0], 1ull);
+        if (bad) atomicAdd(&cnt[1], 1ull);
+        if (!bad && diff) atomicAdd(&cnt[2], 1ull);
+        if (bad && !diff) atomicAdd(&cnt[3], 1ull);
+    }
 }

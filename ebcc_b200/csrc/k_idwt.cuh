@@ -149,14 +149,21 @@ struct ErrStat {
     unsigned long long n_over;     // samples with |d - rec| > target           (get_error_target_quantile)
     unsigned max_err_bits;         // max |d - rec| as float bits                 (get_max_error)
     unsigned rmin_key, rmax_key;   // ordered keys of min / max of (d - rec)      (findMinMaxf on the residual)
-    unsigned pad;
-    double sum_err;                // sum of (d - rec) in double                  (get_mean_error)
+    int sum_exp;                   // sum_fx counts units of 2^(sum_exp - ERR_FX_BITS)
+    long long sum_fx;              // sum of (d - rec), fixed point               (get_mean_error)
 };
+// The mean error feeds the header's min / max (src/ebcc_codec.c:863-868), so the sum must not depend on the order in
+// which CTAs and warps finish: every term is rounded to a fixed-point integer (units of 2^(e - 39), |term| < 2^e,
+// at most 2^22 terms) and the integers are added with 64-bit atomics -- exact, hence order-free; the rounding is
+// 2^-39 of the value range per term, far below one ulp of the f32 it ends up in.
+#define ERR_FX_BITS 39
+__device__ __forceinline__ long long err_fx(float r, int e) { return __double2ll_rn(ldexp((double)r, ERR_FX_BITS - e)); }
+__host__ __device__ __forceinline__ int err_fx_exp(float bound) { int e = 0; (void)frexpf(bound, &e); return e; }
 
 __global__ void k_errstat_init(ErrStat *es, int n)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) { es[i].n_over = 0; es[i].max_err_bits = 0; es[i].rmin_key = 0xffffffffu; es[i].rmax_key = 0; es[i].pad = 0; es[i].sum_err = 0.0; }
+    if (i < n) { es[i].n_over = 0; es[i].max_err_bits = 0; es[i].rmin_key = 0xffffffffu; es[i].rmax_key = 0; es[i].sum_exp = 0; es[i].sum_fx = 0; }
 }
 
 __device__ __forceinline__ float key_to_f32(unsigned k)
@@ -174,7 +181,8 @@ __global__ void k_finalize(const float *__restrict__ coef, float *out, const Fra
     unsigned long long over = 0;
     float mx = 0.0f;
     unsigned kmin = 0xffffffffu, kmax = 0;
-    double sum = 0.0;
+    long long sum = 0;
+    const int ex = err_fx_exp(range);         // |orig - decoded| <= max - min < 2^ex
     const size_t base = (size_t)frame * n;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float v = j2k_pixel_to_float(coef[base + i], mn, range);
@@ -185,7 +193,7 @@ __global__ void k_finalize(const float *__restrict__ coef, float *out, const Fra
             mx = fmaxf(mx, e);
             const unsigned k = f32_order_key(r);
             kmin = min(kmin, k); kmax = max(kmax, k);
-            sum += (double)r;
+            sum += err_fx(r, ex);
         }
     }
     if (!orig) return;
@@ -201,6 +209,7 @@ __global__ void k_finalize(const float *__restrict__ coef, float *out, const Fra
         atomicMax(&es[frame].max_err_bits, __float_as_uint(mx));
         atomicMin(&es[frame].rmin_key, kmin);
         atomicMax(&es[frame].rmax_key, kmax);
-        atomicAdd(&es[frame].sum_err, sum);
+        atomicAdd((unsigned long long *)&es[frame].sum_fx, (unsigned long long)sum);
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0) es[frame].sum_exp = ex;
 }

@@ -40,7 +40,7 @@
 struct SpGeom { int W, H, Wp, Hp, lx, ly; };
 
 struct SpInfo {                 // per frame
-    double sum;                 // sum of the padded image (for the DC term)
+    long long sum;              // sum of the padded image in units of 2^-30 (for the DC term): integer, hence order-free
     float rmin, rmax;           // residual range
     int dc;                     // floor(mean), 0..255
     int maxabs;                 // max |coefficient|
@@ -59,7 +59,7 @@ __global__ void k_sp_init(SpInfo *info, const float *rmm, const unsigned *budget
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     SpInfo &s = info[i];
-    s.sum = 0.0; s.rmin = rmm[2 * i]; s.rmax = rmm[2 * i + 1]; s.dc = 0; s.maxabs = 0; s.step0 = 0;
+    s.sum = 0; s.rmin = rmm[2 * i]; s.rmax = rmm[2 * i + 1]; s.dc = 0; s.maxabs = 0; s.step0 = 0;
     s.budget = budget[i]; s.emitted = 0; s.nbytes = 0; s.active = active[i];
     for (int p = 0; p < 32; ++p) { s.ref_base[p] = SP_NOPOS; s.lsp_before[p] = 0; }
 }
@@ -70,7 +70,7 @@ __global__ void k_sp_load(const float *__restrict__ orig, const float *__restric
     if (!info[frame].active) return;
     const float rmin = info[frame].rmin, range = __fsub_rn(info[frame].rmax, rmin);
     const size_t n = (size_t)g.Wp * g.Hp, nsrc = (size_t)g.W * g.H;
-    double sum = 0.0;
+    long long sum = 0;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const int y = (int)(i / g.Wp), x = (int)(i - (size_t)y * g.Wp);
         float v = 0.0f;
@@ -81,10 +81,10 @@ __global__ void k_sp_load(const float *__restrict__ orig, const float *__restric
             v = __fmul_rn(__fdiv_rn(__fsub_rn(r, rmin), range), 255.0f);
         }
         img[(size_t)frame * n + i] = v;
-        sum += (double)v;
+        sum += __double2ll_rn((double)v * 1073741824.0);        // v in [0, 255]: < 2^38 per term, < 2^61 per frame
     }
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if ((threadIdx.x & 31) == 0) atomicAdd(&info[frame].sum, sum);
+    if ((threadIdx.x & 31) == 0) atomicAdd((unsigned long long *)&info[frame].sum, (unsigned long long)sum);
 }
 
 __global__ void k_sp_subdc(float *img, SpInfo *info, SpGeom g)
@@ -92,7 +92,8 @@ __global__ void k_sp_subdc(float *img, SpInfo *info, SpGeom g)
     const int frame = blockIdx.y;
     if (!info[frame].active) return;
     const size_t n = (size_t)g.Wp * g.Hp;
-    const double dc = floor(info[frame].sum / (double)n);
+    // floor(mean) (dwt.h:319-334); the terms are non-negative, integer division is the floor
+    const long long dc = info[frame].sum / ((long long)n << 30);
     const float dcf = (float)dc;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
         img[(size_t)frame * n + i] = __fsub_rn(img[(size_t)frame * n + i], dcf);
@@ -602,15 +603,18 @@ __global__ void k_sp_errstat(const float *__restrict__ img, const float *__restr
     if (Pbits[frame] == 0) return;
     const float rmin = info[frame].rmin, range = __fsub_rn(info[frame].rmax, rmin), dc = (float)info[frame].dc;
     const size_t n = (size_t)g.W * g.H, np = (size_t)g.Wp * g.Hp;
-    float mx = 0.0f; double sum = 0.0;
+    float mx = 0.0f; long long sum = 0;
+    // |orig - dec| and the de-normalised residual both lie within the residual range: |e| <= 2 max(|rmin|, |rmax|) < 2^ex
+    const int ex = err_fx_exp(__fmul_rn(2.0f, fmaxf(fabsf(rmin), fabsf(info[frame].rmax))));
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         const int y = (int)(i / g.W), x = (int)(i - (size_t)y * g.W);
         const float r = sp_pixel_to_residual(img[(size_t)frame * np + (size_t)y * g.Wp + x], dc, rmin, range);
         const float e = __fsub_rn(orig[(size_t)frame * n + i], __fadd_rn(dec[(size_t)frame * n + i], r));
-        mx = fmaxf(mx, fabsf(e)); sum += (double)e;
+        mx = fmaxf(mx, fabsf(e)); sum += err_fx(e, ex);
     }
     for (int o = 16; o > 0; o >>= 1) { mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o)); sum += __shfl_xor_sync(0xffffffffu, sum, o); }
-    if ((threadIdx.x & 31) == 0) { atomicMax(&es[frame].max_err_bits, __float_as_uint(mx)); atomicAdd(&es[frame].sum_err, sum); }
+    if ((threadIdx.x & 31) == 0) { atomicMax(&es[frame].max_err_bits, __float_as_uint(mx)); atomicAdd((unsigned long long *)&es[frame].sum_fx, (unsigned long long)sum); }
+    if (blockIdx.x == 0 && threadIdx.x == 0) es[frame].sum_exp = ex;
 }
 
 // decode path: out += residual

@@ -150,15 +150,30 @@ __device__ __forceinline__ unsigned cf_sigpass_col(unsigned f, unsigned n, const
     return fresh;
 }
 
+// rows b4 of the stripe column with flag-word index p became significant in coding pass `pass`
+__device__ __forceinline__ void t1_rec_pass(unsigned char *rec_pass, size_t base, int W, int p, unsigned b4, int pass)
+{
+    const int s = p / CF_W - 1, x = p - (s + 1) * CF_W - 1;
+    unsigned char *d = rec_pass + base + (size_t)(4 * s) * W + x;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        if ((b4 >> j) & 1u) d[(size_t)j * W] = (unsigned char)pass;
+}
+
 // 3 CTAs per SM caps the kernel at 40 registers: room for the long-lived MQ CTAs of other batches in flight
 #ifndef T1_MIN_CTAS
 #define T1_MIN_CTAS 3
 #endif
-__global__ void __launch_bounds__(T1_THREADS, T1_MIN_CTAS)
+template <bool REC>
+__global__ void __launch_bounds__(T1_THREADS, REC ? 2 : T1_MIN_CTAS)      // the recording stores need a few more registers
 k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, const BandDesc *__restrict__ bands,
         const T1Luts *__restrict__ g_luts, const unsigned char *__restrict__ zc_lut, CblkOut *cbout, unsigned char *sym_pool,
-        int W, int H, int ncblks, size_t sym_stride)
+        int W, int H, int ncblks, size_t sym_stride, int *rec_val, unsigned char *rec_pass, FrameStat *stat)
 {
+    // REC: rec_val / rec_pass (compression-ratio search): the *recording* a tier-1 decoder of the complete
+    // segment would leave behind -- per sample the decoded value after all passes, sign * (2 M + 1) in the decoder's
+    // half units (t1.c:582-1140), and the coding pass in which the sample became significant.  The encoder knows both:
+    // k_recon_dequant rebuilds from them what "decode the first n passes" yields for any n, without decoding anything.
     __shared__ unsigned F[CF_WORDS];        // flag words
     __shared__ unsigned N[CF_WORDS];        // significance gained in the running pass, same neighbourhood layout
     __shared__ unsigned SG[CF_WORDS];       // static: sign of rows -1..4 of the column (bits 0..5)
@@ -209,6 +224,10 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
                     mag[k][j] = (unsigned)a;
                     if (v < 0) sgn4[k] |= 1u << j;
                     mymax = max(mymax, a);
+                    if (REC) {
+                        const int m = a >> 6;
+                        rec_val[(size_t)frame * H * W + (size_t)(cb.ty + 4 * s + j) * W + cb.tx + x] = m ? (v < 0 ? -(2 * m + 1) : 2 * m + 1) : 0;
+                    }
                 }
             N[sidx[k]] = sgn4[k];          // staging for SG
         }
@@ -275,8 +294,10 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
                 const int p = sidx[k];
                 const unsigned f = F[p];
                 unsigned coded = 0;
-                if ((~cf_own4(f) & ((1u << lim[k]) - 1u)) != 0)
-                    cf_sigpass_col<true>(f, N[p], mag[k], one, lim[k], sgn4[k], zc, SG, p, &luts, bpno, sq[0], coded, nm[0]);
+                if ((~cf_own4(f) & ((1u << lim[k]) - 1u)) != 0) {
+                    const unsigned fr = cf_sigpass_col<true>(f, N[p], mag[k], one, lim[k], sgn4[k], zc, SG, p, &luts, bpno, sq[0], coded, nm[0]);
+                    if (REC && fr) t1_rec_pass(rec_pass, (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx, W, p, fr, passno);
+                }
                 // state: the word absorbs what its neighbourhood gained, rows coded here are marked pi
                 const unsigned w = f | N[p] | (coded << 24);
                 F[p] = w;
@@ -314,7 +335,10 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
 #pragma unroll
                 for (int j = 0; j < 4; ++j) bits |= ((mag[k][j] & one) ? 1u : 0u) << j;
                 fresh[k] = cand & bits;
-                if (fresh[k]) cf_scatter(N, sidx[k], fresh[k]);
+                if (fresh[k]) {
+                    cf_scatter(N, sidx[k], fresh[k]);
+                    if (REC) t1_rec_pass(rec_pass, (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx, W, sidx[k], fresh[k], first ? passno : passno + 2);
+                }
             }
             __syncthreads();
 #pragma unroll
@@ -383,7 +407,9 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
         for (int q = 0; q < 3; ++q) {
             const unsigned tot = (unsigned)(total3 >> (21 * q)) & 0x1fffffu, off = (unsigned)(excl >> (21 * q)) & 0x1fffffu;
             unsigned char *dst = sym + base + off;
-            for (int i = 0; i < sq[q].cnt; ++i) dst[i] = sq[q].p[i];
+            // the slice holds the worst case (1.5 symbols per sample and plane + one sign, build_plan); checked all the same
+            const int room = (int)cb.sym_cap - (int)(base + off), cn = min(sq[q].cnt, max(room, 0));
+            for (int i = 0; i < cn; ++i) dst[i] = sq[q].p[i];
             base += tot;
             if (tid == 0 && (q == 2 || !first)) {
                 const int pn = first ? passno : passno + q;
@@ -398,6 +424,7 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
 
     // ---- distortion per pass: opj_t1_getwmsedec, accumulated in pass order (t1.c:1416-1449, 2655) --
     if (tid == 0) {
+        if (total_syms > cb.sym_cap) atomicOr(&stat[frame].flags, STAT_OVERFLOW);
         out->totalpasses = passno;
         const double wn = bd->wnorm;
         double cum = 0.0;
@@ -452,13 +479,14 @@ struct MqEnc {
     unsigned a, c;
     int ct;
     int pos;                  // index of the pending (not yet stored) byte, -1 = OPJ's fake byte
+    int cap;                  // bytes the block's slice of the MQ pool holds
     unsigned pend;
     unsigned char *dst;
 };
 
 __device__ __forceinline__ void mq_advance(MqEnc &q, unsigned nb)
 {
-    if (q.pos >= 0) q.dst[q.pos] = (unsigned char)q.pend;
+    if (q.pos >= 0 && q.pos < q.cap) q.dst[q.pos] = (unsigned char)q.pend;
     q.pos++; q.pend = nb;
 }
 
@@ -479,9 +507,39 @@ __device__ __forceinline__ void mq_byteout(MqEnc &q)
     }
 }
 
-// end of coding pass p: segment length as opj_t1_encode_cblk records it (t1.c:2655-2699)
-__device__ __forceinline__ void mq_pass_end(MqEnc &q, CblkOut *out, int p, int npasses)
+// Is "decode passes 0..p from the segment cut at R bytes" the same as decoding them from the complete segment?
+// OPJ cuts a non-terminated pass at numbytes + 3 (t1.c:2673-2683), which is usually but not always enough; the
+// compression-ratio search has to know, because its probes must see what a real decoder sees.  The MQ decoder is an
+// exact interval decoder: it reproduces the symbols up to the end of pass p if and only if the value it reads lies in
+// the coder's interval [L, L + a) at that point.  Beyond the cut it reads the synthetic 0xFF 0xFF marker of
+// opj_mqc_init_dec, i.e. one-bits for ever (mqc_inl.h:77-99: c += 0xff00, ct = 8).  In units of a's LSB, relative to
+// everything before the coder's pending byte (index pos, value pend, may still take a carry):
+//     L = pend * 2^s + c,  s = 27 - ct        (bit 27 - ct of c is the carry into the pending byte, byteout mqc.c:492-523)
+//     X = sum_{i = pos}^{R-1} v[i] * 2^(s - off_i)  +  2^(s - off_{R-1})      (final bytes, then the ones)
+//         off_pos = 0, off_{i+1} = off_i + (v[i] == 0xff ? 7 : 8)               (bit stuffing)
+// and the cut is safe iff X <= L + a (X minus "an infinitesimal" is what the decoder sees).  Everything is scaled by
+// 2^8 so that the exponents stay non-negative (R - 1 - pos <= 2: at most two whole bytes lie behind the pending one).
+__device__ __forceinline__ bool mq_cut_proven(unsigned a, unsigned c, int ct, unsigned pend, int pos, int R, const unsigned char *v)
 {
+    if (R - 1 < pos || R - 1 - pos > 2) return false;       // cannot happen (rate >= numbytes + 1); a real decode settles it
+    const int s = 27 - ct + 8;
+    unsigned long long X = 0;
+    int off = 0, last = 0;
+    for (int i = pos; i < R; ++i) {
+        const unsigned vi = i < 0 ? 0u : (unsigned)v[i];      // index -1: OPJ's fake byte in front of the segment, never carried into
+        X += (unsigned long long)vi << (s - off);
+        last = off;
+        off += vi == 0xffu ? 7 : 8;
+    }
+    X += 1ull << (s - last);
+    const unsigned long long U = ((((unsigned long long)pend << (27 - ct)) + c + a) << 8);
+    return X <= U;
+}
+
+// end of coding pass p: segment length as opj_t1_encode_cblk records it (t1.c:2655-2699)
+__device__ __forceinline__ void mq_pass_end(MqEnc &q, CblkOut *out, int p, int npasses, bool snap)
+{
+    if (snap) { out->mqs[p][0] = q.c | ((unsigned)q.ct << 28); out->mqs[p][1] = q.a | (q.pend << 16); out->mqs[p][2] = (unsigned)q.pos; }
     if (p == npasses - 1) {
         // opj_mqc_flush (mqc.c:212-227)
         unsigned tempc = q.c + q.a;
@@ -509,8 +567,11 @@ template <int L>
 __global__ void __launch_bounds__(MQ_THREADS(L), MQ_MIN_CTAS)
 k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char *__restrict__ sym_pool,
         unsigned char *mq_pool, const MqTable *__restrict__ g_tab, int ncblks, int nframes,
-        size_t sym_stride, size_t mq_stride)
+        size_t sym_stride, size_t mq_stride, T1CutState *cuts, FrameStat *stat)
 {
+    // cuts != nullptr (compression-ratio search): the coder state at every pass end is kept and, once the segment is
+    // complete, every pass gets its verdict "cut at rate[p] decodes like the complete segment" (mq_cut_proven)
+    const bool snap = cuts != nullptr;
     constexpr int G = 32 / L;                     // lanes per code-block
     constexpr int R = L < 8 ? L : 8;              // 16-byte loads per lane and refill
     constexpr int CH = 16 * G * R;                // symbol bytes per refill and block: 512 (L <= 8), 256, 128
@@ -551,7 +612,7 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
     for (int k = gl; k < 16; k += G) stage[blk][CH + k] = 0;       // look-ahead slack behind the refill
 
     MqEnc q;
-    q.a = 0x8000; q.c = 0; q.ct = 12; q.pos = -1; q.pend = 0;
+    q.a = 0x8000; q.c = 0; q.ct = 12; q.pos = -1; q.pend = 0; q.cap = (int)cb.mq_cap;
     q.dst = mq_pool + (size_t)frame * mq_stride + cb.mq_off;
 
     unsigned char *stg = stage[blk];
@@ -615,15 +676,20 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
             }
             i += n;
             if (i == end) {
-                mq_pass_end(q, out, p, npasses);
+                mq_pass_end(q, out, p, npasses, snap);
                 end = ++p < npasses ? out->nsym_end[p] : 0xffffffffu;
             }
         }
     }
+    if (coder && valid && snap && npasses <= 0) {
+        T1CutState &cs = cuts[(size_t)frame * ncblks + cbi];
+        cs.np_dec = 0; cs.scratch_np = 0; cs.bad[0] = cs.bad[1] = cs.bad[2] = cs.bad[3] = 0;
+    }
     if (!coder || npasses <= 0) return;
-    for (; p < npasses; ++p) mq_pass_end(q, out, p, npasses);
+    for (; p < npasses; ++p) mq_pass_end(q, out, p, npasses, snap);
     // final pending byte (beyond numbytes) is never part of the stream
     int last = q.pos;
+    if (last > q.cap) { atomicOr(&stat[frame].flags, STAT_OVERFLOW); last = q.cap; }
     out->datalen = last;
     // monotone fix-up, then strip a trailing 0xFF from each pass (t1.c:2700-2723)
     for (int pp = npasses - 1; pp >= 0; --pp) {
@@ -633,5 +699,17 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
     for (int pp = 0; pp < npasses; ++pp) {
         int r = out->rate[pp];
         if (r > 0 && q.dst[r - 1] == 0xff) out->rate[pp] = r - 1;
+    }
+    if (snap) {
+        unsigned bad[4] = {0, 0, 0, 0};
+        for (int pp = 0; pp < npasses; ++pp) {
+            const unsigned w0 = out->mqs[pp][0], w1 = out->mqs[pp][1];
+            const bool ok = pp < 128 && mq_cut_proven(w1 & 0xffffu, w0 & 0x0fffffffu, (int)(w0 >> 28), (w1 >> 16) & 0xffu, (int)out->mqs[pp][2],
+                                                      out->rate[pp], q.dst);
+            if (!ok && pp < 128) bad[pp >> 5] |= 1u << (pp & 31);
+        }
+        T1CutState &cs = cuts[(size_t)frame * ncblks + cbi];
+        cs.np_dec = npasses; cs.scratch_np = 0;
+        cs.bad[0] = bad[0]; cs.bad[1] = bad[1]; cs.bad[2] = bad[2]; cs.bad[3] = bad[3];
     }
 }

@@ -21,6 +21,7 @@ typedef struct ebcc_cuda_ctx ebcc_cuda_ctx;
 
 #define EBCC_FRAME_CONST 1      /* min == max: no codestream produced          */
 #define EBCC_FRAME_NANINF 2     /* NaN or Inf in the frame (reference exit(1)) */
+#define EBCC_FRAME_OVERFLOW 4   /* a code-block outgrew its work-buffer slice (cannot happen within the stated bounds): no stream */
 
 /* stage names for ebcc_cuda_stage_ms */
 enum {
@@ -63,7 +64,11 @@ typedef struct {
     double sum_err;              /* sum of (d - decoded), double accumulation */
     size_t stream_bytes;         /* codestream length at this ratio */
 } ebcc_probe_result;
-int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *ctx, size_t nframes);
+/* for_search != 0: the analysis also leaves behind what the probes of the compression-ratio search need -- the
+ * tier-1 recording (decoded value + pass of significance per sample, straight from the encoder's context modelling)
+ * and, per code-block and pass, whether the segment cut at that pass decodes like the complete one */
+int ebcc_cuda_analyze(ebcc_cuda_ctx *ctx, size_t nframes, int for_search);
+int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *ctx, size_t nframes);   /* = ebcc_cuda_analyze(ctx, nframes, 1) */
 int ebcc_cuda_rate_probe(ebcc_cuda_ctx *ctx, size_t nframes, const float *cr, const float *targets, int with_streams,
                          ebcc_probe_result *res);
 
@@ -141,6 +146,7 @@ int ebcc_cuda_t1_totals(ebcc_cuda_ctx *ctx, size_t nframes, unsigned long long *
 
 /* debug/test taps on the resident batch (device -> host copies of intermediates) */
 int ebcc_cuda_debug_coef(ebcc_cuda_ctx *ctx, size_t frame, float *dst);
+int ebcc_cuda_debug_check_cuts(ebcc_cuda_ctx *ctx, size_t nframes, unsigned long long counts[4]);
 int ebcc_cuda_debug_spiht_stream(ebcc_cuda_ctx *ctx, size_t frame, uint8_t *dst, size_t cap, size_t *len);
 int ebcc_cuda_debug_cblk(ebcc_cuda_ctx *ctx, size_t frame, size_t cblk, int *numbps, int *totalpasses,
                          int *rates, double *dists, int *numpasses);

@@ -115,15 +115,38 @@ def check_residual_stage(frame, cr, verbose=False, probes=(1.0, 0.5, 0.23, 0.07)
     return bool(ok)
 
 
+def check_cuts(frames):
+    """every truncation point of every code-block: recording + verdict of the encoder vs a real truncated decode.
+    Returns (cuts checked, flagged unproven, flagged proven but different, flagged unproven but equal)."""
+    f = np.ascontiguousarray(frames, dtype=np.float32)
+    b, h, w = f.shape
+    lib = cuda_api()
+    lib.ebcc_cuda_debug_check_cuts.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+    ctx = C.c_void_p(lib.ebcc_cuda_ctx_create(0))
+    assert ctx.value
+    try:
+        assert lib.ebcc_cuda_reserve(ctx, h, w, b) == 0
+        assert lib.ebcc_cuda_upload(ctx, f.ctypes.data, b) == 0
+        assert lib.ebcc_cuda_analyze_resident(ctx, b) == 0
+        cnt = (C.c_ulonglong * 4)()
+        assert lib.ebcc_cuda_debug_check_cuts(ctx, b, cnt) == 0
+        return tuple(int(x) for x in cnt)
+    finally:
+        lib.ebcc_cuda_ctx_destroy(ctx)
+
+
 def probe_sequence(frames, crs, target, recording):
     """error statistics of a sequence of rate probes over a resident batch; recording=False forces a real tier-1
-    decode of every block in every probe (EBCC_NO_RECORDING=1)"""
+    decode of every block in every probe (EBCC_NO_RECORDING=1), recording="decoder" makes the recordings with the
+    tier-1 decoder and its truncation shadows (EBCC_DECODER_RECORDING=1) instead of taking them from the encoder"""
     import os
     f = np.ascontiguousarray(frames, dtype=np.float32)
     b, h, w = f.shape
-    if recording:
-        os.environ.pop("EBCC_NO_RECORDING", None)
-    else:
+    os.environ.pop("EBCC_NO_RECORDING", None)
+    os.environ.pop("EBCC_DECODER_RECORDING", None)
+    if recording == "decoder":
+        os.environ["EBCC_DECODER_RECORDING"] = "1"
+    elif not recording:
         os.environ["EBCC_NO_RECORDING"] = "1"
     lib = cuda_api()
     ctx = C.c_void_p(lib.ebcc_cuda_ctx_create(0))
@@ -142,4 +165,5 @@ def probe_sequence(frames, crs, target, recording):
     finally:
         lib.ebcc_cuda_ctx_destroy(ctx)
         os.environ.pop("EBCC_NO_RECORDING", None)
+        os.environ.pop("EBCC_DECODER_RECORDING", None)
     return out

@@ -115,6 +115,21 @@ def test_batch_equals_single_max_error(built):
         assert np.abs(H.decode(lib, got) - frames[t].ravel()).max() <= 0.1
 
 
+@pytest.mark.parametrize("shape,nf", [((96, 160), 2), ((64, 64), 3), ((200, 130), 1)])
+def test_every_cut_verdict_small(built, shape, nf):
+    """the encoder's recording + its verdict per truncation point vs a real truncated decode, for EVERY pass of EVERY block"""
+    checked, unproven, wrong, pessimistic = S.check_cuts(H.synth_stack(nf, shape[0], shape[1]))
+    assert checked > 0 and wrong == 0, (checked, unproven, wrong, pessimistic)
+
+
+def test_every_cut_verdict_full_frames(built):
+    frames = np.concatenate([H.synth_stack(2), np.load(os.path.join(GOLDEN, "era5_t2m_721x1440.npy"))[None]], axis=0)
+    checked, unproven, wrong, pessimistic = S.check_cuts(frames)
+    print("cuts checked %d, unproven %d, proven-but-different %d, unproven-but-equal %d" % (checked, unproven, wrong, pessimistic))
+    assert checked > 20000 and wrong == 0
+    assert pessimistic == 0          # the criterion is exact: a cut it rejects really decodes differently
+
+
 def test_recording_equals_real_decodes(built):
     """CR-search probes served from the pass recording (one tier-1 decode + truncation shadows) must give exactly the
     statistics of probes that decode every block for real, for ratios below and above the recorded one."""
@@ -123,3 +138,4 @@ def test_recording_equals_real_decodes(built):
     a = S.probe_sequence(frames, crs, 0.3, True)
     b = S.probe_sequence(frames, crs, 0.3, False)
     assert a == b
+    assert a == S.probe_sequence(frames, crs, 0.3, "decoder")       # round-1 recordings (tier-1 decoder + shadows) agree too

@@ -105,6 +105,7 @@ static inline double __dsub_rn(double a, double b) { return a - b; }
 static inline double __dmul_rn(double a, double b) { return a * b; }
 static inline double __ddiv_rn(double a, double b) { return a / b; }
 static inline int __float2int_rn(float a) { return (int)lrintf(a); }
+static inline long long __double2ll_rn(double a) { return llrint(a); }
 static inline int __float2int_rz(float a) { return (int)a; }
 static inline unsigned __float2uint_rz(float a) { return a <= 0 ? 0u : (unsigned)a; }
 static inline float __int2float_rn(int a) { return (float)a; }
