@@ -14,7 +14,10 @@
 #else
 #include <cuda_runtime.h>
 #include <stdint.h>
-#define EBCC_LAUNCH(kern, grid, block, smem, stream, ...) kern<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+// every kernel launch of the library goes through this macro and is counted process-wide (ebcc_cuda_total_launches)
+static unsigned long long g_ebcc_launches = 0;
+#define EBCC_LAUNCH(kern, grid, block, smem, stream, ...) \
+    (__atomic_fetch_add(&g_ebcc_launches, 1ull, __ATOMIC_RELAXED), kern<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__))
 #define EBCC_DYN_SMEM(type, name) extern __shared__ __align__(16) unsigned char name##_raw_[]; type *name = (type *)name##_raw_
 #endif
 #include <stddef.h>
@@ -77,7 +80,11 @@ struct CblkOut {
 // a decode of the complete segment (OPJ truncates non-terminated MQ segments at numbytes+3, which is not always
 // enough; mq_cut_proven in k_t1.cuh).  scratch_np: pass count of the real truncated decode the scratch plane
 // currently holds for this block (0 = none).
-struct T1CutState { int np_dec; int scratch_np; unsigned bad[4]; };
+// first_entry: index of the block's first entry in the pool of pre-decoded unproven cuts (k_t1_dec_cuts), its entries
+// follow in pass order; < 0: not pooled, such a cut is decoded when a probe asks for it.
+struct T1CutState { int np_dec; int scratch_np; unsigned bad[4]; int first_entry; int pad; };
+struct T1CutEntry { unsigned bi; int np; };        // block (frame * ncblks + cblk), passes to decode from the segment cut at rate[np - 1]
+#define T1_CUT_WORDS (J2K_CBLK * J2K_CBLK)         // ints per pool entry: the decoded block, row stride J2K_CBLK
 
 struct Plan {
     int H, W, nbands, ncblks;

@@ -27,6 +27,17 @@
         }                                                                                            \
     } while (0)
 
+// ---- per-kernel-class device times (bench.py's roofline; off by default) -------------------------------------------
+// When switched on (ebcc_cuda_kernel_timing(1)) every launch group below is bracketed by two CUDA events on the stream it
+// is launched on; the pairs are read back at the pipeline's next synchronisation point and added up process-wide, so
+// the figures describe the kernels in the configuration that is actually running (all pipelines in flight).
+#include <pthread.h>
+static int g_kt_on = 0;
+static pthread_mutex_t g_kt_mu = PTHREAD_MUTEX_INITIALIZER;
+static double g_kt_ms[EBCC_KT_COUNT];
+static unsigned long long g_kt_n[EBCC_KT_COUNT];
+#define KT_RING 192
+
 // ---- compaction of the per-frame codestreams into one contiguous buffer --------------------------
 __global__ void k_offsets(const ProbeOut *__restrict__ pout, unsigned long long *offs, int nframes)
 {
@@ -299,6 +310,8 @@ struct ebcc_cuda_ctx {
     int *d_scratch;            // [B][H][W] per-probe real decodes of blocks the recording cannot serve
     unsigned char *d_spass;    // [B][H][W] pass in which each sample became significant (recording)
     DecState *d_dstate;        // [B][ncblks]
+    T1CutEntry *d_cut_list;    // unproven truncation points of the batch and their pre-decoded blocks (k_t1_dec_cuts)
+    int *d_cut_count, *d_cut_pool, cut_cap;
     unsigned *d_decsave;       // [B][ncblks][DEC_SAVE_WORDS] decoder state of each block's recording (resumed by later probes)
     int use_recording;         // 0: every probe decodes every block for real (EBCC_NO_RECORDING=1)
     int rec_from_encoder;      // recording + cut verdicts come from the encoder (k_t1_cm / k_t1_mq); 0: from k_t1_dec (EBCC_DECODER_RECORDING=1)
@@ -348,6 +361,8 @@ struct ebcc_cuda_ctx {
     // multi-tile images (dims[0] > 1, src/ebcc_codec.c:105-180): this context holds the image-level data (input,
     // min/max, decoded image, residual layer, assembled codestreams); tile t of every image of the batch is coded by
     // tile[t], a light context with the tile's own geometry that shares this context's stream and look-up tables
+    cudaEvent_t kt_ev[2 * KT_RING];   // kernel-class timing: event pairs recorded since the last synchronisation
+    int kt_id[KT_RING], kt_n, kt_have;
     int crowd;                 // pipelines at work on this device (hint from the host codec), see mq_lanes()
     int env_mq_lanes, env_dec_lanes, env_no_recording, env_dec_recording, env_debug_lanes;   // tuning / debugging variables, read once per host call (read_env)
     int ntiles;
@@ -357,15 +372,66 @@ struct ebcc_cuda_ctx {
 };
 
 static void read_env(ebcc_cuda_ctx *c);
+static ebcc_cuda_ctx *ctx_root_mut(ebcc_cuda_ctx *c) { return c->parent ? c->parent : c; }
+
+// scope of one launch group of kernel class `id`
+struct KT {
+    ebcc_cuda_ctx *r; int slot;
+    KT(ebcc_cuda_ctx *c, int id) : r(NULL), slot(-1)
+    {
+        if (!g_kt_on) return;
+        r = ctx_root_mut(c);
+        if (!r->kt_have) { for (int i = 0; i < 2 * KT_RING; ++i) cudaEventCreate(&r->kt_ev[i]); r->kt_have = 1; }
+        if (r->kt_n >= KT_RING) { r = NULL; return; }
+        slot = r->kt_n++; r->kt_id[slot] = id;
+        cudaEventRecord(r->kt_ev[2 * slot], r->stream);
+    }
+    ~KT() { if (r) cudaEventRecord(r->kt_ev[2 * slot + 1], r->stream); }
+};
+
+// after a synchronisation of the pipeline's stream: every recorded pair has completed
+static void kt_harvest(ebcc_cuda_ctx *c)
+{
+    ebcc_cuda_ctx *r = ctx_root_mut(c);
+    if (!r->kt_n) return;
+    pthread_mutex_lock(&g_kt_mu);
+    for (int i = 0; i < r->kt_n; ++i) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, r->kt_ev[2 * i], r->kt_ev[2 * i + 1]) == cudaSuccess) { g_kt_ms[r->kt_id[i]] += ms; g_kt_n[r->kt_id[i]]++; }
+        else (void)cudaGetLastError();
+    }
+    pthread_mutex_unlock(&g_kt_mu);
+    r->kt_n = 0;
+}
+
+extern "C" void ebcc_cuda_kernel_timing(int enable)
+{
+    pthread_mutex_lock(&g_kt_mu);
+    for (int i = 0; i < EBCC_KT_COUNT; ++i) { g_kt_ms[i] = 0; g_kt_n[i] = 0; }
+    g_kt_on = enable;
+    pthread_mutex_unlock(&g_kt_mu);
+}
+
+extern "C" int ebcc_cuda_kernel_timing_report(double *ms, unsigned long long *groups, int n)
+{
+    pthread_mutex_lock(&g_kt_mu);
+    for (int i = 0; i < n && i < EBCC_KT_COUNT; ++i) { ms[i] = g_kt_ms[i]; groups[i] = g_kt_n[i]; }
+    pthread_mutex_unlock(&g_kt_mu);
+    return EBCC_KT_COUNT;
+}
 
 // Wait for the pipeline's stream.  Several pipelines (and, on a multi-GPU box, several ranks) share the host cores:
 // the waiting thread sleeps on a blocking-sync event unless EBCC_SPIN_SYNC=1 asks for the lower-latency spin wait.
 static cudaError_t ctx_sync(ebcc_cuda_ctx *c)
 {
-    if (c->spin_sync) return cudaStreamSynchronize(c->stream);
-    cudaError_t e = cudaEventRecord(c->ev_sync, c->stream);
-    if (e != cudaSuccess) return e;
-    return cudaEventSynchronize(c->ev_sync);
+    cudaError_t e;
+    if (c->spin_sync) e = cudaStreamSynchronize(c->stream);
+    else {
+        e = cudaEventRecord(c->ev_sync, c->stream);
+        if (e == cudaSuccess) e = cudaEventSynchronize(c->ev_sync);
+    }
+    if (e == cudaSuccess) kt_harvest(c);
+    return e;
 }
 
 
@@ -448,6 +514,7 @@ static void free_buffers(ebcc_cuda_ctx *c)
     cudaFreeHost(c->h_pout); cudaFreeHost(c->h_stat); cudaFreeHost(c->h_offs); cudaFreeHost(c->h_maxlen);
     cudaFreeHost(c->h_packed); cudaFreeHost(c->h_stage);
     cudaFree(c->d_streams); cudaFree(c->d_slens); cudaFree(c->d_status); cudaFree(c->d_jobs); cudaFree(c->d_iplane); cudaFree(c->d_scratch); cudaFree(c->d_spass); cudaFree(c->d_dstate); cudaFree(c->d_decsave);
+    cudaFree(c->d_cut_list); cudaFree(c->d_cut_count); cudaFree(c->d_cut_pool); c->d_cut_list = NULL; c->d_cut_count = NULL; c->d_cut_pool = NULL;
     c->d_scratch = NULL; c->d_spass = NULL; c->d_dstate = NULL; c->d_decsave = NULL;
     cudaFree(c->d_dcoef); cudaFree(c->d_dec); cudaFree(c->d_es); cudaFree(c->d_targets);
     cudaFreeHost(c->h_es); cudaFreeHost(c->h_status); cudaFreeHost(c->h_slens); cudaFreeHost(c->h_targets); cudaFreeHost(c->h_streams);
@@ -484,6 +551,7 @@ extern "C" void ebcc_cuda_ctx_destroy(ebcc_cuda_ctx *c)
     free_buffers(c);
     cudaFree(c->d_luts); cudaFree(c->d_mqtab); cudaFree(c->d_declut); cudaFree(c->d_step_tab);
     for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventDestroy(c->ev[i]);
+    if (c->kt_have) for (int i = 0; i < 2 * KT_RING; ++i) cudaEventDestroy(c->kt_ev[i]);
     cudaStreamDestroy(c->stream);
     free(c);
 }
@@ -557,6 +625,11 @@ static int reserve_alloc(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes, i
     CK(cudaMalloc((void **)&c->d_scratch, B * N * sizeof(int)));
     CK(cudaMalloc((void **)&c->d_spass, B * N));
     CK(cudaMalloc((void **)&c->d_dstate, B * pl->ncblks * sizeof(DecState)));
+    // about 13 unproven cuts per 721 x 1440 frame (1 in 1000 of ~13 400 truncation points): room for several times that
+    c->cut_cap = (int)(B * (size_t)(pl->ncblks / 3 + 8) + 256);
+    CK(cudaMalloc((void **)&c->d_cut_list, (size_t)c->cut_cap * sizeof(T1CutEntry)));
+    CK(cudaMalloc((void **)&c->d_cut_count, sizeof(int)));
+    CK(cudaMalloc((void **)&c->d_cut_pool, (size_t)c->cut_cap * T1_CUT_WORDS * sizeof(int)));
     CK(cudaMalloc((void **)&c->d_decsave, B * pl->ncblks * (size_t)DEC_SAVE_WORDS * sizeof(unsigned)));
     CK(cudaMalloc((void **)&c->d_dcoef, B * N * sizeof(float)));
     CK(cudaMalloc((void **)&c->d_dec, B * N * sizeof(float)));
@@ -660,6 +733,7 @@ static int launch_dwt(ebcc_cuda_ctx *c, int B)
 {
     const Plan *pl = &c->plan;
     const int W = pl->W, H = pl->H;
+    KT kt_(c, EBCC_KT_DWT);
     for (int r = J2K_NRES - 1; r >= 1; --r) {
         const int rw = pl->res_w[r], rh = pl->res_h[r];
         // vertical: strips of CW columns, full height in shared memory
@@ -722,6 +796,7 @@ extern "C" void ebcc_cuda_set_crowd(ebcc_cuda_ctx *c, int pipelines_at_work) { i
 static int launch_minmax(ebcc_cuda_ctx *c, int B)
 {
     const int N = c->plan.H * c->plan.W;
+    KT kt_(c, EBCC_KT_MINMAX);
     EBCC_LAUNCH(k_stat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_stat, B);
     // enough CTAs to keep every SM loading: 74 per frame for a batch, 296 for a handful of frames
     EBCC_LAUNCH(k_minmax, dim3(B >= 8 ? 74u : 296u, (unsigned)B), dim3(256), 0, c->stream, c->d_in, c->d_stat, N);
@@ -783,6 +858,7 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int f
     if (launch_dwt(c, B)) return -1;
 
     mark(c, EBCC_ST_T1_CM);
+    KT *kt_cm = new KT(c, EBCC_KT_T1_CM);
     if (c->rec_from_encoder)
         EBCC_LAUNCH(k_t1_cm<true>, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
                     c->d_coef, c->d_cblks, c->d_bands, c->d_luts, (const unsigned char *)c->d_declut, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks,
@@ -791,8 +867,10 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int f
         EBCC_LAUNCH(k_t1_cm<false>, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
                     c->d_coef, c->d_cblks, c->d_bands, c->d_luts, (const unsigned char *)c->d_declut, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks,
                     pl->sym_stride, (int *)NULL, (unsigned char *)NULL, c->d_stat);
+    delete kt_cm;
     mark(c, EBCC_ST_T1_MQ);
     {
+        KT kt_(c, EBCC_KT_T1_MQ);
         const long long jobs = (long long)pl->ncblks * B;
         const int lanes = mq_lanes(c, jobs);                     // code-blocks per warp: 1, 2, 4, 8, 16 or 32
         if (ctx_root(c)->env_debug_lanes) fprintf(stderr, "[ebcc-cuda] mq lanes %d (crowd %d, jobs %lld)\n", lanes, ctx_crowd(c), jobs);
@@ -805,6 +883,18 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int f
 #undef MQ_GO
     }
     c->launches += 2;
+    if (c->rec_from_encoder) {
+        // every unproven truncation point of the batch is decoded now, all of them side by side (see k_t1_dec_cuts)
+        KT kt_(c, EBCC_KT_T1_DEC);
+        const long long jobs = (long long)pl->ncblks * B;
+        CK(cudaMemsetAsync(c->d_cut_count, 0, sizeof(int), c->stream));
+        EBCC_LAUNCH(k_cut_collect, dim3((unsigned)((jobs + 255) / 256)), dim3(256), 0, c->stream, (const CblkOut *)c->d_cbout, c->d_dstate, c->d_cut_list,
+                    c->d_cut_count, c->cut_cap, jobs);
+        EBCC_LAUNCH(k_t1_dec_cuts, dim3((unsigned)((c->cut_cap + CUT_WPC - 1) / CUT_WPC)), dim3(CUT_WPC * 32), 0, c->stream, c->d_cblks, (const CblkOut *)c->d_cbout,
+                    (const T1CutEntry *)c->d_cut_list, (const int *)c->d_cut_count, c->cut_cap, (const unsigned char *)c->d_mq, pl->mq_stride, c->d_declut,
+                    c->d_cut_pool, pl->ncblks);
+        c->launches += 2;
+    }
     CK(cudaGetLastError());
     return 0;
 }
@@ -833,11 +923,15 @@ static int launch_rate_stage(ebcc_cuda_ctx *c, int B, const float *cr, int with_
     for (int i = 0; i < B; ++i) c->h_maxlen[i] = tile_maxlen(pl->H, pl->W, cr[i], pl->main_header_len, pl->ntiles);
     CK(cudaMemcpyAsync(c->d_maxlen, c->h_maxlen, sizeof(int) * B, cudaMemcpyHostToDevice, c->stream));
     mark(c, EBCC_ST_PCRD_T2);
-    EBCC_LAUNCH(k_pcrd_t2, dim3((unsigned)B), dim3(T2_THREADS), t2_smem_bytes(pl->ncblks, pl->nnodes), c->stream,
-                c->d_plan, c->d_cblks, c->d_cbout, c->d_maxlen, c->d_out, c->d_body_off, c->d_pout, c->d_stat);
+    {
+        KT kt_(c, EBCC_KT_PCRD_T2);
+        EBCC_LAUNCH(k_pcrd_t2, dim3((unsigned)B), dim3(T2_THREADS), t2_smem_bytes(pl->ncblks, pl->nnodes), c->stream,
+                    c->d_plan, c->d_cblks, c->d_cbout, c->d_maxlen, c->d_out, c->d_body_off, c->d_pout, c->d_stat);
+    }
     c->launches += 1;
     mark(c, EBCC_ST_BODIES);
     if (with_bodies) {
+        KT kt_(c, EBCC_KT_BODIES);
         EBCC_LAUNCH(k_t2_bodies, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(128), 0, c->stream,
                     c->d_plan, c->d_cblks, c->d_cbout, c->d_mq, c->d_body_off, c->d_out, c->d_pout);
         EBCC_LAUNCH(k_offsets, dim3(1), dim3(32), 0, c->stream, c->d_pout, c->d_offs, B);
@@ -869,6 +963,7 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
     const long long njobs = (long long)pl->ncblks * B;
     const bool probe = orig != NULL;         // probe of the CR search: jobs come from the encoder, the recording is used
     {
+        KT kt_(c, EBCC_KT_T1_DEC);
         const int lanes = dec_lanes(c);                         // code-blocks per warp of the tier-1 decoder: 1, 2, 4 or 8
         const long long per_cta = (long long)DEC_WPC(lanes) * lanes;
         const dim3 grid((unsigned)((njobs + per_cta - 1) / per_cta)), block((unsigned)(DEC_WPC(lanes) * 32));
@@ -879,12 +974,15 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
         if (lanes == 8) DEC_GO(8); else if (lanes == 4) DEC_GO(4); else if (lanes == 2) DEC_GO(2); else DEC_GO(1);
 #undef DEC_GO
     }
+    KT *kt_rc = new KT(c, EBCC_KT_RECON);
     if (probe)
         EBCC_LAUNCH(k_recon_dequant, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_plan, c->d_cbout, c->d_dstate, c->d_jobs,
-                    c->d_iplane, c->d_spass, c->d_scratch, c->d_dcoef);
+                    c->d_iplane, c->d_spass, c->d_scratch, c->d_dcoef, c->d_cblks, (const int *)c->d_cut_pool);
     else
         EBCC_LAUNCH(k_dequant, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_iplane, c->d_dcoef, c->d_plan, B);
+    delete kt_rc;
     c->launches += 2;
+    KT *kt_iw = new KT(c, EBCC_KT_IDWT);
     for (int r = 1; r < J2K_NRES; ++r) {
         const int rw = pl->res_w[r], rh = pl->res_h[r];
         int RH = 4;
@@ -897,6 +995,8 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
                     (size_t)rh * CW * sizeof(float), c->stream, c->d_dcoef, W, H, rw, rh, pl->res_h[r - 1], pl->cas_v[r]);
         c->launches += 2;
     }
+    delete kt_iw;
+    KT kt_fin(c, EBCC_KT_FINALIZE);
     if (orig) { EBCC_LAUNCH(k_errstat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_es, B); c->launches++; }
     EBCC_LAUNCH(k_finalize, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_dcoef, c->d_dec, c->d_stat, orig,
                 orig ? c->d_targets : (const float *)NULL, c->d_es, N);
@@ -1013,6 +1113,7 @@ extern "C" int ebcc_cuda_residual_encode(ebcc_cuda_ctx *c, size_t nframes, const
     CK(cudaMemsetAsync(c->sp.D, 0, (size_t)B * Np * 4, c->stream));
     CK(cudaMemsetAsync(c->sp.L, 0, (size_t)B * Np * 4, c->stream));
     const dim3 ge(148 * 2, (unsigned)B);
+    KT *kt_fw = new KT(c, EBCC_KT_SP_FWD);
     EBCC_LAUNCH(k_sp_load, ge, dim3(256), 0, c->stream, c->d_in, c->d_dec, c->d_sp_img0, c->d_sp_info, g);
     EBCC_LAUNCH(k_sp_subdc, ge, dim3(256), 0, c->stream, c->d_sp_img0, c->d_sp_info, g);
     c->launches += 3;
@@ -1029,7 +1130,9 @@ extern "C" int ebcc_cuda_residual_encode(ebcc_cuda_ctx *c, size_t nframes, const
     EBCC_LAUNCH(k_sp_desc, dim3(148, (unsigned)B), dim3(256), 0, c->stream, c->sp.coef, c->sp.D, c->sp.L, c->d_sp_info, g, g.Wp / 4, g.Hp / 4, g.Wp / 2, g.Hp / 2);
     EBCC_LAUNCH(k_sp_desc, dim3(148, (unsigned)B), dim3(256), 0, c->stream, c->sp.coef, c->sp.D, c->sp.L, c->d_sp_info, g, g.Wp / 8, g.Hp / 8, g.Wp / 4, g.Hp / 4);
     EBCC_LAUNCH(k_sp_desc, dim3(148, (unsigned)B), dim3(256), 0, c->stream, c->sp.coef, c->sp.D, c->sp.L, c->d_sp_info, g, 0, 0, g.Wp / 8, g.Hp / 8);
-    EBCC_LAUNCH(k_sp_encode, dim3((unsigned)B), dim3(SP_THREADS), 0, c->stream, c->sp, c->d_sp_info, g, c->d_step_tab);
+    delete kt_fw;
+    { KT kt_(c, EBCC_KT_SP_ENCODE);
+    EBCC_LAUNCH(k_sp_encode, dim3((unsigned)B), dim3(SP_THREADS), 0, c->stream, c->sp, c->d_sp_info, g, c->d_step_tab); }
     c->launches += 5;
     CK(cudaMemcpyAsync(c->h_sp_info, c->d_sp_info, sizeof(SpInfo) * B, cudaMemcpyDeviceToHost, c->stream));
     CK(ctx_sync(c));
@@ -1075,12 +1178,14 @@ extern "C" int ebcc_cuda_residual_probe(ebcc_cuda_ctx *c, size_t nframes, const 
     }
     CK(cudaMemcpyAsync(c->d_sp_P, c->h_sp_P, 4 * B, cudaMemcpyHostToDevice, c->stream));
     const dim3 ge(148 * 2, (unsigned)B);
+    KT *kt_pr = new KT(c, EBCC_KT_SP_PROBE);
     EBCC_LAUNCH(k_sp_recon, ge, dim3(256), 0, c->stream, c->sp, c->d_sp_info, c->d_sp_P, c->d_sp_img0, g);
     c->launches++;
     if (sp_launch_inverse(c, B)) return -1;
     EBCC_LAUNCH(k_errstat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_es2, B);
     EBCC_LAUNCH(k_sp_errstat, ge, dim3(256), 0, c->stream, c->d_sp_img0, c->d_in, c->d_dec, c->d_sp_info, c->d_sp_P, c->d_es2, g);
     c->launches += 2;
+    delete kt_pr;
     CK(cudaMemcpyAsync(c->h_es2, c->d_es2, sizeof(ErrStat) * B, cudaMemcpyDeviceToHost, c->stream));
     CK(ctx_sync(c));
     CK(cudaGetLastError());
@@ -1106,10 +1211,12 @@ extern "C" int ebcc_cuda_residual_pack(ebcc_cuda_ctx *c, size_t nframes, const s
     size_t maxn = 0;
     for (int i = 0; i < B; ++i) if (coeffs_size[i] > maxn) maxn = coeffs_size[i];
     const int nch = (int)((maxn + Z_CHUNK - 1) / Z_CHUNK);
+    KT *kt_z = new KT(c, EBCC_KT_ZSTD_ENC);
     EBCC_LAUNCH(k_zstd_compress_chunks, dim3((unsigned)nch, (unsigned)B), dim3(ZC_THREADS), sizeof(ZEncWork), c->stream, (const unsigned char *)c->sp.bits,
                 c->sp.bits_words * 4, c->d_zsrc_len, c->d_zblk, c->d_zblen, c->zmaxchunks);
     EBCC_LAUNCH(k_zstd_assemble, dim3((unsigned)B), dim3(256), 0, c->stream, c->d_zblk, c->d_zblen, c->zmaxchunks, c->d_zsrc_len, c->d_zout,
                 c->zstride, c->d_zlen);
+    delete kt_z;
     c->launches++;
     c->launches++;
     CK(cudaMemcpyAsync(c->h_zlen, c->d_zlen, 4 * B, cudaMemcpyDeviceToHost, c->stream));
@@ -1178,8 +1285,11 @@ extern "C" int ebcc_cuda_decode_batch_tiled(ebcc_cuda_ctx *c, const uint8_t *con
     EBCC_LAUNCH(k_set_stat, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_stat, (const float *)c->d_es, B);
     c->launches++;
     if (T == 1) {
-        EBCC_LAUNCH(k_t2_parse, dim3((unsigned)B), dim3(32), (size_t)pl->nnodes * 4 * sizeof(int), c->stream,
-                    c->d_plan, c->d_cblks, c->d_streams, pl->out_stride, c->d_slens, c->d_jobs, c->d_status);
+        {
+            KT kt_(c, EBCC_KT_T2_PARSE);
+            EBCC_LAUNCH(k_t2_parse, dim3((unsigned)B), dim3(32), (size_t)pl->nnodes * 4 * sizeof(int), c->stream,
+                        c->d_plan, c->d_cblks, c->d_streams, pl->out_stride, c->d_slens, c->d_jobs, c->d_status);
+        }
         c->launches++;
         if (run_decode_stage(c, B, c->d_streams, pl->out_stride, NULL)) return -1;
     } else {
@@ -1216,13 +1326,22 @@ extern "C" int ebcc_cuda_decode_batch_tiled(ebcc_cuda_ctx *c, const uint8_t *con
         CK(cudaMemcpyAsync(c->d_zcap, c->h_zcap, 4 * B, cudaMemcpyHostToDevice, c->stream));
         CK(cudaMemsetAsync(c->sp.bits, 0, (size_t)B * c->sp.bits_words * 4, c->stream));
         EBCC_LAUNCH(k_sp_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_sp_info, c->d_sp_rmm, c->d_sp_budget, c->d_sp_active, B);
-        EBCC_LAUNCH(k_zstd_decompress, dim3((unsigned)B), dim3(32), 0, c->stream, c->d_zin, c->zstride, c->d_zsrc_len, (unsigned char *)c->sp.bits,
-                    c->sp.bits_words * 4, c->d_zcap, c->d_zlen, c->d_zdec_work);
-        EBCC_LAUNCH(k_sp_decode, dim3((unsigned)B), dim3(32), 0, c->stream, (const unsigned char *)c->sp.bits, c->sp.bits_words * 4, (const int *)c->d_zcap, c->sp,
-                    c->d_sp_info, c->d_sp_img0, g, c->d_maxlen);
+        {
+            KT kt_(c, EBCC_KT_ZSTD_DEC);
+            EBCC_LAUNCH(k_zstd_decompress, dim3((unsigned)B), dim3(32), 0, c->stream, c->d_zin, c->zstride, c->d_zsrc_len, (unsigned char *)c->sp.bits,
+                        c->sp.bits_words * 4, c->d_zcap, c->d_zlen, c->d_zdec_work);
+        }
+        {
+            KT kt_(c, EBCC_KT_SP_DECODE);
+            EBCC_LAUNCH(k_sp_decode, dim3((unsigned)B), dim3(32), 0, c->stream, (const unsigned char *)c->sp.bits, c->sp.bits_words * 4, (const int *)c->d_zcap, c->sp,
+                        c->d_sp_info, c->d_sp_img0, g, c->d_maxlen);
+        }
         c->launches += 3;
-        if (sp_launch_inverse(c, B)) return -1;
-        EBCC_LAUNCH(k_sp_add_residual, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_sp_img0, c->d_dec, c->d_sp_info, g);
+        {
+            KT kt_(c, EBCC_KT_SP_INV);
+            if (sp_launch_inverse(c, B)) return -1;
+            EBCC_LAUNCH(k_sp_add_residual, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_sp_img0, c->d_dec, c->d_sp_info, g);
+        }
         c->launches++;
         CK(cudaMemcpyAsync(c->h_zlen, c->d_zlen, 4 * B, cudaMemcpyDeviceToHost, c->stream));
         CK(cudaMemcpyAsync(c->h_maxlen, c->d_maxlen, 4 * B, cudaMemcpyDeviceToHost, c->stream));
@@ -1309,6 +1428,7 @@ extern "C" void ebcc_cuda_set_profiling(ebcc_cuda_ctx *c, int enabled) { if (c) 
 extern "C" float ebcc_cuda_stage_ms(ebcc_cuda_ctx *c, int stage) { return (c && stage >= 0 && stage < EBCC_ST_COUNT) ? c->stage_ms[stage] : -1.0f; }
 extern "C" int ebcc_cuda_sync(ebcc_cuda_ctx *c) { if (!c) return -1; CK(cudaSetDevice(c->device)); CK(ctx_sync(c)); return 0; }
 extern "C" unsigned long long ebcc_cuda_launch_count(ebcc_cuda_ctx *c) { return c ? c->launches : 0; }
+extern "C" unsigned long long ebcc_cuda_total_launches(void) { return __atomic_load_n(&g_ebcc_launches, __ATOMIC_RELAXED); }
 
 extern "C" int ebcc_cuda_debug_coef(ebcc_cuda_ctx *c, size_t frame, float *dst)
 {
@@ -1352,7 +1472,8 @@ extern "C" int ebcc_cuda_t1_totals(ebcc_cuda_ctx *c, size_t nframes, unsigned lo
 // test tap: after ebcc_cuda_analyze(for_search = 1), checks EVERY truncation point of EVERY code-block of the first nframes
 // frames: the block is decoded for real from the segment cut at rate[np - 1] and compared with what the recording +
 // verdict would reconstruct.  counts[0] cuts checked, [1] flagged unproven, [2] flagged proven but different from the real
-// decode (must be 0), [3] flagged unproven although equal.  Leaves the PCRD allocation of the context clobbered.
+// decode (must be 0), [3] flagged unproven although equal, [4] unproven cuts found pre-decoded in the pool, [5] pool entries
+// that differ from the real decode (must be 0).  Leaves the PCRD allocation of the context clobbered.
 extern "C" int ebcc_cuda_debug_check_cuts(ebcc_cuda_ctx *c, size_t nframes, unsigned long long *counts)
 {
     if (!c || nframes == 0 || nframes > c->cap_frames || c->ntiles > 1 || !c->for_search) return -1;
@@ -1361,8 +1482,8 @@ extern "C" int ebcc_cuda_debug_check_cuts(ebcc_cuda_ctx *c, size_t nframes, unsi
     const int B = (int)nframes;
     const long long njobs = (long long)pl->ncblks * B;
     unsigned long long *d_cnt = NULL;
-    CK(cudaMalloc((void **)&d_cnt, 4 * sizeof(unsigned long long)));
-    CK(cudaMemsetAsync(d_cnt, 0, 4 * sizeof(unsigned long long), c->stream));
+    CK(cudaMalloc((void **)&d_cnt, 6 * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(d_cnt, 0, 6 * sizeof(unsigned long long), c->stream));
     unsigned long long prev = 0;
     for (int np = 1; np < J2K_MAXPASSES; ++np) {
         EBCC_LAUNCH(k_dbg_force_np, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cbout, njobs, np);
@@ -1373,8 +1494,8 @@ extern "C" int ebcc_cuda_debug_check_cuts(ebcc_cuda_ctx *c, size_t nframes, unsi
                     c->d_jobs, c->d_mq, pl->mq_stride, c->d_declut, c->d_iplane, (unsigned char *)NULL, c->d_scratch, (const CblkOut *)c->d_cbout,
                     c->d_dstate, c->d_decsave, pl->W, pl->H, pl->ncblks, B);
         EBCC_LAUNCH(k_dbg_compare, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(128), 0, c->stream, c->d_cblks, c->d_cbout, c->d_dstate, c->d_iplane,
-                    c->d_spass, c->d_scratch, d_cnt, np, pl->W, pl->H, pl->ncblks);
-        CK(cudaMemcpyAsync(counts, d_cnt, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+                    c->d_spass, c->d_scratch, d_cnt, np, pl->W, pl->H, pl->ncblks, (const int *)c->d_cut_pool);
+        CK(cudaMemcpyAsync(counts, d_cnt, 6 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
         CK(ctx_sync(c));
         if (counts[0] == prev) break;          // no block has this many passes
         prev = counts[0];

@@ -17,6 +17,7 @@
 #include "k_t1.cuh"
 #include "k_t2.cuh"
 
+// mode 4 = the cut was decoded ahead of time into the pool of unproven cuts, entry `pad` (k_t1_dec_cuts)
 // mode: 0 = nothing to do, 1 = decode into the recording plane (iplane + pass-of-significance plane), continuing
 //       the block's saved decoder state if it has one,
 //       2 = decode into the scratch plane (a truncation the recording cannot reproduce, see DecState),
@@ -477,7 +478,7 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJ
     const int blk = warp * L + (lane < L ? lane : 0);
     T1DecState S;
     S.F = F[blk]; S.cx = cxs[blk]; S.tab = tab; S.W = W; S.pass = 0;
-    DecState ds; ds.np_dec = 0; ds.scratch_np = 0; ds.bad[0] = ds.bad[1] = ds.bad[2] = ds.bad[3] = 0;
+    DecState ds; ds.np_dec = 0; ds.scratch_np = 0; ds.bad[0] = ds.bad[1] = ds.bad[2] = ds.bad[3] = 0; ds.first_entry = -1; ds.pad = 0;
     if (mine) {
         S.zc = zc + v.cb.orient * 512;
         if (search) ds = dstate[v.bi];
@@ -559,6 +560,65 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJ
     }
 }
 
+// ---- unproven cuts, decoded ahead of the search --------------------------------------------------------------------------
+// About one truncation point in a thousand does not decode like the complete segment (mq_cut_proven).  A probe that
+// picks such a point needs the real thing, and one block is a serial chain of several milliseconds: decoded on demand
+// it would set the pace of every probe.  So right after tier-1 every unproven (block, pass count) of the batch becomes
+// an entry of a list and ONE launch decodes them all side by side, each into its own 64 x 64 slot of a pool.
+__global__ void k_cut_collect(const CblkOut *__restrict__ cbout, T1CutState *dstate, T1CutEntry *list, int *count, int cap, long long njobs)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= njobs) return;
+    T1CutState &d = dstate[i];
+    const int n = __popc(d.bad[0]) + __popc(d.bad[1]) + __popc(d.bad[2]) + __popc(d.bad[3]);
+    if (n == 0) return;
+    const int first = atomicAdd(count, n);
+    if (first + n > cap) return;                  // pool full: these cuts are decoded when a probe asks (first_entry stays < 0)
+    d.first_entry = first;
+    int e = first;
+    for (int p = 0; p < 128 && p < cbout[i].totalpasses; ++p)
+        if ((d.bad[p >> 5] >> (p & 31)) & 1u) { list[e].bi = (unsigned)i; list[e].np = p + 1; ++e; }
+}
+
+#define CUT_WPC 4
+__global__ void __launch_bounds__(CUT_WPC * 32)
+k_t1_dec_cuts(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cbout, const T1CutEntry *__restrict__ list, const int *__restrict__ count,
+              int cap, const unsigned char *__restrict__ pool, size_t pool_stride, const DecLuts *__restrict__ g_luts, int *cut_pool, int ncblks)
+{
+    __shared__ unsigned F[CUT_WPC][DEC_FWORDS];
+    __shared__ unsigned cxs[CUT_WPC][20];
+    __shared__ unsigned tab[94];
+    __shared__ unsigned char zc[4 * 512];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n = min(*count, cap);
+    if (blockIdx.x * CUT_WPC >= n) return;
+    for (int i = tid; i < 94; i += blockDim.x) tab[i] = g_luts->mq[i];
+    for (int i = tid; i < 4 * 512; i += blockDim.x) zc[i] = g_luts->zc[i];
+    __syncthreads();
+    const int e = blockIdx.x * CUT_WPC + warp;
+    if (e >= n) return;
+    const T1CutEntry en = list[e];
+    const int k = (int)(en.bi % (unsigned)ncblks), frame = (int)(en.bi / (unsigned)ncblks);
+    const CblkDesc cb = cblks[k];
+    int *dst = cut_pool + (size_t)e * T1_CUT_WORDS;
+    for (int i = lane; i < DEC_FWORDS; i += 32) F[warp][i] = 0;
+    for (int i = lane; i < cb.h * J2K_CBLK; i += 32) dst[i] = 0;
+    __syncwarp();
+    if (lane != 0) return;
+    const CblkOut &co = cbout[en.bi];
+    if (en.np <= 0 || co.numbps <= 0) return;
+    unsigned *cx = cxs[warp];
+    for (int i = 0; i < 19; ++i) cx[i] = tab[0];
+    cx[CTX_UNI] = tab[46 << 1]; cx[CTX_AGG] = tab[3 << 1]; cx[CTX_ZC] = tab[4 << 1];
+    T1DecState S;
+    S.F = F[warp]; S.cx = cx; S.tab = tab; S.W = J2K_CBLK; S.pass = 0; S.zc = zc + cb.orient * 512;
+    S.plane = dst; S.spass = nullptr;
+    MqDec q;
+    mqd_init(q, pool + (size_t)frame * pool_stride + cb.mq_off, co.rate[en.np - 1], nullptr);
+    DecState dummy; dummy.np_dec = 0; dummy.scratch_np = 0; dummy.bad[0] = dummy.bad[1] = dummy.bad[2] = dummy.bad[3] = 0; dummy.first_entry = -1; dummy.pad = 0;
+    t1d_passes(S, q, cb.w, cb.h, co.numbps, 0, en.np, nullptr, 0, dummy);
+}
+
 // decode jobs for the encoder's own allocation (compression-ratio search).  Block k is recorded (mode 1) when the
 // allocation needs more passes than its recording holds, served from the recording (mode 0) when the recording can
 // reproduce "first numpasses passes", and decoded for real into the scratch plane (mode 2) otherwise.
@@ -579,6 +639,13 @@ __global__ void k_jobs_from_enc(const CblkDesc *__restrict__ cblks, const CblkOu
         const DecState &d = dstate[i];
         if (np > d.np_dec) { j.mode = 1; j.len = c.datalen; }          // record (on) from the complete segment
         else if ((np - 1) < 128 && !((d.bad[(np - 1) >> 5] >> ((np - 1) & 31)) & 1u)) j.mode = 0;
+        else if (d.first_entry >= 0) {
+            // pre-decoded by k_t1_dec_cuts: entry = first + number of unproven cuts of this block below this one
+            int rank = 0;
+            for (int w = 0; w < ((np - 1) >> 5); ++w) rank += __popc(d.bad[w]);
+            rank += __popc(d.bad[(np - 1) >> 5] & ((1u << ((np - 1) & 31)) - 1u));
+            j.mode = 4; j.pad = d.first_entry + rank;
+        }
         else j.mode = d.scratch_np == np ? 3 : 2;
     }
     jobs[i] = j;
@@ -587,7 +654,7 @@ __global__ void k_jobs_from_enc(const CblkDesc *__restrict__ cblks, const CblkOu
 __global__ void k_dstate_reset(DecState *d, long long n)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) { d[i].np_dec = 0; d[i].scratch_np = 0; d[i].bad[0] = d[i].bad[1] = d[i].bad[2] = d[i].bad[3] = 0; }
+    if (i < n) { d[i].np_dec = 0; d[i].scratch_np = 0; d[i].bad[0] = d[i].bad[1] = d[i].bad[2] = d[i].bad[3] = 0; d[i].first_entry = -1; d[i].pad = 0; }
 }
 
 // Probe reconstruction: integer tier-1 output of "the first numpasses passes" for every sample, taken from the
@@ -610,7 +677,7 @@ __device__ __forceinline__ int recon_value(int v, int ps, int np, int npd, int n
 
 __global__ void k_recon_dequant(const Plan *__restrict__ plan, const CblkOut *__restrict__ cbout, const DecState *__restrict__ dstate,
                                 const DecJob *__restrict__ jobs, const int *__restrict__ iplane, const unsigned char *__restrict__ spass,
-                                const int *__restrict__ scratch, float *coef)
+                                const int *__restrict__ scratch, float *coef, const CblkDesc *__restrict__ cblks, const int *__restrict__ cut_pool)
 {
     const int W = plan->W, H = plan->H, ncblks = plan->ncblks;
     const size_t n = (size_t)W * H;
@@ -625,10 +692,14 @@ __global__ void k_recon_dequant(const Plan *__restrict__ plan, const CblkOut *__
             band = 1 + 3 * (r - 1) + (o - 1);
         }
         const BandDesc &bd = plan->bands[band];
-        const int k = bd.first_cblk + ((y - bd.offy) >> 6) * bd.cw + ((x - bd.offx) >> 6);
+        int gy = (y - bd.offy) >> 6, k = bd.first_cblk + gy * bd.cw + ((x - bd.offx) >> 6);
+        // tiles below the first one: the block grid is anchored on the canvas, the band's first block row may be a partial one
+        while (gy + 1 < bd.ch && y >= cblks[k].ty + cblks[k].h) { ++gy; k += bd.cw; }
         const size_t bi = (size_t)frame * ncblks + k, si = (size_t)frame * n + i;
         int v;
-        if (jobs[bi].mode >= 2) v = scratch[si];
+        const int md = jobs[bi].mode;
+        if (md == 4) v = cut_pool[(size_t)jobs[bi].pad * T1_CUT_WORDS + (size_t)(y - cblks[k].ty) * J2K_CBLK + (x - cblks[k].tx)];
+        else if (md >= 2) v = scratch[si];
         else {
             const int np = cbout[bi].numpasses;
             v = np > 0 ? recon_value(iplane[si], spass[si], np, dstate[bi].np_dec, cbout[bi].numbps) : 0;   // a block that was never included has no recording
@@ -774,25 +845,36 @@ __global__ void k_dbg_force_np(CblkOut *cbout, long long n, int np)
 }
 
 // grid (ncblks, nframes): block k of a frame, cut after np passes: recording vs the real truncated decode in `scratch`.
-// cnt[0] cuts checked, [1] flagged unproven, [2] flagged proven but DIFFERENT (must stay 0), [3] flagged unproven but equal
+// cnt[0] cuts checked, [1] flagged unproven, [2] flagged proven but DIFFERENT (must stay 0), [3] flagged unproven but equal,
+// [4] unproven cuts found in the pre-decoded pool, [5] pool entries that differ from the real decode (must stay 0)
 __global__ void k_dbg_compare(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cbout, const DecState *__restrict__ dstate,
                               const int *__restrict__ iplane, const unsigned char *__restrict__ spass, const int *__restrict__ scratch,
-                              unsigned long long *cnt, int np, int W, int H, int ncblks)
+                              unsigned long long *cnt, int np, int W, int H, int ncblks, const int *__restrict__ cut_pool)
 {
     const int k = blockIdx.x, frame = blockIdx.y;
     const size_t bi = (size_t)frame * ncblks + k;
     if (cbout[bi].numpasses != np || np <= 0) return;
     const CblkDesc cb = cblks[k];
     const int npd = dstate[bi].np_dec, numbps = cbout[bi].numbps;
-    int diff = 0;
+    int diff = 0, pdiff = 0;
+    const int bad = (np - 1) >= 128 || ((dstate[bi].bad[(np - 1) >> 5] >> ((np - 1) & 31)) & 1u);
+    int entry = -1;
+    if (bad && np - 1 < 128 && dstate[bi].first_entry >= 0) {
+        int rank = 0;
+        for (int w = 0; w < ((np - 1) >> 5); ++w) rank += __popc(dstate[bi].bad[w]);
+        rank += __popc(dstate[bi].bad[(np - 1) >> 5] & ((1u << ((np - 1) & 31)) - 1u));
+        entry = dstate[bi].first_entry + rank;
+    }
     for (int i = threadIdx.x; i < cb.w * cb.h; i += blockDim.x) {
         const int y = i / cb.w, x = i - y * cb.w;
         const size_t si = (size_t)frame * W * H + (size_t)(cb.ty + y) * W + cb.tx + x;
         if (recon_value(iplane[si], spass[si], np, npd, numbps) != scratch[si]) diff = 1;
+        if (entry >= 0 && cut_pool[(size_t)entry * T1_CUT_WORDS + (size_t)y * J2K_CBLK + x] != scratch[si]) pdiff = 1;
     }
     diff = __syncthreads_or(diff);
+    pdiff = __syncthreads_or(pdiff);
     if (threadIdx.x == 0) {
-        const int bad = (np - 1) >= 128 || ((dstate[bi].bad[(np - 1) >> 5] >> ((np - 1) & 31)) & 1u);
+        if (entry >= 0) { atomicAdd(&cnt[4], 1ull); if (pdiff) atomicAdd(&cnt[5], 1ull); }
         atomicAdd(&cnt[0], 1ull);
         if (bad) atomicAdd(&cnt[1], 1ull);
         if (!bad && diff) atomicAdd(&cnt[2], 1ull);

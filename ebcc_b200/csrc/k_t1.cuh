@@ -683,7 +683,7 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
     }
     if (coder && valid && snap && npasses <= 0) {
         T1CutState &cs = cuts[(size_t)frame * ncblks + cbi];
-        cs.np_dec = 0; cs.scratch_np = 0; cs.bad[0] = cs.bad[1] = cs.bad[2] = cs.bad[3] = 0;
+        cs.np_dec = 0; cs.scratch_np = 0; cs.bad[0] = cs.bad[1] = cs.bad[2] = cs.bad[3] = 0; cs.first_entry = -1; cs.pad = 0;
     }
     if (!coder || npasses <= 0) return;
     for (; p < npasses; ++p) mq_pass_end(q, out, p, npasses, snap);
@@ -709,7 +709,7 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
             if (!ok && pp < 128) bad[pp >> 5] |= 1u << (pp & 31);
         }
         T1CutState &cs = cuts[(size_t)frame * ncblks + cbi];
-        cs.np_dec = npasses; cs.scratch_np = 0;
+        cs.np_dec = npasses; cs.scratch_np = 0; cs.first_entry = -1; cs.pad = 0;
         cs.bad[0] = bad[0]; cs.bad[1] = bad[1]; cs.bad[2] = bad[2]; cs.bad[3] = bad[3];
     }
 }

@@ -29,7 +29,21 @@ enum {
     EBCC_ST_BODIES, EBCC_ST_D2H, EBCC_ST_COUNT
 };
 
+/* kernel classes of ebcc_cuda_kernel_timing_report */
+enum {
+    EBCC_KT_MINMAX = 0, EBCC_KT_DWT, EBCC_KT_T1_CM, EBCC_KT_T1_MQ, EBCC_KT_PCRD_T2, EBCC_KT_BODIES, EBCC_KT_T1_DEC, EBCC_KT_RECON,
+    EBCC_KT_IDWT, EBCC_KT_FINALIZE, EBCC_KT_SP_FWD, EBCC_KT_SP_ENCODE, EBCC_KT_SP_PROBE, EBCC_KT_ZSTD_ENC, EBCC_KT_T2_PARSE,
+    EBCC_KT_ZSTD_DEC, EBCC_KT_SP_DECODE, EBCC_KT_SP_INV, EBCC_KT_COUNT
+};
+#define EBCC_KT_NAMES "minmax,dwt,t1_cm,t1_mq,pcrd_t2,bodies,t1_dec,recon,idwt,finalize,sp_fwd,sp_encode,sp_probe,zstd_enc,t2_parse,zstd_dec,sp_decode,sp_inv"
+
 int ebcc_cuda_device_count(void);
+
+/* process-wide: enable != 0 clears the accumulators and brackets every launch group of every pipeline with CUDA events on
+ * its stream; the report returns, per kernel class, the summed device milliseconds and the number of launch groups timed
+ * since then (read back at the pipelines' synchronisation points).  Returns EBCC_KT_COUNT. */
+void ebcc_cuda_kernel_timing(int enable);
+int ebcc_cuda_kernel_timing_report(double *ms, unsigned long long *groups, int n);
 
 /* one context = one device + one stream + reusable work buffers; not thread-safe (callers lock) */
 ebcc_cuda_ctx *ebcc_cuda_ctx_create(int device);
@@ -125,6 +139,8 @@ void ebcc_cuda_set_profiling(ebcc_cuda_ctx *ctx, int enabled);
 /* milliseconds spent in a stage during the last pass (valid after ebcc_cuda_sync) */
 float ebcc_cuda_stage_ms(ebcc_cuda_ctx *ctx, int stage);
 int ebcc_cuda_sync(ebcc_cuda_ctx *ctx);
+/* kernels launched by every context of the process so far */
+unsigned long long ebcc_cuda_total_launches(void);
 /* number of kernel launches issued by this context so far */
 unsigned long long ebcc_cuda_launch_count(ebcc_cuda_ctx *ctx);
 
@@ -146,7 +162,7 @@ int ebcc_cuda_t1_totals(ebcc_cuda_ctx *ctx, size_t nframes, unsigned long long *
 
 /* debug/test taps on the resident batch (device -> host copies of intermediates) */
 int ebcc_cuda_debug_coef(ebcc_cuda_ctx *ctx, size_t frame, float *dst);
-int ebcc_cuda_debug_check_cuts(ebcc_cuda_ctx *ctx, size_t nframes, unsigned long long counts[4]);
+int ebcc_cuda_debug_check_cuts(ebcc_cuda_ctx *ctx, size_t nframes, unsigned long long counts[6]);
 int ebcc_cuda_debug_spiht_stream(ebcc_cuda_ctx *ctx, size_t frame, uint8_t *dst, size_t cap, size_t *len);
 int ebcc_cuda_debug_cblk(ebcc_cuda_ctx *ctx, size_t frame, size_t cblk, int *numbps, int *totalpasses,
                          int *rates, double *dists, int *numpasses);

@@ -117,7 +117,8 @@ def check_residual_stage(frame, cr, verbose=False, probes=(1.0, 0.5, 0.23, 0.07)
 
 def check_cuts(frames):
     """every truncation point of every code-block: recording + verdict of the encoder vs a real truncated decode.
-    Returns (cuts checked, flagged unproven, flagged proven but different, flagged unproven but equal)."""
+    Returns (cuts checked, flagged unproven, flagged proven but different, flagged unproven but equal, unproven cuts found
+    in the pre-decoded pool, pool entries that differ from the real decode)."""
     f = np.ascontiguousarray(frames, dtype=np.float32)
     b, h, w = f.shape
     lib = cuda_api()
@@ -128,7 +129,7 @@ def check_cuts(frames):
         assert lib.ebcc_cuda_reserve(ctx, h, w, b) == 0
         assert lib.ebcc_cuda_upload(ctx, f.ctypes.data, b) == 0
         assert lib.ebcc_cuda_analyze_resident(ctx, b) == 0
-        cnt = (C.c_ulonglong * 4)()
+        cnt = (C.c_ulonglong * 6)()
         assert lib.ebcc_cuda_debug_check_cuts(ctx, b, cnt) == 0
         return tuple(int(x) for x in cnt)
     finally:

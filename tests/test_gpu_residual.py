@@ -118,16 +118,17 @@ def test_batch_equals_single_max_error(built):
 @pytest.mark.parametrize("shape,nf", [((96, 160), 2), ((64, 64), 3), ((200, 130), 1)])
 def test_every_cut_verdict_small(built, shape, nf):
     """the encoder's recording + its verdict per truncation point vs a real truncated decode, for EVERY pass of EVERY block"""
-    checked, unproven, wrong, pessimistic = S.check_cuts(H.synth_stack(nf, shape[0], shape[1]))
-    assert checked > 0 and wrong == 0, (checked, unproven, wrong, pessimistic)
+    checked, unproven, wrong, pessimistic, pooled, pool_wrong = S.check_cuts(H.synth_stack(nf, shape[0], shape[1]))
+    assert checked > 0 and wrong == 0 and pooled == unproven and pool_wrong == 0, (checked, unproven, wrong, pessimistic, pooled, pool_wrong)
 
 
 def test_every_cut_verdict_full_frames(built):
     frames = np.concatenate([H.synth_stack(2), np.load(os.path.join(GOLDEN, "era5_t2m_721x1440.npy"))[None]], axis=0)
-    checked, unproven, wrong, pessimistic = S.check_cuts(frames)
-    print("cuts checked %d, unproven %d, proven-but-different %d, unproven-but-equal %d" % (checked, unproven, wrong, pessimistic))
+    checked, unproven, wrong, pessimistic, pooled, pool_wrong = S.check_cuts(frames)
+    print("cuts checked %d, unproven %d, proven-but-different %d, unproven-but-equal %d, pooled %d, pool-differs %d" % (checked, unproven, wrong, pessimistic, pooled, pool_wrong))
     assert checked > 20000 and wrong == 0
     assert pessimistic == 0          # the criterion is exact: a cut it rejects really decodes differently
+    assert pooled == unproven and pool_wrong == 0     # every unproven cut was decoded ahead of the search, correctly
 
 
 def test_recording_equals_real_decodes(built):

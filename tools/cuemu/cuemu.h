@@ -41,8 +41,9 @@ static inline uint4 make_uint4(unsigned a, unsigned b, unsigned c, unsigned d) {
 // ---- launch -------------------------------------------------------------------------------
 void cuemu_launch(dim3 grid, dim3 block, size_t dyn_smem, const std::function<void()> &body);
 extern unsigned char *cuemu_dyn_smem_ptr;
+static unsigned long long g_ebcc_launches = 0;
 #define EBCC_LAUNCH(kern, grid, block, smem, stream, ...) \
-    cuemu_launch((grid), (block), (smem), [=]() { kern(__VA_ARGS__); })
+    ++g_ebcc_launches, cuemu_launch((grid), (block), (smem), [=]() { kern(__VA_ARGS__); })
 #define EBCC_DYN_SMEM(type, name) type *name = (type *)cuemu_dyn_smem_ptr
 
 // ---- synchronisation ----------------------------------------------------------------------
