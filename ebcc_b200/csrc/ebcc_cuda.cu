@@ -312,6 +312,8 @@ struct ebcc_cuda_ctx {
     DecState *d_dstate;        // [B][ncblks]
     T1CutEntry *d_cut_list;    // unproven truncation points of the batch and their pre-decoded blocks (k_t1_dec_cuts)
     int *d_cut_count, *d_cut_pool, cut_cap;
+    int *h_cut_count;          // pinned copy of the batch's number of unproven cuts
+    int cut_known, cut_overflow;   // read back after the analysis: when every unproven cut sits in the pool no probe launches the tier-1 decoder
     unsigned *d_decsave;       // [B][ncblks][DEC_SAVE_WORDS] decoder state of each block's recording (resumed by later probes)
     int use_recording;         // 0: every probe decodes every block for real (EBCC_NO_RECORDING=1)
     int rec_from_encoder;      // recording + cut verdicts come from the encoder (k_t1_cm / k_t1_mq); 0: from k_t1_dec (EBCC_DECODER_RECORDING=1)
@@ -363,8 +365,15 @@ struct ebcc_cuda_ctx {
     // tile[t], a light context with the tile's own geometry that shares this context's stream and look-up tables
     cudaEvent_t kt_ev[2 * KT_RING];   // kernel-class timing: event pairs recorded since the last synchronisation
     int kt_id[KT_RING], kt_n, kt_have;
+    // The long serial kernels (MQ coder, decode of the unproven cuts) run on a second stream of the LOWEST priority,
+    // everything else on `stream`, which has the highest: with a dozen pipelines in flight the shared memory of every SM is
+    // full of resident MQ CTAs, and without priorities the short kernels of the other pipelines (9/7 passes, context
+    // modelling, rate allocation, probes) queue behind MQ CTAs that are still waiting for a place themselves.
+    cudaStream_t stream_lo;
+    cudaEvent_t ev_fork, ev_join;
+    int prio_split;
     int crowd;                 // pipelines at work on this device (hint from the host codec), see mq_lanes()
-    int env_mq_lanes, env_dec_lanes, env_no_recording, env_dec_recording, env_debug_lanes;   // tuning / debugging variables, read once per host call (read_env)
+    int env_mq_lanes, env_dec_lanes, env_no_recording, env_dec_recording, env_debug_lanes, env_t1rec_ctas, env_dwt_cw;   // tuning / debugging variables, read once per host call (read_env)
     int ntiles;
     ebcc_cuda_ctx *tile[EBCC_MAX_TILES];
     ebcc_cuda_ctx *parent;
@@ -376,17 +385,18 @@ static ebcc_cuda_ctx *ctx_root_mut(ebcc_cuda_ctx *c) { return c->parent ? c->par
 
 // scope of one launch group of kernel class `id`
 struct KT {
-    ebcc_cuda_ctx *r; int slot;
-    KT(ebcc_cuda_ctx *c, int id) : r(NULL), slot(-1)
+    ebcc_cuda_ctx *r; int slot; cudaStream_t st;
+    KT(ebcc_cuda_ctx *c, int id, cudaStream_t on = NULL) : r(NULL), slot(-1), st(on)
     {
         if (!g_kt_on) return;
         r = ctx_root_mut(c);
+        if (!st) st = r->stream;
         if (!r->kt_have) { for (int i = 0; i < 2 * KT_RING; ++i) cudaEventCreate(&r->kt_ev[i]); r->kt_have = 1; }
         if (r->kt_n >= KT_RING) { r = NULL; return; }
         slot = r->kt_n++; r->kt_id[slot] = id;
-        cudaEventRecord(r->kt_ev[2 * slot], r->stream);
+        cudaEventRecord(r->kt_ev[2 * slot], st);
     }
-    ~KT() { if (r) cudaEventRecord(r->kt_ev[2 * slot + 1], r->stream); }
+    ~KT() { if (r) cudaEventRecord(r->kt_ev[2 * slot + 1], st); }
 };
 
 // after a synchronisation of the pipeline's stream: every recorded pair has completed
@@ -452,7 +462,18 @@ extern "C" ebcc_cuda_ctx *ebcc_cuda_ctx_create(int device)
     if (cudaSetDevice(device) != cudaSuccess) return NULL;
     ebcc_cuda_ctx *c = (ebcc_cuda_ctx *)calloc(1, sizeof(*c));
     c->device = device; c->ntiles = 1;
-    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { free(c); return NULL; }
+    {
+        int least = 0, greatest = 0;
+        cudaDeviceGetStreamPriorityRange(&least, &greatest);
+        const char *ps = getenv("EBCC_PRIO_SPLIT");
+        c->prio_split = !(ps && ps[0] == '0') && least != greatest;
+        if (cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, c->prio_split ? greatest : 0) != cudaSuccess) { free(c); return NULL; }
+        if (c->prio_split) {
+            if (cudaStreamCreateWithPriority(&c->stream_lo, cudaStreamNonBlocking, least) != cudaSuccess) { cudaStreamDestroy(c->stream); free(c); return NULL; }
+            cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+            cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
+        }
+    }
     for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventCreate(&c->ev[i]);
     cudaEventCreateWithFlags(&c->ev_sync, cudaEventBlockingSync | cudaEventDisableTiming);
     { const char *sp = getenv("EBCC_SPIN_SYNC"); c->spin_sync = sp && sp[0] == '1'; }
@@ -515,6 +536,7 @@ static void free_buffers(ebcc_cuda_ctx *c)
     cudaFreeHost(c->h_packed); cudaFreeHost(c->h_stage);
     cudaFree(c->d_streams); cudaFree(c->d_slens); cudaFree(c->d_status); cudaFree(c->d_jobs); cudaFree(c->d_iplane); cudaFree(c->d_scratch); cudaFree(c->d_spass); cudaFree(c->d_dstate); cudaFree(c->d_decsave);
     cudaFree(c->d_cut_list); cudaFree(c->d_cut_count); cudaFree(c->d_cut_pool); c->d_cut_list = NULL; c->d_cut_count = NULL; c->d_cut_pool = NULL;
+    cudaFreeHost(c->h_cut_count); c->h_cut_count = NULL;
     c->d_scratch = NULL; c->d_spass = NULL; c->d_dstate = NULL; c->d_decsave = NULL;
     cudaFree(c->d_dcoef); cudaFree(c->d_dec); cudaFree(c->d_es); cudaFree(c->d_targets);
     cudaFreeHost(c->h_es); cudaFreeHost(c->h_status); cudaFreeHost(c->h_slens); cudaFreeHost(c->h_targets); cudaFreeHost(c->h_streams);
@@ -552,6 +574,7 @@ extern "C" void ebcc_cuda_ctx_destroy(ebcc_cuda_ctx *c)
     cudaFree(c->d_luts); cudaFree(c->d_mqtab); cudaFree(c->d_declut); cudaFree(c->d_step_tab);
     for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventDestroy(c->ev[i]);
     if (c->kt_have) for (int i = 0; i < 2 * KT_RING; ++i) cudaEventDestroy(c->kt_ev[i]);
+    if (c->prio_split) { cudaStreamDestroy(c->stream_lo); cudaEventDestroy(c->ev_fork); cudaEventDestroy(c->ev_join); }
     cudaStreamDestroy(c->stream);
     free(c);
 }
@@ -629,6 +652,7 @@ static int reserve_alloc(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes, i
     c->cut_cap = (int)(B * (size_t)(pl->ncblks / 3 + 8) + 256);
     CK(cudaMalloc((void **)&c->d_cut_list, (size_t)c->cut_cap * sizeof(T1CutEntry)));
     CK(cudaMalloc((void **)&c->d_cut_count, sizeof(int)));
+    CK(cudaMallocHost((void **)&c->h_cut_count, sizeof(int)));
     CK(cudaMalloc((void **)&c->d_cut_pool, (size_t)c->cut_cap * T1_CUT_WORDS * sizeof(int)));
     CK(cudaMalloc((void **)&c->d_decsave, B * pl->ncblks * (size_t)DEC_SAVE_WORDS * sizeof(unsigned)));
     CK(cudaMalloc((void **)&c->d_dcoef, B * N * sizeof(float)));
@@ -737,7 +761,7 @@ static int launch_dwt(ebcc_cuda_ctx *c, int B)
     for (int r = J2K_NRES - 1; r >= 1; --r) {
         const int rw = pl->res_w[r], rh = pl->res_h[r];
         // vertical: strips of CW columns, full height in shared memory
-        int CW = 32;
+        int CW = ctx_root_mut(c)->env_dwt_cw;
         while ((size_t)rh * CW * sizeof(float) > 96 * 1024 && CW > 4) CW >>= 1;
         dim3 bv((unsigned)CW, (unsigned)(512 / CW));
         dim3 gv((unsigned)((rw + CW - 1) / CW), (unsigned)B);
@@ -776,6 +800,11 @@ static void read_env(ebcc_cuda_ctx *c)
     e = getenv("EBCC_DECODER_RECORDING");           // cross-check aid: recordings made by the tier-1 decoder (round-1 path)
     c->env_dec_recording = e && e[0] == '1';
     c->env_debug_lanes = getenv("EBCC_DEBUG_LANES") != NULL;
+    e = getenv("EBCC_T1REC_CTAS");                  // tuning: CTAs per SM the recording variant of k_t1_cm is compiled for (2 or 3)
+    c->env_t1rec_ctas = e ? atoi(e) : 2;
+    e = getenv("EBCC_DWT_CW");                      // tuning: columns per CTA of the vertical 9/7 passes (shared memory = height x columns x 4 bytes)
+    c->env_dwt_cw = e ? atoi(e) : 32;
+    if (c->env_dwt_cw != 4 && c->env_dwt_cw != 8 && c->env_dwt_cw != 16 && c->env_dwt_cw != 32) c->env_dwt_cw = 32;
 }
 static int mq_lanes(const ebcc_cuda_ctx *c, long long jobs)
 {
@@ -859,24 +888,35 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int f
 
     mark(c, EBCC_ST_T1_CM);
     KT *kt_cm = new KT(c, EBCC_KT_T1_CM);
-    if (c->rec_from_encoder)
-        EBCC_LAUNCH(k_t1_cm<true>, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
+    if (c->rec_from_encoder && ctx_root(c)->env_t1rec_ctas == 3)
+        EBCC_LAUNCH((k_t1_cm<true, 3>), dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
+                    c->d_coef, c->d_cblks, c->d_bands, c->d_luts, (const unsigned char *)c->d_declut, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks,
+                    pl->sym_stride, c->d_iplane, c->d_spass, c->d_stat);
+    else if (c->rec_from_encoder)
+        EBCC_LAUNCH((k_t1_cm<true, 2>), dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
                     c->d_coef, c->d_cblks, c->d_bands, c->d_luts, (const unsigned char *)c->d_declut, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks,
                     pl->sym_stride, c->d_iplane, c->d_spass, c->d_stat);
     else
-        EBCC_LAUNCH(k_t1_cm<false>, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
+        EBCC_LAUNCH((k_t1_cm<false, T1_MIN_CTAS>), dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
                     c->d_coef, c->d_cblks, c->d_bands, c->d_luts, (const unsigned char *)c->d_declut, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks,
                     pl->sym_stride, (int *)NULL, (unsigned char *)NULL, c->d_stat);
     delete kt_cm;
     mark(c, EBCC_ST_T1_MQ);
+    ebcc_cuda_ctx *root = ctx_root_mut(c);
+    cudaStream_t ls = c->stream;                   // stream of the long serial kernels
+    if (root->prio_split) {
+        CK(cudaEventRecord(root->ev_fork, c->stream));
+        CK(cudaStreamWaitEvent(root->stream_lo, root->ev_fork, 0));
+        ls = root->stream_lo;
+    }
     {
-        KT kt_(c, EBCC_KT_T1_MQ);
+        KT kt_(c, EBCC_KT_T1_MQ, ls);
         const long long jobs = (long long)pl->ncblks * B;
         const int lanes = mq_lanes(c, jobs);                     // code-blocks per warp: 1, 2, 4, 8, 16 or 32
         if (ctx_root(c)->env_debug_lanes) fprintf(stderr, "[ebcc-cuda] mq lanes %d (crowd %d, jobs %lld)\n", lanes, ctx_crowd(c), jobs);
         const long long per_cta = (long long)MQ_WARPS(lanes) * lanes;
         const dim3 grid((unsigned)((jobs + per_cta - 1) / per_cta)), block(MQ_THREADS(lanes));
-#define MQ_GO(LL) EBCC_LAUNCH(k_t1_mq<LL>, grid, block, 0, c->stream, c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, \
+#define MQ_GO(LL) EBCC_LAUNCH(k_t1_mq<LL>, grid, block, 0, ls, c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, \
                               c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride, c->rec_from_encoder ? c->d_dstate : (T1CutState *)NULL, c->d_stat)
         if (lanes == 32) MQ_GO(32); else if (lanes == 16) MQ_GO(16); else if (lanes == 8) MQ_GO(8); else if (lanes == 4) MQ_GO(4);
         else if (lanes == 2) MQ_GO(2); else MQ_GO(1);
@@ -885,16 +925,22 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int f
     c->launches += 2;
     if (c->rec_from_encoder) {
         // every unproven truncation point of the batch is decoded now, all of them side by side (see k_t1_dec_cuts)
-        KT kt_(c, EBCC_KT_T1_DEC);
+        KT kt_(c, EBCC_KT_T1_DEC, ls);
         const long long jobs = (long long)pl->ncblks * B;
-        CK(cudaMemsetAsync(c->d_cut_count, 0, sizeof(int), c->stream));
-        EBCC_LAUNCH(k_cut_collect, dim3((unsigned)((jobs + 255) / 256)), dim3(256), 0, c->stream, (const CblkOut *)c->d_cbout, c->d_dstate, c->d_cut_list,
+        CK(cudaMemsetAsync(c->d_cut_count, 0, sizeof(int), ls));
+        EBCC_LAUNCH(k_cut_collect, dim3((unsigned)((jobs + 255) / 256)), dim3(256), 0, ls, (const CblkOut *)c->d_cbout, c->d_dstate, c->d_cut_list,
                     c->d_cut_count, c->cut_cap, jobs);
-        EBCC_LAUNCH(k_t1_dec_cuts, dim3((unsigned)((c->cut_cap + CUT_WPC - 1) / CUT_WPC)), dim3(CUT_WPC * 32), 0, c->stream, c->d_cblks, (const CblkOut *)c->d_cbout,
+        EBCC_LAUNCH(k_t1_dec_cuts, dim3((unsigned)((c->cut_cap + CUT_WPC - 1) / CUT_WPC)), dim3(CUT_WPC * 32), 0, ls, c->d_cblks, (const CblkOut *)c->d_cbout,
                     (const T1CutEntry *)c->d_cut_list, (const int *)c->d_cut_count, c->cut_cap, (const unsigned char *)c->d_mq, pl->mq_stride, c->d_declut,
                     c->d_cut_pool, pl->ncblks);
+        CK(cudaMemcpyAsync(c->h_cut_count, c->d_cut_count, sizeof(int), cudaMemcpyDeviceToHost, ls));
         c->launches += 2;
     }
+    if (root->prio_split) {
+        CK(cudaEventRecord(root->ev_join, ls));
+        CK(cudaStreamWaitEvent(c->stream, root->ev_join, 0));
+    }
+    c->cut_known = 0; c->cut_overflow = 1;
     CK(cudaGetLastError());
     return 0;
 }
@@ -962,7 +1008,8 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
     const int W = pl->W, H = pl->H, N = W * H;
     const long long njobs = (long long)pl->ncblks * B;
     const bool probe = orig != NULL;         // probe of the CR search: jobs come from the encoder, the recording is used
-    {
+    // a probe whose batch has every unproven cut in the pool has nothing to decode: recording, verdicts and pool serve it
+    if (!(probe && c->rec_from_encoder && c->use_recording && c->cut_known && !c->cut_overflow)) {
         KT kt_(c, EBCC_KT_T1_DEC);
         const int lanes = dec_lanes(c);                         // code-blocks per warp of the tier-1 decoder: 1, 2, 4 or 8
         const long long per_cta = (long long)DEC_WPC(lanes) * lanes;
@@ -989,7 +1036,7 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
         while ((size_t)rw * RH * sizeof(float) > 64 * 1024 && RH > 1) RH >>= 1;
         EBCC_LAUNCH(k_idwt_h, dim3((unsigned)((rh + RH - 1) / RH), (unsigned)B), dim3(128, (unsigned)RH),
                     (size_t)rw * RH * sizeof(float), c->stream, c->d_dcoef, W, H, rw, rh, pl->res_w[r - 1]);
-        int CW = 32;
+        int CW = ctx_root(c)->env_dwt_cw;
         while ((size_t)rh * CW * sizeof(float) > 96 * 1024 && CW > 4) CW >>= 1;
         EBCC_LAUNCH(k_idwt_v, dim3((unsigned)((rw + CW - 1) / CW), (unsigned)B), dim3((unsigned)CW, (unsigned)(512 / CW)),
                     (size_t)rh * CW * sizeof(float), c->stream, c->d_dcoef, W, H, rw, rh, pl->res_h[r - 1], pl->cas_v[r]);
@@ -1013,6 +1060,13 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
 static int probe_launch(ebcc_cuda_ctx *c, int B, const float *targets)
 {
     const Plan *pl = &c->plan;
+    if (c->rec_from_encoder && !c->cut_known) {
+        // first probe after the analysis: how many unproven cuts did the batch have?  (the host codec has synchronised
+        // already, the wait is over before it starts)
+        CK(ctx_sync(c));
+        c->cut_overflow = *c->h_cut_count > c->cut_cap;
+        c->cut_known = 1;
+    }
     for (int i = 0; i < B; ++i) c->h_targets[i] = targets[i];
     CK(cudaMemcpyAsync(c->d_targets, c->h_targets, sizeof(float) * B, cudaMemcpyHostToDevice, c->stream));
     const long long njobs = (long long)pl->ncblks * B;

@@ -164,8 +164,8 @@ __device__ __forceinline__ void t1_rec_pass(unsigned char *rec_pass, size_t base
 #ifndef T1_MIN_CTAS
 #define T1_MIN_CTAS 3
 #endif
-template <bool REC>
-__global__ void __launch_bounds__(T1_THREADS, REC ? 2 : T1_MIN_CTAS)      // the recording stores need a few more registers
+template <bool REC, int MINB>      // MINB CTAs per SM: 3 caps the kernel at 40 registers, 2 at 64 (the recording stores like a few more)
+__global__ void __launch_bounds__(T1_THREADS, MINB)
 k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, const BandDesc *__restrict__ bands,
         const T1Luts *__restrict__ g_luts, const unsigned char *__restrict__ zc_lut, CblkOut *cbout, unsigned char *sym_pool,
         int W, int H, int ncblks, size_t sym_stride, int *rec_val, unsigned char *rec_pass, FrameStat *stat)

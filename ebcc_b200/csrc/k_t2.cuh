@@ -36,15 +36,14 @@ __host__ __device__ inline size_t t2_smem_bytes(int ncblks, int nnodes)
 
 __device__ __forceinline__ int t2_floorlog2(int a) { return a > 1 ? 31 - __clz(a) : 0; }
 
-// append n bits (value v, n <= 32) to a 128-bit MSB-first accumulator
+// append n bits (value v < 2^n, 1 <= n <= 32) to a 128-bit MSB-first accumulator
 __device__ __forceinline__ void hb_put(unsigned long long &hi, unsigned long long &lo, int &used, unsigned v, int n)
 {
-    for (int i = n - 1; i >= 0; --i) {
-        unsigned b = (v >> i) & 1u;
-        if (used < 64) hi |= (unsigned long long)b << (63 - used);
-        else lo |= (unsigned long long)b << (127 - used);
-        used++;
-    }
+    const int end = used + n;
+    if (end <= 64) hi |= (unsigned long long)v << (64 - end);
+    else if (used >= 64) lo |= (unsigned long long)v << (128 - end);
+    else { hi |= (unsigned long long)v >> (end - 64); lo |= (unsigned long long)v << (128 - end); }
+    used = end;
 }
 
 // CTA exclusive scan of a[0..n) in place; returns total.  All threads must call.
@@ -68,6 +67,57 @@ __device__ int cta_exscan(int *a, int n, int *scratch /* >= T2_THREADS/32 + 1 */
     return total;
 }
 
+// zero-bit-plane tag tree (tgt.c:200-262 over band->numbps - cblk->numbps): the same for every allocation of a launch
+__device__ void t2_tree_static(const Plan *__restrict__ plan, const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ co, T2Smem &s)
+{
+    const int tid = threadIdx.x, nt = blockDim.x;
+    for (int k = tid; k < plan->ncblks; k += nt) {
+        const CblkDesc &cb = cblks[k];
+        const BandDesc &bd = plan->bands[cb.band];
+        s.nd_imsb[bd.tt_base + cb.gy * bd.cw + cb.gx] = bd.numbps - co[k].numbps;
+    }
+    __syncthreads();
+    for (int bi = tid >> 5; bi < plan->nbands; bi += nt >> 5) {
+        const BandDesc &bd = plan->bands[bi];
+        for (int l = 1; l < bd.tt_nlev; ++l) {
+            const int w = bd.tt_w[l], h = bd.tt_h[l], cwp = bd.tt_w[l - 1], chp = bd.tt_h[l - 1];
+            for (int n = tid & 31; n < w * h; n += 32) {
+                int nx = n % w, ny = n / w, imsb = T2_INF;
+                for (int dy = 0; dy < 2; ++dy)
+                    for (int dx = 0; dx < 2; ++dx) {
+                        int cx = 2 * nx + dx, cy = 2 * ny + dy;
+                        if (cx < cwp && cy < chp) imsb = min(imsb, s.nd_imsb[bd.tt_base + bd.tt_off[l - 1] + cy * cwp + cx]);
+                    }
+                s.nd_imsb[bd.tt_base + bd.tt_off[l] + n] = imsb;
+            }
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+}
+
+// exclusive scans of a[0..n) and b[0..n) in one pass (totals < 2^31 each): the pair travels as one 64-bit word
+__device__ void cta_exscan2(int *a, int *b, int n, unsigned long long *scratch /* >= T2_THREADS/32 */)
+{
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int per = (n + nt - 1) / nt;
+    const int lo = min(n, tid * per), hi = min(n, lo + per);
+    unsigned long long sum = 0;
+    for (int i = lo; i < hi; ++i) sum += ((unsigned long long)(unsigned)b[i] << 32) | (unsigned)a[i];
+    unsigned long long incl = sum;
+    for (int o = 1; o < 32; o <<= 1) { unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o); if ((tid & 31) >= o) incl += t; }
+    if ((tid & 31) == 31) scratch[tid >> 5] = incl;
+    __syncthreads();
+    unsigned long long off = incl - sum;
+    for (int w = 0; w < (tid >> 5); ++w) off += scratch[w];
+    for (int i = lo; i < hi; ++i) {
+        const unsigned long long v = ((unsigned long long)(unsigned)b[i] << 32) | (unsigned)a[i];
+        a[i] = (int)(unsigned)off; b[i] = (int)(off >> 32);
+        off += v;
+    }
+    __syncthreads();
+}
+
 // One tier-2 run over the current allocation.  Returns the total packet bytes (headers + bodies).
 // If dst != nullptr the packet headers are stored at their final offsets and body_off[k] receives
 // the destination offset of each included block's MQ segment.
@@ -77,42 +127,41 @@ __device__ int t2_run(const Plan *__restrict__ plan, const CblkDesc *__restrict_
     const int tid = threadIdx.x, nt = blockDim.x;
     const int ncblks = plan->ncblks, nnodes = plan->nnodes;
 
-    // ---- tag-tree node aggregates, leaves first ------------------------------------------------
+    // ---- tag-tree node aggregates: leaves by block, then every band's (small) tree bottom-up by one warp --------
+    // (the zero-bit-plane minima do not depend on the allocation: t2_tree_static fills nd_imsb once per launch)
     for (int k = tid; k < ncblks; k += nt) {
         const CblkDesc &cb = cblks[k];
         const BandDesc &bd = plan->bands[cb.band];
         int node = bd.tt_base + cb.gy * bd.cw + cb.gx;
         int np = s.numpasses[k];
         s.nd_incl[node] = np > 0;
-        s.nd_imsb[node] = bd.numbps - co[k].numbps;
         s.nd_first[node] = np > 0 ? (cb.gy * bd.cw + cb.gx) : T2_INF;
         s.bodylen[k] = np > 0 ? co[k].rate[np - 1] : 0;
     }
     __syncthreads();
-    for (int l = 1; l < 8; ++l) {
-        for (int bi = 0; bi < plan->nbands; ++bi) {
-            const BandDesc &bd = plan->bands[bi];
-            if (l >= bd.tt_nlev) continue;
+    for (int bi = tid >> 5; bi < plan->nbands; bi += nt >> 5) {
+        const BandDesc &bd = plan->bands[bi];
+        for (int l = 1; l < bd.tt_nlev; ++l) {
             const int w = bd.tt_w[l], h = bd.tt_h[l], cwp = bd.tt_w[l - 1], chp = bd.tt_h[l - 1];
-            for (int n = tid; n < w * h; n += nt) {
+            for (int n = tid & 31; n < w * h; n += 32) {
                 int nx = n % w, ny = n / w;
-                int incl = 0, imsb = T2_INF, first = T2_INF;
+                int incl = 0, first = T2_INF;
                 for (int dy = 0; dy < 2; ++dy)
                     for (int dx = 0; dx < 2; ++dx) {
                         int cx = 2 * nx + dx, cy = 2 * ny + dy;
                         if (cx < cwp && cy < chp) {
                             int c = bd.tt_base + bd.tt_off[l - 1] + cy * cwp + cx;
                             incl |= s.nd_incl[c];
-                            imsb = min(imsb, s.nd_imsb[c]);
                             first = min(first, s.nd_first[c]);
                         }
                     }
                 int me = bd.tt_base + bd.tt_off[l] + n;
-                s.nd_incl[me] = incl; s.nd_imsb[me] = imsb; s.nd_first[me] = first;
+                s.nd_incl[me] = incl; s.nd_first[me] = first;
             }
+            __syncwarp();
         }
-        __syncthreads();
     }
+    __syncthreads();
     (void)nnodes;
 
     // ---- per-block header bits --------------------------------------------------------------------
@@ -141,8 +190,7 @@ __device__ int t2_run(const Plan *__restrict__ plan, const CblkDesc *__restrict_
                 int node = bd.tt_base + bd.tt_off[l] + (y >> l) * bd.tt_w[l] + (x >> l);
                 int v = s.nd_imsb[node];
                 if (s.nd_first[node] == leaf) {
-                    int z = v - pv;
-                    while (z > 0) { int c = min(z, 32); hb_put(hi, lo, used, 0, c); z -= c; }
+                    used += max(v - pv, 0);                      // v - pv zero bits
                     hb_put(hi, lo, used, 1, 1);
                 }
                 pv = v;
@@ -158,16 +206,15 @@ __device__ int t2_run(const Plan *__restrict__ plan, const CblkDesc *__restrict_
             const int lg = t2_floorlog2(np);
             int inc = t2_floorlog2(len) + 1 - (3 + lg);
             if (inc < 0) inc = 0;
-            for (int i = 0; i < inc; ++i) hb_put(hi, lo, used, 1, 1);
-            hb_put(hi, lo, used, 0, 1);
+            if (inc > 0) hb_put(hi, lo, used, (1u << inc) - 1u, inc);      // comma code: inc ones, one zero
+            used += 1;
             hb_put(hi, lo, used, (unsigned)len, 3 + inc + lg);
         }
         s.hb[2 * k] = hi; s.hb[2 * k + 1] = lo; s.nbits[k] = used;
     }
     if (tid == 0) { s.nbits[ncblks] = 0; s.bodylen[ncblks] = 0; }
     __syncthreads();
-    cta_exscan(s.nbits, ncblks + 1, scratch);        // nbits[k] = bit offset, nbits[ncblks] = total
-    cta_exscan(s.bodylen, ncblks + 1, scratch);
+    cta_exscan2(s.nbits, s.bodylen, ncblks + 1, (unsigned long long *)scratch);      // nbits[k] = bit offset, nbits[ncblks] = total; bodylen alike
 
     // ---- scatter the bits of every packet into one MSB-first bit buffer (32-bit aligned packets) ---
     __shared__ int pk_bitbase[J2K_NRES], pk_nbits[J2K_NRES], pk_hdr[J2K_NRES], pk_off[J2K_NRES + 1];
@@ -261,17 +308,29 @@ __device__ int t2_run(const Plan *__restrict__ plan, const CblkDesc *__restrict_
     return total;
 }
 
-// opj_tcd_makelayer for one block (tcd.c:283-318): passes kept while thresh - dd/dr < DBL_EPSILON
+// opj_tcd_makelayer for one block (tcd.c:283-318): passes kept while thresh - dd/dr < DBL_EPSILON.  The rate and
+// distortion of the last pass kept travel in registers and the tables are read four passes ahead, so no load sits on
+// the serial chain of divisions and compares (the arithmetic, and hence every decision, is the reference's).
 __device__ __forceinline__ int t2_makelayer_block(const CblkOut &c, double thresh)
 {
-    if (thresh < 0) return c.totalpasses;
-    int n = 0;
-    for (int p = 0; p < c.totalpasses; ++p) {
-        unsigned dr; double dd;
-        if (n == 0) { dr = (unsigned)c.rate[p]; dd = c.dist[p]; }
-        else { dr = (unsigned)(c.rate[p] - c.rate[n - 1]); dd = __dsub_rn(c.dist[p], c.dist[n - 1]); }
-        if (!dr) { if (dd != 0) n = p + 1; continue; }
-        if (__dsub_rn(thresh, __ddiv_rn(dd, (double)dr)) < 2.2204460492503131e-16) n = p + 1;
+    const int tp = c.totalpasses;
+    if (thresh < 0) return tp;
+    int n = 0, rprev = 0;
+    double dprev = 0.0;
+    for (int p0 = 0; p0 < tp; p0 += 4) {
+        int r[4]; double d[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { const int p = min(p0 + j, tp - 1); r[j] = c.rate[p]; d[j] = c.dist[p]; }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (p0 + j >= tp) break;
+            const unsigned dr = (unsigned)(r[j] - rprev);
+            const double dd = n == 0 ? d[j] : __dsub_rn(d[j], dprev);
+            bool keep;
+            if (!dr) keep = dd != 0;
+            else keep = __dsub_rn(thresh, __ddiv_rn(dd, (double)dr)) < 2.2204460492503131e-16;
+            if (keep) { n = p0 + j + 1; rprev = r[j]; dprev = d[j]; }
+        }
     }
     return n;
 }
@@ -292,7 +351,7 @@ k_pcrd_t2(const Plan *__restrict__ plan, const CblkDesc *__restrict__ cblks, Cbl
 {
     EBCC_DYN_SMEM(unsigned char, smem);
     __shared__ double red_min[T2_THREADS / 32], red_max[T2_THREADS / 32];
-    __shared__ int scratch[T2_THREADS / 32 + 1];
+    __shared__ __align__(8) int scratch[2 * (T2_THREADS / 32) + 2];
     const int tid = threadIdx.x, nt = blockDim.x, frame = blockIdx.x;
     const int ncblks = plan->ncblks, nnodes = plan->nnodes;
     if (stat && (stat[frame].flags & (STAT_CONST | STAT_NANINF))) {
@@ -340,6 +399,7 @@ k_pcrd_t2(const Plan *__restrict__ plan, const CblkDesc *__restrict__ cblks, Cbl
     __syncthreads();
     for (int w = 0; w < (nt >> 5); ++w) { if (red_min[w] < mn) mn = red_min[w]; if (red_max[w] > mx) mx = red_max[w]; }
 
+    t2_tree_static(plan, cblks, co, s);
     const int maxlen = maxlen_arr[frame];
     double goodthresh = -1.0;
     int iters = 0;

@@ -167,6 +167,8 @@ static inline cudaError_t cudaDeviceSynchronize() { return 0; }
 static inline cudaError_t cudaSetDevice(int) { return 0; }
 static inline cudaError_t cudaGetDevice(int *d) { *d = 0; return 0; }
 static inline cudaError_t cudaGetDeviceCount(int *d) { *d = 1; return 0; }
+static inline cudaError_t cudaDeviceGetStreamPriorityRange(int *l, int *g) { *l = 0; *g = 0; return 0; }
+static inline cudaError_t cudaStreamCreateWithPriority(cudaStream_t *s, unsigned, int) { *s = 0; return 0; }
 cudaError_t cudaEventCreate(cudaEvent_t *e);
 static inline cudaError_t cudaEventCreateWithFlags(cudaEvent_t *e, unsigned) { return cudaEventCreate(e); }
 cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t s = 0);
