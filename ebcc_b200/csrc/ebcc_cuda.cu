@@ -1646,3 +1646,61 @@ extern "C" int ebcc_cuda_bench_resident_pipelined(ebcc_cuda_ctx **ctxs, int nctx
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(ts);
     return rc;
 }
+
+// ---- allocation-free entry point (no counterpart in the reference) -----------
+// Frame statistics (findMinMaxf + check_nan_inf) of device-resident frames for callers that must not allocate: code
+// under CUDA graph capture, tight serving loops.  The FrameStat records k_minmax reduces into with atomics -- the scratch
+// memory a context normally holds in its cudaMalloc'ed d_stat -- live in a file-scope __device__ array instead, which
+// every GPU that loads the library keeps until exit (EBCC_NOALLOC_MAX_FRAMES x 32 bytes = 128 KiB).  In host code the
+// array's name is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress, taken once per
+// device with that device current.  All calls share the array, so calls that overlap on the GPU (different streams
+// without ordering) race; k_stat_init clears the records a call uses before the reduction touches them.
+static __device__ __align__(256) FrameStat g_noalloc_stat[EBCC_NOALLOC_MAX_FRAMES];
+#define NOALLOC_MAX_DEVICES 64
+static FrameStat *g_noalloc_ptr[NOALLOC_MAX_DEVICES];
+static pthread_mutex_t g_noalloc_mu = PTHREAD_MUTEX_INITIALIZER;
+
+__global__ void k_stat_export(const FrameStat *__restrict__ stat, float *minv, float *maxv, int *flags, int nframes)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nframes) { minv[i] = stat[i].minv; maxv[i] = stat[i].maxv; flags[i] = stat[i].flags; }
+}
+
+extern "C" int ebcc_cuda_frame_stats_noalloc(const float *d_frames, size_t nframes, size_t samples_per_frame,
+                                             float *d_minv, float *d_maxv, int *d_flags, void *stream)
+{
+    if (!d_frames || !d_minv || !d_maxv || !d_flags || nframes == 0 || samples_per_frame == 0) {
+        fprintf(stderr, "[ebcc-cuda] ebcc_cuda_frame_stats_noalloc: null pointer or empty batch\n");
+        return -1;
+    }
+    if (nframes > EBCC_NOALLOC_MAX_FRAMES || samples_per_frame > 0x7fffffffull) {
+        fprintf(stderr, "[ebcc-cuda] ebcc_cuda_frame_stats_noalloc: %zu frames of %zu samples exceed the static scratch "
+                        "(at most %d frames of at most 2^31-1 samples per call)\n", nframes, samples_per_frame, EBCC_NOALLOC_MAX_FRAMES);
+        return -1;
+    }
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) { fprintf(stderr, "[ebcc-cuda] ebcc_cuda_frame_stats_noalloc: device %d out of range\n", dev); return -1; }
+    pthread_mutex_lock(&g_noalloc_mu);
+    FrameStat *stat = g_noalloc_ptr[dev];
+    if (!stat) {                                       // set-up, once per device, with that device current
+        cudaError_t e = cudaGetSymbolAddress((void **)&stat, g_noalloc_stat);
+        if (e != cudaSuccess || !stat) {
+            pthread_mutex_unlock(&g_noalloc_mu);
+            fprintf(stderr, "[ebcc-cuda] cudaGetSymbolAddress(g_noalloc_stat) failed on device %d: %s\n", dev, cudaGetErrorString(e));
+            (void)cudaGetLastError();
+            return -1;
+        }
+        g_noalloc_ptr[dev] = stat;
+    }
+    pthread_mutex_unlock(&g_noalloc_mu);
+    cudaStream_t s = (cudaStream_t)stream;
+    const int B = (int)nframes, N = (int)samples_per_frame;
+    const dim3 gsmall((unsigned)((B + 127) / 128));
+    EBCC_LAUNCH(k_stat_init, gsmall, dim3(128), 0, s, stat, B);               // the shared records start from scratch
+    EBCC_LAUNCH(k_minmax, dim3(B >= 8 ? 74u : 296u, (unsigned)B), dim3(256), 0, s, d_frames, stat, N);
+    EBCC_LAUNCH(k_minmax_final, gsmall, dim3(128), 0, s, d_frames, stat, N, B);
+    EBCC_LAUNCH(k_stat_export, gsmall, dim3(128), 0, s, stat, d_minv, d_maxv, d_flags, B);
+    CK(cudaGetLastError());
+    return 0;
+}

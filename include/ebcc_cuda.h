@@ -89,6 +89,18 @@ int ebcc_cuda_rate_probe(ebcc_cuda_ctx *ctx, size_t nframes, const float *cr, co
 int ebcc_cuda_rate_probe_streams_only(ebcc_cuda_ctx *ctx, size_t nframes, const float *cr);
 int ebcc_cuda_frame_stats(ebcc_cuda_ctx *ctx, size_t nframes, float *minv, float *maxv, int *flags);
 
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops).  The min / max / flags stage of the encoder
+ * (what ebcc_cuda_frame_stats reports after an analysis pass) on nframes device-resident frames of samples_per_frame
+ * floats each, on the CURRENT device, enqueued on `stream` (a cudaStream_t, NULL = default stream); the results land in
+ * the caller's DEVICE arrays d_minv / d_maxv / d_flags once the stream has run (the call does not synchronise).
+ * Allocates nothing: the per-frame reduction records live in a static __device__ array of
+ * EBCC_NOALLOC_MAX_FRAMES entries (128 KiB per GPU, held until exit); more frames per call are rejected with -1.
+ * All calls share that array: calls that overlap on the GPU race, so order them on one stream or with events. */
+#define EBCC_NOALLOC_MAX_FRAMES 4096
+int ebcc_cuda_frame_stats_noalloc(const float *d_frames, size_t nframes, size_t samples_per_frame,
+                                  float *d_minv, float *d_maxv, int *d_flags, void *stream);
+
 /* Residual layer on the resident batch (src/ebcc_codec.c:744-817): SPIHT encode of the normalised residual of the
  * last rate probe with a bit budget (spiht_encode), probes of the truncation search (spiht_decode of a prefix +
  * get_max_error / get_mean_error), and the zstd stage.  active[i] == 0 skips frame i. */

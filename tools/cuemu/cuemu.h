@@ -134,7 +134,7 @@ static inline float fminf_(float a, float b) { return fminf(a, b); }
 
 // ---- runtime API subset -----------------------------------------------------------------------
 typedef int cudaError_t;
-typedef int cudaStream_t;
+typedef intptr_t cudaStream_t;
 typedef struct cuemu_event { double t; } *cudaEvent_t;
 enum { cudaSuccess = 0 };
 enum cudaMemcpyKind { cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice, cudaMemcpyDefault };
@@ -177,5 +177,6 @@ static inline cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, unsigne
 cudaError_t cudaEventElapsedTime(float *ms, cudaEvent_t a, cudaEvent_t b);
 static inline cudaError_t cudaEventDestroy(cudaEvent_t e) { free(e); return 0; }
 template <typename F> static inline cudaError_t cudaFuncSetAttribute(F, cudaFuncAttribute, int) { return 0; }
+template <typename T> static inline cudaError_t cudaGetSymbolAddress(void **p, T &sym) { *p = (void *)&sym; return 0; }
 template <typename T> static inline cudaError_t cudaMemcpyToSymbol(T &sym, const void *src, size_t n, size_t off = 0, cudaMemcpyKind = cudaMemcpyHostToDevice)
 { memcpy((char *)&sym + off, src, n); return 0; }
