@@ -8,6 +8,7 @@
 #include "k_t2.cuh"
 #include "k_dec.cuh"
 #include "k_idwt.cuh"
+#include "k_idwt_fused.cuh"
 #include "k_spiht.cuh"
 #include "k_zstd.cuh"
 #include "../../include/ebcc_cuda.h"
@@ -306,6 +307,7 @@ struct ebcc_cuda_ctx {
     unsigned char *d_streams;  // [B][out_stride] codestreams to decode
     int *d_slens, *d_status;
     DecJob *d_jobs;            // [B][ncblks]
+    uint2 *d_rjobs;            // [B][ncblks] compact per-block records of a probe (k_jobs_from_enc -> k_idwt_tile)
     int *d_iplane;             // [B][H][W] tier-1 decoder output (integer, Mallat layout); the recording of the CR search
     int *d_scratch;            // [B][H][W] per-probe real decodes of blocks the recording cannot serve
     unsigned char *d_spass;    // [B][H][W] pass in which each sample became significant (recording)
@@ -319,6 +321,8 @@ struct ebcc_cuda_ctx {
     int rec_from_encoder;      // recording + cut verdicts come from the encoder (k_t1_cm / k_t1_mq); 0: from k_t1_dec (EBCC_DECODER_RECORDING=1)
     int for_search;            // the running analysis feeds a compression-ratio search
     float *d_dcoef;            // [B][H][W] dequantised coefficients / IDWT work plane
+    float *d_dcoef2;           // [B][H][W] second work plane: the fused IDWT levels ping-pong between the two
+    int skip_dec;              // this probe's decoded frames are not needed (search probe: only the statistics are)
     float *d_dec;              // [B][H][W] decoded frames
     ErrStat *d_es;
     float *d_targets;
@@ -374,6 +378,7 @@ struct ebcc_cuda_ctx {
     int prio_split;
     int crowd;                 // pipelines at work on this device (hint from the host codec), see mq_lanes()
     int env_mq_lanes, env_dec_lanes, env_no_recording, env_dec_recording, env_debug_lanes, env_t1rec_ctas, env_dwt_cw;   // tuning / debugging variables, read once per host call (read_env)
+    int env_fused_idwt, env_fused_dwt, env_sp_serial;
     int ntiles;
     ebcc_cuda_ctx *tile[EBCC_MAX_TILES];
     ebcc_cuda_ctx *parent;
@@ -534,11 +539,11 @@ static void free_buffers(ebcc_cuda_ctx *c)
     cudaFree(c->d_maxlen); cudaFree(c->d_body_off); cudaFree(c->d_pout); cudaFree(c->d_offs);
     cudaFreeHost(c->h_pout); cudaFreeHost(c->h_stat); cudaFreeHost(c->h_offs); cudaFreeHost(c->h_maxlen);
     cudaFreeHost(c->h_packed); cudaFreeHost(c->h_stage);
-    cudaFree(c->d_streams); cudaFree(c->d_slens); cudaFree(c->d_status); cudaFree(c->d_jobs); cudaFree(c->d_iplane); cudaFree(c->d_scratch); cudaFree(c->d_spass); cudaFree(c->d_dstate); cudaFree(c->d_decsave);
+    cudaFree(c->d_streams); cudaFree(c->d_slens); cudaFree(c->d_status); cudaFree(c->d_jobs); cudaFree(c->d_rjobs); c->d_rjobs = NULL; cudaFree(c->d_iplane); cudaFree(c->d_scratch); cudaFree(c->d_spass); cudaFree(c->d_dstate); cudaFree(c->d_decsave);
     cudaFree(c->d_cut_list); cudaFree(c->d_cut_count); cudaFree(c->d_cut_pool); c->d_cut_list = NULL; c->d_cut_count = NULL; c->d_cut_pool = NULL;
     cudaFreeHost(c->h_cut_count); c->h_cut_count = NULL;
     c->d_scratch = NULL; c->d_spass = NULL; c->d_dstate = NULL; c->d_decsave = NULL;
-    cudaFree(c->d_dcoef); cudaFree(c->d_dec); cudaFree(c->d_es); cudaFree(c->d_targets);
+    cudaFree(c->d_dcoef); cudaFree(c->d_dcoef2); c->d_dcoef2 = NULL; cudaFree(c->d_dec); cudaFree(c->d_es); cudaFree(c->d_targets);
     cudaFreeHost(c->h_es); cudaFreeHost(c->h_status); cudaFreeHost(c->h_slens); cudaFreeHost(c->h_targets); cudaFreeHost(c->h_streams);
     c->d_streams = NULL; c->d_slens = c->d_status = NULL; c->d_jobs = NULL; c->d_iplane = NULL; c->d_dcoef = c->d_dec = NULL;
     c->d_es = NULL; c->d_targets = NULL; c->h_es = NULL; c->h_status = c->h_slens = NULL; c->h_targets = NULL; c->h_streams = NULL;
@@ -644,6 +649,7 @@ static int reserve_alloc(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes, i
     CK(cudaMalloc((void **)&c->d_slens, B * sizeof(int)));
     CK(cudaMalloc((void **)&c->d_status, B * sizeof(int)));
     CK(cudaMalloc((void **)&c->d_jobs, B * pl->ncblks * sizeof(DecJob)));
+    CK(cudaMalloc((void **)&c->d_rjobs, B * pl->ncblks * sizeof(uint2)));
     CK(cudaMalloc((void **)&c->d_iplane, B * N * sizeof(int)));
     CK(cudaMalloc((void **)&c->d_scratch, B * N * sizeof(int)));
     CK(cudaMalloc((void **)&c->d_spass, B * N));
@@ -656,6 +662,7 @@ static int reserve_alloc(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes, i
     CK(cudaMalloc((void **)&c->d_cut_pool, (size_t)c->cut_cap * T1_CUT_WORDS * sizeof(int)));
     CK(cudaMalloc((void **)&c->d_decsave, B * pl->ncblks * (size_t)DEC_SAVE_WORDS * sizeof(unsigned)));
     CK(cudaMalloc((void **)&c->d_dcoef, B * N * sizeof(float)));
+    CK(cudaMalloc((void **)&c->d_dcoef2, B * N * sizeof(float)));
     CK(cudaMalloc((void **)&c->d_dec, B * N * sizeof(float)));
     CK(cudaMalloc((void **)&c->d_es, B * sizeof(ErrStat)));
     CK(cudaMalloc((void **)&c->d_targets, B * sizeof(float)));
@@ -758,6 +765,24 @@ static int launch_dwt(ebcc_cuda_ctx *c, int B)
     const Plan *pl = &c->plan;
     const int W = pl->W, H = pl->H;
     KT kt_(c, EBCC_KT_DWT);
+    if (ctx_root_mut(c)->env_fused_dwt) {
+        // one launch per level: vertical + horizontal analysis of a tile in shared memory; the LL band travels through the
+        // decoder's two work planes (idle during the analysis), the high bands go straight to their place
+        for (int r = J2K_NRES - 1; r >= 1; --r) {
+            DwtFusedArgs a;
+            const bool first = r == J2K_NRES - 1;
+            a.in = first ? c->d_in : (((J2K_NRES - 1 - r) & 1) ? c->d_dcoef : c->d_dcoef2);
+            a.ll_out = r == 1 ? c->d_coef : (((J2K_NRES - 1 - r) & 1) ? c->d_dcoef2 : c->d_dcoef);
+            a.coef = c->d_coef; a.stat = c->d_stat; a.W = W; a.H = H;
+            a.rw = pl->res_w[r]; a.rh = pl->res_h[r]; a.snw = pl->res_w[r - 1]; a.snh = pl->res_h[r - 1];
+            const dim3 grid((unsigned)((a.rw + FT_TW - 1) / FT_TW), (unsigned)((a.rh + FT_TH - 1) / FT_TH), (unsigned)B);
+            void (*kern)(DwtFusedArgs) = pl->cas_v[r] == 0 ? (first ? k_dwt_tile<true, 0> : k_dwt_tile<false, 0>)
+                                                           : (first ? k_dwt_tile<true, 1> : k_dwt_tile<false, 1>);
+            EBCC_LAUNCH(kern, grid, dim3(FT_THREADS), 0, c->stream, a);
+            c->launches++;
+        }
+        return 0;
+    }
     for (int r = J2K_NRES - 1; r >= 1; --r) {
         const int rw = pl->res_w[r], rh = pl->res_h[r];
         // vertical: strips of CW columns, full height in shared memory
@@ -802,6 +827,12 @@ static void read_env(ebcc_cuda_ctx *c)
     c->env_debug_lanes = getenv("EBCC_DEBUG_LANES") != NULL;
     e = getenv("EBCC_T1REC_CTAS");                  // tuning: CTAs per SM the recording variant of k_t1_cm is compiled for (2 or 3)
     c->env_t1rec_ctas = e ? atoi(e) : 2;
+    e = getenv("EBCC_FUSED_IDWT");                  // 0: the unfused inverse transform (k_dequant / k_recon_dequant, k_idwt_h / k_idwt_v, k_finalize)
+    c->env_fused_idwt = !(e && e[0] == '0');
+    e = getenv("EBCC_SP_DECODE_SERIAL");            // cross-check aid: the one-thread SPIHT list decoder
+    c->env_sp_serial = e && e[0] == '1';
+    e = getenv("EBCC_FUSED_DWT");                   // 0: the unfused forward transform (k_dwt_v / k_dwt_h)
+    c->env_fused_dwt = !(e && e[0] == '0');
     e = getenv("EBCC_DWT_CW");                      // tuning: columns per CTA of the vertical 9/7 passes (shared memory = height x columns x 4 bytes)
     c->env_dwt_cw = e ? atoi(e) : 32;
     if (c->env_dwt_cw != 4 && c->env_dwt_cw != 8 && c->env_dwt_cw != 16 && c->env_dwt_cw != 32) c->env_dwt_cw = 32;
@@ -1021,6 +1052,37 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
         if (lanes == 8) DEC_GO(8); else if (lanes == 4) DEC_GO(4); else if (lanes == 2) DEC_GO(2); else DEC_GO(1);
 #undef DEC_GO
     }
+    // The fused path serves decodes and every probe the recording, the verdicts and the pool of pre-decoded cuts answer by
+    // themselves (no tier-1 decoder ran above); the rare probe that had to decode blocks into the scratch plane takes the
+    // unfused kernels below.
+    const bool no_t1_decode = probe && c->rec_from_encoder && c->use_recording && c->cut_known && !c->cut_overflow;
+    if (ctx_root(c)->env_fused_idwt && (!probe || no_t1_decode)) {
+        KT kt_iw(c, EBCC_KT_IDWT);
+        if (orig) { EBCC_LAUNCH(k_errstat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_es, B); c->launches++; }
+        for (int r = 1; r < J2K_NRES; ++r) {
+            IdwtFusedArgs a;
+            a.plan = c->d_plan; a.cblks = c->d_cblks; a.iplane = c->d_iplane; a.spass = c->d_spass;
+            a.cut_pool = (const int *)c->d_cut_pool; a.rjobs = c->d_rjobs;
+            a.ll_in = (r & 1) ? c->d_dcoef2 : c->d_dcoef;
+            a.out = (r & 1) ? c->d_dcoef : c->d_dcoef2;
+            a.r = r; a.rw = pl->res_w[r]; a.rh = pl->res_h[r]; a.snw = pl->res_w[r - 1]; a.snh = pl->res_h[r - 1];
+            a.stat = c->d_stat; a.orig = orig; a.targets = orig ? c->d_targets : (const float *)NULL; a.es = c->d_es;
+            const dim3 grid((unsigned)((a.rw + FT_TW - 1) / FT_TW), (unsigned)((a.rh + FT_TH - 1) / FT_TH), (unsigned)B);
+            const bool fin = r == J2K_NRES - 1;
+            if (fin) a.out = (probe && c->skip_dec) ? (float *)NULL : c->d_dec;
+            void (*kern)(IdwtFusedArgs);
+            if (pl->cas_v[r] == 0)
+                kern = probe ? (fin ? k_idwt_tile<IDF_SRC_RECON, true, 0> : k_idwt_tile<IDF_SRC_RECON, false, 0>)
+                             : (fin ? k_idwt_tile<IDF_SRC_IPLANE, true, 0> : k_idwt_tile<IDF_SRC_IPLANE, false, 0>);
+            else
+                kern = probe ? (fin ? k_idwt_tile<IDF_SRC_RECON, true, 1> : k_idwt_tile<IDF_SRC_RECON, false, 1>)
+                             : (fin ? k_idwt_tile<IDF_SRC_IPLANE, true, 1> : k_idwt_tile<IDF_SRC_IPLANE, false, 1>);
+            EBCC_LAUNCH(kern, grid, dim3(FT_THREADS), 0, c->stream, a);
+            c->launches++;
+        }
+        CK(cudaGetLastError());
+        return 0;
+    }
     KT *kt_rc = new KT(c, EBCC_KT_RECON);
     if (probe)
         EBCC_LAUNCH(k_recon_dequant, dim3(148 * 2, (unsigned)B), dim3(256), 0, c->stream, c->d_plan, c->d_cbout, c->d_dstate, c->d_jobs,
@@ -1071,7 +1133,7 @@ static int probe_launch(ebcc_cuda_ctx *c, int B, const float *targets)
     CK(cudaMemcpyAsync(c->d_targets, c->h_targets, sizeof(float) * B, cudaMemcpyHostToDevice, c->stream));
     const long long njobs = (long long)pl->ncblks * B;
     EBCC_LAUNCH(k_jobs_from_enc, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cblks, c->d_cbout, c->d_dstate, c->d_jobs,
-                pl->ncblks, B, c->use_recording);
+                pl->ncblks, B, c->use_recording, c->d_rjobs);
     c->launches++;
     if (run_decode_stage(c, B, c->d_mq, pl->mq_stride, c->d_in)) return -1;
     CK(cudaMemcpyAsync(c->h_es, c->d_es, sizeof(ErrStat) * B, cudaMemcpyDeviceToHost, c->stream));
@@ -1099,6 +1161,7 @@ extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const floa
     CK(cudaSetDevice(c->device));
     const int B = (int)nframes;
     if (launch_rate_stage(c, B, cr, with_streams)) return -1;
+    c->skip_dec = !with_streams && c->ntiles == 1;      // the decoded frames of a search probe are never read, its statistics are
     if (c->ntiles > 1) {
         const int T = c->ntiles, hl = c->tile[0]->plan.main_header_len;
         for (int t = 0; t < T; ++t) if (probe_launch(c->tile[t], B, targets)) return -1;
@@ -1387,8 +1450,12 @@ extern "C" int ebcc_cuda_decode_batch_tiled(ebcc_cuda_ctx *c, const uint8_t *con
         }
         {
             KT kt_(c, EBCC_KT_SP_DECODE);
-            EBCC_LAUNCH(k_sp_decode, dim3((unsigned)B), dim3(32), 0, c->stream, (const unsigned char *)c->sp.bits, c->sp.bits_words * 4, (const int *)c->d_zcap, c->sp,
-                        c->d_sp_info, c->d_sp_img0, g, c->d_maxlen);
+            if (ctx_root(c)->env_sp_serial)
+                EBCC_LAUNCH(k_sp_decode_serial, dim3((unsigned)B), dim3(32), 0, c->stream, (const unsigned char *)c->sp.bits, c->sp.bits_words * 4, (const int *)c->d_zcap, c->sp,
+                            c->d_sp_info, c->d_sp_img0, g, c->d_maxlen);
+            else
+                EBCC_LAUNCH(k_sp_decode, dim3((unsigned)B), dim3(32), 0, c->stream, (const unsigned char *)c->sp.bits, c->sp.bits_words * 4, (const int *)c->d_zcap, c->sp,
+                            c->d_sp_info, c->d_sp_img0, g, c->d_maxlen);
         }
         c->launches += 3;
         {
@@ -1542,7 +1609,7 @@ extern "C" int ebcc_cuda_debug_check_cuts(ebcc_cuda_ctx *c, size_t nframes, unsi
     for (int np = 1; np < J2K_MAXPASSES; ++np) {
         EBCC_LAUNCH(k_dbg_force_np, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cbout, njobs, np);
         EBCC_LAUNCH(k_jobs_from_enc, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cblks, c->d_cbout, c->d_dstate, c->d_jobs,
-                    pl->ncblks, B, 0);
+                    pl->ncblks, B, 0, (uint2 *)NULL);
         const long long per_cta = (long long)DEC_WPC(1);
         EBCC_LAUNCH(k_t1_dec<1>, dim3((unsigned)((njobs + per_cta - 1) / per_cta)), dim3((unsigned)(DEC_WPC(1) * 32)), 0, c->stream, c->d_cblks, c->d_order,
                     c->d_jobs, c->d_mq, pl->mq_stride, c->d_declut, c->d_iplane, (unsigned char *)NULL, c->d_scratch, (const CblkOut *)c->d_cbout,

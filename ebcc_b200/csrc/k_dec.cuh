@@ -623,7 +623,7 @@ k_t1_dec_cuts(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cb
 // allocation needs more passes than its recording holds, served from the recording (mode 0) when the recording can
 // reproduce "first numpasses passes", and decoded for real into the scratch plane (mode 2) otherwise.
 __global__ void k_jobs_from_enc(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cbout, const DecState *__restrict__ dstate,
-                                DecJob *jobs, int ncblks, int nframes, int use_recording)
+                                DecJob *jobs, int ncblks, int nframes, int use_recording, uint2 *rjobs)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (long long)ncblks * nframes) return;
@@ -649,6 +649,9 @@ __global__ void k_jobs_from_enc(const CblkDesc *__restrict__ cblks, const CblkOu
         else j.mode = d.scratch_np == np ? 3 : 2;
     }
     jobs[i] = j;
+    // compact record for the fused inverse transform (k_idwt_tile): mode | np << 8 | recorded passes << 16 | bit-planes << 24, pool entry
+    if (rjobs) rjobs[i] = make_uint2((unsigned)j.mode | ((unsigned)np << 8) | ((unsigned)(use_recording ? dstate[i].np_dec : 0) << 16) | ((unsigned)c.numbps << 24),
+                                     (unsigned)j.pad);
 }
 
 __global__ void k_dstate_reset(DecState *d, long long n)

@@ -36,6 +36,7 @@ struct uint2 { unsigned x, y; };
 static inline uint2 make_uint2(unsigned a, unsigned b) { uint2 r = {a, b}; return r; }
 struct float4 { float x, y, z, w; };
 struct uint4 { unsigned x, y, z, w; };
+static inline float4 make_float4(float a, float b, float c, float d) { float4 r = {a, b, c, d}; return r; }
 static inline uint4 make_uint4(unsigned a, unsigned b, unsigned c, unsigned d) { uint4 r = {a, b, c, d}; return r; }
 
 // ---- launch -------------------------------------------------------------------------------
@@ -107,6 +108,7 @@ static inline double __dmul_rn(double a, double b) { return a * b; }
 static inline double __ddiv_rn(double a, double b) { return a / b; }
 static inline int __float2int_rn(float a) { return (int)lrintf(a); }
 static inline long long __double2ll_rn(double a) { return llrint(a); }
+static inline double __longlong_as_double(long long a) { double d; memcpy(&d, &a, 8); return d; }
 static inline int __float2int_rz(float a) { return (int)a; }
 static inline unsigned __float2uint_rz(float a) { return a <= 0 ? 0u : (unsigned)a; }
 static inline float __int2float_rn(int a) { return (float)a; }
@@ -121,6 +123,12 @@ static inline int __ffs(int x) { return __builtin_ffs(x); }
 static inline int __popc(unsigned x) { return __builtin_popcount(x); }
 static inline int __popcll(unsigned long long x) { return __builtin_popcountll(x); }
 static inline unsigned __brev(unsigned x) { unsigned r = 0; for (int i = 0; i < 32; ++i) if (x >> i & 1) r |= 1u << (31 - i); return r; }
+static inline unsigned __byte_perm(unsigned a, unsigned b, unsigned sel)
+{
+    unsigned long long v = ((unsigned long long)b << 32) | a; unsigned r = 0;
+    for (int i = 0; i < 4; ++i) r |= (unsigned)((v >> (8 * ((sel >> (4 * i)) & 7))) & 0xff) << (8 * i);
+    return r;
+}
 static inline unsigned __funnelshift_l(unsigned lo, unsigned hi, unsigned s) { s &= 31; return s ? (hi << s) | (lo >> (32 - s)) : hi; }
 static inline unsigned __funnelshift_r(unsigned lo, unsigned hi, unsigned s) { s &= 31; return s ? (lo >> s) | (hi << (32 - s)) : lo; }
 template <typename T> static inline T __ldg(const T *p) { return *p; }
