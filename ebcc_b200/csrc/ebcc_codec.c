@@ -113,32 +113,78 @@ static int dims_are_valid(const size_t dims[NDIMS])
  * Every encode / decode call (and every worker of a multi-batch call) owns one pipeline while it runs, so callers on
  * several threads -- or several batches of one call -- are in flight on the device at the same time: the kernels of
  * one batch fill the issue slots the latency-bound tier-1 coder of another leaves idle.  EBCC_PIPELINES (1..16,
- * default 4) bounds how many. */
+ * default 4) bounds how many PER GPU.
+ *
+ * The pool spans GPUs: frames are independent (the reference's frame loop, src/ebcc_codec.c:1007-1046), so the batches of
+ * one call are dealt to the pipelines of every device of EBCC_CUDA_DEVICES ("0,1,3", or "all"); slot k lives on device
+ * k mod n, hence the first n workers of a call land on n different GPUs.  No data travels between GPUs: each batch is
+ * uploaded to, coded on and downloaded from its own device, the per-frame sizes meet on the host where the EBCK container
+ * is laid out by a prefix sum.  EBCC_CUDA_DEVICE (one ordinal) keeps a process on one GPU, which is what a launcher with
+ * one process per GPU sets; with neither variable every visible GPU is used. */
 #define EBCC_MAX_PIPELINES 16
+#define EBCC_MAX_DEVICES 16
+#define EBCC_MAX_SLOTS (EBCC_MAX_PIPELINES * EBCC_MAX_DEVICES)
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
 static pthread_cond_t g_cv = PTHREAD_COND_INITIALIZER;
-static ebcc_cuda_ctx *g_pool[EBCC_MAX_PIPELINES];
-static int g_busy[EBCC_MAX_PIPELINES];
+static ebcc_cuda_ctx *g_pool[EBCC_MAX_SLOTS];
+static int g_busy[EBCC_MAX_SLOTS];
 static int g_expected;     /* workers the running multi-batch calls are about to start (they may not have a pipeline yet) */
 static pid_t g_ctx_pid = 0;
+static int g_devs[EBCC_MAX_DEVICES], g_ndev = 0;   /* device ordinals the pool spans; resolved once per process */
 
-static int n_pipelines(void)
+/* caller holds g_mu */
+static void resolve_devices(void)
+{
+    if (g_ndev > 0) return;
+    const char *list = getenv("EBCC_CUDA_DEVICES"), *one = getenv("EBCC_CUDA_DEVICE");
+    if (list && *list && strcmp(list, "all") != 0) {
+        const char *p = list;
+        while (*p && g_ndev < EBCC_MAX_DEVICES) {
+            char *end = NULL;
+            const long v = strtol(p, &end, 10);
+            if (end == p) break;
+            if (v >= 0) g_devs[g_ndev++] = (int)v;
+            p = end;
+            while (*p == ',' || *p == ' ') ++p;
+        }
+    } else if (!list && one) {
+        g_devs[g_ndev++] = atoi(one);
+    } else {
+        int n = ebcc_cuda_device_count();
+        if (n > EBCC_MAX_DEVICES) n = EBCC_MAX_DEVICES;
+        for (int d = 0; d < n; ++d) g_devs[g_ndev++] = d;
+    }
+    if (g_ndev == 0) g_devs[g_ndev++] = 0;           /* no device: ctx creation fails loudly below */
+}
+
+static int pipelines_per_device(void)
 {
     const char *env = getenv("EBCC_PIPELINES");
     long v = env ? atol(env) : 4;
     return v < 1 ? 1 : (v > EBCC_MAX_PIPELINES ? EBCC_MAX_PIPELINES : (int)v);
 }
 
+/* pipelines over all devices of the pool */
+static int n_pipelines(void)
+{
+    pthread_mutex_lock(&g_mu);
+    resolve_devices();
+    const int nd = g_ndev;
+    pthread_mutex_unlock(&g_mu);
+    return pipelines_per_device() * nd;
+}
+
 /* blocks until a pipeline is free; NULL when no CUDA device is usable */
 static ebcc_cuda_ctx *acquire_ctx(void)
 {
-    const int np = n_pipelines();
     pthread_mutex_lock(&g_mu);
     const pid_t me = getpid();
     if (g_ctx_pid != me) {               /* contexts inherited through fork are abandoned, not reused */
-        for (int k = 0; k < EBCC_MAX_PIPELINES; ++k) { g_pool[k] = NULL; g_busy[k] = 0; }
+        for (int k = 0; k < EBCC_MAX_SLOTS; ++k) { g_pool[k] = NULL; g_busy[k] = 0; }
         g_ctx_pid = me;
     }
+    resolve_devices();
+    const int np = pipelines_per_device() * g_ndev;
     for (;;) {
         for (int k = 0; k < np; ++k) {
             if (g_busy[k]) continue;
@@ -146,9 +192,7 @@ static ebcc_cuda_ctx *acquire_ctx(void)
             if (!g_pool[k]) {
                 /* created outside the lock (the slot is already ours): callers that start together build their pipelines
                  * side by side instead of queueing behind one another's cudaMalloc / pinned allocations */
-                int dev = 0;
-                const char *env = getenv("EBCC_CUDA_DEVICE");
-                if (env) dev = atoi(env);
+                const int dev = g_devs[k % g_ndev];
                 pthread_mutex_unlock(&g_mu);
                 ebcc_cuda_ctx *c = ebcc_cuda_ctx_create(dev);
                 pthread_mutex_lock(&g_mu);
@@ -169,12 +213,12 @@ static ebcc_cuda_ctx *acquire_ctx(void)
     }
 }
 
-/* tells the device layer how crowded the GPU is: the largest number of pipelines seen at work (held right now, or about
- * to be by the multi-batch calls in flight) during the last two seconds.  The memory matters: callers on several threads
- * start and finish at slightly different times, and a call that sized its kernels for an empty GPU while fifteen others
- * are about to start would hog the SMs (measured: 22.6 -> 5 GB/s end to end without it). */
-static int g_crowd_max;
-static double g_crowd_t;
+/* tells the device layer how crowded ITS GPU is: the largest number of pipelines seen at work there (held right now, or
+ * about to be by the multi-batch calls in flight) during the last two seconds.  The memory matters: callers on several
+ * threads start and finish at slightly different times, and a call that sized its kernels for an empty GPU while fifteen
+ * others are about to start would hog the SMs (measured: 22.6 -> 5 GB/s end to end without it). */
+static int g_crowd_max[EBCC_MAX_DEVICES];
+static double g_crowd_t[EBCC_MAX_DEVICES];
 
 static void hint_crowd(ebcc_cuda_ctx *ctx)
 {
@@ -182,11 +226,16 @@ static void hint_crowd(ebcc_cuda_ctx *ctx)
     clock_gettime(CLOCK_MONOTONIC, &ts);
     const double now = (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
     pthread_mutex_lock(&g_mu);
+    const int nd = g_ndev > 0 ? g_ndev : 1;
+    int slot = 0;
+    for (int k = 0; k < EBCC_MAX_SLOTS; ++k) if (g_pool[k] == ctx) { slot = k; break; }
+    const int d = slot % nd;
     int busy = 0;
-    for (int k = 0; k < EBCC_MAX_PIPELINES; ++k) busy += g_busy[k];
-    if (g_expected > busy) busy = g_expected;
-    if (busy >= g_crowd_max || now - g_crowd_t > 2.0) { g_crowd_max = busy; g_crowd_t = now; }
-    busy = g_crowd_max;
+    for (int k = d; k < EBCC_MAX_SLOTS; k += nd) busy += g_busy[k];
+    const int expected = (g_expected + nd - 1) / nd;             /* the workers of a call spread evenly over the devices */
+    if (expected > busy) busy = expected;
+    if (busy >= g_crowd_max[d] || now - g_crowd_t[d] > 2.0) { g_crowd_max[d] = busy; g_crowd_t[d] = now; }
+    busy = g_crowd_max[d];
     pthread_mutex_unlock(&g_mu);
     ebcc_cuda_set_crowd(ctx, busy);
 }
@@ -202,8 +251,8 @@ static void expect_workers(int delta)
 static void release_ctx(ebcc_cuda_ctx *ctx)
 {
     pthread_mutex_lock(&g_mu);
-    for (int k = 0; k < EBCC_MAX_PIPELINES; ++k) if (g_pool[k] == ctx) g_busy[k] = 0;
-    pthread_cond_signal(&g_cv);
+    for (int k = 0; k < EBCC_MAX_SLOTS; ++k) if (g_pool[k] == ctx) g_busy[k] = 0;
+    pthread_cond_broadcast(&g_cv);
     pthread_mutex_unlock(&g_mu);
 }
 
@@ -635,7 +684,7 @@ size_t ebcc_encode_batch(const float *frames, size_t nframes, const codec_config
     const size_t nbatches = (nframes + job.maxb - 1) / job.maxb;
     int nworkers = n_pipelines();
     if ((size_t)nworkers > nbatches) nworkers = (int)nbatches;
-    pthread_t th[EBCC_MAX_PIPELINES];
+    pthread_t th[EBCC_MAX_SLOTS];
     int started = 0;
     expect_workers(nworkers);
     for (int k = 1; k < nworkers; ++k) if (pthread_create(&th[started], NULL, enc_worker, &job) == 0) started++;
@@ -857,7 +906,7 @@ static size_t decode_batch_impl(uint8_t *const *streams, const size_t *stream_si
     pthread_mutex_init(&job.mu, NULL);
     int nworkers = n_pipelines();
     if ((size_t)nworkers > job.ngroups) nworkers = (int)job.ngroups;
-    pthread_t th[EBCC_MAX_PIPELINES];
+    pthread_t th[EBCC_MAX_SLOTS];
     int started = 0;
     expect_workers(nworkers);
     for (int k = 1; k < nworkers; ++k) if (pthread_create(&th[started], NULL, dec_worker, &job) == 0) started++;

@@ -1454,7 +1454,7 @@ extern "C" int ebcc_cuda_decode_batch_tiled(ebcc_cuda_ctx *c, const uint8_t *con
                 EBCC_LAUNCH(k_sp_decode_serial, dim3((unsigned)B), dim3(32), 0, c->stream, (const unsigned char *)c->sp.bits, c->sp.bits_words * 4, (const int *)c->d_zcap, c->sp,
                             c->d_sp_info, c->d_sp_img0, g, c->d_maxlen);
             else
-                EBCC_LAUNCH(k_sp_decode, dim3((unsigned)B), dim3(32), 0, c->stream, (const unsigned char *)c->sp.bits, c->sp.bits_words * 4, (const int *)c->d_zcap, c->sp,
+                EBCC_LAUNCH(k_sp_decode, dim3((unsigned)B), dim3(SPD_THREADS), 0, c->stream, (const unsigned char *)c->sp.bits, c->sp.bits_words * 4, (const int *)c->d_zcap, c->sp,
                             c->d_sp_info, c->d_sp_img0, g, c->d_maxlen);
         }
         c->launches += 3;

@@ -187,6 +187,9 @@ __device__ __forceinline__ void mqd_init(MqDec &q, const unsigned char *data, in
 }
 
 // a context is a copy of its pair's table word, so one shared-memory load brings qe, mps and both successors
+// SH: truncation shadows may be armed (the cross-check recordings of the compression-ratio search); a plain decode
+// (ebcc_decode, the pool of unproven cuts) compiles without every shadow test
+template <bool SH>
 __device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned *ctx, const unsigned *tab)
 {
     const unsigned e = *ctx, qe = e & 0xffffu, mps = e >> 30;
@@ -202,16 +205,18 @@ __device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned *ctx, const un
         else { d = mps; ren = false; }
     }
     const int nshift = ren ? __clz((int)a1) - 16 : 0;
-    if (q.sh_on) mqd_shadow_step(q.sw, q.sh_on, qe, a0, mps, d, nshift, q.data);
+    if (SH && q.sh_on) mqd_shadow_step(q.sw, q.sh_on, qe, a0, mps, d, nshift, q.data);
     if (ren) {
         *ctx = tab[(d == mps) ? ((e >> 16) & 127u) : ((e >> 23) & 127u)];
-        // main decoder: shifts with fork checks at every byte read
         int n = nshift;
-        while (n > 0) {
-            if (q.m.ct == 0) mqd_main_bytein(q, n);
-            const int s = n < (int)q.m.ct ? n : (int)q.m.ct;
-            q.m.c <<= s; q.m.ct -= (unsigned)s; n -= s;
-        }
+        if (!SH && n <= (int)q.m.ct) { q.m.c <<= n; q.m.ct -= (unsigned)n; }      // the usual case: the bits are in the register
+        else
+            while (n > 0) {
+                // main decoder: shifts, with fork checks at every byte read when shadows ride along
+                if (q.m.ct == 0) { if (SH) mqd_main_bytein(q, n); else mqc_bytein(q.m, q.data); }
+                const int s = n < (int)q.m.ct ? n : (int)q.m.ct;
+                q.m.c <<= s; q.m.ct -= (unsigned)s; n -= s;
+            }
         q.a = a1 << nshift;
     } else q.a = a0;
     return d;
@@ -219,6 +224,7 @@ __device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned *ctx, const un
 
 struct T1DecState {
     unsigned *F;                 // flag words of this block
+    unsigned short *F2;          // candidate words of this block (sig4 | nb4 << 4 | pi4 << 8)
     unsigned *cx;                // 19 contexts (table words)
     const unsigned char *zc;     // zero-coding LUT of this orientation
     const unsigned *tab;
@@ -227,25 +233,50 @@ struct T1DecState {
     int W, pass;
 };
 
+// Second word per stripe column (16 bits), kept next to the flag word so that a pass finds the rows it has to visit with
+// one load and three logic operations instead of testing the four rows one by one:
+//   bits 0-3 sig4 (row significant), 4-7 nb4 (row has a significant neighbour), 8-11 pi4 (row coded in this plane's
+//   significance pass; mirror of DF_PI).  All bits zero <=> flag word zero.
+#define D2_SIG(f2) ((f2) & 0xfu)
+#define D2_NB(f2) (((f2) >> 4) & 0xfu)
+#define D2_PI(f2) (((f2) >> 8) & 0xfu)
+__device__ __forceinline__ unsigned d2_from_flags(unsigned f)
+{
+    unsigned r = 0;
+    for (int ci = 0; ci < 4; ++ci) {
+        if (f & DF_SIG(ci)) r |= 1u << ci;
+        if (f & DF_NB(ci)) r |= 0x10u << ci;
+        if (f & DF_PI(ci)) r |= 0x100u << ci;
+    }
+    return r;
+}
+
 // sample (stripe word index p, row ci) becomes significant with sign s: update the neighbourhood bits
-__device__ __forceinline__ void t1d_set_sig(T1DecState &S, int p, int ci, unsigned s, unsigned &f)
+__device__ __forceinline__ void t1d_set_sig(T1DecState &S, int p, int ci, unsigned s, unsigned &f, unsigned &f2)
 {
     f |= DF_SIG(ci) | (s ? DF_CHI(ci) : 0u);
+    f2 |= (1u << ci) | ((((5u << ci) >> 1) & 0xfu) << 4);            // own column: rows ci - 1 and ci + 1 gain a neighbour
+    const unsigned short side = (unsigned short)((((7u << ci) >> 1) & 0xfu) << 4);   // left / right column: rows ci - 1 .. ci + 1
     S.F[p - 1] |= 1u << ((ci + 1) * 3 + 2);
     S.F[p + 1] |= 1u << ((ci + 1) * 3 + 0);
+    S.F2[p - 1] |= side;
+    S.F2[p + 1] |= side;
     if (ci == 0) {
         S.F[p - DEC_FW] |= (1u << 16) | (s ? DF_CHI(4) : 0u);
         S.F[p - DEC_FW - 1] |= 1u << 17;
         S.F[p - DEC_FW + 1] |= 1u << 15;
+        S.F2[p - DEC_FW] |= 0x80; S.F2[p - DEC_FW - 1] |= 0x80; S.F2[p - DEC_FW + 1] |= 0x80;      // row 3 of the stripe above
     }
     if (ci == 3) {
         S.F[p + DEC_FW] |= (1u << 1) | (s ? DF_CHI(-1) : 0u);
         S.F[p + DEC_FW - 1] |= 1u << 2;
         S.F[p + DEC_FW + 1] |= 1u << 0;
+        S.F2[p + DEC_FW] |= 0x10; S.F2[p + DEC_FW - 1] |= 0x10; S.F2[p + DEC_FW + 1] |= 0x10;      // row 0 of the stripe below
     }
 }
 
 // decode the sign of (p, ci); returns 1 for negative
+template <bool SH>
 __device__ __forceinline__ unsigned t1d_sign(T1DecState &S, MqDec &q, int p, int ci, unsigned f)
 {
     const unsigned fl = S.F[p - 1], fr = S.F[p + 1];
@@ -255,7 +286,7 @@ __device__ __forceinline__ unsigned t1d_sign(T1DecState &S, MqDec &q, int p, int
     const int nn = (f >> (18 + ci)) & 1, ns = (f >> (18 + ci + 2)) & 1;
     const int hc = t1_contrib(se, ne, sw, nw), vc = t1_contrib(sn, nn, ss, ns);
     const int e = t1_sc_lut(hc, vc);
-    const unsigned v = mqd_decode(q, S.cx + CTX_SC + (e & 7), S.tab);
+    const unsigned v = mqd_decode<SH>(q, S.cx + CTX_SC + (e & 7), S.tab);
     return v ^ (unsigned)(e >> 3);
 }
 
@@ -265,80 +296,101 @@ __device__ __forceinline__ void t1d_new_sig(T1DecState &S, int y, int x, unsigne
     if (S.spass) S.spass[(size_t)y * S.W + x] = (unsigned char)S.pass;
 }
 
+template <bool SH>
 __device__ void t1d_clnpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
 {
     const int oneplushalf = 3 << bpno;
     for (int s = 0, y0 = 0; y0 < h; ++s, y0 += 4) {
         const int lim = min(4, h - y0);
+        const unsigned limmask = (1u << lim) - 1u;
         for (int x = 0; x < w; ++x) {
             const int p = (s + 1) * DEC_FW + x + 1;
-            unsigned f = S.F[p];
-            int first = 0, partial = 0;
-            if (lim == 4 && f == 0) {
-                if (!mqd_decode(q, S.cx + CTX_AGG, S.tab)) continue;
-                unsigned r = mqd_decode(q, S.cx + CTX_UNI, S.tab);
-                r = (r << 1) | mqd_decode(q, S.cx + CTX_UNI, S.tab);
-                first = (int)r; partial = 1;
-            }
-            for (int ci = first; ci < lim; ++ci) {
-                if (!partial && (f & (DF_SIG(ci) | DF_PI(ci)))) continue;
-                if (!partial) {
-                    const unsigned ctx = S.zc[(f >> (ci * 3)) & 0x1ffu];
-                    if (!mqd_decode(q, S.cx + CTX_ZC + ctx, S.tab)) continue;
+            unsigned f2 = S.F2[p];
+            unsigned cand = ~(D2_SIG(f2) | D2_PI(f2)) & limmask;            // rows neither significant nor coded in the significance pass
+            unsigned f;
+            if (lim == 4 && (f2 & 0xfffu) == 0) {                           // flag word all zero: run-length mode
+                if (!mqd_decode<SH>(q, S.cx + CTX_AGG, S.tab)) continue;
+                unsigned r = mqd_decode<SH>(q, S.cx + CTX_UNI, S.tab);
+                r = (r << 1) | mqd_decode<SH>(q, S.cx + CTX_UNI, S.tab);
+                f = 0;
+                const unsigned sg = t1d_sign<SH>(S, q, p, (int)r, f);
+                t1d_new_sig(S, y0 + (int)r, x, sg, oneplushalf);
+                t1d_set_sig(S, p, (int)r, sg, f, f2);
+                cand &= ~((2u << r) - 1u);                                   // the rows behind it are coded normally
+            } else {
+                if (cand == 0) {                                            // nothing to code; the pass still ends the plane for this column
+                    if (f2 & 0xf00u) { S.F[p] &= ~(0xfu << 24); S.F2[p] = (unsigned short)(f2 & ~0xf00u); }
+                    continue;
                 }
-                partial = 0;
-                const unsigned sg = t1d_sign(S, q, p, ci, f);
+                f = S.F[p];
+            }
+            while (cand) {
+                const int ci = __ffs((int)cand) - 1;
+                cand &= cand - 1u;
+                const unsigned ctx = S.zc[(f >> (ci * 3)) & 0x1ffu];
+                if (!mqd_decode<SH>(q, S.cx + CTX_ZC + ctx, S.tab)) continue;
+                const unsigned sg = t1d_sign<SH>(S, q, p, ci, f);
                 t1d_new_sig(S, y0 + ci, x, sg, oneplushalf);
-                t1d_set_sig(S, p, ci, sg, f);
+                t1d_set_sig(S, p, ci, sg, f, f2);
             }
             S.F[p] = f & ~(0xfu << 24);
+            S.F2[p] = (unsigned short)(f2 & ~0xf00u);
         }
     }
 }
 
+template <bool SH>
 __device__ void t1d_sigpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
 {
     const int oneplushalf = 3 << bpno;
     for (int s = 0, y0 = 0; y0 < h; ++s, y0 += 4) {
         const int lim = min(4, h - y0);
+        const unsigned limmask = (1u << lim) - 1u;
         for (int x = 0; x < w; ++x) {
             const int p = (s + 1) * DEC_FW + x + 1;
+            unsigned f2 = S.F2[p];
+            unsigned cand = D2_NB(f2) & ~(D2_SIG(f2) | D2_PI(f2)) & limmask;   // insignificant rows with a significant neighbour
+            if (cand == 0) continue;
             unsigned f = S.F[p];
-            if (f == 0) continue;
-            for (int ci = 0; ci < lim; ++ci) {
-                if ((f & (DF_SIG(ci) | DF_PI(ci))) == 0 && (f & DF_NB(ci)) != 0) {
-                    const unsigned ctx = S.zc[(f >> (ci * 3)) & 0x1ffu];
-                    if (mqd_decode(q, S.cx + CTX_ZC + ctx, S.tab)) {
-                        const unsigned sg = t1d_sign(S, q, p, ci, f);
-                        t1d_new_sig(S, y0 + ci, x, sg, oneplushalf);
-                        t1d_set_sig(S, p, ci, sg, f);
-                    }
-                    f |= DF_PI(ci);
+            do {
+                const int ci = __ffs((int)cand) - 1;
+                const unsigned ctx = S.zc[(f >> (ci * 3)) & 0x1ffu];
+                if (mqd_decode<SH>(q, S.cx + CTX_ZC + ctx, S.tab)) {
+                    const unsigned sg = t1d_sign<SH>(S, q, p, ci, f);
+                    t1d_new_sig(S, y0 + ci, x, sg, oneplushalf);
+                    t1d_set_sig(S, p, ci, sg, f, f2);
                 }
-            }
-            S.F[p] = f;
+                f |= DF_PI(ci); f2 |= 0x100u << ci;
+                // a row that just turned significant makes the rows behind it candidates
+                cand = D2_NB(f2) & ~(D2_SIG(f2) | D2_PI(f2)) & limmask & ~((2u << ci) - 1u);
+            } while (cand);
+            S.F[p] = f; S.F2[p] = (unsigned short)f2;
         }
     }
 }
 
+template <bool SH>
 __device__ void t1d_refpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
 {
     const int poshalf = 1 << bpno;
     for (int s = 0, y0 = 0; y0 < h; ++s, y0 += 4) {
         const int lim = min(4, h - y0);
+        const unsigned limmask = (1u << lim) - 1u;
         for (int x = 0; x < w; ++x) {
             const int p = (s + 1) * DEC_FW + x + 1;
+            const unsigned f2 = S.F2[p];
+            unsigned cand = D2_SIG(f2) & ~D2_PI(f2) & limmask;              // significant before this plane
+            if (cand == 0) continue;
             unsigned f = S.F[p];
-            if (f == 0) continue;
-            for (int ci = 0; ci < lim; ++ci) {
-                if ((f & (DF_SIG(ci) | DF_PI(ci))) == DF_SIG(ci)) {
-                    const int ctx = (f & DF_MU(ci)) ? CTX_MAG + 2 : ((f & DF_NB(ci)) ? CTX_MAG + 1 : CTX_MAG);
-                    const unsigned v = mqd_decode(q, S.cx + ctx, S.tab);
-                    const unsigned neg = (f >> (18 + ci + 1)) & 1u;
-                    atomicAdd(S.plane + (size_t)(y0 + ci) * S.W + x, (v ^ neg) ? poshalf : -poshalf);
-                    f |= DF_MU(ci);
-                }
-            }
+            do {
+                const int ci = __ffs((int)cand) - 1;
+                cand &= cand - 1u;
+                const int ctx = (f & DF_MU(ci)) ? CTX_MAG + 2 : ((f & DF_NB(ci)) ? CTX_MAG + 1 : CTX_MAG);
+                const unsigned v = mqd_decode<SH>(q, S.cx + ctx, S.tab);
+                const unsigned neg = (f >> (18 + ci + 1)) & 1u;
+                atomicAdd(S.plane + (size_t)(y0 + ci) * S.W + x, (v ^ neg) ? poshalf : -poshalf);
+                f |= DF_MU(ci);
+            } while (cand);
             S.F[p] = f;
         }
     }
@@ -347,6 +399,7 @@ __device__ void t1d_refpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
 // coding passes p0 .. p1-1 of one block (pass 0 = cleanup of the top bit-plane, then sig / ref / cleanup per plane).
 // rates != nullptr: truncation shadows for the cuts rates[0 .. nrates-1]; the verdict of cut p lands in ds.bad when
 // pass p ends.
+template <bool SH>
 __device__ void t1d_passes(T1DecState &S, MqDec &q, int w, int h, int numbps, int p0, int p1,
                            const int *rates, int nrates, DecState &ds)
 {
@@ -354,9 +407,9 @@ __device__ void t1d_passes(T1DecState &S, MqDec &q, int w, int h, int numbps, in
         const int passtype = p == 0 ? 2 : (p - 1) % 3, bpno = p == 0 ? numbps - 1 : numbps - 2 - (p - 1) / 3;
         if (bpno < 0) break;
         S.pass = p;
-        if (passtype == 0) t1d_sigpass(S, q, w, h, bpno);
-        else if (passtype == 1) t1d_refpass(S, q, w, h, bpno);
-        else t1d_clnpass(S, q, w, h, bpno);
+        if (passtype == 0) t1d_sigpass<SH>(S, q, w, h, bpno);
+        else if (passtype == 1) t1d_refpass<SH>(S, q, w, h, bpno);
+        else t1d_clnpass<SH>(S, q, w, h, bpno);
         if (rates) {
             const int pn = p + DEC_NSHADOW;
             if (mqd_retire(q.sw, q.sh_on, pn < nrates ? rates[pn] : -1, q.maxread) && p < 128) ds.bad[p >> 5] |= 1u << (p & 31);
@@ -437,6 +490,7 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJ
 {
     constexpr int NB = DEC_WPC(L) * L;          // blocks per CTA
     __shared__ unsigned F[NB][DEC_FWORDS];
+    __shared__ unsigned short F2[NB][DEC_FWORDS];
     __shared__ unsigned cxs[NB][20];
     __shared__ MqShadows shw[NB];
     __shared__ int need2[NB];
@@ -457,9 +511,9 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJ
         const bool resume = v.mode == 1 && search && dstate[v.bi].np_dec > 0;
         if (resume) {
             const unsigned *sv = save + v.bi * DEC_SAVE_WORDS;
-            for (int i = lane; i < DEC_FWORDS; i += 32) Fb[i] = sv[i];
+            for (int i = lane; i < DEC_FWORDS; i += 32) { Fb[i] = sv[i]; F2[warp * L + sb][i] = (unsigned short)d2_from_flags(sv[i]); }
         } else {
-            for (int i = lane; i < DEC_FWORDS; i += 32) Fb[i] = 0;
+            for (int i = lane; i < DEC_FWORDS; i += 32) { Fb[i] = 0; F2[warp * L + sb][i] = 0; }
             int *dst = (v.mode == 1 ? iplane : scratch) + v.o;
             unsigned char *sp = (v.mode == 1 && spass) ? spass + v.o : nullptr;
             for (int i = lane; i < v.cb.w * v.cb.h; i += 32) {
@@ -477,7 +531,7 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJ
     const bool mine = lane < L && dec_view(v, job0 + lane, cblks, order, jobs, W, H, ncblks, nframes);
     const int blk = warp * L + (lane < L ? lane : 0);
     T1DecState S;
-    S.F = F[blk]; S.cx = cxs[blk]; S.tab = tab; S.W = W; S.pass = 0;
+    S.F = F[blk]; S.F2 = F2[blk]; S.cx = cxs[blk]; S.tab = tab; S.W = W; S.pass = 0;
     DecState ds; ds.np_dec = 0; ds.scratch_np = 0; ds.bad[0] = ds.bad[1] = ds.bad[2] = ds.bad[3] = 0; ds.first_entry = -1; ds.pad = 0;
     if (mine) {
         S.zc = zc + v.cb.orient * 512;
@@ -507,7 +561,8 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJ
                         q.fork_at = mqd_next_fork(&shw[blk], q.sh_on);
                     }
                 }
-                t1d_passes(S, q, v.cb.w, v.cb.h, v.jb.numbps, ds.np_dec, v.jb.np, rates, nrates, ds);
+                if (rates) t1d_passes<true>(S, q, v.cb.w, v.cb.h, v.jb.numbps, ds.np_dec, v.jb.np, rates, nrates, ds);
+                else t1d_passes<false>(S, q, v.cb.w, v.cb.h, v.jb.numbps, ds.np_dec, v.jb.np, rates, nrates, ds);
                 ds.np_dec = v.jb.np;
                 if (search) mqd_save(q, cx, sv + DEC_SAVE_MQ);
             }
@@ -534,7 +589,7 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJ
         }
         if (need2[warp * L + sb] && (u.mode == 2 ? false : true)) {
             // recording just made, cut not reproducible: the scratch decode starts from a clean block
-            for (int i = lane; i < DEC_FWORDS; i += 32) Fb[i] = 0;
+            for (int i = lane; i < DEC_FWORDS; i += 32) { Fb[i] = 0; F2[warp * L + sb][i] = 0; }
             for (int i = lane; i < u.cb.w * u.cb.h; i += 32) {
                 const int y = i / u.cb.w, x = i - y * u.cb.w;
                 scratch[u.o + (size_t)y * W + x] = 0;
@@ -553,7 +608,7 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJ
             MqDec q;
             mqd_init(q, pool + (size_t)v.frame * pool_stride + v.jb.off, search ? cbout[v.bi].rate[v.jb.np - 1] : v.jb.len, nullptr);
             DecState dummy = ds;
-            t1d_passes(S, q, v.cb.w, v.cb.h, v.jb.numbps, 0, v.jb.np, nullptr, 0, dummy);
+            t1d_passes<false>(S, q, v.cb.w, v.cb.h, v.jb.numbps, 0, v.jb.np, nullptr, 0, dummy);
         }
         if (search) { ds.scratch_np = v.jb.np; dstate[v.bi] = ds; }
         if (v.jb.mode == 1) jobs[v.bi].mode = 2;
@@ -586,6 +641,7 @@ k_t1_dec_cuts(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cb
               int cap, const unsigned char *__restrict__ pool, size_t pool_stride, const DecLuts *__restrict__ g_luts, int *cut_pool, int ncblks)
 {
     __shared__ unsigned F[CUT_WPC][DEC_FWORDS];
+    __shared__ unsigned short F2[CUT_WPC][DEC_FWORDS];
     __shared__ unsigned cxs[CUT_WPC][20];
     __shared__ unsigned tab[94];
     __shared__ unsigned char zc[4 * 512];
@@ -601,7 +657,7 @@ k_t1_dec_cuts(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cb
     const int k = (int)(en.bi % (unsigned)ncblks), frame = (int)(en.bi / (unsigned)ncblks);
     const CblkDesc cb = cblks[k];
     int *dst = cut_pool + (size_t)e * T1_CUT_WORDS;
-    for (int i = lane; i < DEC_FWORDS; i += 32) F[warp][i] = 0;
+    for (int i = lane; i < DEC_FWORDS; i += 32) { F[warp][i] = 0; F2[warp][i] = 0; }
     for (int i = lane; i < cb.h * J2K_CBLK; i += 32) dst[i] = 0;
     __syncwarp();
     if (lane != 0) return;
@@ -611,12 +667,12 @@ k_t1_dec_cuts(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cb
     for (int i = 0; i < 19; ++i) cx[i] = tab[0];
     cx[CTX_UNI] = tab[46 << 1]; cx[CTX_AGG] = tab[3 << 1]; cx[CTX_ZC] = tab[4 << 1];
     T1DecState S;
-    S.F = F[warp]; S.cx = cx; S.tab = tab; S.W = J2K_CBLK; S.pass = 0; S.zc = zc + cb.orient * 512;
+    S.F = F[warp]; S.F2 = F2[warp]; S.cx = cx; S.tab = tab; S.W = J2K_CBLK; S.pass = 0; S.zc = zc + cb.orient * 512;
     S.plane = dst; S.spass = nullptr;
     MqDec q;
     mqd_init(q, pool + (size_t)frame * pool_stride + cb.mq_off, co.rate[en.np - 1], nullptr);
     DecState dummy; dummy.np_dec = 0; dummy.scratch_np = 0; dummy.bad[0] = dummy.bad[1] = dummy.bad[2] = dummy.bad[3] = 0; dummy.first_entry = -1; dummy.pad = 0;
-    t1d_passes(S, q, cb.w, cb.h, co.numbps, 0, en.np, nullptr, 0, dummy);
+    t1d_passes<false>(S, q, cb.w, cb.h, co.numbps, 0, en.np, nullptr, 0, dummy);
 }
 
 // decode jobs for the encoder's own allocation (compression-ratio search).  Block k is recorded (mode 1) when the

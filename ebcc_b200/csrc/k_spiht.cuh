@@ -632,69 +632,67 @@ __global__ void k_sp_add_residual(const float *__restrict__ img, float *out, con
 }
 
 // ---- warp-cooperative list decoder for stored streams (spiht_re.c:319-430, 477-520) ----------------------------------
-// One warp per frame.  The list coder is serial only in WHERE an entry's bits sit: an entry of the LIP takes 1 or 2 bits, one
-// of the LIS 1 to 9, depending on the bits themselves.  So the warp walks a list 32 entries at a time: every lane runs the
-// same short loop over the chunk (bits from a register window, no memory access) that yields each entry's bit offset; then
-// the lanes fetch their own bits, apply them to their own pixel and append to the lists at positions given by a warp
-// prefix sum -- list loads, pixel updates and appends of 32 entries travel together instead of one dependent global
-// access after the other.  Entries appended to the LIS while it is scanned form the next wave, as in k_sp_encode.  The
-// refinement pass is one bit per entry at a closed-form position.  Truncated streams: the reference checks its bit budget
-// after every bit; an action is applied iff the check before it passed, which is a comparison of the action's own bit
-// count with the budget, and the decode ends with the chunk in which the budget ran out.
+// One CTA of SPD_THREADS per frame; warp 0 walks the lists, all warps share the passes that need no parsing.  The list
+// coder is serial only in WHERE an entry's bits sit: an entry of the LIP takes 1 or 2 bits, one of the LIS 1 to 9,
+// depending on the bits themselves.  So warp 0 takes a list 32 entries at a time: a short warp-uniform loop over the
+// chunk yields each entry's bit offset -- it works on a register window of the stream, skips a whole run of
+// insignificant entries (one 0 bit each, whatever their kind) with one count-leading-zeros, and spends instructions
+// only on significant ones; then the lanes pick their own bits out of the window (shuffles, no memory access), apply
+// them to their own pixel and append to the lists at positions given by a warp prefix sum.  List loads (the next chunk
+// is prefetched), pixel updates and appends of 32 entries travel together instead of one dependent global access after
+// the other.  Entries appended to the LIS while it is scanned form the next wave, as in k_sp_encode.  The refinement
+// pass is one bit per entry at a closed-form position: the whole CTA.  Truncated streams: the reference checks its bit
+// budget after every bit; an action is applied iff the check before it passed, which is a comparison of the action's own
+// bit count with the budget, and the decode ends with the chunk in which the budget ran out.
+#define SPD_THREADS 128
 struct SpWarpBits {
     const unsigned *words; int nw;       // the stream as 32-bit words (bytes in stream order), zero beyond nw
     int k0; unsigned held;               // lane l holds word k0 + l, MSB-first
-    unsigned long long w; int wk;        // window: words wk and wk + 1
 };
 __device__ __forceinline__ unsigned spw_load(const unsigned *words, int nw, int k)
 {
     return (k >= 0 && k < nw) ? __byte_perm(words[k], 0u, 0x0123) : 0u;
 }
-// all lanes: position the window at bit pos (called at chunk starts; a chunk consumes at most 9 words)
+// all lanes: make sure the words of a chunk that starts at bit pos (at most 9 words + look-ahead) are held
 __device__ __forceinline__ void spw_seek(SpWarpBits &b, unsigned pos, int lane)
 {
     const int k = (int)(pos >> 5);
-    if (k < b.k0 || k + 12 > b.k0 + 32) { b.k0 = k; b.held = spw_load(b.words, b.nw, k + lane); }
-    b.wk = k;
-    const unsigned hi = __shfl_sync(0xffffffffu, b.held, k - b.k0), lo = __shfl_sync(0xffffffffu, b.held, k + 1 - b.k0);
-    b.w = ((unsigned long long)hi << 32) | lo;
+    if (k < b.k0 || k + 14 > b.k0 + 32) { b.k0 = k; b.held = spw_load(b.words, b.nw, k + lane); }
 }
-// all lanes, same pos: the bit at pos (>= the window's start); slides the window forward when needed
-__device__ __forceinline__ unsigned spw_bit(SpWarpBits &b, unsigned pos)
+// the 32 bits starting at pos, picked out of the held words (pos may differ per lane)
+__device__ __forceinline__ unsigned spw_bits32(const SpWarpBits &b, unsigned pos)
 {
-    while ((int)(pos >> 5) > b.wk) {
-        ++b.wk;
-        const unsigned nx = __shfl_sync(0xffffffffu, b.held, (b.wk + 1 - b.k0) & 31);
-        b.w = (b.w << 32) | nx;
-    }
-    return (unsigned)(b.w >> (63u - (pos - ((unsigned)b.wk << 5)))) & 1u;
+    const int k = ((int)(pos >> 5) - b.k0) & 31;
+    const unsigned hi = __shfl_sync(0xffffffffu, b.held, k), lo = __shfl_sync(0xffffffffu, b.held, (k + 1) & 31);
+    return __funnelshift_l(lo, hi, pos & 31u);
 }
-// per lane: the 32 bits starting at pos
+// per thread, any position: straight from memory (header, refinement pass)
 __device__ __forceinline__ unsigned spw_own(const SpWarpBits &b, unsigned pos)
 {
     const int k = (int)(pos >> 5);
     return __funnelshift_l(spw_load(b.words, b.nw, k + 1), spw_load(b.words, b.nw, k), pos & 31u);
 }
 
-// grid = nframes, block = 32.  streams: [frame][stride]; lens[frame] = coeffs_size bytes (0 = none).
+// grid = nframes, block = SPD_THREADS.  streams: [frame][stride]; lens[frame] = coeffs_size bytes (0 = none).
 // img receives the integer-valued coefficient plane (float), geometry must match g.  status[frame] != 0 on malformed input.
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(SPD_THREADS)
 k_sp_decode(const unsigned char *__restrict__ streams, size_t stride, const int *__restrict__ lens, SpBufs b,
             SpInfo *info, float *img, SpGeom g, int *status)
 {
-    const int frame = blockIdx.x, lane = threadIdx.x;
+    __shared__ unsigned s_pos, s_cnt, s_lsp_prev, s_stop;
+    const int frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lt = (1u << lane) - 1u;
     SpInfo &inf = info[frame];
     const size_t Np = (size_t)g.Wp * g.Hp, fo = (size_t)frame * Np;
-    if (lens[frame] <= 0) { if (lane == 0) { inf.active = 0; status[frame] = 0; } return; }
+    if (lens[frame] <= 0) { if (tid == 0) { inf.active = 0; status[frame] = 0; } return; }
     float *data = img + fo;
-    for (size_t i = lane; i < Np; i += 32) data[i] = 0.0f;
-    if (lane == 0) { inf.active = 1; status[frame] = 1; }
+    for (size_t i = tid; i < Np; i += SPD_THREADS) data[i] = 0.0f;
+    if (tid == 0) { inf.active = 1; status[frame] = 1; }
     SpWarpBits wb;
-    wb.words = (const unsigned *)(streams + (size_t)frame * stride); wb.nw = (lens[frame] + 3) >> 2; wb.k0 = -1000; wb.held = 0; wb.w = 0; wb.wk = 0;
-    // header (uniform): 'I' 'M' 'S', stages(6), size_x(12), size_y(12), extra_x(10), extra_y(10), colour(1), bits0(29), dc(8), step(8)
+    wb.words = (const unsigned *)(streams + (size_t)frame * stride); wb.nw = (lens[frame] + 3) >> 2; wb.k0 = -1000; wb.held = 0;
+    // header (every thread reads it): 'I' 'M' 'S', stages(6), size_x(12), size_y(12), extra_x(10), extra_y(10), colour(1), bits0(29), dc(8), step(8)
     unsigned hp = 0;
-    auto hdr = [&](int n) { unsigned v = 0; for (int i = 0; i < n; ++i) { v = (v << 1) | (spw_own(wb, hp) >> 31); ++hp; } return v; };
+    auto hdr = [&](int n) { const unsigned v = spw_own(wb, hp) >> (32 - n); hp += (unsigned)n; return v; };
     if (hdr(8) != 'I' || hdr(8) != 'M' || hdr(8) != 'S') return;
     const unsigned stages = hdr(6), sx_ = hdr(12), sy_ = hdr(12), ex_ = hdr(10), ey_ = hdr(10);
     hdr(1);
@@ -705,13 +703,13 @@ k_sp_decode(const unsigned char *__restrict__ streams, size_t stride, const int 
     if (num_bits <= 128) return;
     num_bits -= 128;
     const int dc = (int)hdr(8), step0 = (int)hdr(8);
-    if (lane == 0) inf.dc = dc;
+    if (tid == 0) inf.dc = dc;
     if (step0 > 30) return;
     unsigned *lip = b.lip0 + fo, *lsp = b.lsp + fo;
     int *lis = b.lis0 + 2 * fo;
     // initial lists (spiht_re.c:64-77): LIP = the LL band row-major, LIS = its pixels with an odd coordinate, same order
     const int half = g.lx >> 1;
-    for (int i = lane; i < g.lx * g.ly; i += 32) {
+    for (int i = tid; i < g.lx * g.ly; i += SPD_THREADS) {
         const int y = i / g.lx, x = i - y * g.lx;
         lip[i] = (unsigned)(x + y * g.Wp);
         if ((x & 1) || (y & 1)) {
@@ -720,123 +718,144 @@ k_sp_decode(const unsigned char *__restrict__ streams, size_t stride, const int 
         }
     }
     unsigned lip_n = (unsigned)(g.lx * g.ly), lsp_n = 0, lis_n = (unsigned)(((g.ly + 1) >> 1) * half + (g.ly >> 1) * g.lx);
-    unsigned pos = hp, cnt = 0;            // absolute bit position; payload bits consumed so far
-    __syncwarp();
-    if (lane == 0) status[frame] = 0;
+    unsigned pos = hp, cnt = 0;            // absolute bit position; payload bits consumed so far (warp 0 keeps them, shared memory hands them on)
+    if (tid == 0) { status[frame] = 0; s_stop = 0; }
+    __syncthreads();
     for (int step = step0; step >= 0; --step) {
         const float one = (float)(1 << step);
-        const unsigned lsp_prev = lsp_n;
-        // ---- LIP pass: 1 bit, + 1 sign bit when significant ----
-        unsigned keep = 0;
-        for (unsigned base = 0; base < lip_n; base += 32) {
-            const unsigned n = min(32u, lip_n - base);
-            const bool valid = lane < (int)n;
-            const unsigned pix = valid ? lip[base + lane] : 0u;
-            spw_seek(wb, pos, lane);
-            unsigned off = 0, myoff = 0;
-            for (unsigned e = 0; e < n; ++e) { if (lane == (int)e) myoff = off; off += 1u + spw_bit(wb, pos + off); }
-            const unsigned own = spw_own(wb, pos + myoff);
-            const bool sig = valid && (own >> 31), applied = valid && cnt + myoff + 1u <= num_bits;
-            if (sig && applied) data[pix] = ((own >> 30) & 1u) ? -one : one;
-            const unsigned bs = __ballot_sync(0xffffffffu, sig && applied), bk = __ballot_sync(0xffffffffu, valid && !sig);
-            if (sig && applied) lsp[lsp_n + __popc(bs & lt)] = pix;
-            __syncwarp();
-            if (valid && !sig) lip[keep + __popc(bk & lt)] = pix;
-            lsp_n += __popc(bs); keep += __popc(bk);
-            pos += off; cnt += off;
-            if (cnt > num_bits) return;
-        }
-        lip_n = keep;
-        // ---- LIS pass, wave by wave ----
-        unsigned wbeg = 0, wend = lis_n, tail = lis_n;
-        while (wbeg < wend) {
-            for (unsigned base = wbeg; base < wend; base += 32) {
-                const unsigned n = min(32u, wend - base);
+        if (warp == 0) {
+            const unsigned lsp_prev = lsp_n;
+            bool stop = false;
+            // ---- LIP pass: 1 bit, + 1 sign bit when significant ----
+            unsigned keep = 0;
+            unsigned nxt = lane < (int)lip_n ? lip[lane] : 0u;
+            for (unsigned base = 0; base < lip_n && !stop; base += 32) {
+                const unsigned n = min(32u, lip_n - base);
                 const bool valid = lane < (int)n;
-                const int item = valid ? lis[base + lane] : 0;
-                const bool isA = item > 0;
-                const int pix = isA ? item - 1 : -item - 1;
+                const unsigned pix = nxt;
+                nxt = base + 32 + lane < lip_n ? lip[base + 32 + lane] : 0u;        // next chunk travels while this one is parsed
                 spw_seek(wb, pos, lane);
-                unsigned off = 0, myoff = 0;
-                for (unsigned e = 0; e < n; ++e) {
-                    const bool eA = __shfl_sync(0xffffffffu, (int)isA, (int)e) != 0;
-                    if (lane == (int)e) myoff = off;
-                    unsigned len = 1;
-                    if (spw_bit(wb, pos + off) && eA)
-                        for (int k = 0; k < 4; ++k) len += 1u + spw_bit(wb, pos + off + len);
-                    off += len;
+                unsigned off = 0, myoff = 0, e = 0;
+                while (e < n) {
+                    const unsigned z = min((unsigned)__clz((int)spw_bits32(wb, pos + off)), n - e);   // run of insignificant entries
+                    if (lane >= (int)e && lane < (int)(e + z)) myoff = off + ((unsigned)lane - e);
+                    e += z; off += z;
+                    if (e < n && z < 32u) { if (lane == (int)e) myoff = off; e += 1; off += 2; }   // a significant one: bit + sign
                 }
-                const unsigned own = spw_own(wb, pos + myoff);
-                const bool sig = valid && (own >> 31) && cnt + myoff + 1u <= num_bits;       // entries beyond the budget do nothing
-                int sx = 0, sy = 0;
-                unsigned nlsp = 0, nlip = 0, nlis = 0, csig = 0, cneg = 0, capp = 0;
-                if (sig) {
-                    const int y = pix / g.Wp, x = pix - y * g.Wp;
-                    sp_succ(g, x, y, sx, sy);
-                    if (isA) {
-                        unsigned p = 1;                                   // next bit of this entry
-                        for (int k = 0; k < 4; ++k) {
-                            const unsigned cs = (own >> (31u - p)) & 1u;
-                            const bool ok = cnt + myoff + p + 1u <= num_bits;      // the child's significance bit is inside the budget
-                            ++p;
-                            if (ok) capp |= 1u << k;
-                            if (cs) { csig |= 1u << k; if ((own >> (31u - p)) & 1u) cneg |= 1u << k; ++p; }
-                        }
-                        nlsp = (unsigned)__popc(csig & capp); nlip = (unsigned)__popc(~csig & capp & 15u);
-                        int gx, gy;
-                        nlis = sp_succ(g, sx, sy, gx, gy) ? 1u : 0u;
-                    } else nlis = 4;
-                }
-                // exclusive prefix sums of the three append counts (packed 10 bits each: at most 32 * 4 = 128 per chunk)
-                unsigned pk = nlsp | (nlip << 10) | (nlis << 20), inc = pk;
-                for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
-                const unsigned tot = __shfl_sync(0xffffffffu, inc, 31), ex = inc - pk;
-                if (sig) {
-                    unsigned ol = lsp_n + (ex & 1023u), oi = lip_n + ((ex >> 10) & 1023u), ot = tail + (ex >> 20);
-                    if (isA) {
-                        for (int k = 0; k < 4; ++k) {
-                            if (!((capp >> k) & 1u)) continue;
-                            const unsigned cp = (unsigned)((sy + (k >> 1)) * g.Wp + sx + (k & 1));
-                            if ((csig >> k) & 1u) { lsp[ol++] = cp; data[cp] = ((cneg >> k) & 1u) ? -one : one; }
-                            else lip[oi++] = cp;
-                        }
-                        if (nlis) lis[ot] = -(pix + 1);
-                    } else {
-                        for (int k = 0; k < 4; ++k) lis[ot + k] = (sy + (k >> 1)) * g.Wp + sx + (k & 1) + 1;
-                    }
-                    lis[base + lane] = 0;                             // removed
-                }
-                lsp_n += tot & 1023u; lip_n += (tot >> 10) & 1023u; tail += tot >> 20;
+                const unsigned own = spw_bits32(wb, pos + myoff);
+                const bool sig = valid && (own >> 31), applied = valid && cnt + myoff + 1u <= num_bits;
+                if (sig && applied) data[pix] = ((own >> 30) & 1u) ? -one : one;
+                const unsigned bs = __ballot_sync(0xffffffffu, sig && applied), bk = __ballot_sync(0xffffffffu, valid && !sig);
+                if (sig && applied) lsp[lsp_n + __popc(bs & lt)] = pix;
+                if (valid && !sig) lip[keep + __popc(bk & lt)] = pix;
+                lsp_n += __popc(bs); keep += __popc(bk);
                 pos += off; cnt += off;
-                if (cnt > num_bits) return;
+                if (cnt > num_bits) stop = true;
             }
-            wbeg = wend; wend = tail;
-            __syncwarp();
+            lip_n = keep;
+            // ---- LIS pass, wave by wave ----
+            unsigned wbeg = 0, wend = lis_n, tail = lis_n;
+            while (wbeg < wend && !stop) {
+                int nxi = wbeg + lane < wend ? lis[wbeg + lane] : 0;
+                for (unsigned base = wbeg; base < wend && !stop; base += 32) {
+                    const unsigned n = min(32u, wend - base);
+                    const bool valid = lane < (int)n;
+                    const int item = nxi;
+                    nxi = base + 32 + lane < wend ? lis[base + 32 + lane] : 0;
+                    const bool isA = item > 0;
+                    const int pix = isA ? item - 1 : -item - 1;
+                    const unsigned amask = __ballot_sync(0xffffffffu, isA);
+                    spw_seek(wb, pos, lane);
+                    unsigned off = 0, myoff = 0, e = 0;
+                    while (e < n) {
+                        const unsigned z = min((unsigned)__clz((int)spw_bits32(wb, pos + off)), n - e);
+                        if (lane >= (int)e && lane < (int)(e + z)) myoff = off + ((unsigned)lane - e);
+                        e += z; off += z;
+                        if (e < n && z < 32u) {
+                            unsigned len = 1;
+                            if ((amask >> e) & 1u) {                    // children: significance bit, + sign when set
+                                unsigned c = spw_bits32(wb, pos + off + 1u);
+                                for (int k = 0; k < 4; ++k) { const unsigned cs = c >> 31; c <<= 1u + cs; len += 1u + cs; }
+                            }
+                            if (lane == (int)e) myoff = off;
+                            e += 1; off += len;
+                        }
+                    }
+                    const unsigned own = spw_bits32(wb, pos + myoff);
+                    const bool sig = valid && (own >> 31) && cnt + myoff + 1u <= num_bits;       // entries beyond the budget do nothing
+                    int sx = 0, sy = 0;
+                    unsigned nlsp = 0, nlip = 0, nlis = 0, csig = 0, cneg = 0, capp = 0;
+                    if (sig) {
+                        const int y = pix / g.Wp, x = pix - y * g.Wp;
+                        sp_succ(g, x, y, sx, sy);
+                        if (isA) {
+                            unsigned p = 1;                                   // next bit of this entry
+                            for (int k = 0; k < 4; ++k) {
+                                const unsigned cs = (own >> (31u - p)) & 1u;
+                                const bool ok = cnt + myoff + p + 1u <= num_bits;      // the child's significance bit is inside the budget
+                                ++p;
+                                if (ok) capp |= 1u << k;
+                                if (cs) { csig |= 1u << k; if ((own >> (31u - p)) & 1u) cneg |= 1u << k; ++p; }
+                            }
+                            nlsp = (unsigned)__popc(csig & capp); nlip = (unsigned)__popc(~csig & capp & 15u);
+                            int gx, gy;
+                            nlis = sp_succ(g, sx, sy, gx, gy) ? 1u : 0u;
+                        } else nlis = 4;
+                    }
+                    // exclusive prefix sums of the three append counts (packed 10 bits each: at most 32 * 4 = 128 per chunk)
+                    unsigned pk = nlsp | (nlip << 10) | (nlis << 20), inc = pk;
+                    for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+                    const unsigned tot = __shfl_sync(0xffffffffu, inc, 31), ex = inc - pk;
+                    if (sig) {
+                        unsigned ol = lsp_n + (ex & 1023u), oi = lip_n + ((ex >> 10) & 1023u), ot = tail + (ex >> 20);
+                        if (isA) {
+                            for (int k = 0; k < 4; ++k) {
+                                if (!((capp >> k) & 1u)) continue;
+                                const unsigned cp = (unsigned)((sy + (k >> 1)) * g.Wp + sx + (k & 1));
+                                if ((csig >> k) & 1u) { lsp[ol++] = cp; data[cp] = ((cneg >> k) & 1u) ? -one : one; }
+                                else lip[oi++] = cp;
+                            }
+                            if (nlis) lis[ot] = -(pix + 1);
+                        } else {
+                            for (int k = 0; k < 4; ++k) lis[ot + k] = (sy + (k >> 1)) * g.Wp + sx + (k & 1) + 1;
+                        }
+                        lis[base + lane] = 0;                             // removed
+                    }
+                    lsp_n += tot & 1023u; lip_n += (tot >> 10) & 1023u; tail += tot >> 20;
+                    pos += off; cnt += off;
+                    if (cnt > num_bits) stop = true;
+                }
+                wbeg = wend; wend = tail;
+                __syncwarp();
+            }
+            // consolidate: surviving items keep their order
+            if (!stop) {
+                keep = 0;
+                for (unsigned base = 0; base < tail; base += 32) {
+                    const int item = base + lane < tail ? lis[base + lane] : 0;
+                    const unsigned bk = __ballot_sync(0xffffffffu, item != 0);
+                    if (item != 0) lis[keep + __popc(bk & lt)] = item;
+                    keep += __popc(bk);
+                }
+                lis_n = keep;
+            }
+            if (lane == 0) { s_pos = pos; s_cnt = cnt; s_lsp_prev = lsp_prev; s_stop = stop ? 1u : 0u; }
         }
-        // consolidate: surviving items keep their order
-        keep = 0;
-        for (unsigned base = 0; base < tail; base += 32) {
-            const int item = base + lane < tail ? lis[base + lane] : 0;
-            const unsigned bk = __ballot_sync(0xffffffffu, item != 0);
-            __syncwarp();
-            if (item != 0) lis[keep + __popc(bk & lt)] = item;
-            keep += __popc(bk);
-        }
-        lis_n = keep;
-        __syncwarp();
-        // ---- refinement pass: one bit per entry the LSP held before this plane ----
-        for (unsigned base = 0; base < lsp_prev; base += 32) {
-            const unsigned i = base + lane;
-            if (i < lsp_prev && cnt + i <= num_bits) {                // applied iff the check after the previous bit passed
+        __syncthreads();
+        if (s_stop) return;
+        // ---- refinement pass: one bit per entry the LSP held before this plane; the whole CTA ----
+        const unsigned rpos = s_pos, rcnt = s_cnt, lsp_prev = s_lsp_prev;
+        for (unsigned i = tid; i < lsp_prev; i += SPD_THREADS) {
+            if (rcnt + i <= num_bits) {                               // applied iff the check after the previous bit passed
                 const unsigned pix = lsp[i];
                 const int vi = (int)data[pix];
-                if (spw_own(wb, pos + i) >> 31) data[pix] = (float)(vi >= 0 ? (vi | (1 << step)) : -((-vi) | (1 << step)));
+                if (spw_own(wb, rpos + i) >> 31) data[pix] = (float)(vi >= 0 ? (vi | (1 << step)) : -((-vi) | (1 << step)));
                 else data[pix] = (float)(vi & ~(1 << step));
             }
         }
-        pos += lsp_prev; cnt += lsp_prev;
+        pos = rpos + lsp_prev; cnt = rcnt + lsp_prev;
         if (cnt > num_bits) return;
-        __syncwarp();
+        __syncthreads();
     }
 }
 
