@@ -44,7 +44,7 @@ NSAMP = HH * WW
 FRAME_BYTES = NSAMP * 4
 BATCH = 24
 # device pipelines (batches in flight) per GPU: the same at every rank count
-PIPES = int(os.environ.get("EBCC_BENCH_PIPES", "12"))
+PIPES = int(os.environ.get("EBCC_BENCH_PIPES", "16"))
 FRAMES = BATCH * PIPES
 DISTINCT = 48
 MODE, ERR = H.MAX_ERROR, 0.1
@@ -477,15 +477,23 @@ def run_ours(args):
 # what bounds it.  "probe" classes run once per probe of a search, the figure is per launch group and frame.
 def kernel_table(out_bytes_per_frame):
     N, Np = NSAMP, 736 * 1440
+    # dwt: fused forward levels (k_dwt_tile) read their input once and write their output once: 8N * 4/3
+    # idwt: one launch group = the five fused levels of a search probe (k_idwt_tile): 3/4 of every level's inputs come from the
+    #       recording (value 4 B + pass of significance 1 B), 1/4 from the previous level's output (4 B), levels 1-4 write 4 B per
+    #       sample, the last level reads the original frame (4 B) and writes nothing but statistics: 5N + 4N/3 + 4N/3 + 4N = 11.7N
     return {
         "minmax": ("hbm", 4 * N), "dwt": ("hbm", 4 * N * 2 * (4 / 3)), "t1_cm": ("int_issue", 4 * N + 12.4 * N + 5 * N),
         "t1_mq": ("int_issue", 12.4 * N + out_bytes_per_frame * 4), "pcrd_t2": ("int_issue", 298 * 48 * 12),
         "bodies": ("hbm", 3 * out_bytes_per_frame), "t1_dec": ("int_issue", 0), "recon": ("hbm", (4 + 1 + 4) * N),
-        "idwt": ("hbm", 4 * N * 2 * (4 / 3)), "finalize": ("hbm", 12 * N), "sp_fwd": ("hbm", 8 * N + 4 * Np * (1 + 2 * 2 * (4 / 3)) + 12 * Np),
+        "idwt": ("hbm", (5 + 4 / 3 + 4 / 3 + 4) * N), "finalize": ("hbm", 12 * N), "sp_fwd": ("hbm", 8 * N + 4 * Np * (1 + 2 * 2 * (4 / 3)) + 12 * Np),
         "sp_encode": ("int_issue", 12 * Np), "sp_probe": ("hbm", 12 * Np + 4 * Np * 2 * 2 * (4 / 3) + 12 * N), "zstd_enc": ("int_issue", 2 * out_bytes_per_frame),
         "t2_parse": ("int_issue", out_bytes_per_frame), "zstd_dec": ("int_issue", out_bytes_per_frame), "sp_decode": ("int_issue", 12 * Np),
         "sp_inv": ("hbm", 4 * Np * 2 * 2 * (4 / 3) + 8 * N)}
 
+
+# DRAM traffic (dram__bytes_read.sum + dram__bytes_write.sum) per launch group of 24 frames from the committed ncu --set full
+# captures (profiles/r02_ncu_*.md), MB; launch groups not listed: not captured
+TRAFFIC_MB = {"minmax": 104.4, "dwt": 192.1, "t1_cm": 480.8, "t1_mq": 351.8, "pcrd_t2": 5.6, "t1_dec": 0.5, "idwt": 237.0, "sp_encode": 104.7, "zstd_enc": 0.2}
 
 # warp instructions per 24-frame launch of the tier-1 kernels, from the committed ncu --set full captures (profiles/)
 WARP_INST_PER_BATCH = {"t1_cm": 2.08e9, "t1_mq": 0.67e9}
@@ -502,7 +510,8 @@ def build_line(args, world, value, dev_s, wall_s, plain_s, e2e_s, pg_s, dd_s, dh
         per_group_ms = ms / n
         gbs = bpf * BATCH / (per_group_ms * 1e-3) / 1e9 if bpf else None
         kernels[name] = {"bound": bound, "ms_per_step": ms / K, "launch_groups_per_step": n / K, "ms_per_launch_group": per_group_ms,
-                         "algorithmic_MB_per_launch_group": bpf * BATCH / 1e6, "GBps": gbs, "frac_of_hbm_peak": (gbs / peak) if gbs else None}
+                         "algorithmic_MB_per_launch_group": bpf * BATCH / 1e6, "GBps": gbs, "frac_of_hbm_peak": (gbs / peak) if gbs else None,
+                         "dram_traffic_MB_per_launch_group": TRAFFIC_MB.get(name)}
         if name in WARP_INST_PER_BATCH:
             gi = WARP_INST_PER_BATCH[name] / (per_group_ms * 1e-3) / 1e9
             kernels[name]["int_issue"] = {"warp_inst_per_launch_group": WARP_INST_PER_BATCH[name], "achieved_ginst_s": gi,
@@ -512,7 +521,7 @@ def build_line(args, world, value, dev_s, wall_s, plain_s, e2e_s, pg_s, dd_s, dh
     if dom:
         d = kernels[dom]
         roof = {"kernel": dom, "bound": "hbm", "achieved": d["GBps"], "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                "frac": d["frac_of_hbm_peak"], "traffic": None, "true_bound": d["bound"],
+                "frac": d["frac_of_hbm_peak"], "traffic": (TRAFFIC_MB[dom] * 1e6) if dom in TRAFFIC_MB else None, "true_bound": d["bound"],
                 "share_of_kernel_time": d["ms_per_step"] / sum(k["ms_per_step"] for k in kernels.values()),
                 "note": "kernel classes are timed with CUDA events on their own streams with all %d pipelines in flight, i.e. in the "
                         "configuration `value` is measured in; their sum exceeds the step time because pipelines overlap" % PIPES}

@@ -388,11 +388,27 @@ struct ebcc_cuda_ctx {
 static void read_env(ebcc_cuda_ctx *c);
 static ebcc_cuda_ctx *ctx_root_mut(ebcc_cuda_ctx *c) { return c->parent ? c->parent : c; }
 
+// NVTX: every launch group is also an NVTX range named after its kernel class ("ebcc/dwt", "ebcc/t1_cm", ...), so that a
+// timeline (Nsight Systems, ncu --nvtx) shows the stages of the hot path; header-only NVTX 3 costs a null-pointer test when
+// no tool is attached.  Switch off with -DEBCC_NO_NVTX.
+#if !defined(EBCC_CUEMU) && !defined(EBCC_NO_NVTX)
+#include <nvtx3/nvToolsExt.h>
+static const char *const k_kt_nvtx[EBCC_KT_COUNT] = {
+    "ebcc/minmax", "ebcc/dwt", "ebcc/t1_cm", "ebcc/t1_mq", "ebcc/pcrd_t2", "ebcc/bodies", "ebcc/t1_dec", "ebcc/recon", "ebcc/idwt", "ebcc/finalize",
+    "ebcc/sp_fwd", "ebcc/sp_encode", "ebcc/sp_probe", "ebcc/zstd_enc", "ebcc/t2_parse", "ebcc/zstd_dec", "ebcc/sp_decode", "ebcc/sp_inv"};
+#define EBCC_NVTX_PUSH(id) nvtxRangePushA(k_kt_nvtx[id])
+#define EBCC_NVTX_POP() nvtxRangePop()
+#else
+#define EBCC_NVTX_PUSH(id) ((void)0)
+#define EBCC_NVTX_POP() ((void)0)
+#endif
+
 // scope of one launch group of kernel class `id`
 struct KT {
     ebcc_cuda_ctx *r; int slot; cudaStream_t st;
     KT(ebcc_cuda_ctx *c, int id, cudaStream_t on = NULL) : r(NULL), slot(-1), st(on)
     {
+        EBCC_NVTX_PUSH(id);
         if (!g_kt_on) return;
         r = ctx_root_mut(c);
         if (!st) st = r->stream;
@@ -401,7 +417,7 @@ struct KT {
         slot = r->kt_n++; r->kt_id[slot] = id;
         cudaEventRecord(r->kt_ev[2 * slot], st);
     }
-    ~KT() { if (r) cudaEventRecord(r->kt_ev[2 * slot + 1], st); }
+    ~KT() { if (r) cudaEventRecord(r->kt_ev[2 * slot + 1], st); EBCC_NVTX_POP(); }
 };
 
 // after a synchronisation of the pipeline's stream: every recorded pair has completed
@@ -702,6 +718,10 @@ static int reserve_alloc(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes, i
     }
     c->cap_frames = nframes;
     // large dynamic shared memory opt-ins
+    CK(cudaFuncSetAttribute(k_t1_dec<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_SMEM_BYTES(1)));
+    CK(cudaFuncSetAttribute(k_t1_dec<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_SMEM_BYTES(2)));
+    CK(cudaFuncSetAttribute(k_t1_dec<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_SMEM_BYTES(4)));
+    CK(cudaFuncSetAttribute(k_t1_dec<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_SMEM_BYTES(8)));
     CK(cudaFuncSetAttribute(k_idwt_v, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(k_idwt_h, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(k_t2_parse, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
@@ -1045,7 +1065,7 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
         const int lanes = dec_lanes(c);                         // code-blocks per warp of the tier-1 decoder: 1, 2, 4 or 8
         const long long per_cta = (long long)DEC_WPC(lanes) * lanes;
         const dim3 grid((unsigned)((njobs + per_cta - 1) / per_cta)), block((unsigned)(DEC_WPC(lanes) * 32));
-#define DEC_GO(LL) EBCC_LAUNCH(k_t1_dec<LL>, grid, block, 0, c->stream, c->d_cblks, c->d_order, c->d_jobs, pool, pool_stride, c->d_declut, \
+#define DEC_GO(LL) EBCC_LAUNCH(k_t1_dec<LL>, grid, block, DEC_SMEM_BYTES(LL), c->stream, c->d_cblks, c->d_order, c->d_jobs, pool, pool_stride, c->d_declut, \
                                c->d_iplane, probe ? c->d_spass : (unsigned char *)NULL, c->d_scratch,                                  \
                                probe ? (const CblkOut *)c->d_cbout : (const CblkOut *)NULL, probe ? c->d_dstate : (DecState *)NULL,   \
                                probe ? c->d_decsave : (unsigned *)NULL, W, H, pl->ncblks, B)
@@ -1611,7 +1631,7 @@ extern "C" int ebcc_cuda_debug_check_cuts(ebcc_cuda_ctx *c, size_t nframes, unsi
         EBCC_LAUNCH(k_jobs_from_enc, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cblks, c->d_cbout, c->d_dstate, c->d_jobs,
                     pl->ncblks, B, 0, (uint2 *)NULL);
         const long long per_cta = (long long)DEC_WPC(1);
-        EBCC_LAUNCH(k_t1_dec<1>, dim3((unsigned)((njobs + per_cta - 1) / per_cta)), dim3((unsigned)(DEC_WPC(1) * 32)), 0, c->stream, c->d_cblks, c->d_order,
+        EBCC_LAUNCH(k_t1_dec<1>, dim3((unsigned)((njobs + per_cta - 1) / per_cta)), dim3((unsigned)(DEC_WPC(1) * 32)), DEC_SMEM_BYTES(1), c->stream, c->d_cblks, c->d_order,
                     c->d_jobs, c->d_mq, pl->mq_stride, c->d_declut, c->d_iplane, (unsigned char *)NULL, c->d_scratch, (const CblkOut *)c->d_cbout,
                     c->d_dstate, c->d_decsave, pl->W, pl->H, pl->ncblks, B);
         EBCC_LAUNCH(k_dbg_compare, dim3((unsigned)pl->ncblks, (unsigned)B), dim3(128), 0, c->stream, c->d_cblks, c->d_cbout, c->d_dstate, c->d_iplane,
@@ -1711,6 +1731,32 @@ extern "C" int ebcc_cuda_bench_resident_pipelined(ebcc_cuda_ctx **ctxs, int nctx
     if (!rc) CK(cudaEventElapsedTime(total_ms, e0, e1));
     for (int k = 0; k < nctx; ++k) { cudaEventDestroy(done[k]); if (flush[k]) cudaFree(flush[k]); }
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(ts);
+    return rc;
+}
+
+// test tap: one zstd frame through the device decompressor (k_zstd_decompress), nothing else of the codec involved.
+// Returns 0 and *out_len = bytes produced, or -2 when the decoder rejects the frame.  Allocates its own scratch.
+extern "C" int ebcc_cuda_debug_zstd_decompress(int device, const uint8_t *frame, size_t n, uint8_t *out, size_t cap, size_t *out_len)
+{
+    if (!frame || !out || !out_len || n == 0 || n > 0x7fffffffu || cap > 0x7fffffffu) return -1;
+    CK(cudaSetDevice(device));
+    unsigned char *d_in = NULL, *d_out = NULL; unsigned *d_len = NULL; ZDecWork *d_work = NULL;
+    const size_t stride = (n + 64 + 15) & ~(size_t)15;
+    CK(cudaMalloc((void **)&d_in, stride)); CK(cudaMalloc((void **)&d_out, cap + 64)); CK(cudaMalloc((void **)&d_len, 3 * sizeof(unsigned)));
+    CK(cudaMalloc((void **)&d_work, sizeof(ZDecWork)));
+    CK(cudaMemset(d_in, 0, stride));
+    CK(cudaMemcpy(d_in, frame, n, cudaMemcpyHostToDevice));
+    const unsigned h[3] = {(unsigned)n, (unsigned)cap, 0u};
+    CK(cudaMemcpy(d_len, h, sizeof(h), cudaMemcpyHostToDevice));
+    EBCC_LAUNCH(k_zstd_decompress, dim3(1), dim3(32), 0, (cudaStream_t)0, (const unsigned char *)d_in, stride, (const unsigned *)d_len, d_out, cap + 64,
+                (const unsigned *)(d_len + 1), d_len + 2, d_work);
+    CK(cudaDeviceSynchronize());
+    unsigned got = 0;
+    CK(cudaMemcpy(&got, d_len + 2, sizeof(got), cudaMemcpyDeviceToHost));
+    int rc = 0;
+    if (got == 0xffffffffu || got > cap) rc = -2;
+    else { CK(cudaMemcpy(out, d_out, got, cudaMemcpyDeviceToHost)); *out_len = got; }
+    cudaFree(d_in); cudaFree(d_out); cudaFree(d_len); cudaFree(d_work);
     return rc;
 }
 

@@ -473,6 +473,7 @@ __device__ __forceinline__ bool dec_view(DecView &v, long long job, const CblkDe
 
 // Warps per CTA for L blocks per warp: 8 blocks (39 KB of flag words) per CTA from L = 2 on.
 #define DEC_WPC(L) ((L) == 1 ? 4 : 8 / (L))
+#define DEC_SMEM_BYTES(L) ((size_t)(DEC_WPC(L) * (L)) * DEC_FWORDS * (sizeof(unsigned) + sizeof(unsigned short)))
 
 // grid = ceil(ncblks * nframes / (DEC_WPC(L) * L)) CTAs.  A warp owns L code-blocks; lanes 0 .. L-1 decode one each
 // (SIMT: they share every instruction they have in common, which trades a longer serial chain per block for fewer
@@ -489,8 +490,10 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJ
          const CblkOut *__restrict__ cbout, DecState *dstate, unsigned *save, int W, int H, int ncblks, int nframes)
 {
     constexpr int NB = DEC_WPC(L) * L;          // blocks per CTA
-    __shared__ unsigned F[NB][DEC_FWORDS];
-    __shared__ unsigned short F2[NB][DEC_FWORDS];
+    // flag words + candidate words of the CTA's blocks: dynamic shared memory (DEC_SMEM_BYTES(L): 57 KB for eight blocks)
+    EBCC_DYN_SMEM(unsigned, dynsm);
+    unsigned (*F)[DEC_FWORDS] = (unsigned (*)[DEC_FWORDS])dynsm;
+    unsigned short (*F2)[DEC_FWORDS] = (unsigned short (*)[DEC_FWORDS])(dynsm + NB * DEC_FWORDS);
     __shared__ unsigned cxs[NB][20];
     __shared__ MqShadows shw[NB];
     __shared__ int need2[NB];

@@ -176,6 +176,8 @@ int ebcc_cuda_t1_totals(ebcc_cuda_ctx *ctx, size_t nframes, unsigned long long *
 int ebcc_cuda_debug_coef(ebcc_cuda_ctx *ctx, size_t frame, float *dst);
 int ebcc_cuda_debug_check_cuts(ebcc_cuda_ctx *ctx, size_t nframes, unsigned long long counts[6]);
 int ebcc_cuda_debug_spiht_stream(ebcc_cuda_ctx *ctx, size_t frame, uint8_t *dst, size_t cap, size_t *len);
+/* one zstd frame through the device decompressor alone (tests: frames written by the reference's ZSTD_compress) */
+int ebcc_cuda_debug_zstd_decompress(int device, const uint8_t *frame, size_t n, uint8_t *out, size_t cap, size_t *out_len);
 int ebcc_cuda_debug_cblk(ebcc_cuda_ctx *ctx, size_t frame, size_t cblk, int *numbps, int *totalpasses,
                          int *rates, double *dists, int *numpasses);
 
