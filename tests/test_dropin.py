@@ -149,6 +149,35 @@ def test_h5z_callback_product(built, mode, err, shape):
 
 
 @gpu
+@pytest.mark.parametrize("mode,err", [(H.NONE, None), (H.MAX_ERROR, 0.05)])
+def test_batch_route_writes_what_the_filter_callback_writes(built, mode, err):
+    """libhdf5 calls a filter once per chunk and waits for it (src/h5z_ebcc.c:124-148), so chunk writes cannot be batched
+    behind the callback.  The high-throughput route is on the caller's side: ebcc_encode_batch over all the chunks, then
+    direct chunk writes (H5Dwrite_chunk / h5py write_direct_chunk with filter_mask 0).  What lands in the file must be what
+    the callback would have produced, chunk by chunk."""
+    lib = H.prod_lib()
+    lib.ebcc_encode_batch.restype = C.c_size_t
+    frames = H.synth_stack(7, 64, 96)
+    frames[4] = -2.5                                                       # a constant chunk
+    n = len(frames)
+    cfg = H.CodecConfig(); cfg.dims[:] = [1, 64, 96]; cfg.base_cr = 12.0; cfg.mode = mode; cfg.error = err or 0.0
+    outs, sizes = (C.POINTER(C.c_uint8) * n)(), (C.c_size_t * n)()
+    assert lib.ebcc_encode_batch(frames.ctypes.data_as(C.c_void_p), C.c_size_t(n), C.byref(cfg), outs, sizes) == n
+    cd = D.cd_values(64, 96, 12.0, mode, err)
+    for i in range(n):
+        batch_chunk = C.string_at(outs[i], sizes[i])
+        lib.free_buffer(outs[i])
+        ret, _, buf = D.h5z_filter(lib, 0, cd, frames[i].tobytes())
+        assert ret == len(batch_chunk) and D.take(buf, ret) == batch_chunk, i
+        # and the read side: the callback decodes the chunk the batch call wrote
+        m, _, back = D.h5z_filter(lib, D.H5Z_FLAG_REVERSE, cd, batch_chunk)
+        assert m == frames[i].size
+        dec = np.frombuffer(D.take(back, 4 * m), dtype=np.float32)
+        # (the bound is enforced before the reference's mean adjustment shifts min / max, src/ebcc_codec.c:863-868: allow the shift)
+        assert np.abs(dec - frames[i].ravel()).max() <= (1.5 * err if mode == H.MAX_ERROR else 5.0)
+
+
+@gpu
 def test_h5z_callback_failure_returns_zero(built):
     """HDF5 convention: 0 = failure; the input chunk is freed and replaced by NULL like the reference does"""
     ret, size, buf = D.h5z_filter(H.prod_lib(), D.H5Z_FLAG_REVERSE, D.cd_values(64, 64, 10.0, H.NONE), b"EBCC" + bytes(60))
