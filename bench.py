@@ -42,7 +42,7 @@ import harness as H  # noqa: E402
 HH, WW, BASE_CR = 721, 1440, 30.0
 NSAMP = HH * WW
 FRAME_BYTES = NSAMP * 4
-BATCH = 24
+BATCH = int(os.environ.get("EBCC_BENCH_BATCH", "24"))
 # device pipelines (batches in flight) per GPU: the same at every rank count
 PIPES = int(os.environ.get("EBCC_BENCH_PIPES", "16"))
 FRAMES = BATCH * PIPES
@@ -374,7 +374,13 @@ def run_ours(args):
     pg_s, _ = timed(dist, local, lambda: cd.encode(pageable.ctypes.data), K2, 1)
     del pageable
     # ---- decompress: streams of the last step -> caller buffers ----
-    dd_s, _ = timed(dist, local, lambda: cd.decode(dec_dev.data_ptr()), K2, 1)
+    cd.decode(dec_dev.data_ptr())
+    lib.ebcc_cuda_kernel_timing(1)                              # kernel classes of the decompress path, same method as above
+    dd_s, _ = timed(dist, local, lambda: cd.decode(dec_dev.data_ptr()), K2, 0)
+    dkt_ms, dkt_n = (C.c_double * len(KT_NAMES))(), (C.c_ulonglong * len(KT_NAMES))()
+    lib.ebcc_cuda_kernel_timing_report(dkt_ms, dkt_n, len(KT_NAMES))
+    lib.ebcc_cuda_kernel_timing(0)
+    dec_kernels = {n: {"ms_per_step": ms / K2, "launch_groups_per_step": k / K2, "ms_per_launch_group": ms / k} for n, ms, k in zip(KT_NAMES, dkt_ms, dkt_n) if k}
     dh_s, _ = timed(dist, local, lambda: cd.decode(dec_host.data_ptr()), K2, 1)
 
     # ---- bound check over every frame of the step (default mode: the reference's mean adjustment shifts min / max) ----
@@ -466,6 +472,7 @@ def run_ours(args):
                           "note": "default mode: the reference adds the mean error to the header's min / max after the bound was enforced "
                                   "(src/ebcc_codec.c:863-868), so a decoded sample may exceed the target by that shift; identical in both codecs",
                           "host_and_device_decodes_equal": host_equal}
+    line["decompress"]["kernels"] = dec_kernels
     line["parity"] = parity
     line["modes"] = modes
     if cpu_baseline:

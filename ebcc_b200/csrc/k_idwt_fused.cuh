@@ -117,6 +117,19 @@ __device__ __forceinline__ void ft_col_window(float (&v)[24], float c0, float c1
     }
 }
 
+// j2k_pixel_to_float (k_idwt.cuh) with cheaper instructions and the same bits:
+//   * lrintf + 32768 clamped to [0, 65535]: the float -> int conversion saturates, so clamp(t, -32768, 32767) + 32768 in 32-bit
+//     integers equals the 64-bit form for every input (NaN converts to 0 in both);
+//   * p / 65535 in f32: the double product p * (1 / 65535) rounded to f32 is the correctly rounded quotient -- p < 2^16, so the
+//     exact quotient is at least 2^-41 (relative) away from any f32 rounding boundary unless it is exact, far more than the
+//     2^-52 the double arithmetic can be off -- hence identical to __fdiv_rn.
+__device__ __forceinline__ float ft_pixel_to_float(float v, float mn, float range)
+{
+    const int p = min(max(__float2int_rn(v), -32768), 32767) + 32768;
+    const float q = (float)__dmul_rn((double)p, 1.0 / 65535.0);
+    return __fadd_rn(__fmul_rn(q, range), mn);
+}
+
 // ---- inverse -----------------------------------------------------------------------------------------------------------------
 // grid = (ceil(rw / FT_TW), ceil(rh / FT_TH), frames), block = FT_THREADS.  CAS = row parity of the level's canvas origin.
 template <int SRC, bool FINAL, int CAS>
@@ -216,7 +229,7 @@ __global__ void __launch_bounds__(FT_THREADS) k_idwt_tile(IdwtFusedArgs a)
     // ---- 3: columns, straight to global memory ----
     float mn = 0.0f, range = 0.0f, target = 0.0f;
     double fxs = 0.0;
-    unsigned long long over = 0; float mxe = 0.0f; unsigned kmin = 0xffffffffu, kmax = 0; long long sum = 0; int ex = 0;
+    unsigned over = 0; float mxe = 0.0f; unsigned kmin = 0xffffffffu, kmax = 0; long long sum = 0; int ex = 0;
     if (FINAL) {
         mn = a.stat[frame].minv; range = __fsub_rn(a.stat[frame].maxv, mn);
         target = a.targets ? a.targets[frame] : 0.0f;
@@ -249,7 +262,7 @@ __global__ void __launch_bounds__(FT_THREADS) k_idwt_tile(IdwtFusedArgs a)
                     const size_t gi = fbase + (size_t)Y * W + X;
                     if (!FINAL) a.out[gi] = v[i];
                     else {
-                        const float f = j2k_pixel_to_float(v[i], mn, range);
+                        const float f = ft_pixel_to_float(v[i], mn, range);
                         if (a.out) a.out[gi] = f;
                         if (a.orig) {
                             const float rr = __fsub_rn(og[i - 4], f), e = fabsf(rr);
@@ -273,7 +286,7 @@ __global__ void __launch_bounds__(FT_THREADS) k_idwt_tile(IdwtFusedArgs a)
             sum += __shfl_xor_sync(0xffffffffu, sum, o);
         }
         if (lane == 0) {
-            if (over) atomicAdd(&a.es[frame].n_over, over);
+            if (over) atomicAdd(&a.es[frame].n_over, (unsigned long long)over);
             atomicMax(&a.es[frame].max_err_bits, __float_as_uint(mxe));
             atomicMin(&a.es[frame].rmin_key, kmin);
             atomicMax(&a.es[frame].rmax_key, kmax);

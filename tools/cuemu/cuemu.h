@@ -106,7 +106,13 @@ static inline double __dadd_rn(double a, double b) { return a + b; }
 static inline double __dsub_rn(double a, double b) { return a - b; }
 static inline double __dmul_rn(double a, double b) { return a * b; }
 static inline double __ddiv_rn(double a, double b) { return a / b; }
-static inline int __float2int_rn(float a) { return (int)lrintf(a); }
+static inline int __float2int_rn(float a)      // saturating like cvt.rni.s32.f32; NaN -> 0
+{
+    if (!(a == a)) return 0;
+    if (a >= 2147483648.0f) return 2147483647;
+    if (a <= -2147483648.0f) return -2147483647 - 1;
+    return (int)lrintf(a);
+}
 static inline long long __double2ll_rn(double a) { return llrint(a); }
 static inline double __longlong_as_double(long long a) { double d; memcpy(&d, &a, 8); return d; }
 static inline int __float2int_rz(float a) { return (int)a; }
