@@ -369,10 +369,16 @@ static void memo_put(memo_t *m, float cr, unsigned long long n_over)
 
 /* runs the search for every frame with run[i] != 0; result_cr[i] receives the ratio the reference would settle on */
 static int search_batch(ebcc_cuda_ctx *ctx, size_t nb, const int *run, const float *start_cr, const double *q0, double target,
-                        const float *err_target, size_t tot_size, memo_t *memo, float *result_cr, float *last_cr)
+                        const float *err_target, size_t tot_size, memo_t *memo, float *result_cr, float *last_cr, double cap_quantile)
 {
     crsearch_t *st = (crsearch_t *)calloc(nb, sizeof(*st));
     int *need = (int *)calloc(nb, sizeof(int));
+    /* Every decision of crs_advance is a comparison of q = 1 - n_over / N with a quantile target 1 - e (q < target,
+     * |q - target| > 1e-8, q == 1), here and in the later search that reuses the memo with a smaller e.  All of them have
+     * the same outcome for every count >= (e + 1e-8) N + 2, so the device may stop counting there (and stop looking at
+     * the frame).  Trace logging prints the exact quantile of every probe like the reference: no cap then. */
+    const unsigned long long cap = (g_log_level <= LOG_TRACE || !(cap_quantile >= 0.0) || !(cap_quantile <= 1.0)) ? 0ull
+                                   : (unsigned long long)floor((cap_quantile + 1e-8) * (double)tot_size) + 2ull;
     ebcc_probe_result *pr = (ebcc_probe_result *)calloc(nb, sizeof(*pr));
     int rc = 0;
     for (size_t i = 0; i < nb; ++i) { if (run[i]) crs_init(&st[i], start_cr[i], q0[i], target); else st[i].phase = PH_DONE; result_cr[i] = start_cr[i]; }
@@ -390,7 +396,7 @@ static int search_batch(ebcc_cuda_ctx *ctx, size_t nb, const int *run, const flo
         }
         if (!any_dev) { if (!any) break; else continue; }
         for (size_t i = 0; i < nb; ++i) if (need[i]) last_cr[i] = st[i].pending;
-        if (TIMED(TM_PROBE, ebcc_cuda_rate_probe(ctx, nb, last_cr, err_target, 0, pr))) { rc = -1; break; }
+        if (TIMED(TM_PROBE, ebcc_cuda_rate_probe_capped(ctx, nb, last_cr, err_target, cap, pr))) { rc = -1; break; }
         for (size_t i = 0; i < nb; ++i) {
             if (!need[i]) continue;
             memo_put(&memo[i], st[i].pending, pr[i].n_over);
@@ -464,7 +470,7 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
             start[i] = config->base_cr;
             mean[i] = p0[i].sum_err / N;                            /* get_mean_error after the first decode, :709 */
         }
-        if (search_batch(ctx, nb, run, start, q0, base_quantile_target, tgt, N, memo, cr1, cr)) goto out;
+        if (search_batch(ctx, nb, run, start, q0, base_quantile_target, tgt, N, memo, cr1, cr, base_error_quantile)) goto out;
         if (TIMED(TM_PROBE, ebcc_cuda_rate_probe(ctx, nb, cr1, tgt, 1, p1))) goto out;
         for (size_t i = 0; i < nb; ++i) {
             const double q = 1. - ((double)p1[i].n_over / N);
@@ -561,7 +567,7 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
                 memo_find(&memo[i], start[i], &n);
                 q0[i] = 1. - ((double)n / N);
             }
-            if (search_batch(ctx, nb, run, start, q0, 1.0, tgt, N, memo, cr2, cr)) goto out;
+            if (search_batch(ctx, nb, run, start, q0, 1.0, tgt, N, memo, cr2, cr, base_error_quantile)) goto out;
             if (TIMED(TM_PROBE, ebcc_cuda_rate_probe(ctx, nb, cr2, tgt, 1, p2))) goto out;
             if (TIMED(TM_DOWNLOAD, ebcc_cuda_download(ctx, nb, streams, ssz, NULL, NULL, NULL))) goto out;
             for (size_t i = 0; i < nb; ++i) {

@@ -323,6 +323,7 @@ struct ebcc_cuda_ctx {
     float *d_dcoef;            // [B][H][W] dequantised coefficients / IDWT work plane
     float *d_dcoef2;           // [B][H][W] second work plane: the fused IDWT levels ping-pong between the two
     int skip_dec;              // this probe's decoded frames are not needed (search probe: only the statistics are)
+    unsigned long long probe_cap;   // search probe: violation counts are only needed up to this value (0: exact), see k_idwt_tile
     float *d_dec;              // [B][H][W] decoded frames
     ErrStat *d_es;
     float *d_targets;
@@ -1087,6 +1088,7 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
             a.out = (r & 1) ? c->d_dcoef : c->d_dcoef2;
             a.r = r; a.rw = pl->res_w[r]; a.rh = pl->res_h[r]; a.snw = pl->res_w[r - 1]; a.snh = pl->res_h[r - 1];
             a.stat = c->d_stat; a.orig = orig; a.targets = orig ? c->d_targets : (const float *)NULL; a.es = c->d_es;
+            a.cap = (probe && c->skip_dec) ? ctx_root(c)->probe_cap : 0ull;
             const dim3 grid((unsigned)((a.rw + FT_TW - 1) / FT_TW), (unsigned)((a.rh + FT_TH - 1) / FT_TH), (unsigned)B);
             const bool fin = r == J2K_NRES - 1;
             if (fin) a.out = (probe && c->skip_dec) ? (float *)NULL : c->d_dec;
@@ -1172,6 +1174,20 @@ static int gather_tiles(ebcc_cuda_ctx *c, int B)
                              (size_t)B, cudaMemcpyDeviceToDevice, c->stream));
     }
     return 0;
+}
+
+// search probe: like ebcc_cuda_rate_probe(with_streams = 0), but n_over only has to be exact below cap -- a frame that
+// reaches cap violations is not examined any further and reports some count >= cap; max_err / rmin / rmax / sum_err of
+// such a frame are those of the part examined
+extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const float *cr, const float *targets, int with_streams, ebcc_probe_result *res);
+extern "C" int ebcc_cuda_rate_probe_capped(ebcc_cuda_ctx *c, size_t nframes, const float *cr, const float *targets, unsigned long long cap,
+                                           ebcc_probe_result *res)
+{
+    if (!c) return -1;
+    c->probe_cap = cap;
+    const int rc = ebcc_cuda_rate_probe(c, nframes, cr, targets, 0, res);
+    c->probe_cap = 0;
+    return rc;
 }
 
 extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const float *cr, const float *targets,

@@ -62,6 +62,7 @@ struct IdwtFusedArgs {
     float *out;                          // this level's output, row stride W (last level: decoded frame, may be NULL)
     int r, rw, rh, snw, snh;             // level, its size, low-pass counts
     const FrameStat *stat; const float *orig; const float *targets; ErrStat *es;      // last level only
+    unsigned long long cap;              // last level of a search probe: a frame whose violation count has reached cap is not looked at any further (0: exact counts)
 };
 
 // whole-sample symmetric extension of a line of n samples
@@ -143,18 +144,34 @@ __global__ void __launch_bounds__(FT_THREADS) k_idwt_tile(IdwtFusedArgs a)
     const int X0 = blockIdx.x * FT_TW, Y0 = blockIdx.y * FT_TH;
     const bool hx = a.rw > 1, vx = a.rh > 1;                 // a line of one sample is neither transformed nor scaled
     const int ncblks = plan->ncblks;
+    if (FINAL && a.cap) {
+        // A search probe only has to tell "violations >= cap" from an exact smaller count (the host's decisions are
+        // comparisons of the count with the quantile target): once the tiles finished so far have seen cap violations the
+        // rest of the frame is skipped.  Most probes of a search fail, and fail in the first tiles.
+        __shared__ int s_skip;
+        if (tid == 0) s_skip = *(volatile unsigned long long *)&a.es[frame].n_over >= a.cap;
+        __syncthreads();
+        if (s_skip) return;
+    }
 
     // ---- 1: load (+ dequantise / reconstruct), de-interleaved columns, horizontal scaling folded in ----
     // Per tile row (one warp) two groups of samples: low-pass columns (slots 0..63) and high-pass columns (64..127), each from one
     // band or from the previous level's output.  All loads of a row are issued before the first use (12 independent
     // requests per thread in flight), the arithmetic follows.
-    const bool interior = X0 >= FT_HALO && X0 + FT_TW + FT_HALO <= a.rw;
+    // the Mallat column of each of this thread's four slots does not depend on the row
+    int mxs[4];
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+        const int high = it >> 1, k = lane + 32 * (it & 1);          // warp-uniform half
+        const int X = ft_reflect(X0 - FT_HALO + 2 * k + high, a.rw);
+        mxs[it] = ((hx && high) ? a.snw : 0) + (X >> 1);             // (the mirror keeps the parity; a 1-sample line has no high-pass part)
+    }
     for (int lr = warp; lr < FT_ROWS; lr += FT_THREADS / 32) {
         const int Y = ft_reflect(Y0 - FT_HALO + lr, a.rh);
         const int ylow = vx ? ((Y & 1) == CAS) : (a.snh > 0);
         const int my = (ylow ? 0 : a.snh) + (Y >> 1);                    // Mallat row
         const size_t rowbase = fbase + (size_t)my * W;
-        int mxs[4], qv[4], kbs[4]; unsigned psv[4]; uint2 rjv[4]; float lv[4], stepv[2];
+        int qv[4], kbs[4]; unsigned psv[4]; uint2 rjv[4]; float lv[4], stepv[2];
         const bool ll_row = ylow && a.r > 1;                             // this row's low-pass columns come from the previous level
         // band of each half, and (probe) the code-block row of this Mallat row inside it
         int kb0[2], offx[2];
@@ -173,12 +190,9 @@ __global__ void __launch_bounds__(FT_THREADS) k_idwt_tile(IdwtFusedArgs a)
         }
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
-            const int high = it >> 1, k = lane + 32 * (it & 1);          // warp-uniform half
-            const int Xv = X0 - FT_HALO + 2 * k + high;
-            const int X = interior ? Xv : ft_reflect(Xv, a.rw);
-            const int xhigh = hx ? high : 0;                             // (the mirror keeps the parity; a 1-sample line has no high-pass part)
-            const int mx = (xhigh ? a.snw : 0) + (X >> 1);
-            mxs[it] = mx; lv[it] = 0.0f; qv[it] = 0; psv[it] = 0; rjv[it] = make_uint2(0u, 0u); kbs[it] = 0;
+            const int xhigh = hx ? (it >> 1) : 0;
+            const int mx = mxs[it];
+            lv[it] = 0.0f; qv[it] = 0; psv[it] = 0; rjv[it] = make_uint2(0u, 0u); kbs[it] = 0;
             if (!xhigh && ll_row) lv[it] = a.ll_in[rowbase + mx];
             else {
                 qv[it] = a.iplane[rowbase + mx];
@@ -241,10 +255,13 @@ __global__ void __launch_bounds__(FT_THREADS) k_idwt_tile(IdwtFusedArgs a)
         const int X = X0 + c;
         float v[24], og[16];
         if (FINAL && a.orig) {                                           // the original frame's samples travel while the columns are lifted
+            const float *op = a.orig + fbase + (size_t)(Y0 + 16 * h) * W + X;
+            if (X0 + FT_TW <= a.rw && Y0 + FT_TH <= a.rh) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const int Y = Y0 + 16 * h + i;
-                og[i] = (X < a.rw && Y < a.rh) ? a.orig[fbase + (size_t)Y * W + X] : 0.0f;
+                for (int i = 0; i < 16; ++i) og[i] = op[(size_t)i * W];
+            } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) og[i] = (X < a.rw && Y0 + 16 * h + i < a.rh) ? op[(size_t)i * W] : 0.0f;
             }
         }
 #pragma unroll
@@ -296,6 +313,18 @@ __global__ void __launch_bounds__(FT_THREADS) k_idwt_tile(IdwtFusedArgs a)
     }
 }
 
+// scale_shift (k_dwt.cuh) without the f32 division: q = fl32(x / range) equals fl32((double)x * (1 / (double)range)) for all
+// f32 x, range -- a quotient of two 24-bit significands is either a rounding boundary of f32 exactly or at least 2^-49
+// (relative) away from one, and reciprocal + product in double are off by less than 2^-51 -- so the conversion to f32 rounds
+// the same way (checked on 4e8 random pairs besides).  Three FP64-pipe instructions instead of the division subroutine,
+// which was 53 % of the stall samples of the first level.
+__device__ __forceinline__ float ft_scale_shift(float d, float mn, double rcp_range)
+{
+    const float q = (float)__dmul_rn((double)__fsub_rn(d, mn), rcp_range);
+    const int u = (int)(__float2uint_rz(__fmul_rn(q, 65535.0f)) & 0xffffu);
+    return (float)(u - 32768);
+}
+
 // ---- forward -----------------------------------------------------------------------------------------------------------------
 struct DwtFusedArgs {
     const float *in;                     // level's input, row stride W: raw frame (first level) or the previous level's LL plane
@@ -314,8 +343,8 @@ __global__ void __launch_bounds__(FT_THREADS) k_dwt_tile(DwtFusedArgs a)
     const size_t fbase = (size_t)frame * W * a.H;
     const int X0 = blockIdx.x * FT_TW, Y0 = blockIdx.y * FT_TH;
     const bool hx = a.rw > 1, vx = a.rh > 1;
-    float mn = 0.0f, range = 0.0f;
-    if (FIRST) { mn = a.stat[frame].minv; range = __fsub_rn(a.stat[frame].maxv, mn); }
+    float mn = 0.0f; double rcp_range = 0.0;
+    if (FIRST) { mn = a.stat[frame].minv; rcp_range = __ddiv_rn(1.0, (double)__fsub_rn(a.stat[frame].maxv, mn)); }
 
     // ---- 1: load, natural order ----
     for (int lr = warp; lr < FT_ROWS; lr += FT_THREADS / 32) {
@@ -324,7 +353,7 @@ __global__ void __launch_bounds__(FT_THREADS) k_dwt_tile(DwtFusedArgs a)
         for (int it = 0; it < 4; ++it) {
             const int lx = lane + 32 * it;
             float v = a.in[rowbase + ft_reflect(X0 - FT_HALO + lx, a.rw)];
-            if (FIRST) v = scale_shift(v, mn, range);
+            if (FIRST) v = ft_scale_shift(v, mn, rcp_range);
             s2[lr * FT_P2 + lx] = v;
         }
     }

@@ -86,6 +86,11 @@ int ebcc_cuda_analyze_resident(ebcc_cuda_ctx *ctx, size_t nframes);   /* = ebcc_
 int ebcc_cuda_rate_probe(ebcc_cuda_ctx *ctx, size_t nframes, const float *cr, const float *targets, int with_streams,
                          ebcc_probe_result *res);
 
+/* a probe of the search itself: the host only compares n_over with the quantile target, so the count has to be exact only
+ * below cap; a frame that reaches cap violations is not examined further (its n_over is some value >= cap, its other
+ * statistics cover the examined part only).  cap == 0: ebcc_cuda_rate_probe(with_streams = 0). */
+int ebcc_cuda_rate_probe_capped(ebcc_cuda_ctx *ctx, size_t nframes, const float *cr, const float *targets, unsigned long long cap,
+                                ebcc_probe_result *res);
 int ebcc_cuda_rate_probe_streams_only(ebcc_cuda_ctx *ctx, size_t nframes, const float *cr);
 int ebcc_cuda_frame_stats(ebcc_cuda_ctx *ctx, size_t nframes, float *minv, float *maxv, int *flags);
 
