@@ -711,6 +711,25 @@ size_t ebcc_encode(float *data, codec_config_t *config, uint8_t **out_buffer)
     return size;
 }
 
+/* Decoded frames the library allocates itself (the caller frees them with free_buffer = free, like the reference's).  A fresh
+ * 4 MB malloc is faulted in page by page inside the device-to-host copy; a 2 MB-aligned block that asks for transparent huge
+ * pages takes two faults instead of a thousand where the kernel grants them (it is a hint: plain pages otherwise). */
+#include <sys/mman.h>
+static void *frame_alloc(size_t bytes)
+{
+    const size_t huge = (size_t)2 << 20;
+    if (bytes >= huge) {
+        void *p = NULL;
+        if (posix_memalign(&p, huge, bytes) == 0 && p) {
+#ifdef MADV_HUGEPAGE
+            (void)madvise(p, bytes & ~(huge - 1), MADV_HUGEPAGE);
+#endif
+            return p;
+        }
+    }
+    return malloc(bytes);
+}
+
 /* ---- batched decode (reference ebcc_decode, src/ebcc_codec.c:1215-1320) --------------------------------- */
 typedef struct {
     int ok, const_field;
@@ -830,7 +849,7 @@ static void *dec_worker(void *arg)
         size_t nb = 0;
         for (size_t j = i; j < jb->ends[g]; ++j) {
             if (!ps[j].ok || ps[j].const_field) continue;
-            if (!jb->outs[j]) { jb->outs[j] = (float *)malloc(T * H * W * sizeof(float)); jb->owned[j] = 1; }
+            if (!jb->outs[j]) { jb->outs[j] = (float *)frame_alloc(T * H * W * sizeof(float)); jb->owned[j] = 1; }
             if (!jb->outs[j]) { ps[j].ok = 0; continue; }
             js[nb] = ps[j].tail; jn[nb] = ps[j].tail_size; mn[nb] = ps[j].minval; mx[nb] = ps[j].maxval; dst[nb] = jb->outs[j]; idx[nb] = j;
             memset(&rs[nb], 0, sizeof(rs[nb]));

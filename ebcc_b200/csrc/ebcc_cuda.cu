@@ -1089,7 +1089,7 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
             a.r = r; a.rw = pl->res_w[r]; a.rh = pl->res_h[r]; a.snw = pl->res_w[r - 1]; a.snh = pl->res_h[r - 1];
             a.stat = c->d_stat; a.orig = orig; a.targets = orig ? c->d_targets : (const float *)NULL; a.es = c->d_es;
             a.cap = (probe && c->skip_dec) ? ctx_root(c)->probe_cap : 0ull;
-            const dim3 grid((unsigned)((a.rw + FT_TW - 1) / FT_TW), (unsigned)((a.rh + FT_TH - 1) / FT_TH), (unsigned)B);
+            const dim3 grid((unsigned)B, (unsigned)(((a.rw + FT_TW - 1) / FT_TW) * ((a.rh + FT_TH - 1) / FT_TH)));
             const bool fin = r == J2K_NRES - 1;
             if (fin) a.out = (probe && c->skip_dec) ? (float *)NULL : c->d_dec;
             void (*kern)(IdwtFusedArgs);

@@ -132,16 +132,19 @@ __device__ __forceinline__ float ft_pixel_to_float(float v, float mn, float rang
 }
 
 // ---- inverse -----------------------------------------------------------------------------------------------------------------
-// grid = (ceil(rw / FT_TW), ceil(rh / FT_TH), frames), block = FT_THREADS.  CAS = row parity of the level's canvas origin.
+// grid = (frames, tiles of the level), block = FT_THREADS: the frame index varies fastest in CTA dispatch order, so at any time
+// every frame has only a few dozen tiles in flight and the early exit of capped search probes (below) finds the counts of the
+// tiles before it.  CAS = row parity of the level's canvas origin.
 template <int SRC, bool FINAL, int CAS>
 __global__ void __launch_bounds__(FT_THREADS) k_idwt_tile(IdwtFusedArgs a)
 {
     __shared__ __align__(16) float s1[FT_ROWS * FT_P1];
     __shared__ __align__(16) float s2[FT_ROWS * FT_P2];
     const Plan *plan = a.plan;
-    const int W = plan->W, frame = blockIdx.z, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int W = plan->W, frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t fbase = (size_t)frame * W * plan->H;
-    const int X0 = blockIdx.x * FT_TW, Y0 = blockIdx.y * FT_TH;
+    const int ntx = (a.rw + FT_TW - 1) / FT_TW, tyi = (int)blockIdx.y / ntx, txi = (int)blockIdx.y - tyi * ntx;
+    const int X0 = txi * FT_TW, Y0 = tyi * FT_TH;
     const bool hx = a.rw > 1, vx = a.rh > 1;                 // a line of one sample is neither transformed nor scaled
     const int ncblks = plan->ncblks;
     if (FINAL && a.cap) {
@@ -309,7 +312,7 @@ __global__ void __launch_bounds__(FT_THREADS) k_idwt_tile(IdwtFusedArgs a)
             atomicMax(&a.es[frame].rmax_key, kmax);
             atomicAdd((unsigned long long *)&a.es[frame].sum_fx, (unsigned long long)sum);
         }
-        if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) a.es[frame].sum_exp = ex;
+        if (blockIdx.y == 0 && tid == 0) a.es[frame].sum_exp = ex;
     }
 }
 
