@@ -112,7 +112,7 @@ static int dims_are_valid(const size_t dims[NDIMS])
 /* ---- process-wide pool of device pipelines (context + stream each), created lazily and re-created after fork.
  * Every encode / decode call (and every worker of a multi-batch call) owns one pipeline while it runs, so callers on
  * several threads -- or several batches of one call -- are in flight on the device at the same time: the kernels of
- * one batch fill the issue slots the latency-bound tier-1 coder of another leaves idle.  EBCC_PIPELINES (1..16,
+ * one batch fill the issue slots the latency-bound tier-1 coder of another leaves idle.  EBCC_PIPELINES (1..32,
  * default 4) bounds how many PER GPU.
  *
  * The pool spans GPUs: frames are independent (the reference's frame loop, src/ebcc_codec.c:1007-1046), so the batches of
@@ -121,7 +121,7 @@ static int dims_are_valid(const size_t dims[NDIMS])
  * uploaded to, coded on and downloaded from its own device, the per-frame sizes meet on the host where the EBCK container
  * is laid out by a prefix sum.  EBCC_CUDA_DEVICE (one ordinal) keeps a process on one GPU, which is what a launcher with
  * one process per GPU sets; with neither variable every visible GPU is used. */
-#define EBCC_MAX_PIPELINES 16
+#define EBCC_MAX_PIPELINES 32
 #define EBCC_MAX_DEVICES 16
 #define EBCC_MAX_SLOTS (EBCC_MAX_PIPELINES * EBCC_MAX_DEVICES)
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
