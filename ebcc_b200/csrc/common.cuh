@@ -39,6 +39,15 @@ struct FrameStat {
 #define STAT_NANINF 2
 #define STAT_OVERFLOW 4    // a code-block outgrew its slice of the symbol or MQ pool: the frame fails loudly
 
+// per-frame error statistics of one reconstruction against the original frame
+struct ErrStat {
+    unsigned long long n_over;     // samples with |d - rec| > target           (get_error_target_quantile)
+    unsigned max_err_bits;         // max |d - rec| as float bits                 (get_max_error)
+    unsigned rmin_key, rmax_key;   // ordered keys of min / max of (d - rec)      (findMinMaxf on the residual)
+    int sum_exp;                   // sum_fx counts units of 2^(sum_exp - ERR_FX_BITS)
+    long long sum_fx;              // sum of (d - rec), fixed point               (get_mean_error)
+};
+
 struct BandDesc {
     int resno, orient, level;
     int offx, offy, bw, bh;      // position / size inside the Mallat-layout tile buffer

@@ -307,6 +307,7 @@ enum { TM_ANALYZE, TM_PROBE, TM_RESID_ENC, TM_RESID_PROBE, TM_PACK, TM_DOWNLOAD,
 static const char *const k_tm_names[TM_COUNT] = {"upload+analyze", "rate probes", "spiht encode", "spiht probes", "zstd pack", "download"};
 /* per thread: every worker of a multi-batch call (and every concurrent caller) times its own batches */
 static _Thread_local double g_tm[TM_COUNT]; static _Thread_local int g_tm_calls[TM_COUNT]; static _Thread_local int g_profile = 0;
+static _Thread_local unsigned long g_probe_needed, g_probe_run;   /* frame-probes the searches asked for / the lock-step rounds executed */
 static double now_ms(void) { struct timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return t.tv_sec * 1e3 + t.tv_nsec * 1e-6; }
 #define TIMED(slot, expr) ({ double t0_ = g_profile ? now_ms() : 0; int r_ = (expr); if (g_profile) { g_tm[slot] += now_ms() - t0_; g_tm_calls[slot]++; } r_; })
 
@@ -395,7 +396,8 @@ static int search_batch(ebcc_cuda_ctx *ctx, size_t nb, const int *run, const flo
             }
         }
         if (!any_dev) { if (!any) break; else continue; }
-        for (size_t i = 0; i < nb; ++i) if (need[i]) last_cr[i] = st[i].pending;
+        for (size_t i = 0; i < nb; ++i) if (need[i]) { last_cr[i] = st[i].pending; g_probe_needed++; }
+        g_probe_run += nb;
         if (TIMED(TM_PROBE, ebcc_cuda_rate_probe_capped(ctx, nb, last_cr, err_target, cap, pr))) { rc = -1; break; }
         for (size_t i = 0; i < nb; ++i) {
             if (!need[i]) continue;
@@ -446,7 +448,8 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
     int *use_pure = (int *)calloc(nb, sizeof(int));
 
     g_profile = getenv("EBCC_PROFILE") != NULL;
-    if (g_profile) { memset(g_tm, 0, sizeof(g_tm)); memset(g_tm_calls, 0, sizeof(g_tm_calls)); }
+    const double t_call0 = g_profile ? now_ms() : 0;
+    if (g_profile) { memset(g_tm, 0, sizeof(g_tm)); memset(g_tm_calls, 0, sizeof(g_tm_calls)); g_probe_needed = g_probe_run = 0; }
     hint_crowd(ctx);
     if (ebcc_cuda_reserve_tiled(ctx, T, H, W, nb)) { rc = -2; goto out; }     /* -2: the caller retries with fewer frames per batch */
     if (TIMED(TM_ANALYZE, ebcc_cuda_upload(ctx, frames, nb) || ebcc_cuda_analyze(ctx, nb, mode != NONE) || ebcc_cuda_sync(ctx))) goto out;
@@ -612,6 +615,9 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
     if (g_profile) {
         fprintf(stderr, "[ebcc profile] %lu frames:", nb);
         for (int k = 0; k < TM_COUNT; ++k) fprintf(stderr, " %s %.1f ms/%d;", k_tm_names[k], g_tm[k], g_tm_calls[k]);
+        double dev = 0; for (int k = 0; k < TM_COUNT; ++k) dev += g_tm[k];
+        fprintf(stderr, " host side (copies, assembly) %.1f ms of %.1f;", now_ms() - t_call0 - dev, now_ms() - t_call0);
+        fprintf(stderr, " search rounds: %lu frame-probes needed of %lu run;", g_probe_needed, g_probe_run);
         fputc('\n', stderr);
     }
 out:

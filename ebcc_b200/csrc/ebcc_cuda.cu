@@ -38,6 +38,8 @@ static pthread_mutex_t g_kt_mu = PTHREAD_MUTEX_INITIALIZER;
 static double g_kt_ms[EBCC_KT_COUNT];
 static unsigned long long g_kt_n[EBCC_KT_COUNT];
 #define KT_RING 192
+#define UPLOAD_SLOTS 4
+#define UPLOAD_SLOT_BYTES ((size_t)8 << 20)
 
 // ---- compaction of the per-frame codestreams into one contiguous buffer --------------------------
 __global__ void k_offsets(const ProbeOut *__restrict__ pout, unsigned long long *offs, int nframes)
@@ -321,6 +323,7 @@ struct ebcc_cuda_ctx {
     int rec_from_encoder;      // recording + cut verdicts come from the encoder (k_t1_cm / k_t1_mq); 0: from k_t1_dec (EBCC_DECODER_RECORDING=1)
     int for_search;            // the running analysis feeds a compression-ratio search
     float *d_dcoef;            // [B][H][W] dequantised coefficients / IDWT work plane
+    char *h_up[4]; cudaEvent_t ev_up[4];   // pinned staging ring for uploads from pageable memory (ebcc_cuda_upload)
     float *d_dcoef2;           // [B][H][W] second work plane: the fused IDWT levels ping-pong between the two
     int skip_dec;              // this probe's decoded frames are not needed (search probe: only the statistics are)
     unsigned long long probe_cap;   // search probe: violation counts are only needed up to this value (0: exact), see k_idwt_tile
@@ -379,7 +382,7 @@ struct ebcc_cuda_ctx {
     int prio_split;
     int crowd;                 // pipelines at work on this device (hint from the host codec), see mq_lanes()
     int env_mq_lanes, env_dec_lanes, env_no_recording, env_dec_recording, env_debug_lanes, env_t1rec_ctas, env_dwt_cw;   // tuning / debugging variables, read once per host call (read_env)
-    int env_fused_idwt, env_fused_dwt, env_sp_serial;
+    int env_fused_idwt, env_fused_dwt, env_sp_serial, env_kt_whole;
     int ntiles;
     ebcc_cuda_ctx *tile[EBCC_MAX_TILES];
     ebcc_cuda_ctx *parent;
@@ -596,6 +599,7 @@ extern "C" void ebcc_cuda_ctx_destroy(ebcc_cuda_ctx *c)
     cudaFree(c->d_luts); cudaFree(c->d_mqtab); cudaFree(c->d_declut); cudaFree(c->d_step_tab);
     for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventDestroy(c->ev[i]);
     if (c->kt_have) for (int i = 0; i < 2 * KT_RING; ++i) cudaEventDestroy(c->kt_ev[i]);
+    for (int k = 0; k < UPLOAD_SLOTS; ++k) if (c->h_up[k]) { cudaFreeHost(c->h_up[k]); cudaEventDestroy(c->ev_up[k]); }
     if (c->prio_split) { cudaStreamDestroy(c->stream_lo); cudaEventDestroy(c->ev_fork); cudaEventDestroy(c->ev_join); }
     cudaStreamDestroy(c->stream);
     free(c);
@@ -775,8 +779,36 @@ extern "C" int ebcc_cuda_upload(ebcc_cuda_ctx *c, const float *frames, size_t nf
     CK(cudaSetDevice(c->device));
     const size_t bytes = nframes * (size_t)c->plan.H * c->plan.W * sizeof(float);
     mark(c, EBCC_ST_H2D);
-    // cudaMemcpyDefault: frames may be host memory (pinned or pageable) or a device buffer of any GPU of the process
-    // (unified virtual addressing), e.g. a tensor produced on the device -- then no H2D copy happens at all
+#ifndef EBCC_CUEMU
+    // Pageable caller memory (what HDF5, zarr and numpy hand over): cudaMemcpyAsync would stage it through the driver's own
+    // bounce buffer, synchronously and at a fraction of the link rate.  The pipeline stages it itself through a small ring
+    // of pinned slots: this thread copies slice k + 1 into a slot while the copy engine moves slice k, and the threads of
+    // the other pipelines do the same side by side, so together they fill the link.
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, frames) != cudaSuccess) { (void)cudaGetLastError(); at.type = cudaMemoryTypeUnregistered; }
+    if (at.type == cudaMemoryTypeUnregistered && bytes > 0) {
+        if (!c->h_up[0]) {
+            for (int k = 0; k < UPLOAD_SLOTS; ++k) {
+                CK(cudaMallocHost((void **)&c->h_up[k], UPLOAD_SLOT_BYTES));
+                CK(cudaEventCreateWithFlags(&c->ev_up[k], cudaEventDisableTiming));
+            }
+        }
+        const char *src = (const char *)frames;
+        size_t off = 0;
+        for (int k = 0; off < bytes; ++k) {
+            const int slot = k % UPLOAD_SLOTS;
+            const size_t n = bytes - off < UPLOAD_SLOT_BYTES ? bytes - off : UPLOAD_SLOT_BYTES;
+            if (k >= UPLOAD_SLOTS) CK(cudaEventSynchronize(c->ev_up[slot]));      // the slot's previous slice has left
+            memcpy(c->h_up[slot], src + off, n);
+            CK(cudaMemcpyAsync((char *)c->d_in + off, c->h_up[slot], n, cudaMemcpyHostToDevice, c->stream));
+            CK(cudaEventRecord(c->ev_up[slot], c->stream));
+            off += n;
+        }
+        return 0;
+    }
+#endif
+    // cudaMemcpyDefault: frames may be pinned host memory or a device buffer of any GPU of the process (unified virtual
+    // addressing), e.g. a tensor produced on the device -- then no H2D copy happens at all
     CK(cudaMemcpyAsync(c->d_in, frames, bytes, cudaMemcpyDefault, c->stream));
     return 0;
 }
@@ -850,6 +882,7 @@ static void read_env(ebcc_cuda_ctx *c)
     c->env_t1rec_ctas = e ? atoi(e) : 2;
     e = getenv("EBCC_FUSED_IDWT");                  // 0: the unfused inverse transform (k_dequant / k_recon_dequant, k_idwt_h / k_idwt_v, k_finalize)
     c->env_fused_idwt = !(e && e[0] == '0');
+    c->env_kt_whole = getenv("EBCC_KT_WHOLE_PROBE") != NULL;
     e = getenv("EBCC_SP_DECODE_SERIAL");            // cross-check aid: the one-thread SPIHT list decoder
     c->env_sp_serial = e && e[0] == '1';
     e = getenv("EBCC_FUSED_DWT");                   // 0: the unfused forward transform (k_dwt_v / k_dwt_h)
@@ -1079,7 +1112,7 @@ static int run_decode_stage(ebcc_cuda_ctx *c, int B, const unsigned char *pool, 
     const bool no_t1_decode = probe && c->rec_from_encoder && c->use_recording && c->cut_known && !c->cut_overflow;
     if (ctx_root(c)->env_fused_idwt && (!probe || no_t1_decode)) {
         KT kt_iw(c, EBCC_KT_IDWT);
-        if (orig) { EBCC_LAUNCH(k_errstat_init, dim3((unsigned)((B + 127) / 128)), dim3(128), 0, c->stream, c->d_es, B); c->launches++; }
+        // (a probe's statistics were reset by k_jobs_from_enc)
         for (int r = 1; r < J2K_NRES; ++r) {
             IdwtFusedArgs a;
             a.plan = c->d_plan; a.cblks = c->d_cblks; a.iplane = c->d_iplane; a.spass = c->d_spass;
@@ -1155,7 +1188,7 @@ static int probe_launch(ebcc_cuda_ctx *c, int B, const float *targets)
     CK(cudaMemcpyAsync(c->d_targets, c->h_targets, sizeof(float) * B, cudaMemcpyHostToDevice, c->stream));
     const long long njobs = (long long)pl->ncblks * B;
     EBCC_LAUNCH(k_jobs_from_enc, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cblks, c->d_cbout, c->d_dstate, c->d_jobs,
-                pl->ncblks, B, c->use_recording, c->d_rjobs);
+                pl->ncblks, B, c->use_recording, c->d_rjobs, c->d_es);
     c->launches++;
     if (run_decode_stage(c, B, c->d_mq, pl->mq_stride, c->d_in)) return -1;
     CK(cudaMemcpyAsync(c->h_es, c->d_es, sizeof(ErrStat) * B, cudaMemcpyDeviceToHost, c->stream));
@@ -1196,7 +1229,10 @@ extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const floa
     if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
     CK(cudaSetDevice(c->device));
     const int B = (int)nframes;
-    if (launch_rate_stage(c, B, cr, with_streams)) return -1;
+    // measurement aid (EBCC_KT_WHOLE_PROBE=1): the whole probe as one span of the otherwise unused class "recon", to compare
+    // with the sum of its launch groups (what queueing between them costs when many pipelines are in flight)
+    KT *whole = (ctx_root(c)->env_kt_whole && c->ntiles == 1) ? new KT(c, EBCC_KT_RECON) : (KT *)NULL;
+    if (launch_rate_stage(c, B, cr, with_streams)) { delete whole; return -1; }
     c->skip_dec = !with_streams && c->ntiles == 1;      // the decoded frames of a search probe are never read, its statistics are
     if (c->ntiles > 1) {
         const int T = c->ntiles, hl = c->tile[0]->plan.main_header_len;
@@ -1219,7 +1255,8 @@ extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const floa
             c->h_pout[i].stream_bytes = bytes;
         }
     } else {
-        if (probe_launch(c, B, targets)) return -1;
+        if (probe_launch(c, B, targets)) { delete whole; return -1; }
+        delete whole;
         CK(ctx_sync(c));
     }
     for (int i = 0; i < B; ++i) {
@@ -1406,6 +1443,64 @@ __global__ void k_set_stat(FrameStat *stat, const float *mm, int n)
     if (i < n) { stat[i].minv = mm[2 * i]; stat[i].maxv = mm[2 * i + 1]; stat[i].flags = 0; }
 }
 
+// decoded frames of the resident batch -> the callers' buffers.  Pinned host memory and device memory take an asynchronous
+// copy each; pageable host memory (malloc'ed buffers, numpy arrays) is served through the pinned ring of ebcc_cuda_upload,
+// the other way round: the copy engine fills slot k + 1 while this thread copies slot k to its destination.
+static int download_frames(ebcc_cuda_ctx *c, float *const *outs, int B, size_t frame_bytes)
+{
+#ifndef EBCC_CUEMU
+    int npage = 0;
+    for (int i = 0; i < B; ++i) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, outs[i]) != cudaSuccess) { (void)cudaGetLastError(); at.type = cudaMemoryTypeUnregistered; }
+        c->h_targets[i] = at.type == cudaMemoryTypeUnregistered ? 1.0f : 0.0f;      // (h_targets is idle during a decode)
+        npage += at.type == cudaMemoryTypeUnregistered;
+    }
+    for (int i = 0; i < B; ++i)
+        if (c->h_targets[i] == 0.0f)
+            CK(cudaMemcpyAsync(outs[i], (const char *)c->d_dec + (size_t)i * frame_bytes, frame_bytes, cudaMemcpyDefault, c->stream));
+    if (npage == 0) return 0;
+    if (!c->h_up[0]) {
+        for (int k = 0; k < UPLOAD_SLOTS; ++k) {
+            CK(cudaMallocHost((void **)&c->h_up[k], UPLOAD_SLOT_BYTES));
+            CK(cudaEventCreateWithFlags(&c->ev_up[k], cudaEventDisableTiming));
+        }
+    }
+    // slices of at most one slot, frame by frame; `issued` runs UPLOAD_SLOTS - 1 slices ahead of `done`
+    struct Slice { char *dst; size_t off, n; };
+    const size_t per = (frame_bytes + UPLOAD_SLOT_BYTES - 1) / UPLOAD_SLOT_BYTES;
+    const size_t total = (size_t)npage * per;
+    size_t issued = 0, done = 0; int fi = -1; size_t si = per;       // iteration state of `issued`
+    int fd = -1; size_t sd = per;                                    // ... and of `done`
+    auto next = [&](int &f, size_t &sl, Slice &out) {
+        if (++sl >= per) { sl = 0; do { ++f; } while (f < B && c->h_targets[f] == 0.0f); }
+        out.off = sl * UPLOAD_SLOT_BYTES;
+        out.n = frame_bytes - out.off < UPLOAD_SLOT_BYTES ? frame_bytes - out.off : UPLOAD_SLOT_BYTES;
+        out.dst = (char *)outs[f] + out.off;
+        out.off += (size_t)f * frame_bytes;
+    };
+    while (done < total) {
+        while (issued < total && issued < done + UPLOAD_SLOTS) {
+            Slice sl; next(fi, si, sl);
+            const int slot = (int)(issued % UPLOAD_SLOTS);
+            CK(cudaMemcpyAsync(c->h_up[slot], (const char *)c->d_dec + sl.off, sl.n, cudaMemcpyDeviceToHost, c->stream));
+            CK(cudaEventRecord(c->ev_up[slot], c->stream));
+            ++issued;
+        }
+        Slice sl; next(fd, sd, sl);
+        const int slot = (int)(done % UPLOAD_SLOTS);
+        CK(cudaEventSynchronize(c->ev_up[slot]));
+        memcpy(sl.dst, c->h_up[slot], sl.n);
+        ++done;
+    }
+    return 0;
+#else
+    for (int i = 0; i < B; ++i)
+        CK(cudaMemcpyAsync(outs[i], (const char *)c->d_dec + (size_t)i * frame_bytes, frame_bytes, cudaMemcpyDefault, c->stream));
+    return 0;
+#endif
+}
+
 extern "C" int ebcc_cuda_decode_batch_tiled(ebcc_cuda_ctx *c, const uint8_t *const *streams, const size_t *sizes, size_t nframes,
                                             size_t ntiles, size_t H, size_t W, const float *minv, const float *maxv,
                                             const ebcc_residual_in *res, float *const *outs)
@@ -1504,8 +1599,7 @@ extern "C" int ebcc_cuda_decode_batch_tiled(ebcc_cuda_ctx *c, const uint8_t *con
         CK(cudaMemcpyAsync(c->h_maxlen, c->d_maxlen, 4 * B, cudaMemcpyDeviceToHost, c->stream));
     }
     if (T == 1) CK(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
-    for (int i = 0; i < B; ++i)
-        CK(cudaMemcpyAsync(outs[i], c->d_dec + (size_t)i * N, N * sizeof(float), cudaMemcpyDefault, c->stream));   // host or device destination
+    if (download_frames(c, outs, B, (size_t)N * sizeof(float))) return -1;    // host (pinned or pageable) or device destinations
     CK(ctx_sync(c));
     int bad = 0;
     for (int t = 0; T > 1 && t < T; ++t)
@@ -1645,7 +1739,7 @@ extern "C" int ebcc_cuda_debug_check_cuts(ebcc_cuda_ctx *c, size_t nframes, unsi
     for (int np = 1; np < J2K_MAXPASSES; ++np) {
         EBCC_LAUNCH(k_dbg_force_np, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cbout, njobs, np);
         EBCC_LAUNCH(k_jobs_from_enc, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cblks, c->d_cbout, c->d_dstate, c->d_jobs,
-                    pl->ncblks, B, 0, (uint2 *)NULL);
+                    pl->ncblks, B, 0, (uint2 *)NULL, (ErrStat *)NULL);
         const long long per_cta = (long long)DEC_WPC(1);
         EBCC_LAUNCH(k_t1_dec<1>, dim3((unsigned)((njobs + per_cta - 1) / per_cta)), dim3((unsigned)(DEC_WPC(1) * 32)), DEC_SMEM_BYTES(1), c->stream, c->d_cblks, c->d_order,
                     c->d_jobs, c->d_mq, pl->mq_stride, c->d_declut, c->d_iplane, (unsigned char *)NULL, c->d_scratch, (const CblkOut *)c->d_cbout,

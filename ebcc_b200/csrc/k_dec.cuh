@@ -682,9 +682,11 @@ k_t1_dec_cuts(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cb
 // allocation needs more passes than its recording holds, served from the recording (mode 0) when the recording can
 // reproduce "first numpasses passes", and decoded for real into the scratch plane (mode 2) otherwise.
 __global__ void k_jobs_from_enc(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cbout, const DecState *__restrict__ dstate,
-                                DecJob *jobs, int ncblks, int nframes, int use_recording, uint2 *rjobs)
+                                DecJob *jobs, int ncblks, int nframes, int use_recording, uint2 *rjobs, ErrStat *es_reset)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    // the probe's statistics start from scratch (k_errstat_init folded in: one launch less per probe)
+    if (es_reset && i < nframes) { es_reset[i].n_over = 0; es_reset[i].max_err_bits = 0; es_reset[i].rmin_key = 0xffffffffu; es_reset[i].rmax_key = 0; es_reset[i].sum_exp = 0; es_reset[i].sum_fx = 0; }
     if (i >= (long long)ncblks * nframes) return;
     const int k = (int)(i % ncblks);
     const CblkOut &c = cbout[i];

@@ -144,14 +144,7 @@ __device__ __forceinline__ float j2k_pixel_to_float(float v, float mn, float ran
     return __fadd_rn(__fmul_rn(__fdiv_rn((float)p, 65535.0f), range), mn);
 }
 
-// per-frame error statistics of one reconstruction against the original frame
-struct ErrStat {
-    unsigned long long n_over;     // samples with |d - rec| > target           (get_error_target_quantile)
-    unsigned max_err_bits;         // max |d - rec| as float bits                 (get_max_error)
-    unsigned rmin_key, rmax_key;   // ordered keys of min / max of (d - rec)      (findMinMaxf on the residual)
-    int sum_exp;                   // sum_fx counts units of 2^(sum_exp - ERR_FX_BITS)
-    long long sum_fx;              // sum of (d - rec), fixed point               (get_mean_error)
-};
+// (struct ErrStat: common.cuh)
 // The mean error feeds the header's min / max (src/ebcc_codec.c:863-868), so the sum must not depend on the order in
 // which CTAs and warps finish: every term is rounded to a fixed-point integer (units of 2^(e - 39), |term| < 2^e,
 // at most 2^22 terms) and the integers are added with 64-bit atomics -- exact, hence order-free; the rounding is
