@@ -33,7 +33,8 @@ def _encode_batch(lib, frames, h, w, cr, mode=H.NONE, err=0.0):
 
 @pytest.fixture
 def env_guard():
-    keys = ("EBCC_MQ_LANES", "EBCC_DEC_LANES", "EBCC_BATCH_FRAMES", "EBCC_PIPELINES")
+    keys = ("EBCC_MQ_LANES", "EBCC_DEC_LANES", "EBCC_BATCH_FRAMES", "EBCC_PIPELINES", "EBCC_FUSED_DWT", "EBCC_FUSED_IDWT",
+            "EBCC_SP_DECODE_SERIAL", "EBCC_INIT_BASE_ERROR_QUANTILE", "EBCC_DISABLE_PURE_BASE_COMPRESSION_FALLBACK")
     saved = {k: os.environ.get(k) for k in keys}
     yield
     for k, v in saved.items():
@@ -137,3 +138,35 @@ def test_concurrent_callers(built, env_guard):
         for t in range(6):
             assert dec[k][t] is not None
             assert np.array_equal(dec[k][t], H.decode(lib, want[k][t]))
+
+
+def test_cross_check_paths_are_byte_identical(built, env_guard):
+    """The kernels the fused / warp-cooperative ones replaced stay in the library as cross-check paths (EBCC_FUSED_DWT=0,
+    EBCC_FUSED_IDWT=0, EBCC_SP_DECODE_SERIAL=1): forward transform, probe back half, decode back half and SPIHT list decoder
+    must give the same bytes and the same floats either way.  The residual layer is forced on these small frames."""
+    lib = H.prod_lib()
+    lib.ebcc_decode_batch.restype = C.c_size_t
+    os.environ["EBCC_INIT_BASE_ERROR_QUANTILE"] = "1e-2"
+    os.environ["EBCC_DISABLE_PURE_BASE_COMPRESSION_FALLBACK"] = "1"
+    frames = H.synth_stack(4, 181, 263)
+
+    def roundtrip():
+        streams = _encode_batch(lib, frames, 181, 263, 40.0, H.MAX_ERROR, 0.05)
+        n = len(streams)
+        keep = [C.create_string_buffer(s, len(s)) for s in streams]
+        ptrs = (C.c_void_p * n)(*[C.addressof(k) for k in keep])
+        sizes = (C.c_size_t * n)(*[len(s) for s in streams])
+        out = np.zeros((n, 181 * 263), dtype=np.float32)
+        douts = (C.c_void_p * n)(*[out[i].ctypes.data for i in range(n)])
+        cnts = (C.c_size_t * n)()
+        assert lib.ebcc_decode_batch(ptrs, sizes, C.c_size_t(n), douts, cnts) == n
+        return streams, out
+
+    want_s, want_d = roundtrip()
+    assert any(int.from_bytes(s[16:24], "little") > 0 for s in want_s), "no frame carries a residual layer"
+    for key, val in (("EBCC_FUSED_DWT", "0"), ("EBCC_FUSED_IDWT", "0"), ("EBCC_SP_DECODE_SERIAL", "1")):
+        os.environ[key] = val
+        got_s, got_d = roundtrip()
+        os.environ.pop(key)
+        assert got_s == want_s, key
+        assert np.array_equal(got_d.view(np.uint32), want_d.view(np.uint32)), key
