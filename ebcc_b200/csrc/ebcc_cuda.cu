@@ -303,6 +303,7 @@ struct ebcc_cuda_ctx {
     CblkOut *d_cbout;
     int *d_maxlen, *d_body_off;
     ProbeOut *d_pout;
+    PcrdCache *d_pcache;       // [B] threshold -> packet bytes evaluations of the frame's probes since the analysis (k_pcrd_t2)
     unsigned long long *d_offs;
     // decoder side
     DecLuts *d_declut;
@@ -556,7 +557,7 @@ static void free_buffers(ebcc_cuda_ctx *c)
 {
     cudaFree(c->d_plan); cudaFree(c->d_cblks); cudaFree(c->d_order); c->d_order = NULL; cudaFree(c->d_in); cudaFree(c->d_coef); cudaFree(c->d_stat);
     cudaFree(c->d_sym); cudaFree(c->d_mq); cudaFree(c->d_out); cudaFree(c->d_packed); cudaFree(c->d_cbout);
-    cudaFree(c->d_maxlen); cudaFree(c->d_body_off); cudaFree(c->d_pout); cudaFree(c->d_offs);
+    cudaFree(c->d_maxlen); cudaFree(c->d_body_off); cudaFree(c->d_pout); cudaFree(c->d_pcache); c->d_pcache = NULL; cudaFree(c->d_offs);
     cudaFreeHost(c->h_pout); cudaFreeHost(c->h_stat); cudaFreeHost(c->h_offs); cudaFreeHost(c->h_maxlen);
     cudaFreeHost(c->h_packed); cudaFreeHost(c->h_stage);
     cudaFree(c->d_streams); cudaFree(c->d_slens); cudaFree(c->d_status); cudaFree(c->d_jobs); cudaFree(c->d_rjobs); c->d_rjobs = NULL; cudaFree(c->d_iplane); cudaFree(c->d_scratch); cudaFree(c->d_spass); cudaFree(c->d_dstate); cudaFree(c->d_decsave);
@@ -661,6 +662,7 @@ static int reserve_alloc(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes, i
     CK(cudaMalloc((void **)&c->d_maxlen, B * sizeof(int)));
     CK(cudaMalloc((void **)&c->d_body_off, B * pl->ncblks * sizeof(int)));
     CK(cudaMalloc((void **)&c->d_pout, B * sizeof(ProbeOut)));
+    CK(cudaMalloc((void **)&c->d_pcache, B * sizeof(PcrdCache)));
     CK(cudaMalloc((void **)&c->d_offs, (B + 1) * sizeof(unsigned long long)));
     CK(cudaMallocHost((void **)&c->h_pout, B * sizeof(ProbeOut)));
     CK(cudaMallocHost((void **)&c->h_stat, B * sizeof(FrameStat)));
@@ -958,6 +960,7 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int f
     const Plan *pl = &c->plan;
     const int B = (int)nframes;
     c->for_search = for_search;
+    CK(cudaMemsetAsync(c->d_pcache, 0, (size_t)B * sizeof(PcrdCache), c->stream));     // new frames: nothing evaluated yet
     c->use_recording = !ctx_root(c)->env_no_recording;
     c->rec_from_encoder = for_search && c->use_recording && !ctx_root(c)->env_dec_recording;
     if (for_search && !c->rec_from_encoder) {
@@ -1057,7 +1060,7 @@ static int launch_rate_stage(ebcc_cuda_ctx *c, int B, const float *cr, int with_
     {
         KT kt_(c, EBCC_KT_PCRD_T2);
         EBCC_LAUNCH(k_pcrd_t2, dim3((unsigned)B), dim3(T2_THREADS), t2_smem_bytes(pl->ncblks, pl->nnodes), c->stream,
-                    c->d_plan, c->d_cblks, c->d_cbout, c->d_maxlen, c->d_out, c->d_body_off, c->d_pout, c->d_stat);
+                    c->d_plan, c->d_cblks, c->d_cbout, c->d_maxlen, c->d_out, c->d_body_off, c->d_pout, c->d_stat, getenv("EBCC_NO_PCRD_CACHE") ? (PcrdCache *)NULL : c->d_pcache);
     }
     c->launches += 1;
     mark(c, EBCC_ST_BODIES);

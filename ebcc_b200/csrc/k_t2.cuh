@@ -343,11 +343,20 @@ struct ProbeOut {
     double thresh;
 };
 
+// What the probes of one frame's search have in common.  Every probe bisects the same slope interval [mn, mx] with
+// arithmetic midpoints, and the packet bytes of "makelayer at threshold t" do not depend on the byte budget: until the
+// paths of two probes part (the first midpoint that lies between their two answers -- typically after 20 of ~35 steps,
+// because the interval spans many orders of magnitude and the answer sits at its low end) they ask for the very same
+// thresholds.  The cache keeps (threshold, bytes) of every evaluation since the analysis; a later probe answers a
+// midpoint it finds there without makelayer and without the tier-2 dry run.  Exact double matches only.
+#define PC_MAX 192
+struct PcrdCache { int n, have_range; double mn, mx; double thresh[PC_MAX]; int bytes[PC_MAX]; };
+
 // grid = (nframes); one probe per frame.  maxlen[frame] < 0 means "use every pass" (rates <= 1).
 __global__ void __launch_bounds__(T2_THREADS)
 k_pcrd_t2(const Plan *__restrict__ plan, const CblkDesc *__restrict__ cblks, CblkOut *cbout,
           const int *__restrict__ maxlen_arr, unsigned char *out_pool, int *body_off_pool, ProbeOut *pout,
-          const FrameStat *__restrict__ stat)
+          const FrameStat *__restrict__ stat, PcrdCache *cache)
 {
     EBCC_DYN_SMEM(unsigned char, smem);
     __shared__ double red_min[T2_THREADS / 32], red_max[T2_THREADS / 32];
@@ -376,54 +385,74 @@ k_pcrd_t2(const Plan *__restrict__ plan, const CblkDesc *__restrict__ cblks, Cbl
     }
 
     // ---- slope range over all passes (tcd.c:487-541) -------------------------------------------------
+    PcrdCache *pc = cache ? cache + frame : nullptr;
+    const int pc_n0 = pc ? pc->n : 0;
     double mn = 1.7976931348623157e308, mx = 0.0;
-    for (int k = tid; k < ncblks; k += nt) {
-        const CblkOut &c = co[k];
-        for (int p = 0; p < c.totalpasses; ++p) {
-            int dr; double dd;
-            if (p == 0) { dr = c.rate[0]; dd = c.dist[0]; }
-            else { dr = c.rate[p] - c.rate[p - 1]; dd = __dsub_rn(c.dist[p], c.dist[p - 1]); }
-            if (dr == 0) continue;
-            double sl = __ddiv_rn(dd, (double)dr);
-            if (sl < mn) mn = sl;
-            if (sl > mx) mx = sl;
+    if (pc && pc->have_range) {
+        mn = pc->mn; mx = pc->mx;
+        for (int k = tid; k < ncblks; k += nt) s.prevn[k] = 0;
+    } else {
+        for (int k = tid; k < ncblks; k += nt) {
+            const CblkOut &c = co[k];
+            for (int p = 0; p < c.totalpasses; ++p) {
+                int dr; double dd;
+                if (p == 0) { dr = c.rate[0]; dd = c.dist[0]; }
+                else { dr = c.rate[p] - c.rate[p - 1]; dd = __dsub_rn(c.dist[p], c.dist[p - 1]); }
+                if (dr == 0) continue;
+                double sl = __ddiv_rn(dd, (double)dr);
+                if (sl < mn) mn = sl;
+                if (sl > mx) mx = sl;
+            }
+            s.prevn[k] = 0;
         }
-        s.prevn[k] = 0;
+        for (int o = 16; o > 0; o >>= 1) {
+            double a = __shfl_xor_sync(0xffffffffu, mn, o), b = __shfl_xor_sync(0xffffffffu, mx, o);
+            if (a < mn) mn = a;
+            if (b > mx) mx = b;
+        }
+        if ((tid & 31) == 0) { red_min[tid >> 5] = mn; red_max[tid >> 5] = mx; }
+        __syncthreads();
+        for (int w = 0; w < (nt >> 5); ++w) { if (red_min[w] < mn) mn = red_min[w]; if (red_max[w] > mx) mx = red_max[w]; }
+        if (pc && tid == 0) { pc->mn = mn; pc->mx = mx; pc->have_range = 1; }
     }
-    for (int o = 16; o > 0; o >>= 1) {
-        double a = __shfl_xor_sync(0xffffffffu, mn, o), b = __shfl_xor_sync(0xffffffffu, mx, o);
-        if (a < mn) mn = a;
-        if (b > mx) mx = b;
-    }
-    if ((tid & 31) == 0) { red_min[tid >> 5] = mn; red_max[tid >> 5] = mx; }
-    __syncthreads();
-    for (int w = 0; w < (nt >> 5); ++w) { if (red_min[w] < mn) mn = red_min[w]; if (red_max[w] > mx) mx = red_max[w]; }
 
     t2_tree_static(plan, cblks, co, s);
     const int maxlen = maxlen_arr[frame];
     double goodthresh = -1.0;
     int iters = 0;
     if (maxlen >= 0) {
+        __shared__ int sh_hit[2];          // by step parity: a thread still reading step i's verdict must not see step i + 1's reset
         double lo = mn, hi = mx, thresh = 0, stable = 0;
-        int last_ok = 0;
+        int have_prev = 0, prev_total = 0, added = 0;       // prevn[] holds the allocation of the last evaluation, prev_total its bytes
         for (int i = 0; i < 128; ++i) {
             double nt_ = __dmul_rn(__dadd_rn(lo, hi), 0.5);
             if (fabs(__dsub_rn(nt_, thresh)) <= __dmul_rn(0.5 * 1e-5, thresh)) break;
             thresh = nt_;
             iters++;
-            int same = 1;
-            for (int k = tid; k < ncblks; k += nt) {
-                int n = t2_makelayer_block(co[k], thresh);
-                if (n != s.prevn[k]) { same = 0; s.prevn[k] = n; }
-                s.numpasses[k] = n;
+            int total;
+            if (tid == 0) sh_hit[i & 1] = -1;
+            __syncthreads();
+            if (tid < pc_n0 && pc->thresh[tid] == thresh) sh_hit[i & 1] = tid;
+            __syncthreads();
+            const int hit = sh_hit[i & 1];
+            if (hit >= 0) total = pc->bytes[hit];
+            else {
+                int same = 1;
+                for (int k = tid; k < ncblks; k += nt) {
+                    int n = t2_makelayer_block(co[k], thresh);
+                    if (n != s.prevn[k]) { same = 0; s.prevn[k] = n; }
+                    s.numpasses[k] = n;
+                }
+                same = __syncthreads_and(same) && have_prev;
+                total = same ? prev_total : t2_run(plan, cblks, co, s, scratch, nullptr, nullptr);
+                have_prev = 1; prev_total = total;
+                if (pc && tid == 0 && pc_n0 + added < PC_MAX) { pc->thresh[pc_n0 + added] = thresh; pc->bytes[pc_n0 + added] = total; }
+                ++added;
             }
-            same = __syncthreads_and(same) && i != 0;
-            int fail;
-            if (same) fail = !last_ok;
-            else fail = t2_run(plan, cblks, co, s, scratch, nullptr, nullptr) > maxlen;
-            if (fail) { last_ok = 0; lo = thresh; continue; }
-            last_ok = 1; hi = thresh; stable = thresh;
+            if (total > maxlen) { lo = thresh; continue; }
+            hi = thresh; stable = thresh;
         }
+        if (pc && tid == 0) pc->n = min(pc_n0 + added, PC_MAX);
         goodthresh = stable == 0 ? thresh : stable;
     }
     for (int k = tid; k < ncblks; k += nt) {
