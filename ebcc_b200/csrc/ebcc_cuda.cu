@@ -383,7 +383,7 @@ struct ebcc_cuda_ctx {
     int prio_split;
     int crowd;                 // pipelines at work on this device (hint from the host codec), see mq_lanes()
     int env_mq_lanes, env_dec_lanes, env_no_recording, env_dec_recording, env_debug_lanes, env_t1rec_ctas, env_dwt_cw;   // tuning / debugging variables, read once per host call (read_env)
-    int env_fused_idwt, env_fused_dwt, env_sp_serial, env_kt_whole;
+    int env_fused_idwt, env_fused_dwt, env_sp_serial, env_no_pcrd_cache;
     int ntiles;
     ebcc_cuda_ctx *tile[EBCC_MAX_TILES];
     ebcc_cuda_ctx *parent;
@@ -884,7 +884,7 @@ static void read_env(ebcc_cuda_ctx *c)
     c->env_t1rec_ctas = e ? atoi(e) : 2;
     e = getenv("EBCC_FUSED_IDWT");                  // 0: the unfused inverse transform (k_dequant / k_recon_dequant, k_idwt_h / k_idwt_v, k_finalize)
     c->env_fused_idwt = !(e && e[0] == '0');
-    c->env_kt_whole = getenv("EBCC_KT_WHOLE_PROBE") != NULL;
+    c->env_no_pcrd_cache = getenv("EBCC_NO_PCRD_CACHE") != NULL;   // cross-check aid: every probe bisects from scratch
     e = getenv("EBCC_SP_DECODE_SERIAL");            // cross-check aid: the one-thread SPIHT list decoder
     c->env_sp_serial = e && e[0] == '1';
     e = getenv("EBCC_FUSED_DWT");                   // 0: the unfused forward transform (k_dwt_v / k_dwt_h)
@@ -1060,7 +1060,7 @@ static int launch_rate_stage(ebcc_cuda_ctx *c, int B, const float *cr, int with_
     {
         KT kt_(c, EBCC_KT_PCRD_T2);
         EBCC_LAUNCH(k_pcrd_t2, dim3((unsigned)B), dim3(T2_THREADS), t2_smem_bytes(pl->ncblks, pl->nnodes), c->stream,
-                    c->d_plan, c->d_cblks, c->d_cbout, c->d_maxlen, c->d_out, c->d_body_off, c->d_pout, c->d_stat, getenv("EBCC_NO_PCRD_CACHE") ? (PcrdCache *)NULL : c->d_pcache);
+                    c->d_plan, c->d_cblks, c->d_cbout, c->d_maxlen, c->d_out, c->d_body_off, c->d_pout, c->d_stat, ctx_root(c)->env_no_pcrd_cache ? (PcrdCache *)NULL : c->d_pcache);
     }
     c->launches += 1;
     mark(c, EBCC_ST_BODIES);
@@ -1232,10 +1232,7 @@ extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const floa
     if (!c || nframes == 0 || nframes > c->cap_frames) return -1;
     CK(cudaSetDevice(c->device));
     const int B = (int)nframes;
-    // measurement aid (EBCC_KT_WHOLE_PROBE=1): the whole probe as one span of the otherwise unused class "recon", to compare
-    // with the sum of its launch groups (what queueing between them costs when many pipelines are in flight)
-    KT *whole = (ctx_root(c)->env_kt_whole && c->ntiles == 1) ? new KT(c, EBCC_KT_RECON) : (KT *)NULL;
-    if (launch_rate_stage(c, B, cr, with_streams)) { delete whole; return -1; }
+    if (launch_rate_stage(c, B, cr, with_streams)) return -1;
     c->skip_dec = !with_streams && c->ntiles == 1;      // the decoded frames of a search probe are never read, its statistics are
     if (c->ntiles > 1) {
         const int T = c->ntiles, hl = c->tile[0]->plan.main_header_len;
@@ -1258,8 +1255,7 @@ extern "C" int ebcc_cuda_rate_probe(ebcc_cuda_ctx *c, size_t nframes, const floa
             c->h_pout[i].stream_bytes = bytes;
         }
     } else {
-        if (probe_launch(c, B, targets)) { delete whole; return -1; }
-        delete whole;
+        if (probe_launch(c, B, targets)) return -1;
         CK(ctx_sync(c));
     }
     for (int i = 0; i < B; ++i) {
