@@ -729,6 +729,11 @@ static int reserve_alloc(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes, i
     CK(cudaFuncSetAttribute(k_t1_dec<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_SMEM_BYTES(2)));
     CK(cudaFuncSetAttribute(k_t1_dec<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_SMEM_BYTES(4)));
     CK(cudaFuncSetAttribute(k_t1_dec<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_SMEM_BYTES(8)));
+    // four CTAs of the tier-1 decoder per SM need the largest shared-memory carve-out
+    CK(cudaFuncSetAttribute(k_t1_dec<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaFuncSetAttribute(k_t1_dec<2>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaFuncSetAttribute(k_t1_dec<4>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaFuncSetAttribute(k_t1_dec<8>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     CK(cudaFuncSetAttribute(k_idwt_v, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(k_idwt_h, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     CK(cudaFuncSetAttribute(k_t2_parse, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));

@@ -224,7 +224,7 @@ __device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned *ctx, const un
 
 struct T1DecState {
     unsigned *F;                 // flag words of this block
-    unsigned short *F2;          // candidate words of this block (sig4 | nb4 << 4 | pi4 << 8)
+    unsigned char *F2;           // candidate bytes of this block (sig4 | nb4 << 4)
     unsigned *cx;                // 19 contexts (table words)
     const unsigned char *zc;     // zero-coding LUT of this orientation
     const unsigned *tab;
@@ -233,20 +233,20 @@ struct T1DecState {
     int W, pass;
 };
 
-// Second word per stripe column (16 bits), kept next to the flag word so that a pass finds the rows it has to visit with
-// one load and three logic operations instead of testing the four rows one by one:
-//   bits 0-3 sig4 (row significant), 4-7 nb4 (row has a significant neighbour), 8-11 pi4 (row coded in this plane's
-//   significance pass; mirror of DF_PI).  All bits zero <=> flag word zero.
+// Second word per stripe column (one byte), kept next to the flag word so that a pass finds the rows it has to visit with
+// two independent loads and three logic operations instead of testing the four rows one by one:
+//   bits 0-3 sig4 (row significant), 4-7 nb4 (row has a significant neighbour); pi4 (row coded in this plane's
+//   significance pass) comes from the flag word's top byte.  All bits zero <=> flag word zero.  One byte, not two, per
+//   column: with 5 bytes per column eight blocks take 47.5 KB and FOUR CTAs fit an SM (32 serial chains instead of 24).
 #define D2_SIG(f2) ((f2) & 0xfu)
 #define D2_NB(f2) (((f2) >> 4) & 0xfu)
-#define D2_PI(f2) (((f2) >> 8) & 0xfu)
+#define DF_PI4(f) (((f) >> 24) & 0xfu)
 __device__ __forceinline__ unsigned d2_from_flags(unsigned f)
 {
     unsigned r = 0;
     for (int ci = 0; ci < 4; ++ci) {
         if (f & DF_SIG(ci)) r |= 1u << ci;
         if (f & DF_NB(ci)) r |= 0x10u << ci;
-        if (f & DF_PI(ci)) r |= 0x100u << ci;
     }
     return r;
 }
@@ -256,7 +256,7 @@ __device__ __forceinline__ void t1d_set_sig(T1DecState &S, int p, int ci, unsign
 {
     f |= DF_SIG(ci) | (s ? DF_CHI(ci) : 0u);
     f2 |= (1u << ci) | ((((5u << ci) >> 1) & 0xfu) << 4);            // own column: rows ci - 1 and ci + 1 gain a neighbour
-    const unsigned short side = (unsigned short)((((7u << ci) >> 1) & 0xfu) << 4);   // left / right column: rows ci - 1 .. ci + 1
+    const unsigned char side = (unsigned char)((((7u << ci) >> 1) & 0xfu) << 4);   // left / right column: rows ci - 1 .. ci + 1
     S.F[p - 1] |= 1u << ((ci + 1) * 3 + 2);
     S.F[p + 1] |= 1u << ((ci + 1) * 3 + 0);
     S.F2[p - 1] |= side;
@@ -306,9 +306,9 @@ __device__ void t1d_clnpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
         for (int x = 0; x < w; ++x) {
             const int p = (s + 1) * DEC_FW + x + 1;
             unsigned f2 = S.F2[p];
-            unsigned cand = ~(D2_SIG(f2) | D2_PI(f2)) & limmask;            // rows neither significant nor coded in the significance pass
-            unsigned f;
-            if (lim == 4 && (f2 & 0xfffu) == 0) {                           // flag word all zero: run-length mode
+            unsigned f = S.F[p];
+            unsigned cand = ~(D2_SIG(f2) | DF_PI4(f)) & limmask;            // rows neither significant nor coded in the significance pass
+            if (lim == 4 && f2 == 0) {                                      // flag word all zero: run-length mode
                 if (!mqd_decode<SH>(q, S.cx + CTX_AGG, S.tab)) continue;
                 unsigned r = mqd_decode<SH>(q, S.cx + CTX_UNI, S.tab);
                 r = (r << 1) | mqd_decode<SH>(q, S.cx + CTX_UNI, S.tab);
@@ -319,10 +319,9 @@ __device__ void t1d_clnpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
                 cand &= ~((2u << r) - 1u);                                   // the rows behind it are coded normally
             } else {
                 if (cand == 0) {                                            // nothing to code; the pass still ends the plane for this column
-                    if (f2 & 0xf00u) { S.F[p] &= ~(0xfu << 24); S.F2[p] = (unsigned short)(f2 & ~0xf00u); }
+                    if (f & (0xfu << 24)) S.F[p] = f & ~(0xfu << 24);
                     continue;
                 }
-                f = S.F[p];
             }
             while (cand) {
                 const int ci = __ffs((int)cand) - 1;
@@ -334,7 +333,7 @@ __device__ void t1d_clnpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
                 t1d_set_sig(S, p, ci, sg, f, f2);
             }
             S.F[p] = f & ~(0xfu << 24);
-            S.F2[p] = (unsigned short)(f2 & ~0xf00u);
+            S.F2[p] = (unsigned char)f2;
         }
     }
 }
@@ -349,9 +348,9 @@ __device__ void t1d_sigpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
         for (int x = 0; x < w; ++x) {
             const int p = (s + 1) * DEC_FW + x + 1;
             unsigned f2 = S.F2[p];
-            unsigned cand = D2_NB(f2) & ~(D2_SIG(f2) | D2_PI(f2)) & limmask;   // insignificant rows with a significant neighbour
-            if (cand == 0) continue;
             unsigned f = S.F[p];
+            unsigned cand = D2_NB(f2) & ~(D2_SIG(f2) | DF_PI4(f)) & limmask;   // insignificant rows with a significant neighbour
+            if (cand == 0) continue;
             do {
                 const int ci = __ffs((int)cand) - 1;
                 const unsigned ctx = S.zc[(f >> (ci * 3)) & 0x1ffu];
@@ -360,11 +359,11 @@ __device__ void t1d_sigpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
                     t1d_new_sig(S, y0 + ci, x, sg, oneplushalf);
                     t1d_set_sig(S, p, ci, sg, f, f2);
                 }
-                f |= DF_PI(ci); f2 |= 0x100u << ci;
+                f |= DF_PI(ci);
                 // a row that just turned significant makes the rows behind it candidates
-                cand = D2_NB(f2) & ~(D2_SIG(f2) | D2_PI(f2)) & limmask & ~((2u << ci) - 1u);
+                cand = D2_NB(f2) & ~(D2_SIG(f2) | DF_PI4(f)) & limmask & ~((2u << ci) - 1u);
             } while (cand);
-            S.F[p] = f; S.F2[p] = (unsigned short)f2;
+            S.F[p] = f; S.F2[p] = (unsigned char)f2;
         }
     }
 }
@@ -379,9 +378,9 @@ __device__ void t1d_refpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
         for (int x = 0; x < w; ++x) {
             const int p = (s + 1) * DEC_FW + x + 1;
             const unsigned f2 = S.F2[p];
-            unsigned cand = D2_SIG(f2) & ~D2_PI(f2) & limmask;              // significant before this plane
-            if (cand == 0) continue;
             unsigned f = S.F[p];
+            unsigned cand = D2_SIG(f2) & ~DF_PI4(f) & limmask;              // significant before this plane
+            if (cand == 0) continue;
             do {
                 const int ci = __ffs((int)cand) - 1;
                 cand &= cand - 1u;
@@ -473,7 +472,7 @@ __device__ __forceinline__ bool dec_view(DecView &v, long long job, const CblkDe
 
 // Warps per CTA for L blocks per warp: 8 blocks (39 KB of flag words) per CTA from L = 2 on.
 #define DEC_WPC(L) ((L) == 1 ? 4 : 8 / (L))
-#define DEC_SMEM_BYTES(L) ((size_t)(DEC_WPC(L) * (L)) * DEC_FWORDS * (sizeof(unsigned) + sizeof(unsigned short)))
+#define DEC_SMEM_BYTES(L) ((size_t)(DEC_WPC(L) * (L)) * DEC_FWORDS * (sizeof(unsigned) + sizeof(unsigned char)))
 
 // grid = ceil(ncblks * nframes / (DEC_WPC(L) * L)) CTAs.  A warp owns L code-blocks; lanes 0 .. L-1 decode one each
 // (SIMT: they share every instruction they have in common, which trades a longer serial chain per block for fewer
@@ -490,10 +489,10 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJ
          const CblkOut *__restrict__ cbout, DecState *dstate, unsigned *save, int W, int H, int ncblks, int nframes)
 {
     constexpr int NB = DEC_WPC(L) * L;          // blocks per CTA
-    // flag words + candidate words of the CTA's blocks: dynamic shared memory (DEC_SMEM_BYTES(L): 57 KB for eight blocks)
+    // flag words + candidate bytes of the CTA's blocks: dynamic shared memory (DEC_SMEM_BYTES(L): 47.5 KB for eight blocks)
     EBCC_DYN_SMEM(unsigned, dynsm);
     unsigned (*F)[DEC_FWORDS] = (unsigned (*)[DEC_FWORDS])dynsm;
-    unsigned short (*F2)[DEC_FWORDS] = (unsigned short (*)[DEC_FWORDS])(dynsm + NB * DEC_FWORDS);
+    unsigned char (*F2)[DEC_FWORDS] = (unsigned char (*)[DEC_FWORDS])(dynsm + NB * DEC_FWORDS);
     __shared__ unsigned cxs[NB][20];
     __shared__ MqShadows shw[NB];
     __shared__ int need2[NB];
@@ -514,7 +513,7 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJ
         const bool resume = v.mode == 1 && search && dstate[v.bi].np_dec > 0;
         if (resume) {
             const unsigned *sv = save + v.bi * DEC_SAVE_WORDS;
-            for (int i = lane; i < DEC_FWORDS; i += 32) { Fb[i] = sv[i]; F2[warp * L + sb][i] = (unsigned short)d2_from_flags(sv[i]); }
+            for (int i = lane; i < DEC_FWORDS; i += 32) { Fb[i] = sv[i]; F2[warp * L + sb][i] = (unsigned char)d2_from_flags(sv[i]); }
         } else {
             for (int i = lane; i < DEC_FWORDS; i += 32) { Fb[i] = 0; F2[warp * L + sb][i] = 0; }
             int *dst = (v.mode == 1 ? iplane : scratch) + v.o;
@@ -644,7 +643,7 @@ k_t1_dec_cuts(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cb
               int cap, const unsigned char *__restrict__ pool, size_t pool_stride, const DecLuts *__restrict__ g_luts, int *cut_pool, int ncblks)
 {
     __shared__ unsigned F[CUT_WPC][DEC_FWORDS];
-    __shared__ unsigned short F2[CUT_WPC][DEC_FWORDS];
+    __shared__ unsigned char F2[CUT_WPC][DEC_FWORDS];
     __shared__ unsigned cxs[CUT_WPC][20];
     __shared__ unsigned tab[94];
     __shared__ unsigned char zc[4 * 512];
