@@ -192,22 +192,22 @@ __device__ __forceinline__ void mqd_init(MqDec &q, const unsigned char *data, in
 template <bool SH>
 __device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned *ctx, const unsigned *tab)
 {
+    // Branch-free decision (the serial chain pays for every resolved branch): with lz = "code value in the lower
+    // sub-interval" and sw = "sub-intervals exchanged" (a - qe < qe), the decoded bit is mps ^ (lz != sw), the new
+    // interval is qe (lz) or a - qe, and a renormalisation happens exactly when that interval lost its top bit --
+    // mqc_inl.h:100-175 (opj_mqc_mpsexchange / lpsexchange / decode) folded into selects.
     const unsigned e = *ctx, qe = e & 0xffffu, mps = e >> 30;
     const unsigned a0 = q.a - qe;
-    unsigned d, a1 = a0;
-    bool ren;
-    if ((q.m.c >> 16) < qe) {
-        d = (a0 < qe) ? mps : (mps ^ 1u);
-        a1 = qe; ren = true;
-    } else {
-        q.m.c -= qe << 16;
-        if ((a0 & 0x8000u) == 0) { d = (a0 < qe) ? (mps ^ 1u) : mps; ren = true; }
-        else { d = mps; ren = false; }
-    }
-    const int nshift = ren ? __clz((int)a1) - 16 : 0;
+    const bool lz = (q.m.c >> 16) < qe;
+    const unsigned flip = (unsigned)(lz != (a0 < qe));
+    const unsigned d = mps ^ flip;
+    const unsigned a1 = lz ? qe : a0;
+    q.m.c -= lz ? 0u : (qe << 16);
+    const int nshift = __clz((int)a1) - 16;                  // 0 <=> no renormalisation (a1 keeps bit 15)
     if (SH && q.sh_on) mqd_shadow_step(q.sw, q.sh_on, qe, a0, mps, d, nshift, q.data);
-    if (ren) {
-        *ctx = tab[(d == mps) ? ((e >> 16) & 127u) : ((e >> 23) & 127u)];
+    q.a = a1 << nshift;
+    if (nshift) {
+        *ctx = tab[flip ? ((e >> 23) & 127u) : ((e >> 16) & 127u)];
         int n = nshift;
         if (!SH && n <= (int)q.m.ct) { q.m.c <<= n; q.m.ct -= (unsigned)n; }      // the usual case: the bits are in the register
         else
@@ -217,8 +217,7 @@ __device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned *ctx, const un
                 const int s = n < (int)q.m.ct ? n : (int)q.m.ct;
                 q.m.c <<= s; q.m.ct -= (unsigned)s; n -= s;
             }
-        q.a = a1 << nshift;
-    } else q.a = a0;
+    }
     return d;
 }
 
