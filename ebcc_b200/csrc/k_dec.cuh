@@ -190,7 +190,7 @@ __device__ __forceinline__ void mqd_init(MqDec &q, const unsigned char *data, in
 // SH: truncation shadows may be armed (the cross-check recordings of the compression-ratio search); a plain decode
 // (ebcc_decode, the pool of unproven cuts) compiles without every shadow test
 template <bool SH>
-__device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned *ctx, const unsigned *tab)
+__device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned *ctx, mq_saddr tab)
 {
     // Branch-free decision (the serial chain pays for every resolved branch): with lz = "code value in the lower
     // sub-interval" and sw = "sub-intervals exchanged" (a - qe < qe), the decoded bit is mps ^ (lz != sw), the new
@@ -207,7 +207,9 @@ __device__ __forceinline__ unsigned mqd_decode(MqDec &q, unsigned *ctx, const un
     if (SH && q.sh_on) mqd_shadow_step(q.sw, q.sh_on, qe, a0, mps, d, nshift, q.data);
     q.a = a1 << nshift;
     if (nshift) {
-        *ctx = tab[flip ? ((e >> 23) & 127u) : ((e >> 16) & 127u)];
+        // the table by its 32-bit shared address held in a register: the compiler otherwise re-derives the shared window
+        // base (S2UR SR_CgaCtaId ...) in front of this load, on the chain of the next decision with the same context
+        *ctx = mq_ld32(tab + (mq_saddr)(((flip ? (e >> 23) : (e >> 16)) & 127u) * 4u));
         int n = nshift;
         if (!SH && n <= (int)q.m.ct) { q.m.c <<= n; q.m.ct -= (unsigned)n; }      // the usual case: the bits are in the register
         else
@@ -225,8 +227,8 @@ struct T1DecState {
     unsigned *F;                 // flag words of this block
     unsigned char *F2;           // candidate bytes of this block (sig4 | nb4 << 4)
     unsigned *cx;                // 19 contexts (table words)
-    const unsigned char *zc;     // zero-coding LUT of this orientation
-    const unsigned *tab;
+    mq_saddr zc;                 // zero-coding LUT of this orientation (shared address)
+    mq_saddr tab;                // the MQ state table (shared address)
     int *plane;                  // top-left of the block inside the integer coefficient plane
     unsigned char *spass;        // top-left of the block inside the pass-of-significance plane, or nullptr
     int W, pass;
@@ -325,7 +327,7 @@ __device__ void t1d_clnpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
             while (cand) {
                 const int ci = __ffs((int)cand) - 1;
                 cand &= cand - 1u;
-                const unsigned ctx = S.zc[(f >> (ci * 3)) & 0x1ffu];
+                const unsigned ctx = mq_ld8(S.zc + (mq_saddr)((f >> (ci * 3)) & 0x1ffu));
                 if (!mqd_decode<SH>(q, S.cx + CTX_ZC + ctx, S.tab)) continue;
                 const unsigned sg = t1d_sign<SH>(S, q, p, ci, f);
                 t1d_new_sig(S, y0 + ci, x, sg, oneplushalf);
@@ -352,7 +354,7 @@ __device__ void t1d_sigpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
             if (cand == 0) continue;
             do {
                 const int ci = __ffs((int)cand) - 1;
-                const unsigned ctx = S.zc[(f >> (ci * 3)) & 0x1ffu];
+                const unsigned ctx = mq_ld8(S.zc + (mq_saddr)((f >> (ci * 3)) & 0x1ffu));
                 if (mqd_decode<SH>(q, S.cx + CTX_ZC + ctx, S.tab)) {
                     const unsigned sg = t1d_sign<SH>(S, q, p, ci, f);
                     t1d_new_sig(S, y0 + ci, x, sg, oneplushalf);
@@ -532,10 +534,10 @@ k_t1_dec(const CblkDesc *__restrict__ cblks, const int *__restrict__ order, DecJ
     const bool mine = lane < L && dec_view(v, job0 + lane, cblks, order, jobs, W, H, ncblks, nframes);
     const int blk = warp * L + (lane < L ? lane : 0);
     T1DecState S;
-    S.F = F[blk]; S.F2 = F2[blk]; S.cx = cxs[blk]; S.tab = tab; S.W = W; S.pass = 0;
+    S.F = F[blk]; S.F2 = F2[blk]; S.cx = cxs[blk]; S.tab = MQ_OPAQUE(MQ_SADDR(tab)); S.W = W; S.pass = 0;
     DecState ds; ds.np_dec = 0; ds.scratch_np = 0; ds.bad[0] = ds.bad[1] = ds.bad[2] = ds.bad[3] = 0; ds.first_entry = -1; ds.pad = 0;
     if (mine) {
-        S.zc = zc + v.cb.orient * 512;
+        S.zc = MQ_OPAQUE(MQ_SADDR(zc + v.cb.orient * 512));
         if (search) ds = dstate[v.bi];
         const unsigned char *seg = pool + (size_t)v.frame * pool_stride + v.jb.off;
         unsigned *cx = cxs[blk];
@@ -668,7 +670,7 @@ k_t1_dec_cuts(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cb
     for (int i = 0; i < 19; ++i) cx[i] = tab[0];
     cx[CTX_UNI] = tab[46 << 1]; cx[CTX_AGG] = tab[3 << 1]; cx[CTX_ZC] = tab[4 << 1];
     T1DecState S;
-    S.F = F[warp]; S.F2 = F2[warp]; S.cx = cx; S.tab = tab; S.W = J2K_CBLK; S.pass = 0; S.zc = zc + cb.orient * 512;
+    S.F = F[warp]; S.F2 = F2[warp]; S.cx = cx; S.tab = MQ_OPAQUE(MQ_SADDR(tab)); S.W = J2K_CBLK; S.pass = 0; S.zc = MQ_OPAQUE(MQ_SADDR(zc + cb.orient * 512));
     S.plane = dst; S.spass = nullptr;
     MqDec q;
     mqd_init(q, pool + (size_t)frame * pool_stride + cb.mq_off, co.rate[en.np - 1], nullptr);
