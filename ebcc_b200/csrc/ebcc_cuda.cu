@@ -885,8 +885,8 @@ static void read_env(ebcc_cuda_ctx *c)
     e = getenv("EBCC_DECODER_RECORDING");           // cross-check aid: recordings made by the tier-1 decoder (round-1 path)
     c->env_dec_recording = e && e[0] == '1';
     c->env_debug_lanes = getenv("EBCC_DEBUG_LANES") != NULL;
-    e = getenv("EBCC_T1REC_CTAS");                  // tuning: CTAs per SM the recording variant of k_t1_cm is compiled for (2 or 3)
-    c->env_t1rec_ctas = e ? atoi(e) : 2;
+    e = getenv("EBCC_T1REC_CTAS");                  // tuning: CTAs per SM the recording variant of k_t1_cm is compiled for (2: 64 registers; 3, the default: 40, +2.8 % on the pipelined step)
+    c->env_t1rec_ctas = e ? atoi(e) : 3;
     e = getenv("EBCC_FUSED_IDWT");                  // 0: the unfused inverse transform (k_dequant / k_recon_dequant, k_idwt_h / k_idwt_v, k_finalize)
     c->env_fused_idwt = !(e && e[0] == '0');
     c->env_no_pcrd_cache = getenv("EBCC_NO_PCRD_CACHE") != NULL;   // cross-check aid: every probe bisects from scratch
@@ -897,6 +897,13 @@ static void read_env(ebcc_cuda_ctx *c)
     e = getenv("EBCC_DWT_CW");                      // tuning: columns per CTA of the vertical 9/7 passes (shared memory = height x columns x 4 bytes)
     c->env_dwt_cw = e ? atoi(e) : 32;
     if (c->env_dwt_cw != 4 && c->env_dwt_cw != 8 && c->env_dwt_cw != 16 && c->env_dwt_cw != 32) c->env_dwt_cw = 32;
+}
+// measurement aid (EBCC_DEBUG_REPEAT=cm|mq|cuts|idwt|dwt): the named launch group runs twice (same results), which shows
+// what one more of it costs a step with every pipeline in flight
+static int dbg_repeat(const char *cls)
+{
+    static const char *e = getenv("EBCC_DEBUG_REPEAT");
+    return (e && !strcmp(e, cls)) ? 2 : 1;
 }
 static int mq_lanes(const ebcc_cuda_ctx *c, long long jobs)
 {
@@ -977,7 +984,7 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int f
     if (with_minmax && launch_minmax(c, B)) return -1;
 
     mark(c, EBCC_ST_DWT);
-    if (launch_dwt(c, B)) return -1;
+    for (int rep = 0; rep < dbg_repeat("dwt"); ++rep) if (launch_dwt(c, B)) return -1;
 
     mark(c, EBCC_ST_T1_CM);
     KT *kt_cm = new KT(c, EBCC_KT_T1_CM);
@@ -986,6 +993,7 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int f
                     c->d_coef, c->d_cblks, c->d_bands, c->d_luts, (const unsigned char *)c->d_declut, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks,
                     pl->sym_stride, c->d_iplane, c->d_spass, c->d_stat);
     else if (c->rec_from_encoder)
+        for (int rep = 0; rep < dbg_repeat("cm"); ++rep)
         EBCC_LAUNCH((k_t1_cm<true, 2>), dim3((unsigned)pl->ncblks, (unsigned)B), dim3(T1_THREADS), 0, c->stream,
                     c->d_coef, c->d_cblks, c->d_bands, c->d_luts, (const unsigned char *)c->d_declut, c->d_cbout, c->d_sym, pl->W, pl->H, pl->ncblks,
                     pl->sym_stride, c->d_iplane, c->d_spass, c->d_stat);
@@ -1011,8 +1019,10 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int f
         const dim3 grid((unsigned)((jobs + per_cta - 1) / per_cta)), block(MQ_THREADS(lanes));
 #define MQ_GO(LL) EBCC_LAUNCH(k_t1_mq<LL>, grid, block, 0, ls, c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, \
                               c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride, c->rec_from_encoder ? c->d_dstate : (T1CutState *)NULL, c->d_stat)
+        for (int rep = 0; rep < dbg_repeat("mq"); ++rep) {
         if (lanes == 32) MQ_GO(32); else if (lanes == 16) MQ_GO(16); else if (lanes == 8) MQ_GO(8); else if (lanes == 4) MQ_GO(4);
         else if (lanes == 2) MQ_GO(2); else MQ_GO(1);
+        }
 #undef MQ_GO
     }
     c->launches += 2;
@@ -1023,6 +1033,7 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int f
         CK(cudaMemsetAsync(c->d_cut_count, 0, sizeof(int), ls));
         EBCC_LAUNCH(k_cut_collect, dim3((unsigned)((jobs + 255) / 256)), dim3(256), 0, ls, (const CblkOut *)c->d_cbout, c->d_dstate, c->d_cut_list,
                     c->d_cut_count, c->cut_cap, jobs);
+        for (int rep = 0; rep < dbg_repeat("cuts"); ++rep)
         EBCC_LAUNCH(k_t1_dec_cuts, dim3((unsigned)((c->cut_cap + CUT_WPC - 1) / CUT_WPC)), dim3(CUT_WPC * 32), 0, ls, c->d_cblks, (const CblkOut *)c->d_cbout,
                     (const T1CutEntry *)c->d_cut_list, (const int *)c->d_cut_count, c->cut_cap, (const unsigned char *)c->d_mq, pl->mq_stride, c->d_declut,
                     c->d_cut_pool, pl->ncblks);
@@ -1195,10 +1206,12 @@ static int probe_launch(ebcc_cuda_ctx *c, int B, const float *targets)
     for (int i = 0; i < B; ++i) c->h_targets[i] = targets[i];
     CK(cudaMemcpyAsync(c->d_targets, c->h_targets, sizeof(float) * B, cudaMemcpyHostToDevice, c->stream));
     const long long njobs = (long long)pl->ncblks * B;
+    for (int rep = 0; rep < dbg_repeat("idwt"); ++rep) {
     EBCC_LAUNCH(k_jobs_from_enc, dim3((unsigned)((njobs + 255) / 256)), dim3(256), 0, c->stream, c->d_cblks, c->d_cbout, c->d_dstate, c->d_jobs,
                 pl->ncblks, B, c->use_recording, c->d_rjobs, c->d_es);
     c->launches++;
     if (run_decode_stage(c, B, c->d_mq, pl->mq_stride, c->d_in)) return -1;
+    }
     CK(cudaMemcpyAsync(c->h_es, c->d_es, sizeof(ErrStat) * B, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaMemcpyAsync(c->h_pout, c->d_pout, sizeof(ProbeOut) * B, cudaMemcpyDeviceToHost, c->stream));
     return 0;

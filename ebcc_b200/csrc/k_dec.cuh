@@ -291,10 +291,12 @@ __device__ __forceinline__ unsigned t1d_sign(T1DecState &S, MqDec &q, int p, int
     return v ^ (unsigned)(e >> 3);
 }
 
-__device__ __forceinline__ void t1d_new_sig(T1DecState &S, int y, int x, unsigned sg, int oneplushalf)
+// o = offset of the sample inside the plane (the passes keep a per-stripe row base and add x and ci * W: one multiply-add
+// per sample instead of a 64-bit address chain)
+__device__ __forceinline__ void t1d_new_sig(T1DecState &S, int o, unsigned sg, int oneplushalf)
 {
-    atomicAdd(S.plane + (size_t)y * S.W + x, sg ? -oneplushalf : oneplushalf);
-    if (S.spass) S.spass[(size_t)y * S.W + x] = (unsigned char)S.pass;
+    atomicAdd(S.plane + o, sg ? -oneplushalf : oneplushalf);
+    if (S.spass) S.spass[o] = (unsigned char)S.pass;
 }
 
 template <bool SH>
@@ -304,6 +306,7 @@ __device__ void t1d_clnpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
     for (int s = 0, y0 = 0; y0 < h; ++s, y0 += 4) {
         const int lim = min(4, h - y0);
         const unsigned limmask = (1u << lim) - 1u;
+        const int rowo = y0 * S.W;
         for (int x = 0; x < w; ++x) {
             const int p = (s + 1) * DEC_FW + x + 1;
             unsigned f2 = S.F2[p];
@@ -315,7 +318,7 @@ __device__ void t1d_clnpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
                 r = (r << 1) | mqd_decode<SH>(q, S.cx + CTX_UNI, S.tab);
                 f = 0;
                 const unsigned sg = t1d_sign<SH>(S, q, p, (int)r, f);
-                t1d_new_sig(S, y0 + (int)r, x, sg, oneplushalf);
+                t1d_new_sig(S, rowo + x + (int)r * S.W, sg, oneplushalf);
                 t1d_set_sig(S, p, (int)r, sg, f, f2);
                 cand &= ~((2u << r) - 1u);                                   // the rows behind it are coded normally
             } else {
@@ -330,7 +333,7 @@ __device__ void t1d_clnpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
                 const unsigned ctx = mq_ld8(S.zc + (mq_saddr)((f >> (ci * 3)) & 0x1ffu));
                 if (!mqd_decode<SH>(q, S.cx + CTX_ZC + ctx, S.tab)) continue;
                 const unsigned sg = t1d_sign<SH>(S, q, p, ci, f);
-                t1d_new_sig(S, y0 + ci, x, sg, oneplushalf);
+                t1d_new_sig(S, rowo + x + ci * S.W, sg, oneplushalf);
                 t1d_set_sig(S, p, ci, sg, f, f2);
             }
             S.F[p] = f & ~(0xfu << 24);
@@ -346,6 +349,7 @@ __device__ void t1d_sigpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
     for (int s = 0, y0 = 0; y0 < h; ++s, y0 += 4) {
         const int lim = min(4, h - y0);
         const unsigned limmask = (1u << lim) - 1u;
+        const int rowo = y0 * S.W;
         for (int x = 0; x < w; ++x) {
             const int p = (s + 1) * DEC_FW + x + 1;
             unsigned f2 = S.F2[p];
@@ -357,7 +361,7 @@ __device__ void t1d_sigpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
                 const unsigned ctx = mq_ld8(S.zc + (mq_saddr)((f >> (ci * 3)) & 0x1ffu));
                 if (mqd_decode<SH>(q, S.cx + CTX_ZC + ctx, S.tab)) {
                     const unsigned sg = t1d_sign<SH>(S, q, p, ci, f);
-                    t1d_new_sig(S, y0 + ci, x, sg, oneplushalf);
+                    t1d_new_sig(S, rowo + x + ci * S.W, sg, oneplushalf);
                     t1d_set_sig(S, p, ci, sg, f, f2);
                 }
                 f |= DF_PI(ci);
@@ -376,6 +380,7 @@ __device__ void t1d_refpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
     for (int s = 0, y0 = 0; y0 < h; ++s, y0 += 4) {
         const int lim = min(4, h - y0);
         const unsigned limmask = (1u << lim) - 1u;
+        const int rowo = y0 * S.W;
         for (int x = 0; x < w; ++x) {
             const int p = (s + 1) * DEC_FW + x + 1;
             const unsigned f2 = S.F2[p];
@@ -388,7 +393,7 @@ __device__ void t1d_refpass(T1DecState &S, MqDec &q, int w, int h, int bpno)
                 const int ctx = (f & DF_MU(ci)) ? CTX_MAG + 2 : ((f & DF_NB(ci)) ? CTX_MAG + 1 : CTX_MAG);
                 const unsigned v = mqd_decode<SH>(q, S.cx + ctx, S.tab);
                 const unsigned neg = (f >> (18 + ci + 1)) & 1u;
-                atomicAdd(S.plane + (size_t)(y0 + ci) * S.W + x, (v ^ neg) ? poshalf : -poshalf);
+                atomicAdd(S.plane + (rowo + x + ci * S.W), (v ^ neg) ? poshalf : -poshalf);
                 f |= DF_MU(ci);
             } while (cand);
             S.F[p] = f;

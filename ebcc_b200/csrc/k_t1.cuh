@@ -151,20 +151,22 @@ __device__ __forceinline__ unsigned cf_sigpass_col(unsigned f, unsigned n, const
 }
 
 // rows b4 of the stripe column with flag-word index p became significant in coding pass `pass`
-__device__ __forceinline__ void t1_rec_pass(unsigned char *rec_pass, size_t base, int W, int p, unsigned b4, int pass)
+// (recp = the block's top-left sample in the pass plane: one pointer lives through the kernel instead of frame, H, ty, tx)
+__device__ __forceinline__ void t1_rec_pass(unsigned char *recp, int W, int p, unsigned b4, int pass)
 {
     const int s = p / CF_W - 1, x = p - (s + 1) * CF_W - 1;
-    unsigned char *d = rec_pass + base + (size_t)(4 * s) * W + x;
+    unsigned char *d = recp + (4 * s) * W + x;
 #pragma unroll
     for (int j = 0; j < 4; ++j)
-        if ((b4 >> j) & 1u) d[(size_t)j * W] = (unsigned char)pass;
+        if ((b4 >> j) & 1u) d[j * W] = (unsigned char)pass;
 }
 
 // 3 CTAs per SM caps the kernel at 40 registers: room for the long-lived MQ CTAs of other batches in flight
 #ifndef T1_MIN_CTAS
 #define T1_MIN_CTAS 3
 #endif
-template <bool REC, int MINB>      // MINB CTAs per SM: 3 caps the kernel at 40 registers, 2 at 64 (the recording stores like a few more)
+template <bool REC, int MINB>      // MINB CTAs per SM: 3 caps the kernel at 40 registers, 2 at 64 (the recording variant then keeps eight hoisted
+                                   // store addresses in local memory, which costs less than the third CTA brings with other batches in flight)
 __global__ void __launch_bounds__(T1_THREADS, MINB)
 k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, const BandDesc *__restrict__ bands,
         const T1Luts *__restrict__ g_luts, const unsigned char *__restrict__ zc_lut, CblkOut *cbout, unsigned char *sym_pool,
@@ -204,6 +206,8 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
     unsigned sgn4[T1_CPT];
     const float stepsize = bd->stepsize;
     const float *src = coef + (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx;
+    unsigned char *recp = REC ? rec_pass + (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx : nullptr;
+    int *recv = REC ? rec_val + (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx : nullptr;
     int mymax = 0;
 #pragma unroll
     for (int k = 0; k < T1_CPT; ++k) {
@@ -226,7 +230,7 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
                     mymax = max(mymax, a);
                     if (REC) {
                         const int m = a >> 6;
-                        rec_val[(size_t)frame * H * W + (size_t)(cb.ty + 4 * s + j) * W + cb.tx + x] = m ? (v < 0 ? -(2 * m + 1) : 2 * m + 1) : 0;
+                        recv[(4 * s + j) * W + x] = m ? (v < 0 ? -(2 * m + 1) : 2 * m + 1) : 0;
                     }
                 }
             N[sidx[k]] = sgn4[k];          // staging for SG
@@ -296,7 +300,7 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
                 unsigned coded = 0;
                 if ((~cf_own4(f) & ((1u << lim[k]) - 1u)) != 0) {
                     const unsigned fr = cf_sigpass_col<true>(f, N[p], mag[k], one, lim[k], sgn4[k], zc, SG, p, &luts, bpno, sq[0], coded, nm[0]);
-                    if (REC && fr) t1_rec_pass(rec_pass, (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx, W, p, fr, passno);
+                    if (REC && fr) t1_rec_pass(recp, W, p, fr, passno);
                 }
                 // state: the word absorbs what its neighbourhood gained, rows coded here are marked pi
                 const unsigned w = f | N[p] | (coded << 24);
@@ -337,7 +341,7 @@ k_t1_cm(const float *__restrict__ coef, const CblkDesc *__restrict__ cblks, cons
                 fresh[k] = cand & bits;
                 if (fresh[k]) {
                     cf_scatter(N, sidx[k], fresh[k]);
-                    if (REC) t1_rec_pass(rec_pass, (size_t)frame * H * W + (size_t)cb.ty * W + cb.tx, W, sidx[k], fresh[k], first ? passno : passno + 2);
+                    if (REC) t1_rec_pass(recp, W, sidx[k], fresh[k], first ? passno : passno + 2);
                 }
             }
             __syncthreads();
