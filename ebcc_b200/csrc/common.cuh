@@ -94,6 +94,10 @@ struct CblkOut {
 struct T1CutState { int np_dec; int scratch_np; unsigned bad[4]; int first_entry; int pad; };
 struct T1CutEntry { unsigned bi; int np; };        // block (frame * ncblks + cblk), passes to decode from the segment cut at rate[np - 1]
 #define T1_CUT_WORDS (J2K_CBLK * J2K_CBLK)         // ints per pool entry: the decoded block, row stride J2K_CBLK
+// MQ context states (pair index = state * 2 + mps, one byte each) at the end of every clean-up pass of a block: what a decode
+// that starts at a bit-plane boundary needs besides the coder registers in CblkOut::mqs (k_t1_mq writes, k_t1_dec_cuts reads)
+#define T1_SNAP_PLANES ((J2K_MAXPASSES + 2) / 3)
+#define T1_SNAP_BYTES 20
 
 struct Plan {
     int H, W, nbands, ncblks;

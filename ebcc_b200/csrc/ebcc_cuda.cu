@@ -317,6 +317,7 @@ struct ebcc_cuda_ctx {
     DecState *d_dstate;        // [B][ncblks]
     T1CutEntry *d_cut_list;    // unproven truncation points of the batch and their pre-decoded blocks (k_t1_dec_cuts)
     int *d_cut_count, *d_cut_pool, cut_cap;
+    unsigned char *d_ctxsnap;  // [B * ncblks][T1_SNAP_PLANES][T1_SNAP_BYTES] context states at clean-up pass ends (k_t1_mq -> k_t1_dec_cuts)
     int *h_cut_count;          // pinned copy of the batch's number of unproven cuts
     int cut_known, cut_overflow;   // read back after the analysis: when every unproven cut sits in the pool no probe launches the tier-1 decoder
     unsigned *d_decsave;       // [B][ncblks][DEC_SAVE_WORDS] decoder state of each block's recording (resumed by later probes)
@@ -383,7 +384,7 @@ struct ebcc_cuda_ctx {
     int prio_split;
     int crowd;                 // pipelines at work on this device (hint from the host codec), see mq_lanes()
     int env_mq_lanes, env_dec_lanes, env_no_recording, env_dec_recording, env_debug_lanes, env_t1rec_ctas, env_dwt_cw;   // tuning / debugging variables, read once per host call (read_env)
-    int env_fused_idwt, env_fused_dwt, env_sp_serial, env_no_pcrd_cache;
+    int env_fused_idwt, env_fused_dwt, env_sp_serial, env_no_pcrd_cache, env_cuts_from_zero, env_all_unproven;
     int ntiles;
     ebcc_cuda_ctx *tile[EBCC_MAX_TILES];
     ebcc_cuda_ctx *parent;
@@ -561,7 +562,7 @@ static void free_buffers(ebcc_cuda_ctx *c)
     cudaFreeHost(c->h_pout); cudaFreeHost(c->h_stat); cudaFreeHost(c->h_offs); cudaFreeHost(c->h_maxlen);
     cudaFreeHost(c->h_packed); cudaFreeHost(c->h_stage);
     cudaFree(c->d_streams); cudaFree(c->d_slens); cudaFree(c->d_status); cudaFree(c->d_jobs); cudaFree(c->d_rjobs); c->d_rjobs = NULL; cudaFree(c->d_iplane); cudaFree(c->d_scratch); cudaFree(c->d_spass); cudaFree(c->d_dstate); cudaFree(c->d_decsave);
-    cudaFree(c->d_cut_list); cudaFree(c->d_cut_count); cudaFree(c->d_cut_pool); c->d_cut_list = NULL; c->d_cut_count = NULL; c->d_cut_pool = NULL;
+    cudaFree(c->d_cut_list); cudaFree(c->d_cut_count); cudaFree(c->d_cut_pool); cudaFree(c->d_ctxsnap); c->d_ctxsnap = NULL; c->d_cut_list = NULL; c->d_cut_count = NULL; c->d_cut_pool = NULL;
     cudaFreeHost(c->h_cut_count); c->h_cut_count = NULL;
     c->d_scratch = NULL; c->d_spass = NULL; c->d_dstate = NULL; c->d_decsave = NULL;
     cudaFree(c->d_dcoef); cudaFree(c->d_dcoef2); c->d_dcoef2 = NULL; cudaFree(c->d_dec); cudaFree(c->d_es); cudaFree(c->d_targets);
@@ -683,6 +684,7 @@ static int reserve_alloc(ebcc_cuda_ctx *c, size_t H, size_t W, size_t nframes, i
     CK(cudaMalloc((void **)&c->d_cut_count, sizeof(int)));
     CK(cudaMallocHost((void **)&c->h_cut_count, sizeof(int)));
     CK(cudaMalloc((void **)&c->d_cut_pool, (size_t)c->cut_cap * T1_CUT_WORDS * sizeof(int)));
+    CK(cudaMalloc((void **)&c->d_ctxsnap, B * (size_t)pl->ncblks * T1_SNAP_PLANES * T1_SNAP_BYTES));
     CK(cudaMalloc((void **)&c->d_decsave, B * pl->ncblks * (size_t)DEC_SAVE_WORDS * sizeof(unsigned)));
     CK(cudaMalloc((void **)&c->d_dcoef, B * N * sizeof(float)));
     CK(cudaMalloc((void **)&c->d_dcoef2, B * N * sizeof(float)));
@@ -889,6 +891,8 @@ static void read_env(ebcc_cuda_ctx *c)
     c->env_t1rec_ctas = e ? atoi(e) : 3;
     e = getenv("EBCC_FUSED_IDWT");                  // 0: the unfused inverse transform (k_dequant / k_recon_dequant, k_idwt_h / k_idwt_v, k_finalize)
     c->env_fused_idwt = !(e && e[0] == '0');
+    c->env_cuts_from_zero = getenv("EBCC_CUTS_FROM_PASS0") != NULL;   // cross-check aid: every unproven cut decoded from pass 0
+    c->env_all_unproven = getenv("EBCC_DEBUG_ALL_CUTS_UNPROVEN") != NULL;   // test aid: every cut goes to the pool (as far as it holds)
     c->env_no_pcrd_cache = getenv("EBCC_NO_PCRD_CACHE") != NULL;   // cross-check aid: every probe bisects from scratch
     e = getenv("EBCC_SP_DECODE_SERIAL");            // cross-check aid: the one-thread SPIHT list decoder
     c->env_sp_serial = e && e[0] == '1';
@@ -1018,7 +1022,8 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int f
         const long long per_cta = (long long)MQ_WARPS(lanes) * lanes;
         const dim3 grid((unsigned)((jobs + per_cta - 1) / per_cta)), block(MQ_THREADS(lanes));
 #define MQ_GO(LL) EBCC_LAUNCH(k_t1_mq<LL>, grid, block, 0, ls, c->d_cblks, c->d_cbout, c->d_sym, c->d_mq, \
-                              c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride, c->rec_from_encoder ? c->d_dstate : (T1CutState *)NULL, c->d_stat)
+                              c->d_mqtab, pl->ncblks, B, pl->sym_stride, pl->mq_stride, c->rec_from_encoder ? c->d_dstate : (T1CutState *)NULL, c->d_stat, \
+                              (c->rec_from_encoder && !ctx_root(c)->env_cuts_from_zero) ? c->d_ctxsnap : (unsigned char *)NULL, ctx_root(c)->env_all_unproven)
         for (int rep = 0; rep < dbg_repeat("mq"); ++rep) {
         if (lanes == 32) MQ_GO(32); else if (lanes == 16) MQ_GO(16); else if (lanes == 8) MQ_GO(8); else if (lanes == 4) MQ_GO(4);
         else if (lanes == 2) MQ_GO(2); else MQ_GO(1);
@@ -1031,12 +1036,15 @@ static int analyze_impl(ebcc_cuda_ctx *c, size_t nframes, int with_minmax, int f
         KT kt_(c, EBCC_KT_T1_DEC, ls);
         const long long jobs = (long long)pl->ncblks * B;
         CK(cudaMemsetAsync(c->d_cut_count, 0, sizeof(int), ls));
+        // entries a full pool leaves unwritten must read as invalid (k_cut_collect reserves before it checks the room)
+        CK(cudaMemsetAsync(c->d_cut_list, 0xff, (size_t)c->cut_cap * sizeof(T1CutEntry), ls));
         EBCC_LAUNCH(k_cut_collect, dim3((unsigned)((jobs + 255) / 256)), dim3(256), 0, ls, (const CblkOut *)c->d_cbout, c->d_dstate, c->d_cut_list,
                     c->d_cut_count, c->cut_cap, jobs);
         for (int rep = 0; rep < dbg_repeat("cuts"); ++rep)
         EBCC_LAUNCH(k_t1_dec_cuts, dim3((unsigned)((c->cut_cap + CUT_WPC - 1) / CUT_WPC)), dim3(CUT_WPC * 32), 0, ls, c->d_cblks, (const CblkOut *)c->d_cbout,
                     (const T1CutEntry *)c->d_cut_list, (const int *)c->d_cut_count, c->cut_cap, (const unsigned char *)c->d_mq, pl->mq_stride, c->d_declut,
-                    c->d_cut_pool, pl->ncblks);
+                    c->d_cut_pool, pl->ncblks, (const int *)c->d_iplane, (const unsigned char *)c->d_spass,
+                    ctx_root(c)->env_cuts_from_zero ? (const unsigned char *)NULL : (const unsigned char *)c->d_ctxsnap, pl->W, pl->H, B);
         CK(cudaMemcpyAsync(c->h_cut_count, c->d_cut_count, sizeof(int), cudaMemcpyDeviceToHost, ls));
         c->launches += 2;
     }

@@ -643,10 +643,60 @@ __global__ void k_cut_collect(const CblkOut *__restrict__ cbout, T1CutState *dst
         if ((d.bad[p >> 5] >> (p & 31)) & 1u) { list[e].bi = (unsigned)i; list[e].np = p + 1; ++e; }
 }
 
+// value of a sample after the first np coding passes, from its recording (value v after npd >= np passes, pass of
+// significance ps)
+__device__ __forceinline__ int recon_value(int v, int ps, int np, int npd, int numbps)
+{
+    if (np == npd || v == 0) return v;
+    if (ps >= np) return 0;
+    const int kk = ps == 0 ? 0 : (ps + 2) / 3, kr = np / 3;
+    const int b = numbps - 1 - (kr > kk ? kr : kk);
+    const int a = v < 0 ? -v : v;
+    const int mag = ((((a >> 1) >> b) << b) << 1) + (1 << b);
+    return v < 0 ? -mag : mag;
+}
+
 #define CUT_WPC 4
+
+// "Does the segment cut at R bytes decode like the complete one up to the end of the pass whose coder snapshot is (a, c, ct,
+// pend, pos)?" for ANY R (mq_cut_proven, k_t1.cuh, answers it for the pass's own rate, at most two bytes behind the pending
+// one).  Same criterion: the value the decoder reads -- final bytes, then one-bits -- must not exceed L + a.  Bytes whose
+// weight falls below 2^-8 of a's LSB only add a fraction in (0, 1] of that unit, so with true bytes left over the test is
+// A + 1 <= U for the integer part A.
+__device__ __forceinline__ bool mq_cut_covers(unsigned a, unsigned c, int ct, unsigned pend, int pos, int R, const unsigned char *v)
+{
+    if (R - 1 < pos) return false;
+    const int s = 27 - ct + 8;
+    unsigned long long X = 0;
+    int off = 0, last = 0, i = pos;
+    for (; i < R && s - off >= 0; ++i) {
+        const unsigned vi = i < 0 ? 0u : (unsigned)v[i];
+        X += (unsigned long long)vi << (s - off);
+        last = off;
+        off += vi == 0xffu ? 7 : 8;
+    }
+    X += i < R ? 1ull : (1ull << (s - last));
+    const unsigned long long U = ((((unsigned long long)pend << (27 - ct)) + c + a) << 8);
+    return X <= U;
+}
+
+// One entry = (block, np): the block decoded from its segment cut at rate[np - 1], np passes, into the entry's pool slot.
+// Decoding from pass 0 would be a chain over every decision of the block so far.  Instead the entry starts at the
+// bit-plane boundary below its last pass (pass p0 = 1 + 3 j, a significance pass), because everything a decoder holds there
+// is known without decoding:
+//   * sample state: the encoder's recording (value after all passes, pass of first significance) gives significance, sign,
+//     "already refined" and the value after p0 passes (recon_value) of every sample; the flag words follow from those;
+//   * contexts: k_t1_mq saved the 19 context states at the end of every clean-up pass (ctxsnap);
+//   * MQ registers: a is the coder's a at the end of pass p0 - 1 (CblkOut::mqs).  The decoder's C register is linear in the
+//     bytes read and in the subtracted qe's: C = (bits read so far, as the byte-reading half alone shifts them in) minus
+//     (the coder's low bound << 16), modulo 2^32; only the low 16 bits of the coder's c matter.  The byte-reading half is
+//     replayed over N shifts, N = 12 - ct + sum over the bytes before the pending one of (7 after an 0xFF, else 8).
+// Valid iff the cut segment decodes like the complete one up to the end of pass p0 - 1 (mq_cut_covers); otherwise, and for
+// entries whose last pass is pass 0, the chain starts at pass 0 as before.
 __global__ void __launch_bounds__(CUT_WPC * 32)
 k_t1_dec_cuts(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cbout, const T1CutEntry *__restrict__ list, const int *__restrict__ count,
-              int cap, const unsigned char *__restrict__ pool, size_t pool_stride, const DecLuts *__restrict__ g_luts, int *cut_pool, int ncblks)
+              int cap, const unsigned char *__restrict__ pool, size_t pool_stride, const DecLuts *__restrict__ g_luts, int *cut_pool, int ncblks,
+              const int *__restrict__ rec_val, const unsigned char *__restrict__ rec_pass, const unsigned char *__restrict__ ctxsnap, int W, int H, int nframes)
 {
     __shared__ unsigned F[CUT_WPC][DEC_FWORDS];
     __shared__ unsigned char F2[CUT_WPC][DEC_FWORDS];
@@ -662,25 +712,87 @@ k_t1_dec_cuts(const CblkDesc *__restrict__ cblks, const CblkOut *__restrict__ cb
     const int e = blockIdx.x * CUT_WPC + warp;
     if (e >= n) return;
     const T1CutEntry en = list[e];
+    if (en.bi >= (unsigned)ncblks * (unsigned)nframes) return;      // slot reserved by a block that found the pool full
     const int k = (int)(en.bi % (unsigned)ncblks), frame = (int)(en.bi / (unsigned)ncblks);
     const CblkDesc cb = cblks[k];
+    const CblkOut &co = cbout[en.bi];
+    if (en.np > co.totalpasses) return;
+    const unsigned char *seg = pool + (size_t)frame * pool_stride + cb.mq_off;
     int *dst = cut_pool + (size_t)e * T1_CUT_WORDS;
-    for (int i = lane; i < DEC_FWORDS; i += 32) { F[warp][i] = 0; F2[warp][i] = 0; }
-    for (int i = lane; i < cb.h * J2K_CBLK; i += 32) dst[i] = 0;
+    unsigned *Fw = F[warp];
+    for (int i = lane; i < DEC_FWORDS; i += 32) Fw[i] = 0;
+    // start at a bit-plane boundary?
+    const int plast = en.np - 1, R = en.np > 0 ? co.rate[en.np - 1] : 0;
+    int p0 = 0;
+    if (ctxsnap != nullptr && rec_val != nullptr && plast >= 1 && co.numbps > 0 && (plast - 1) / 3 < T1_SNAP_PLANES) {
+        const int q = ((plast - 1) / 3) * 3;                     // the clean-up pass in front of the plane of the last pass
+        const unsigned w0 = co.mqs[q][0], w1 = co.mqs[q][1];
+        if (mq_cut_covers(w1 & 0xffffu, w0 & 0x0fffffffu, (int)(w0 >> 28), (w1 >> 16) & 0xffu, (int)co.mqs[q][2], R, seg)) p0 = q + 1;
+    }
+    __syncwarp();
+    if (p0 == 0) {
+        for (int i = lane; i < cb.h * J2K_CBLK; i += 32) dst[i] = 0;
+    } else {
+        // sample state after p0 passes from the recording: values into the slot, flag words by OR-ing what t1d_set_sig would
+        // have set sample by sample (significance of the 3 x 6 neighbourhood, signs, mu)
+        const int jp = (p0 - 1) / 3;                              // plane index of pass p0
+        const size_t base = (size_t)frame * W * H + (size_t)cb.ty * W + cb.tx;
+        for (int i = lane; i < cb.h * J2K_CBLK; i += 32) {
+            const int y = i / J2K_CBLK, x = i - y * J2K_CBLK;
+            int val = 0;
+            if (x < cb.w) {
+                const int v = rec_val[base + (size_t)y * W + x], ps = rec_pass[base + (size_t)y * W + x];
+                if (v != 0 && ps < p0) {
+                    val = recon_value(v, ps, p0, co.totalpasses, co.numbps);
+                    const unsigned sg = v < 0 ? 1u : 0u;
+                    const int js = ps == 0 ? -1 : (ps - 1) / 3;      // plane of first significance; first refined in plane js + 1
+                    const int ci = y & 3, pw = ((y >> 2) + 1) * DEC_FW + x + 1;
+                    atomicOr(&Fw[pw], DF_SIG(ci) | (sg ? DF_CHI(ci) : 0u) | (js <= jp - 2 ? DF_MU(ci) : 0u));
+                    atomicOr(&Fw[pw - 1], 1u << ((ci + 1) * 3 + 2));
+                    atomicOr(&Fw[pw + 1], 1u << ((ci + 1) * 3 + 0));
+                    if (ci == 0) {
+                        atomicOr(&Fw[pw - DEC_FW], (1u << 16) | (sg ? DF_CHI(4) : 0u));
+                        atomicOr(&Fw[pw - DEC_FW - 1], 1u << 17);
+                        atomicOr(&Fw[pw - DEC_FW + 1], 1u << 15);
+                    }
+                    if (ci == 3) {
+                        atomicOr(&Fw[pw + DEC_FW], (1u << 1) | (sg ? DF_CHI(-1) : 0u));
+                        atomicOr(&Fw[pw + DEC_FW - 1], 1u << 2);
+                        atomicOr(&Fw[pw + DEC_FW + 1], 1u << 0);
+                    }
+                }
+            }
+            dst[i] = val;
+        }
+    }
+    __syncwarp();
+    for (int i = lane; i < DEC_FWORDS; i += 32) F2[warp][i] = (unsigned char)d2_from_flags(Fw[i]);
     __syncwarp();
     if (lane != 0) return;
-    const CblkOut &co = cbout[en.bi];
     if (en.np <= 0 || co.numbps <= 0) return;
     unsigned *cx = cxs[warp];
-    for (int i = 0; i < 19; ++i) cx[i] = tab[0];
-    cx[CTX_UNI] = tab[46 << 1]; cx[CTX_AGG] = tab[3 << 1]; cx[CTX_ZC] = tab[4 << 1];
     T1DecState S;
-    S.F = F[warp]; S.F2 = F2[warp]; S.cx = cx; S.tab = MQ_OPAQUE(MQ_SADDR(tab)); S.W = J2K_CBLK; S.pass = 0; S.zc = MQ_OPAQUE(MQ_SADDR(zc + cb.orient * 512));
+    S.F = Fw; S.F2 = F2[warp]; S.cx = cx; S.tab = MQ_OPAQUE(MQ_SADDR(tab)); S.W = J2K_CBLK; S.pass = 0; S.zc = MQ_OPAQUE(MQ_SADDR(zc + cb.orient * 512));
     S.plane = dst; S.spass = nullptr;
     MqDec q;
-    mqd_init(q, pool + (size_t)frame * pool_stride + cb.mq_off, co.rate[en.np - 1], nullptr);
+    mqd_init(q, seg, R, nullptr);
+    if (p0 == 0) {
+        for (int i = 0; i < 19; ++i) cx[i] = tab[0];
+        cx[CTX_UNI] = tab[46 << 1]; cx[CTX_AGG] = tab[3 << 1]; cx[CTX_ZC] = tab[4 << 1];
+    } else {
+        const int qp = p0 - 1;
+        const unsigned char *sn = ctxsnap + ((size_t)en.bi * T1_SNAP_PLANES + qp / 3) * T1_SNAP_BYTES;
+        for (int i = 0; i < 19; ++i) cx[i] = tab[sn[i] < 94 ? sn[i] : 0];
+        const unsigned w0 = co.mqs[qp][0], w1 = co.mqs[qp][1];
+        const int ct_e = (int)(w0 >> 28), pos = (int)co.mqs[qp][2];
+        int N = 12 - ct_e;
+        for (int i = -1; i < pos; ++i) N += (i >= 0 && seg[i] == 0xffu) ? 7 : 8;
+        mqc_shift(q.m, seg, N);
+        q.m.c -= (w0 & 0xffffu) << 16;
+        q.a = w1 & 0xffffu;
+    }
     DecState dummy; dummy.np_dec = 0; dummy.scratch_np = 0; dummy.bad[0] = dummy.bad[1] = dummy.bad[2] = dummy.bad[3] = 0; dummy.first_entry = -1; dummy.pad = 0;
-    t1d_passes<false>(S, q, cb.w, cb.h, co.numbps, 0, en.np, nullptr, 0, dummy);
+    t1d_passes<false>(S, q, cb.w, cb.h, co.numbps, p0, en.np, nullptr, 0, dummy);
 }
 
 // decode jobs for the encoder's own allocation (compression-ratio search).  Block k is recorded (mode 1) when the
@@ -731,18 +843,6 @@ __global__ void k_dstate_reset(DecState *d, long long n)
 // dequantised: (float)v * (0.5f * stepsize_dec)  (t1.c:1853-1865).
 //   decoder units: |v| = 2*M + 2^b, M = magnitude bits decoded down to plane b, 2^b the half-bit bias
 //   (t1.c:582-1140: oneplushalf on significance, +-poshalf per refinement)
-// value of a sample after the first np coding passes, from its recording (value v after npd >= np passes, pass of
-// significance ps)
-__device__ __forceinline__ int recon_value(int v, int ps, int np, int npd, int numbps)
-{
-    if (np == npd || v == 0) return v;
-    if (ps >= np) return 0;
-    const int kk = ps == 0 ? 0 : (ps + 2) / 3, kr = np / 3;
-    const int b = numbps - 1 - (kr > kk ? kr : kk);
-    const int a = v < 0 ? -v : v;
-    const int mag = ((((a >> 1) >> b) << b) << 1) + (1 << b);
-    return v < 0 ? -mag : mag;
-}
 
 __global__ void k_recon_dequant(const Plan *__restrict__ plan, const CblkOut *__restrict__ cbout, const DecState *__restrict__ dstate,
                                 const DecJob *__restrict__ jobs, const int *__restrict__ iplane, const unsigned char *__restrict__ spass,

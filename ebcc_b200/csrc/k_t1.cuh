@@ -571,7 +571,7 @@ template <int L>
 __global__ void __launch_bounds__(MQ_THREADS(L), MQ_MIN_CTAS)
 k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char *__restrict__ sym_pool,
         unsigned char *mq_pool, const MqTable *__restrict__ g_tab, int ncblks, int nframes,
-        size_t sym_stride, size_t mq_stride, T1CutState *cuts, FrameStat *stat)
+        size_t sym_stride, size_t mq_stride, T1CutState *cuts, FrameStat *stat, unsigned char *ctxsnap, int dbg_all_unproven)
 {
     // cuts != nullptr (compression-ratio search): the coder state at every pass end is kept and, once the segment is
     // complete, every pass gets its verdict "cut at rate[p] decodes like the complete segment" (mq_cut_proven)
@@ -623,6 +623,12 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
     const mq_saddr sba = MQ_SADDR(stg), cxa = MQ_SADDR(cx), taba = MQ_OPAQUE(MQ_SADDR(tabn));
     unsigned i = 0, end = npasses > 0 ? out->nsym_end[0] : 0xffffffffu;
     int p = 0;
+    // context states at the end of clean-up pass pp (passes 0, 3, 6, ...), see T1_SNAP_PLANES
+    auto save_ctx = [&](int pp) {
+        if (!snap || ctxsnap == nullptr || pp % 3 != 0 || pp / 3 >= T1_SNAP_PLANES) return;
+        unsigned char *d = ctxsnap + (((size_t)frame * ncblks + cbi) * T1_SNAP_PLANES + pp / 3) * T1_SNAP_BYTES;
+        for (int k = 0; k < 19; ++k) d[k] = (unsigned char)((mq_ld32(cxa + (mq_saddr)(k * 16)) >> 3) & 127u);
+    };
     uint4 pre[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
@@ -681,6 +687,7 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
             i += n;
             if (i == end) {
                 mq_pass_end(q, out, p, npasses, snap);
+                save_ctx(p);
                 end = ++p < npasses ? out->nsym_end[p] : 0xffffffffu;
             }
         }
@@ -690,7 +697,7 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
         cs.np_dec = 0; cs.scratch_np = 0; cs.bad[0] = cs.bad[1] = cs.bad[2] = cs.bad[3] = 0; cs.first_entry = -1; cs.pad = 0;
     }
     if (!coder || npasses <= 0) return;
-    for (; p < npasses; ++p) mq_pass_end(q, out, p, npasses, snap);
+    for (; p < npasses; ++p) { mq_pass_end(q, out, p, npasses, snap); save_ctx(p); }
     // final pending byte (beyond numbytes) is never part of the stream
     int last = q.pos;
     if (last > q.cap) { atomicOr(&stat[frame].flags, STAT_OVERFLOW); last = q.cap; }
@@ -708,7 +715,7 @@ k_t1_mq(const CblkDesc *__restrict__ cblks, CblkOut *cbout, const unsigned char 
         unsigned bad[4] = {0, 0, 0, 0};
         for (int pp = 0; pp < npasses; ++pp) {
             const unsigned w0 = out->mqs[pp][0], w1 = out->mqs[pp][1];
-            const bool ok = pp < 128 && mq_cut_proven(w1 & 0xffffu, w0 & 0x0fffffffu, (int)(w0 >> 28), (w1 >> 16) & 0xffu, (int)out->mqs[pp][2],
+            const bool ok = !dbg_all_unproven && pp < 128 && mq_cut_proven(w1 & 0xffffu, w0 & 0x0fffffffu, (int)(w0 >> 28), (w1 >> 16) & 0xffu, (int)out->mqs[pp][2],
                                                       out->rate[pp], q.dst);
             if (!ok && pp < 128) bad[pp >> 5] |= 1u << (pp & 31);
         }

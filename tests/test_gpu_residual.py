@@ -131,6 +131,29 @@ def test_every_cut_verdict_full_frames(built):
     assert pooled == unproven and pool_wrong == 0     # every unproven cut was decoded ahead of the search, correctly
 
 
+def test_pool_entries_from_bitplane_boundary(built):
+    """k_t1_dec_cuts starts an entry at the bit-plane boundary below its last pass (sample state from the recording, contexts
+    from the encoder's snapshots, C register replayed from the final bytes) instead of pass 0.  With every cut declared
+    unproven (test aid) the pool fills up with entries of every pass count; each must equal the real truncated decode,
+    and the pool decoded from pass 0 (EBCC_CUTS_FROM_PASS0) must say the same."""
+    frames = np.concatenate([H.synth_stack(1, 300, 460), H.synth_stack(1, 300, 460, level=3)], axis=0)
+    keep = {k: os.environ.get(k) for k in ("EBCC_DEBUG_ALL_CUTS_UNPROVEN", "EBCC_CUTS_FROM_PASS0")}
+    try:
+        os.environ["EBCC_DEBUG_ALL_CUTS_UNPROVEN"] = "1"
+        fast = S.check_cuts(frames)
+        os.environ["EBCC_CUTS_FROM_PASS0"] = "1"
+        slow = S.check_cuts(frames)
+    finally:
+        for k, v in keep.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    checked, unproven, wrong, pessimistic, pooled, pool_wrong = fast
+    assert checked > 2000 and unproven == checked and pooled > 150 and pool_wrong == 0 and wrong == 0, fast
+    assert slow == fast
+
+
 def test_recording_equals_real_decodes(built):
     """CR-search probes served from the pass recording (one tier-1 decode + truncation shadows) must give exactly the
     statistics of probes that decode every block for real, for ratios below and above the recorded one."""
