@@ -34,7 +34,8 @@ def _encode_batch(lib, frames, h, w, cr, mode=H.NONE, err=0.0):
 @pytest.fixture
 def env_guard():
     keys = ("EBCC_MQ_LANES", "EBCC_DEC_LANES", "EBCC_BATCH_FRAMES", "EBCC_PIPELINES", "EBCC_FUSED_DWT", "EBCC_FUSED_IDWT",
-            "EBCC_SP_DECODE_SERIAL", "EBCC_NO_PCRD_CACHE", "EBCC_INIT_BASE_ERROR_QUANTILE", "EBCC_DISABLE_PURE_BASE_COMPRESSION_FALLBACK")
+            "EBCC_SP_DECODE_SERIAL", "EBCC_NO_PCRD_CACHE", "EBCC_CUTS_FROM_PASS0", "EBCC_DEBUG_ALL_CUTS_UNPROVEN",
+            "EBCC_INIT_BASE_ERROR_QUANTILE", "EBCC_DISABLE_PURE_BASE_COMPRESSION_FALLBACK")
     saved = {k: os.environ.get(k) for k in keys}
     yield
     for k, v in saved.items():
@@ -142,9 +143,11 @@ def test_concurrent_callers(built, env_guard):
 
 def test_cross_check_paths_are_byte_identical(built, env_guard):
     """The kernels the fused / warp-cooperative ones replaced stay in the library as cross-check paths (EBCC_FUSED_DWT=0,
-    EBCC_FUSED_IDWT=0, EBCC_SP_DECODE_SERIAL=1, EBCC_NO_PCRD_CACHE=1: every probe bisects its threshold from scratch): forward
-    transform, probe back half, decode back half, SPIHT list decoder and rate allocation must give the same bytes and the
-    same floats either way.  The residual layer is forced on these small frames."""
+    EBCC_FUSED_IDWT=0, EBCC_SP_DECODE_SERIAL=1, EBCC_NO_PCRD_CACHE=1: every probe bisects its threshold from scratch,
+    EBCC_CUTS_FROM_PASS0=1: the pool of unproven cuts decoded from pass 0, EBCC_DEBUG_ALL_CUTS_UNPROVEN=1: every cut declared
+    unproven, so the pool overflows and the probes fall back to real tier-1 decodes): forward transform, probe back half,
+    decode back half, SPIHT list decoder, rate allocation and the handling of unproven cuts must give the same bytes and
+    the same floats either way.  The residual layer is forced on these small frames."""
     lib = H.prod_lib()
     lib.ebcc_decode_batch.restype = C.c_size_t
     os.environ["EBCC_INIT_BASE_ERROR_QUANTILE"] = "1e-2"
@@ -165,7 +168,8 @@ def test_cross_check_paths_are_byte_identical(built, env_guard):
 
     want_s, want_d = roundtrip()
     assert any(int.from_bytes(s[16:24], "little") > 0 for s in want_s), "no frame carries a residual layer"
-    for key, val in (("EBCC_FUSED_DWT", "0"), ("EBCC_FUSED_IDWT", "0"), ("EBCC_SP_DECODE_SERIAL", "1"), ("EBCC_NO_PCRD_CACHE", "1")):
+    for key, val in (("EBCC_FUSED_DWT", "0"), ("EBCC_FUSED_IDWT", "0"), ("EBCC_SP_DECODE_SERIAL", "1"), ("EBCC_NO_PCRD_CACHE", "1"),
+                     ("EBCC_CUTS_FROM_PASS0", "1"), ("EBCC_DEBUG_ALL_CUTS_UNPROVEN", "1")):
         os.environ[key] = val
         got_s, got_d = roundtrip()
         os.environ.pop(key)
