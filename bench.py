@@ -3,9 +3,10 @@
 
 Headline workload (BASELINE.json configs[3], the largest single-GPU configuration; configs[4] is its 1/2/4/8-GPU sweep):
 MAX_ERROR 0.1 K, base_cr 30, synthetic hourly 721x1440 f32 stack.  A *step* = one pass of the compress path over
-FRAMES = PIPES batches of 24 frames per GPU (a stated subsample of the 8760-frame stack: 48 distinct seeded frames per
-rank, tiled with constant offsets), handed to the public C ABI in one ebcc_encode_batch() call, which runs the batches on
-PIPES device pipelines.
+FRAMES = ROUNDS x PIPES batches of 24 frames per GPU (768 frames, 3.2 GB: a stated subsample of the 8760-frame stack, 48
+distinct seeded frames per rank tiled with constant offsets), handed to the public C ABI in one ebcc_encode_batch() call,
+which runs the batches on PIPES device pipelines, ROUNDS = 2 batches each -- the stack is one long call in the reference's
+use, so a step should not consist of pipeline fill and drain alone (one batch per pipeline: 384 frames, about 10 % slower).
 
   value      compress GB/s of f32 input, frames resident in HBM (device pointer through the C ABI), CUDA events around
              the K timed steps (the call returns when the streams are in host memory)
@@ -45,7 +46,14 @@ FRAME_BYTES = NSAMP * 4
 BATCH = int(os.environ.get("EBCC_BENCH_BATCH", "24"))
 # device pipelines (batches in flight) per GPU: the same at every rank count
 PIPES = int(os.environ.get("EBCC_BENCH_PIPES", "16"))
-FRAMES = BATCH * PIPES
+# batches each pipeline works off per step
+ROUNDS = int(os.environ.get("EBCC_BENCH_ROUNDS", "2"))
+try:    # a rank keeps about 7 GB of host memory per round (frames pageable + pinned, decoded frames, the modes' stack)
+    if os.sysconf("SC_PHYS_PAGES") * os.sysconf("SC_PAGE_SIZE") / int(os.environ.get("WORLD_SIZE", "1")) < 32e9:
+        ROUNDS = 1
+except (ValueError, OSError):
+    pass
+FRAMES = BATCH * PIPES * ROUNDS
 DISTINCT = 48
 MODE, ERR = H.MAX_ERROR, 0.1
 os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")   # more than 8 streams need more than the default 8 hardware queues
@@ -536,15 +544,15 @@ def build_line(args, world, value, dev_s, wall_s, plain_s, e2e_s, pg_s, dd_s, dh
             roof["int_issue"] = d["int_issue"]
         # whole step against the integer-issue peak: tier-1 instruction counts of the ncu captures over the step time
         step_s = dev_s / K
-        gi = PIPES * sum(WARP_INST_PER_BATCH.values()) / step_s / 1e9
-        roof["int_issue_step"] = {"bound": "int_issue", "warp_inst_per_step": PIPES * sum(WARP_INST_PER_BATCH.values()),
+        gi = (FRAMES // BATCH) * sum(WARP_INST_PER_BATCH.values()) / step_s / 1e9
+        roof["int_issue_step"] = {"bound": "int_issue", "warp_inst_per_step": (FRAMES // BATCH) * sum(WARP_INST_PER_BATCH.values()),
                                   "achieved_ginst_s": gi, "peak_ginst_s": issue_peak, "frac": gi / issue_peak,
                                   "note": "tier-1 (context modelling + MQ) only; the probes of the search come on top"}
     return {
         "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": K, "warmup": args.warmup,
         "ms_per_step": 1e3 * dev_s / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": CONFIG,
-        "frames_per_step_per_gpu": FRAMES, "batch_frames": BATCH, "pipelines_per_gpu": PIPES, "distinct_frames_per_gpu": DISTINCT,
+        "frames_per_step_per_gpu": FRAMES, "batch_frames": BATCH, "pipelines_per_gpu": PIPES, "batches_per_pipeline_per_step": ROUNDS, "distinct_frames_per_gpu": DISTINCT,
         "l2": "every step reads %.0f MB of frames per GPU and moves ~120 MB of intermediates per frame: far beyond the 126 MB L2" % (in_bytes / 1e6),
         "cr": in_bytes / max(out_bytes, 1), "compressed_bytes_per_step_per_gpu": int(out_bytes),
         "e2e": {"value": world * in_bytes * K / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": int(in_bytes), "d2h_bytes_per_step": int(out_bytes)},

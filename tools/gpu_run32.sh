@@ -1,8 +1,8 @@
 #!/bin/bash
-# round-2 GPU session 32: full GPU suite and the bench line with both arms on the end-of-round build
+# round-2 GPU sessions 32, 38, 44: the bench line with both arms on the end-of-round build
 mkdir -p gpurun_out
 P=gpurun_out/r02end
-timeout 1800 python -m pytest tests -m gpu -x -q > ${P}_pytest.log 2>&1; echo "pytest rc=$?" >> ${P}_pytest.log; tail -3 ${P}_pytest.log
+free -g | head -2; nproc
 timeout 900 python bench.py --impl reference --steps 3 --warmup 1 > ${P}_bench_reference.json 2> ${P}_bench_reference.err; tail -c 400 ${P}_bench_reference.json; echo
 timeout 1500 python bench.py > ${P}_bench.json 2> ${P}_bench.err; echo "bench rc=$?"
 python - <<'PY'
