@@ -2,7 +2,7 @@
 # round-2 GPU session 39 (two GPUs): end-of-round build -- multi-device test, the bench under torch.distributed.run with two ranks
 mkdir -p gpurun_out
 P=gpurun_out/r02end2
-timeout 900 python -m pytest tests/test_gpu_multidevice.py -m gpu -x -q 2>&1 | tail -2
+free -g | head -2; nproc
 timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 8 --warmup 3 > ${P}_bench_2gpu.json 2> ${P}_bench_2gpu.err
 echo "torchrun rc=$?"; tail -c 300 ${P}_bench_2gpu.err; python -c "
 import json; d=json.loads(open('${P}_bench_2gpu.json').read().strip().splitlines()[-1])
