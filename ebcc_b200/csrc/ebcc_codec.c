@@ -496,8 +496,7 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
         for (size_t i = 0; i < nb; ++i) {
             if (!run[i]) continue;
             len1[i] = ssz[i];
-            j2k1[i] = (uint8_t *)malloc(ssz[i] ? ssz[i] : 1);
-            memcpy(j2k1[i], streams[i], ssz[i]);
+            j2k1[i] = (uint8_t *)streams[i];      /* stays valid across the one later download of this batch (pure base-layer fallback) */
             const float cur_max_error = fmaxf(fabsf(p1[i].rmin), fabsf(p1[i].rmax));
             resid[i] = !(cur_max_error <= tgt[i]);
             best_err[i] = -1;
@@ -621,7 +620,7 @@ static int encode_chunk(ebcc_cuda_ctx *ctx, const float *frames, size_t nb, size
         fputc('\n', stderr);
     }
 out:
-    for (size_t i = 0; i < nb; ++i) { free(j2k1[i]); free(zcopy[i]); }
+    for (size_t i = 0; i < nb; ++i) free(zcopy[i]);
     free(streams); free(ssz); free(mn); free(mx); free(fl); free(cr); free(cr1); free(cr2); free(tgt); free(start); free(q0); free(mean);
     free(run); free(resid); free(pure_required); free(memo); free(p0); free(p1); free(p2); free(j2k1); free(len1); free(coeffs_size); free(tb);
     free(zs); free(zcopy); free(zn); free(perr); free(best_err); free(psum); free(thi); free(tlo); free(best_trunc); free(use_pure);

@@ -359,8 +359,10 @@ struct ebcc_cuda_ctx {
     FrameStat *h_stat;
     unsigned long long *h_offs;
     int *h_maxlen;
-    unsigned char *h_packed;
-    size_t h_packed_cap;
+    unsigned char *h_packed;   // pinned destination of the current download; two buffers take turns (h_packed_alt), so the
+    size_t h_packed_cap;       // streams of the previous download stay valid while the next one lands
+    unsigned char *h_packed_alt;
+    size_t h_packed_alt_cap;
     float *h_stage;            // pinned staging for pageable inputs
     size_t h_stage_cap;
     int profiling;
@@ -560,7 +562,7 @@ static void free_buffers(ebcc_cuda_ctx *c)
     cudaFree(c->d_sym); cudaFree(c->d_mq); cudaFree(c->d_out); cudaFree(c->d_packed); cudaFree(c->d_cbout);
     cudaFree(c->d_maxlen); cudaFree(c->d_body_off); cudaFree(c->d_pout); cudaFree(c->d_pcache); c->d_pcache = NULL; cudaFree(c->d_offs);
     cudaFreeHost(c->h_pout); cudaFreeHost(c->h_stat); cudaFreeHost(c->h_offs); cudaFreeHost(c->h_maxlen);
-    cudaFreeHost(c->h_packed); cudaFreeHost(c->h_stage);
+    cudaFreeHost(c->h_packed); cudaFreeHost(c->h_packed_alt); cudaFreeHost(c->h_stage);
     cudaFree(c->d_streams); cudaFree(c->d_slens); cudaFree(c->d_status); cudaFree(c->d_jobs); cudaFree(c->d_rjobs); c->d_rjobs = NULL; cudaFree(c->d_iplane); cudaFree(c->d_scratch); cudaFree(c->d_spass); cudaFree(c->d_dstate); cudaFree(c->d_decsave);
     cudaFree(c->d_cut_list); cudaFree(c->d_cut_count); cudaFree(c->d_cut_pool); cudaFree(c->d_ctxsnap); c->d_ctxsnap = NULL; c->d_cut_list = NULL; c->d_cut_count = NULL; c->d_cut_pool = NULL;
     cudaFreeHost(c->h_cut_count); c->h_cut_count = NULL;
@@ -587,7 +589,7 @@ static void free_buffers(ebcc_cuda_ctx *c)
     c->d_plan = NULL; c->d_cblks = NULL; c->d_in = c->d_coef = NULL; c->d_stat = NULL;
     c->d_sym = c->d_mq = c->d_out = c->d_packed = NULL; c->d_cbout = NULL; c->d_maxlen = c->d_body_off = NULL;
     c->d_pout = NULL; c->d_offs = NULL; c->h_pout = NULL; c->h_stat = NULL; c->h_offs = NULL; c->h_maxlen = NULL;
-    c->h_packed = NULL; c->h_packed_cap = 0; c->h_stage = NULL; c->h_stage_cap = 0; c->h_cblks = NULL;
+    c->h_packed = NULL; c->h_packed_cap = 0; c->h_packed_alt = NULL; c->h_packed_alt_cap = 0; c->h_stage = NULL; c->h_stage_cap = 0; c->h_cblks = NULL;
     c->cap_frames = 0;
 }
 
@@ -1658,6 +1660,8 @@ extern "C" int ebcc_cuda_download(ebcc_cuda_ctx *c, size_t nframes, const uint8_
     CK(cudaMemcpyAsync(c->h_offs, c->d_offs, sizeof(unsigned long long) * (B + 1), cudaMemcpyDeviceToHost, c->stream));
     CK(ctx_sync(c));
     const size_t total = (size_t)c->h_offs[B];
+    { unsigned char *t = c->h_packed; c->h_packed = c->h_packed_alt; c->h_packed_alt = t;
+      const size_t n = c->h_packed_cap; c->h_packed_cap = c->h_packed_alt_cap; c->h_packed_alt_cap = n; }
     if (total > c->h_packed_cap) {
         cudaFreeHost(c->h_packed);
         c->h_packed_cap = total + total / 4 + 4096;

@@ -114,7 +114,8 @@ int ebcc_cuda_residual_probe(ebcc_cuda_ctx *ctx, size_t nframes, const int *acti
 int ebcc_cuda_residual_pack(ebcc_cuda_ctx *ctx, size_t nframes, const size_t *coeffs_size, const uint8_t **frames, size_t *sizes);
 
 /* device -> host: waits for the pass, then returns per-frame codestream sizes, min, max, flags;
- * streams[i] receives a pointer into a context-owned pinned buffer valid until the next call */
+ * streams[i] receives a pointer into a context-owned pinned buffer; two buffers take turns, so the pointers stay valid
+ * until the download after the next one on this context */
 int ebcc_cuda_download(ebcc_cuda_ctx *ctx, size_t nframes, const uint8_t **streams, size_t *sizes,
                        float *minv, float *maxv, int *flags);
 

@@ -17,9 +17,10 @@ except Exception as e:
 PY
 }
 run base A=1
-run cut2 EBCC_PROD_SO=build/var/cut2.so
-run cut1 EBCC_PROD_SO=build/var/cut1.so
-run mq64 EBCC_PROD_SO=build/var/mq64.so
-run cut2mq64 EBCC_PROD_SO=build/var/cut2mq64.so
+run mq16 EBCC_MQ_LANES=16
+run mq8 EBCC_MQ_LANES=8
+run p12 EBCC_BENCH_PIPES=12
+run p20 EBCC_BENCH_PIPES=20
+run r3 EBCC_BENCH_ROUNDS=3
 run base2 A=1
 echo done
