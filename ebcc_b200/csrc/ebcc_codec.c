@@ -113,7 +113,7 @@ static int dims_are_valid(const size_t dims[NDIMS])
  * Every encode / decode call (and every worker of a multi-batch call) owns one pipeline while it runs, so callers on
  * several threads -- or several batches of one call -- are in flight on the device at the same time: the kernels of
  * one batch fill the issue slots the latency-bound tier-1 coder of another leaves idle.  EBCC_PIPELINES (1..32,
- * default 4) bounds how many PER GPU.
+ * default 16) bounds how many PER GPU.
  *
  * The pool spans GPUs: frames are independent (the reference's frame loop, src/ebcc_codec.c:1007-1046), so the batches of
  * one call are dealt to the pipelines of every device of EBCC_CUDA_DEVICES ("0,1,3", or "all"); slot k lives on device
@@ -122,6 +122,10 @@ static int dims_are_valid(const size_t dims[NDIMS])
  * is laid out by a prefix sum.  EBCC_CUDA_DEVICE (one ordinal) keeps a process on one GPU, which is what a launcher with
  * one process per GPU sets; with neither variable every visible GPU is used. */
 #define EBCC_MAX_PIPELINES 32
+/* 16 batches of 24 frames in flight per GPU is where a B200 stops getting faster on 721 x 1440 frames (about 3.2 GB of work
+ * buffers per pipeline, allocated when a pipeline is first used: a call of one batch builds one) */
+#define EBCC_DEFAULT_PIPELINES 16
+#define EBCC_DEFAULT_BATCH_FRAMES 24
 #define EBCC_MAX_DEVICES 16
 #define EBCC_MAX_SLOTS (EBCC_MAX_PIPELINES * EBCC_MAX_DEVICES)
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
@@ -160,7 +164,7 @@ static void resolve_devices(void)
 static int pipelines_per_device(void)
 {
     const char *env = getenv("EBCC_PIPELINES");
-    long v = env ? atol(env) : 4;
+    long v = env ? atol(env) : EBCC_DEFAULT_PIPELINES;
     return v < 1 ? 1 : (v > EBCC_MAX_PIPELINES ? EBCC_MAX_PIPELINES : (int)v);
 }
 
@@ -182,6 +186,9 @@ static ebcc_cuda_ctx *acquire_ctx(void)
     if (g_ctx_pid != me) {               /* contexts inherited through fork are abandoned, not reused */
         for (int k = 0; k < EBCC_MAX_SLOTS; ++k) { g_pool[k] = NULL; g_busy[k] = 0; }
         g_ctx_pid = me;
+        /* more than 8 streams need more than the default 8 hardware queues; read by the driver when CUDA starts in this process
+         * (too late, and harmless, if the application has started it already) */
+        setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
     }
     resolve_devices();
     const int np = pipelines_per_device() * g_ndev;
@@ -259,8 +266,8 @@ static void release_ctx(ebcc_cuda_ctx *ctx)
 static size_t max_batch_frames(void)
 {
     const char *env = getenv("EBCC_BATCH_FRAMES");
-    long v = env ? atol(env) : 32;
-    return v > 0 ? (size_t)v : 32;
+    long v = env ? atol(env) : EBCC_DEFAULT_BATCH_FRAMES;
+    return v > 0 ? (size_t)v : EBCC_DEFAULT_BATCH_FRAMES;
 }
 
 /* ---- frame assembly (reference src/ebcc_codec.c:870-907) ------------------------------------------- */
