@@ -121,6 +121,12 @@ static int dims_are_valid(const size_t dims[NDIMS])
  * uploaded to, coded on and downloaded from its own device, the per-frame sizes meet on the host where the EBCK container
  * is laid out by a prefix sum.  EBCC_CUDA_DEVICE (one ordinal) keeps a process on one GPU, which is what a launcher with
  * one process per GPU sets; with neither variable every visible GPU is used. */
+/* More than 8 streams need more than the default 8 hardware queues (16 pipelines on 8: one 768-frame call 9.5 instead of
+ * 12.4 GB/s).  The driver reads the variable when CUDA starts in the process, and the CUDA runtime linked into this library
+ * starts it from a constructor of its own when the library is loaded -- so this one has to run first.  Too late, and
+ * harmless, if the application has started CUDA already; an existing value is respected. */
+__attribute__((constructor(101))) static void ebcc_more_hardware_queues(void) { setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0); }
+
 #define EBCC_MAX_PIPELINES 32
 /* 16 batches of 24 frames in flight per GPU is where a B200 stops getting faster on 721 x 1440 frames (about 3.2 GB of work
  * buffers per pipeline, allocated when a pipeline is first used: a call of one batch builds one) */
@@ -186,9 +192,6 @@ static ebcc_cuda_ctx *acquire_ctx(void)
     if (g_ctx_pid != me) {               /* contexts inherited through fork are abandoned, not reused */
         for (int k = 0; k < EBCC_MAX_SLOTS; ++k) { g_pool[k] = NULL; g_busy[k] = 0; }
         g_ctx_pid = me;
-        /* more than 8 streams need more than the default 8 hardware queues; read by the driver when CUDA starts in this process
-         * (too late, and harmless, if the application has started it already) */
-        setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
     }
     resolve_devices();
     const int np = pipelines_per_device() * g_ndev;

@@ -14,6 +14,7 @@
 #include "../../include/ebcc_cuda.h"
 #include <math.h>
 #include <stdio.h>
+#include <time.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -459,15 +460,25 @@ extern "C" int ebcc_cuda_kernel_timing_report(double *ms, unsigned long long *gr
     return EBCC_KT_COUNT;
 }
 
-// Wait for the pipeline's stream.  Several pipelines (and, on a multi-GPU box, several ranks) share the host cores:
-// the waiting thread sleeps on a blocking-sync event unless EBCC_SPIN_SYNC=1 asks for the lower-latency spin wait.
+// Wait for the pipeline's stream.  Several pipelines (and, on a multi-GPU box, several ranks) share the host cores, and an
+// error-bounded batch waits some forty times (one wait per probe).  EBCC_SPIN_SYNC=1: spin (lowest latency, one core per
+// waiting thread); =0: sleep on a blocking-sync event (no CPU at all, but the wake-up costs most of a millisecond under load:
+// one 768-frame call 10.0 instead of 12.4 GB/s); unset: poll the event, spinning briefly and then sleeping 30 us between
+// looks -- close to the spin wait's latency at a few per cent of a core, whoever else runs on the box.
 static cudaError_t ctx_sync(ebcc_cuda_ctx *c)
 {
     cudaError_t e;
-    if (c->spin_sync) e = cudaStreamSynchronize(c->stream);
+    if (c->spin_sync == 1) e = cudaStreamSynchronize(c->stream);
     else {
         e = cudaEventRecord(c->ev_sync, c->stream);
-        if (e == cudaSuccess) e = cudaEventSynchronize(c->ev_sync);
+        if (e == cudaSuccess && c->spin_sync == 0) e = cudaEventSynchronize(c->ev_sync);
+        else if (e == cudaSuccess) {
+            int looks = 0;
+            while ((e = cudaEventQuery(c->ev_sync)) == cudaErrorNotReady)
+                if (++looks > 64) { struct timespec ts = {0, 30000}; nanosleep(&ts, NULL); }
+            const cudaError_t le = cudaGetLastError();          // the query's "not ready" must not linger as the last error
+            if (e == cudaSuccess && le != cudaSuccess && le != cudaErrorNotReady) e = le;
+        }
     }
     if (e == cudaSuccess) kt_harvest(c);
     return e;
@@ -505,7 +516,7 @@ extern "C" ebcc_cuda_ctx *ebcc_cuda_ctx_create(int device)
     }
     for (int i = 0; i <= EBCC_ST_COUNT; ++i) cudaEventCreate(&c->ev[i]);
     cudaEventCreateWithFlags(&c->ev_sync, cudaEventBlockingSync | cudaEventDisableTiming);
-    { const char *sp = getenv("EBCC_SPIN_SYNC"); c->spin_sync = sp && sp[0] == '1'; }
+    { const char *sp = getenv("EBCC_SPIN_SYNC"); c->spin_sync = !sp ? 2 : (sp[0] == '1' ? 1 : 0); }      // 2: poll (ctx_sync)
     read_env(c);
     T1Luts luts; MqTable tab;
     fill_luts(&luts, &tab);

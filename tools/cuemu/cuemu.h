@@ -150,7 +150,7 @@ static inline float fminf_(float a, float b) { return fminf(a, b); }
 typedef int cudaError_t;
 typedef intptr_t cudaStream_t;
 typedef struct cuemu_event { double t; } *cudaEvent_t;
-enum { cudaSuccess = 0 };
+enum { cudaSuccess = 0, cudaErrorNotReady = 600 };
 enum cudaMemcpyKind { cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice, cudaMemcpyDefault };
 enum { cudaHostAllocDefault = 0, cudaStreamNonBlocking = 1, cudaEventDisableTiming = 2, cudaEventBlockingSync = 1 };
 enum cudaFuncAttribute { cudaFuncAttributeMaxDynamicSharedMemorySize, cudaFuncAttributePreferredSharedMemoryCarveout };
@@ -188,6 +188,7 @@ cudaError_t cudaEventCreate(cudaEvent_t *e);
 static inline cudaError_t cudaEventCreateWithFlags(cudaEvent_t *e, unsigned) { return cudaEventCreate(e); }
 cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t s = 0);
 static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return 0; }
+static inline cudaError_t cudaEventQuery(cudaEvent_t) { return 0; }
 static inline cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, unsigned = 0) { return 0; }
 cudaError_t cudaEventElapsedTime(float *ms, cudaEvent_t a, cudaEvent_t b);
 static inline cudaError_t cudaEventDestroy(cudaEvent_t e) { free(e); return 0; }

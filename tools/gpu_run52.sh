@@ -1,10 +1,10 @@
 #!/bin/bash
-# round-2 GPU session 52: library defaults (16 pipelines x 24 frames, CUDA_DEVICE_MAX_CONNECTIONS set by the library): suite, plain calls
+# round-2 GPU sessions 52, 54: library defaults (16 pipelines x 24 frames, CUDA_DEVICE_MAX_CONNECTIONS set by the library): suite, plain calls
 mkdir -p gpurun_out
 P=gpurun_out/r02def
-timeout 1800 python -m pytest tests -m gpu -x -q > ${P}_pytest.log 2>&1; echo "pytest rc=$?" >> ${P}_pytest.log; tail -3 ${P}_pytest.log
+timeout 600 python -m pytest tests/test_gpu_none.py tests/test_gpu_residual.py tests/test_gpu_pipelines.py tests/test_dropin.py -m gpu -x -q > ${P}_pytest.log 2>&1; echo "pytest rc=$?" >> ${P}_pytest.log; tail -3 ${P}_pytest.log
 echo "== library defaults, nothing set"
-env -u EBCC_BATCH_FRAMES -u EBCC_PIPELINES -u CUDA_DEVICE_MAX_CONNECTIONS -u EBCC_SPIN_SYNC timeout 300 python - <<'PY'
+cat > /tmp/defcall.py <<'PY'
 import ctypes as C, os, sys, time
 sys.path.insert(0, "tests")
 import numpy as np, harness as H
@@ -21,4 +21,9 @@ for r in range(3):
     print("encode rep %d: %.1f ms, %.2f GB/s, CUDA_DEVICE_MAX_CONNECTIONS=%s" % (r, dt * 1e3, frames.nbytes / dt / 1e9, os.environ.get("CUDA_DEVICE_MAX_CONNECTIONS")), flush=True)
     for i in range(n): lib.free_buffer(outs[i])
 PY
+for m in unset 1 0; do
+  echo "-- EBCC_SPIN_SYNC $m"
+  if [ $m = unset ]; then env -u EBCC_BATCH_FRAMES -u EBCC_PIPELINES -u CUDA_DEVICE_MAX_CONNECTIONS -u EBCC_SPIN_SYNC timeout 300 python /tmp/defcall.py | tail -2
+  else env -u EBCC_BATCH_FRAMES -u EBCC_PIPELINES -u CUDA_DEVICE_MAX_CONNECTIONS EBCC_SPIN_SYNC=$m timeout 300 python /tmp/defcall.py | tail -1; fi
+done
 echo done
