@@ -109,6 +109,24 @@ def test_library_exports_declared_abi(built):
         assert hasattr(lib, name), name
 
 
+def test_library_asks_for_hardware_queues_at_load_time(built):
+    """16 pipelines need more than the driver's default 8 hardware queues (CUDA_DEVICE_MAX_CONNECTIONS); the variable has to be in
+    the environment before the CUDA runtime linked into the library initialises, i.e. before the library's other constructors
+    run -- and a value the application chose must survive."""
+    import subprocess
+    import sys
+    code = ("import ctypes as C, sys\n"
+            "libc = C.CDLL(None); libc.getenv.restype = C.c_char_p\n"
+            "before = libc.getenv(b'CUDA_DEVICE_MAX_CONNECTIONS')\n"
+            "C.CDLL(sys.argv[1])\n"
+            "print(before, libc.getenv(b'CUDA_DEVICE_MAX_CONNECTIONS'))\n")
+    env = {k: v for k, v in os.environ.items() if k != "CUDA_DEVICE_MAX_CONNECTIONS"}
+    r = subprocess.run([sys.executable, "-c", code, H.PROD_SO], capture_output=True, text=True, env=env, timeout=120)
+    assert r.returncode == 0 and r.stdout.split() == ["None", "b'32'"], (r.stdout, r.stderr[-300:])
+    r = subprocess.run([sys.executable, "-c", code, H.PROD_SO], capture_output=True, text=True, env=dict(env, CUDA_DEVICE_MAX_CONNECTIONS="12"), timeout=120)
+    assert r.returncode == 0 and r.stdout.split() == ["b'12'", "b'12'"], (r.stdout, r.stderr[-300:])
+
+
 def test_plugin_info_and_populate_config(built):
     lib = C.CDLL(H.PROD_SO)
     lib.H5PLget_plugin_type.restype = C.c_int
